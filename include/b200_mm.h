@@ -1,0 +1,190 @@
+/* b200_mm.h -- C ABI of the B200-native quantised matrix-multiply path.
+ *
+ * This is the drop-in boundary below the reference's backend plugin interface
+ * (/root/reference/ggml/src/ggml-backend-impl.h:17-210). Every vtable entry of the ggml plugin
+ * (include/ggml_b200.h, zyk-llama.cpp_b200/csrc/ggml_backend/ggml-b200.cpp) is a thin call into
+ * one of the functions below, and the same functions are what tests/ and bench.py drive through
+ * ctypes. Plain pointers and sizes only: no torch, no ggml and no CUDA types in any signature.
+ *
+ * Conventions
+ *   - type ids are the reference's `enum ggml_type` values (ggml/include/ggml.h:389-430).
+ *   - W is a quantised weight matrix of M rows x K elements (ggml ne00 = K, ne01 = M),
+ *     X is f32 activations, N rows of K elements, Y is f32, N rows of M elements:
+ *         Y[n][m] = sum_k W[m][k] * X[n][k]          (ggml_mul_mat, ggml/src/ggml.c:3176-3191)
+ *   - all data pointers are DEVICE pointers unless the name says `host`.
+ *   - `stream` is a b200_stream_t (0 = the device's default stream). Calls are asynchronous on
+ *     that stream unless stated otherwise.
+ *   - return value 0 = success, negative = error; b200_last_error() has the message. There is
+ *     no CPU fallback anywhere: without a usable sm_100 device every compute entry point fails.
+ */
+#ifndef B200_MM_H
+#define B200_MM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define B200_API
+#else
+#define B200_API __attribute__((visibility("default")))
+#endif
+
+/* ggml_type ids this path understands (ggml.h:389-430) */
+enum b200_type {
+    B200_TYPE_F32 = 0,
+    B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q8_0 = 8,
+    B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q6_K = 14,
+    B200_TYPE_Q8_K = 15,
+    B200_TYPE_IQ4_XS = 23,
+    B200_TYPE_I32 = 26,
+};
+
+/* how a weight matrix is stored in HBM */
+enum b200_layout {
+    B200_LAYOUT_CANONICAL = 0, /* ggml block structs, exactly the GGUF bytes (ggml-common.h:170-431) */
+    B200_LAYOUT_PLANES = 1,    /* load-time repack: one plane per block field, see DESIGN.md          */
+};
+
+/* which of the reference's two non-identical Q8_0/Q8_1 activation quantisers to reproduce */
+enum b200_q8_flavour {
+    B200_Q8_REF = 0, /* quantize_row_q8_0_ref / _q8_1_ref   (ggml/src/ggml-quants.c:199-258)            */
+    B200_Q8_X86 = 1, /* quantize_row_q8_0 / _q8_1 AVX2 path (ggml/src/ggml-cpu/arch/x86/quants.c:290-480)
+                        -- what the reference CPU backend runs on x86, hence the default everywhere   */
+};
+
+typedef void * b200_stream_t;
+typedef void * b200_event_t;
+typedef void * b200_graph_t;
+
+/* ---- errors ------------------------------------------------------------------------------- */
+B200_API const char * b200_last_error(void);
+B200_API const char * b200_version(void);
+
+/* ---- devices, memory, streams (replaces ggml_backend_device_i::get_memory/get_props and
+ *      ggml_backend_buffer_type_i::alloc_buffer, ggml-backend-impl.h:17-35,140-182) ------------ */
+B200_API int  b200_device_count(void);
+B200_API int  b200_device_info(int device, char * name, size_t name_len, size_t * free_bytes, size_t * total_bytes,
+                               int * sm_count, int * cc_major, int * cc_minor);
+B200_API int  b200_set_device(int device);
+B200_API void * b200_malloc(int device, size_t bytes);        /* NULL on OOM */
+B200_API int  b200_free(int device, void * ptr);
+B200_API void * b200_malloc_host(size_t bytes);               /* pinned host memory */
+B200_API int  b200_free_host(void * ptr);
+B200_API b200_stream_t b200_stream_create(int device);
+B200_API int  b200_stream_destroy(b200_stream_t stream);
+B200_API int  b200_stream_synchronize(b200_stream_t stream);
+B200_API int  b200_device_synchronize(int device);
+/* buffer_i::set_tensor / get_tensor / memset_tensor / cpy_tensor / clear (ggml-backend-impl.h:41-58) */
+B200_API int  b200_memcpy_h2d(void * dst, const void * host_src, size_t bytes, b200_stream_t stream);
+B200_API int  b200_memcpy_d2h(void * host_dst, const void * src, size_t bytes, b200_stream_t stream);
+B200_API int  b200_memcpy_d2d(void * dst, const void * src, size_t bytes, b200_stream_t stream);
+B200_API int  b200_memcpy_peer(void * dst, int dst_device, const void * src, int src_device, size_t bytes, b200_stream_t stream);
+B200_API int  b200_memset(void * dst, int value, size_t bytes, b200_stream_t stream);
+/* device_i::event_new/free/synchronize, backend_i::event_record/event_wait (ggml-backend-impl.h:112-116,178-181) */
+B200_API b200_event_t b200_event_create(int device);
+B200_API int  b200_event_destroy(b200_event_t ev);
+B200_API int  b200_event_record(b200_event_t ev, b200_stream_t stream);
+B200_API int  b200_event_synchronize(b200_event_t ev);
+B200_API int  b200_stream_wait_event(b200_stream_t stream, b200_event_t ev);
+B200_API int  b200_event_elapsed_ms(b200_event_t start, b200_event_t stop, float * ms);
+
+/* ---- CUDA-graph capture of a sequence of calls on one stream (tg is launch bound) ----------- */
+B200_API int  b200_graph_begin(b200_stream_t stream);
+B200_API b200_graph_t b200_graph_end(b200_stream_t stream);   /* NULL on failure */
+B200_API int  b200_graph_launch(b200_graph_t graph, b200_stream_t stream);
+B200_API int  b200_graph_destroy(b200_graph_t graph);
+
+/* ---- formats -------------------------------------------------------------------------------- */
+B200_API int    b200_type_is_weight(int type);               /* Q4_0 Q8_0 Q4_K Q6_K IQ4_XS          */
+B200_API int    b200_block_elems(int type);                  /* ggml_blck_size                      */
+B200_API size_t b200_block_bytes(int type);                  /* ggml_type_size                      */
+B200_API size_t b200_row_size(int type, int64_t k);          /* ggml_row_size                       */
+B200_API int    b200_act_type(int weight_type);              /* type_traits_cpu[].vec_dot_type      */
+
+/* ---- (3) activation quantiser: f32 rows -> CANONICAL ggml q8 blocks, bit-exact ---------------
+ * replaces quantize_row_q8_0 / _q8_1 / _q8_K (arch/x86/quants.c:290-495, ggml-quants.c:199-258,
+ * 2555-2591) as called from ggml_compute_forward_mul_mat (ggml-cpu.c:1287-1322).
+ *   x        : f32, `nrows` rows of `k` elements, row stride `x_row_stride` ELEMENTS
+ *   y        : nrows * b200_row_size(q8_type, k) bytes, rows packed
+ *   q8_type  : B200_TYPE_Q8_0 | Q8_1 | Q8_K;  flavour: enum b200_q8_flavour (ignored for Q8_K) */
+B200_API int b200_quantize_rows(int q8_type, int flavour, const float * x, int64_t x_row_stride,
+                                void * y, int64_t nrows, int64_t k, b200_stream_t stream);
+
+/* ---- (5) load-time repack into the plane layout and its exact inverse ------------------------
+ * replaces the buffer set_tensor repack hook (ggml_backend_cpu_repack_buffer_set_tensor,
+ * ggml-cpu/repack.cpp:3141-3151); unrepack is what get_tensor needs to hand canonical bytes back.
+ * src and dst must not overlap. One call handles one [m][k] matrix. */
+B200_API int b200_repack_supported(int type, int64_t m, int64_t k);
+B200_API int b200_repack(int type, int64_t m, int64_t k, const void * canonical, void * planes, b200_stream_t stream);
+B200_API int b200_unrepack(int type, int64_t m, int64_t k, const void * planes, void * canonical, b200_stream_t stream);
+
+/* ---- (1)(2) MUL_MAT -------------------------------------------------------------------------- */
+typedef struct b200_mul_mat_args {
+    int32_t type;          /* weight type                                                        */
+    int32_t layout;        /* enum b200_layout of `w`                                            */
+    int64_t m, n, k;
+    const void *  w;       /* m rows; canonical: row stride = w_row_stride bytes (0 = packed)    */
+    int64_t w_row_stride;  /* bytes; must be 0/packed for B200_LAYOUT_PLANES                     */
+    const float * x;       /* n rows of k f32                                                    */
+    int64_t x_row_stride;  /* elements                                                           */
+    float *       y;       /* n rows of m f32                                                    */
+    int64_t y_row_stride;  /* elements                                                           */
+    void *  workspace;     /* >= b200_mul_mat_workspace(type, n, k) bytes, 256 B aligned         */
+    size_t  workspace_size;
+    int32_t flavour;       /* enum b200_q8_flavour for the Q8_0 activation quantiser             */
+    int32_t algo;          /* 0 = auto, 1 = force decode GEMV, 2 = force tensor-core GEMM        */
+    int32_t flags;         /* B200_MM_* bits                                                     */
+    int32_t reserved;
+} b200_mul_mat_args;
+
+enum {
+    B200_MM_X_PREQUANTISED = 1, /* workspace already holds the quantised X of a previous call with the
+                                   same (x, n, k, activation type): skip the quantise kernel (QKV, gate/up) */
+    B200_MM_PDL = 2,            /* launch with programmatic dependent launch: the kernel prefetches its
+                                   weights while the previous kernel on the stream drains               */
+};
+
+B200_API size_t b200_mul_mat_workspace(int type, int64_t n, int64_t k);
+/* replaces ggml_compute_forward_mul_mat (ggml-cpu.c:1227-1427) for a 2-D slice */
+B200_API int    b200_mul_mat(const b200_mul_mat_args * args, b200_stream_t stream);
+
+/* ---- (4) MUL_MAT_ID (ggml.c:3217-3243; CPU driver ggml-cpu.c:1500-1676) ----------------------
+ *   as   : n_as expert matrices, each m rows x k, `as_expert_stride` bytes apart
+ *   b    : f32 [n_tokens][nb1][k] (nb1 == n_used, or 1 = same row for every slot), strides in elements
+ *   ids  : i32 [n_tokens][n_used] on the DEVICE, row stride `ids_row_stride` elements
+ *   y    : f32 [n_tokens][n_used][m], strides in elements
+ * No host synchronisation: expert routing is resolved on the device. */
+typedef struct b200_mul_mat_id_args {
+    int32_t type, layout;
+    int64_t m, k, n_as, n_used, nb1, n_tokens;
+    const void * as;   int64_t as_expert_stride;
+    const float * b;   int64_t b_row_stride, b_token_stride;
+    const int32_t * ids; int64_t ids_row_stride;
+    float * y;         int64_t y_row_stride, y_token_stride;
+    void * workspace;  size_t workspace_size;
+    int32_t flavour, algo, flags, reserved;
+} b200_mul_mat_id_args;
+
+B200_API size_t b200_mul_mat_id_workspace(int type, int64_t k, int64_t n_used, int64_t nb1, int64_t n_tokens);
+B200_API int    b200_mul_mat_id(const b200_mul_mat_id_args * args, b200_stream_t stream);
+
+/* ---- (e) multi-GPU row split ----------------------------------------------------------------
+ * rows [*row_lo, *row_hi) of an m-row weight matrix owned by `rank` of `world` (tile rounded,
+ * cf. get_row_split, ggml-cuda/ggml-cuda.cu:790-803). The exchange step itself (all-gather of the
+ * Y slices) is done by the caller's communicator (NCCL via torch.distributed in bench.py). */
+B200_API int b200_row_split(int64_t m, int world, int rank, int64_t * row_lo, int64_t * row_hi);
+
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+B200_API uint64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_MM_H */

@@ -1,0 +1,226 @@
+"""GPU (-m gpu): the CUDA path through the C ABI against the CPU oracle and the committed golden
+vectors of the reference. Bit-exact for activation quantisation and repack; MUL_MAT within the
+reference's own tolerance (NMSE <= 5e-4, tests/test-backend-ops.cpp:3716-3718, 3852-3854) -- and
+in fact ~1e-12 for the decode path, because the integer arithmetic is the CPU's."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import nmse
+from oracle.oracle import (WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q6_K, Q8_REF, Q8_X86, random_blocks)
+
+pytestmark = pytest.mark.gpu
+MAX_NMSE = 5e-4          # the reference's tolerance for MUL_MAT / MUL_MAT_ID
+DECODE_NMSE = 1e-10      # what the dp4a decode path actually achieves against the CPU arithmetic
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _acts(rng, n, k):
+    x = (rng.standard_normal((n, k)) * rng.uniform(0.01, 30, (n, 1))).astype(np.float32)
+    if n > 2 and k >= 256:
+        x[0, :256] = 0
+        x[1] = np.round(x[1] * 4) / 4
+        x[2, :32] = np.arange(32, dtype=np.float32) + 0.5
+        x[2, 0] = 127.0
+        x[2, 40] = -x[2, 33]
+    return x
+
+
+# ---- (3) activation quantiser: bit-exact -----------------------------------------------------
+@pytest.mark.parametrize("q8", [Q8_0, Q8_1, Q8_K])
+def test_quantise_golden_bit_exact(b200, golden, q8):
+    name = TYPE_NAMES[q8]
+    x = dev(golden["x"])
+    assert np.array_equal(b200.quantize_rows(q8, x, b200.Q8_X86).cpu().numpy(), golden[f"xq_cpu_{name}"])
+    if f"xq_ref_{name}" in golden:
+        assert np.array_equal(b200.quantize_rows(q8, x, b200.Q8_REF).cpu().numpy(), golden[f"xq_ref_{name}"])
+
+
+@pytest.mark.parametrize("q8", [Q8_0, Q8_1, Q8_K])
+@pytest.mark.parametrize("shape", [(1, 256), (7, 4096), (33, 14336), (512, 4096)])
+def test_quantise_vs_oracle_bit_exact(b200, orc, q8, shape):
+    rng = np.random.default_rng(hash((q8,) + shape) % 2**32)
+    x = _acts(rng, *shape)
+    for fl in (Q8_X86, Q8_REF):
+        got = b200.quantize_rows(q8, dev(x), fl).cpu().numpy()
+        assert np.array_equal(got, orc.quantize(q8, x, fl)), f"{TYPE_NAMES[q8]} flavour {fl} shape {shape}"
+
+
+@pytest.mark.parametrize("q8", [Q8_0, Q8_1])
+def test_quantise_ragged_k_and_strided_rows(b200, orc, q8):
+    rng = np.random.default_rng(5)
+    big = _acts(rng, 9, 1000)                       # rows of 1000 floats, only the first 992/32 used
+    for k in (32, 96, 992):
+        xs = dev(big)[:, :k]                        # row stride 1000: unaligned, non-contiguous
+        got = b200.quantize_rows(q8, xs, Q8_X86).cpu().numpy()
+        assert np.array_equal(got, orc.quantize(q8, big[:, :k].copy(), Q8_X86))
+
+
+def test_quantise_empty(b200):
+    x = torch.empty((0, 256), dtype=torch.float32, device="cuda")
+    assert b200.quantize_rows(Q8_K, x).shape == (0, 292)
+
+
+# ---- (5) repack: bit-exact round trip, same bytes as the oracle's layout ------------------------
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("shape", [(1, 256), (16, 512), (96, 4096), (1024, 14336)])
+def test_repack_bit_exact(b200, orc, t, shape):
+    m, k = shape
+    rng = np.random.default_rng(t * 1000 + m)
+    w = random_blocks(t, m, k, rng)
+    wd = dev(w).reshape(-1)
+    p = b200.repack(t, wd, m, k)
+    assert np.array_equal(p.cpu().numpy(), orc.b200_repack(t, w.reshape(-1), m, k))
+    assert torch.equal(b200.unrepack(t, p, m, k), wd)
+
+
+def test_repack_refuses_unaligned_k(b200):
+    assert not b200.repack_supported(Q8_0, 16, 96)
+    w = torch.zeros(16 * 3 * 34, dtype=torch.uint8, device="cuda")
+    with pytest.raises(b200.B200Error):
+        b200.repack(Q8_0, w, 16, 96)
+
+
+# ---- (1) decode MUL_MAT ----------------------------------------------------------------------------
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("tag", ["quant", "rand"])
+def test_mul_mat_golden(b200, golden, t, tag):
+    name = TYPE_NAMES[t]
+    w, x, want = golden[f"w_{name}_{tag}"], golden["x"], golden[f"y_{name}_{tag}"]
+    m, k = w.shape[0], x.shape[1]
+    wd = dev(w).reshape(-1)
+    got_c = b200.mul_mat(t, wd, dev(x), m).cpu().numpy()
+    got_p = b200.mul_mat(t, b200.repack(t, wd, m, k), dev(x), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+    assert nmse(got_c, want) < DECODE_NMSE and nmse(got_p, want) < DECODE_NMSE
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 6, 7, 8, 9, 17])
+def test_mul_mat_decode_all_batches(b200, orc, t, n):
+    rng = np.random.default_rng(t * 100 + n)
+    m, k = 131, 1024                                   # m not a multiple of the rows-per-block
+    w = random_blocks(t, m, k, rng)
+    x = _acts(rng, n, k)
+    want = orc.mul_mat(t, w, x)
+    wd = dev(w).reshape(-1)
+    for layout, wl in ((b200.LAYOUT_CANONICAL, wd), (b200.LAYOUT_PLANES, b200.repack(t, wd, m, k))):
+        got = b200.mul_mat(t, wl, dev(x), m, layout=layout, algo=1).cpu().numpy()
+        assert nmse(got, want) < DECODE_NMSE, f"{TYPE_NAMES[t]} n={n} layout={layout}"
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("tune", [0x0101, 0x0201, 0x0401, 0x0102, 0x0202, 0x0402, 0x0104, 0x0204])
+def test_mul_mat_every_rows_unroll_variant(b200, orc, t, tune):
+    rng = np.random.default_rng(tune)
+    m, k = 77, 2304                                    # 9 super-blocks: ragged against U and the warp step
+    w = random_blocks(t, m, k, rng)
+    x = _acts(rng, 1, k)
+    want = orc.mul_mat(t, w, x)
+    wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    got = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, tune=tune).cpu().numpy()
+    assert nmse(got, want) < DECODE_NMSE
+
+
+@pytest.mark.parametrize("t,k", [(2, 32), (2, 96), (8, 32), (8, 160), (12, 256), (14, 256), (23, 256), (2, 8192), (8, 576)])
+def test_mul_mat_small_and_ragged_k(b200, orc, t, k):
+    rng = np.random.default_rng(k + t)
+    m = 16
+    w = random_blocks(t, m, k, rng)
+    x = rng.standard_normal((2, k)).astype(np.float32)
+    got = b200.mul_mat(t, dev(w).reshape(-1), dev(x), m).cpu().numpy()
+    assert nmse(got, orc.mul_mat(t, w, x)) < DECODE_NMSE
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+def test_mul_mat_strided_operands(b200, orc, t):
+    """W as a row-strided view (test-backend-ops k_v cases), X and Y with padded rows."""
+    rng = np.random.default_rng(t + 9)
+    m, k, kv, n = 24, 512, 768, 3
+    wbig = random_blocks(t, m, kv, rng)
+    rs_k, rs_kv = b200.row_size(t, k), b200.row_size(t, kv)
+    w = wbig[:, :rs_k].copy()
+    x = rng.standard_normal((n, k + 64)).astype(np.float32)
+    y = torch.full((n, m + 5), 7.0, device="cuda")
+    b200.mul_mat(t, dev(wbig).reshape(-1), dev(x)[:, :k], m, w_row_stride=rs_kv, y=y[:, :m])
+    assert nmse(y[:, :m].cpu().numpy(), orc.mul_mat(t, w, x[:, :k].copy())) < DECODE_NMSE
+    assert torch.all(y[:, m:] == 7.0)                   # nothing written past a row (sentinel check)
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+def test_mul_mat_within_reference_tolerance_of_f64_truth(b200, orc, t):
+    rng = np.random.default_rng(t)
+    m, k, n = 64, 4096, 4
+    w = random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)   # test-backend-ops' input distribution
+    got = b200.mul_mat(t, b200.repack(t, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+    assert nmse(got, orc.mul_mat_f64(t, w, x)) < MAX_NMSE
+
+
+# ---- (4) MUL_MAT_ID ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("nb1", [1, 2])
+def test_mul_mat_id_golden(b200, golden, t, nb1):
+    name = TYPE_NAMES[t]
+    as_, ids, b = golden[f"id_as_{name}"], golden[f"id_ids_{name}"], golden[f"id_b{nb1}_{name}"]
+    m = as_.shape[1]
+    got = b200.mul_mat_id(t, dev(as_).reshape(as_.shape[0], -1), dev(b), dev(ids), m).cpu().numpy()
+    assert nmse(got, golden[f"id_y{nb1}_{name}"]) < DECODE_NMSE
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("cfg", [(4, 1, 1), (8, 2, 5), (8, 4, 17), (8, 2, 129)])
+def test_mul_mat_id_vs_oracle(b200, orc, t, cfg):
+    n_as, n_used, n_tok = cfg
+    rng = np.random.default_rng(sum(cfg) + t)
+    m, k = 40, 512
+    as_ = np.stack([random_blocks(t, m, k, rng) for _ in range(n_as)])
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    for nb1 in (1, n_used):
+        b = rng.standard_normal((n_tok, nb1, k)).astype(np.float32)
+        want = orc.mul_mat_id(t, as_, b, ids)
+        flat = dev(as_).reshape(n_as, -1)
+        got = b200.mul_mat_id(t, flat, dev(b), dev(ids), m).cpu().numpy()
+        assert nmse(got, want) < DECODE_NMSE
+        planes = torch.stack([b200.repack(t, flat[e].contiguous(), m, k) for e in range(n_as)])
+        got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+        assert nmse(got, want) < DECODE_NMSE
+
+
+# ---- full-size properties (BASELINE.json shapes; the oracle would take minutes here) -----------------
+@pytest.mark.parametrize("t,m,k", [(Q4_K, 14336, 4096), (Q4_K, 4096, 14336), (Q6_K, 4096, 14336), (Q6_K, 8192, 4096)])
+def test_full_size_linearity_and_sampled_rows(b200, orc, t, m, k):
+    rng = np.random.default_rng(m + k)
+    w = random_blocks(t, m, k, rng)
+    wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    x = rng.standard_normal((2, k)).astype(np.float32)
+    y = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+    rows = rng.choice(m, 48, replace=False)
+    assert nmse(y[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE
+    # positive homogeneity by a power of two is exact through the quantiser: Y(4x) == 4 Y(x) bit for bit
+    y4 = b200.mul_mat(t, wp, dev(x * 4), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+    assert np.array_equal(y4, y * 4)
+    # canonical and plane layouts run different kernels over the same integers
+    yc = b200.mul_mat(t, dev(w).reshape(-1), dev(x), m).cpu().numpy()
+    assert nmse(yc, y) < DECODE_NMSE
+
+
+def test_cuda_graph_replay_and_pdl(b200, orc):
+    rng = np.random.default_rng(11)
+    m, k = 512, 4096
+    w = random_blocks(Q4_K, m, k, rng)
+    x = rng.standard_normal((1, k)).astype(np.float32)
+    s = b200.Stream(0)
+    wd, xd = dev(w).reshape(-1), dev(x)
+    y = torch.zeros((1, m), device="cuda")
+    ws = torch.empty(b200.mul_mat_workspace(Q4_K, 1, k) + 256, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    with b200.Graph(s) as g:
+        for _ in range(3):
+            b200.mul_mat(Q4_K, wd, xd, m, y=y, workspace=ws, flags=b200.MM_PDL, stream=s)
+    for _ in range(2):
+        g.launch()
+    s.synchronize()
+    assert nmse(y.cpu().numpy(), orc.mul_mat(Q4_K, w, x)) < DECODE_NMSE

@@ -1,0 +1,8 @@
+// gemm.h -- internal interface of the prefill tensor-core GEMM (gemm.cu).
+#pragma once
+#include "common.cuh"
+
+size_t b200_gemm_workspace(int type, int64_t n, int64_t k);
+// does the GEMM take this shape? (force = caller set algo == 2)
+bool   b200_gemm_wants(int type, int64_t m, int64_t n, int64_t k, bool force);
+int    b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s);
