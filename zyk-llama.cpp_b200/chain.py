@@ -1,0 +1,124 @@
+"""MatMulChain -- drives the C ABI the way llama-bench drives a backend: every quantised
+MUL_MAT / MUL_MAT_ID node of one forward pass (workloads.py) issued in graph order on one stream,
+captured once into a CUDA graph and replayed per token (tg) or per ubatch (pp).
+
+Reference counterpart: llama_decode -> ggml_backend_sched_compute_splits -> graph_compute
+(/root/reference/src/llama-context.cpp, ggml/src/ggml-backend.cpp:1443-1620) restricted to the
+MUL_MAT nodes, which is the hot path of this repository. Weights are written once through the
+load-time repack (b200_repack, the set_tensor hook), activations live in HBM between nodes.
+
+Row split: with world > 1 every rank keeps rows [lo, hi) of each matrix
+(b200_row_split) and the Y slices are exchanged after each node by `gather` (an all-gather).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import binding as B
+from .workloads import MatMul, buffer_widths, random_weight, row_bytes
+
+
+class MatMulChain:
+    def __init__(self, ops: list[MatMul], n: int, device: int = 0, *, seed: int = 1234, world: int = 1, rank: int = 0,
+                 gather=None, pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None):
+        self.ops, self.n, self.device = ops, n, device
+        self.world, self.rank, self.gather = world, rank, gather
+        self.dev = torch.device(f"cuda:{device}")
+        self.stream = stream or B.Stream(device)
+        self.flags = B.MM_PDL if pdl else 0
+        self.layout = layout
+        gen = torch.Generator(device=self.dev)
+        gen.manual_seed(seed)
+
+        # ---- weights: canonical random blocks -> load-time repack into the plane layout -------------
+        self.weights: list[torch.Tensor] = []
+        self.rows: list[tuple[int, int]] = []
+        for o in ops:
+            lo, hi = B.row_split(o.m, world, rank) if world > 1 else (0, o.m)
+            self.rows.append((lo, hi))
+            mats = []
+            for _ in range(max(1, o.n_expert)):
+                w = random_weight(o.type, hi - lo, o.k, self.dev, gen)
+                if layout == B.LAYOUT_PLANES and hi > lo:
+                    w = B.repack(o.type, w, hi - lo, o.k)
+                mats.append(w)
+            self.weights.append(torch.stack(mats) if o.n_expert else mats[0])
+
+        # ---- activations (f32, [n, width]) and the shared workspace -----------------------------------
+        self.bufs: dict[str, torch.Tensor] = {}
+        for name, width in buffer_widths(ops).items():
+            rows = n
+            if any(o.n_expert and (o.dst == name or (o.src == name and o.src == "act")) for o in ops):
+                rows = n * max(o.n_used for o in ops if o.n_expert)
+            self.bufs[name] = torch.randn((rows, width), device=self.dev, generator=gen)
+        self.ids = None
+        if any(o.n_expert for o in ops):
+            ne = max(o.n_expert for o in ops)
+            nu = max(o.n_used for o in ops)
+            self.ids = torch.stack([torch.randperm(ne, device=self.dev, generator=gen)[:nu] for _ in range(n)]).to(torch.int32).contiguous()
+        need = 0
+        for o in ops:
+            if o.n_expert:
+                need = max(need, int(B.lib.b200_mul_mat_id_workspace(o.type, o.k, o.n_used, o.n_used, n)))
+            else:
+                need = max(need, B.mul_mat_workspace(o.type, n, o.k))
+        self.workspace = torch.empty(need + 512, dtype=torch.uint8, device=self.dev)
+        self.ws_ptr = (self.workspace.data_ptr() + 255) & ~255
+        self.ws_size = self.workspace.numel() - (self.ws_ptr - self.workspace.data_ptr())
+
+        self.calls = self._build_calls()
+        self.graph = None
+        self.kernels_per_step = 0
+        torch.cuda.synchronize(self.dev)
+
+    # one prebuilt ctypes argument struct per node
+    def _build_calls(self):
+        calls = []
+        prev_src = None
+        for o, w, (lo, hi) in zip(self.ops, self.weights, self.rows):
+            x, y = self.bufs[o.src], self.bufs[o.dst]
+            if o.n_expert:
+                nb1 = o.n_used if o.src == "act" else 1
+                a = B.MulMatIdArgs(o.type, self.layout, hi - lo, o.k, o.n_expert, o.n_used, nb1, self.n,
+                                   w.data_ptr(), (hi - lo) * row_bytes(o.type, o.k),
+                                   x.data_ptr(), x.shape[1], nb1 * x.shape[1],
+                                   self.ids.data_ptr(), o.n_used,
+                                   y.data_ptr() + 4 * lo, y.shape[1], o.n_used * y.shape[1],
+                                   self.ws_ptr, self.ws_size, B.Q8_X86, 0, self.flags, 0)
+                calls.append((B.lib.b200_mul_mat_id, a, o, y))
+                prev_src = None
+            else:
+                flags = self.flags | (B.MM_X_PREQUANTISED if prev_src == (o.src, o.k) else 0)
+                a = B.MulMatArgs(o.type, self.layout, hi - lo, self.n, o.k, w.data_ptr(), 0, x.data_ptr(), x.shape[1],
+                                 y.data_ptr() + 4 * lo, y.shape[1], self.ws_ptr, self.ws_size, B.Q8_X86, 0, flags, 0)
+                calls.append((B.lib.b200_mul_mat, a, o, y))
+                prev_src = (o.src, o.k)
+        return calls
+
+    def issue(self):
+        """enqueue one forward pass' worth of MUL_MAT nodes on self.stream (no host sync)"""
+        h = self.stream.handle
+        for fn, a, o, y in self.calls:
+            if fn(C.byref(a), h) != 0:
+                raise B.B200Error(f"{o.name}: {B.lib.b200_last_error().decode()}")
+            if self.gather is not None:
+                self.gather(y, o, self.stream)
+
+    def capture(self):
+        before = B.launch_count()
+        with B.Graph(self.stream) as g:
+            self.issue()
+        self.kernels_per_step = B.launch_count() - before
+        self.graph = g
+        return g
+
+    def step(self):
+        if self.graph is not None:
+            self.graph.launch()
+        else:
+            self.issue()
+
+    def weight_bytes_resident(self) -> int:
+        return sum(w.numel() for w in self.weights)
