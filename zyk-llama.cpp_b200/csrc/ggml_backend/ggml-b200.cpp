@@ -1,0 +1,712 @@
+// ggml-b200.cpp -- the ggml backend plugin (libggml-b200.so): reg / device / buffer_type / buffer /
+// backend vtables of /root/reference/ggml/src/ggml-backend-impl.h:11-251 implemented on top of the
+// C ABI in include/b200_mm.h. Plain C++ (no CUDA headers): every device action is a b200_* call.
+//
+// What the device claims (supports_op): the layout no-ops (NONE / VIEW / RESHAPE / PERMUTE /
+// TRANSPOSE) and GGML_OP_MUL_MAT / GGML_OP_MUL_MAT_ID with Q4_0 / Q8_0 / Q4_K / Q6_K / IQ4_XS
+// weights, f32 activations and f32 results. Everything else stays with the caller's other
+// backends (ggml_backend_sched splits on supports_op, ggml-backend.cpp:787-842).
+//
+// Load-time repack: a whole-tensor set_tensor of a contiguous, non-view weight tensor with
+// ne0 % 256 == 0 is stored in the B200 plane layout (b200_repack); get_tensor hands canonical
+// ggml bytes back (b200_unrepack). The reference hook this replaces is
+// ggml_backend_cpu_repack_buffer_set_tensor (ggml-cpu/repack.cpp:3141-3151). A tensor is demoted
+// back to canonical bytes the moment something needs them in place (partial write, memset, a
+// differently-shaped view used as MUL_MAT src0).
+#include "ggml.h"
+#include "ggml-backend.h"
+#include "ggml-backend-impl.h"
+#include "ggml-impl.h"
+
+#include "b200_mm.h"
+#include "ggml_b200.h"
+
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#define B200_MAX_DEVICES 16
+#define B200_ALIGNMENT   256
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------
+// contexts
+// ---------------------------------------------------------------------------------------------------
+struct device_ctx {
+    int         index = 0;
+    std::string name;         // "B200_0"
+    std::string description;  // "NVIDIA B200"
+    ggml_backend_buffer_type buft{};
+    ggml_backend_buffer_type host_buft{};
+    std::string buft_name, host_buft_name;
+};
+
+struct plane_entry {   // a tensor currently stored in the plane layout
+    int     type;
+    int64_t m, k, nmat;
+    size_t  nbytes;
+};
+
+struct buffer_ctx {
+    int    device = 0;
+    void * base = nullptr;
+    size_t size = 0;
+    std::mutex mu;
+    std::unordered_map<const void *, plane_entry> planes;  // key: tensor->data
+    void * staging = nullptr;
+    size_t staging_size = 0;
+
+    void * stage(size_t n) {   // grow-only scratch for repack / unrepack (load time, get_tensor)
+        if (n > staging_size) {
+            if (staging) { b200_device_synchronize(device); b200_free(device, staging); }
+            staging = b200_malloc(device, n);
+            staging_size = staging ? n : 0;
+        }
+        return staging;
+    }
+};
+
+struct backend_ctx {
+    int           device = 0;
+    std::string   name;
+    b200_stream_t stream = nullptr;
+    void *        workspace = nullptr;
+    size_t        workspace_size = 0;
+};
+
+bool repack_enabled() {
+    static const bool on = [] { const char * e = getenv("GGML_B200_REPACK"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
+device_ctx * dev_of(ggml_backend_buffer_type_t buft) { return (device_ctx *) buft->device->context; }
+
+bool weight_type(enum ggml_type t) { return b200_type_is_weight((int) t) != 0; }
+
+// ---------------------------------------------------------------------------------------------------
+// plane-layout bookkeeping
+// ---------------------------------------------------------------------------------------------------
+bool repack_candidate(const ggml_tensor * t) {
+    return repack_enabled() && weight_type(t->type) && t->view_src == nullptr && ggml_is_contiguous(t) &&
+           t->ne[0] % 256 == 0 && t->ne[1] > 0 && (((uintptr_t) t->data) & 15) == 0 &&
+           b200_repack_supported((int) t->type, t->ne[1], t->ne[0]);
+}
+
+// canonical -> planes, in place through the staging buffer. `canon_dev` holds the canonical bytes.
+bool planes_store(buffer_ctx * bc, const ggml_tensor * t, const void * canon_dev) {
+    const int64_t m = t->ne[1], k = t->ne[0], nmat = t->ne[2] * t->ne[3];
+    const size_t mat = (size_t) m * b200_row_size((int) t->type, k);
+    for (int64_t i = 0; i < nmat; ++i) {
+        if (b200_repack((int) t->type, m, k, (const char *) canon_dev + i * mat, (char *) t->data + i * mat, nullptr) != 0) {
+            GGML_LOG_ERROR("ggml-b200: repack of %s failed: %s\n", t->name, b200_last_error());
+            return false;
+        }
+    }
+    bc->planes[t->data] = plane_entry{(int) t->type, m, k, nmat, mat * (size_t) nmat};
+    return true;
+}
+
+// planes -> canonical bytes in `dst_dev` (device memory, may NOT alias the tensor)
+bool planes_load(const plane_entry & e, const void * data, void * dst_dev) {
+    const size_t mat = e.nbytes / (size_t) e.nmat;
+    for (int64_t i = 0; i < e.nmat; ++i) {
+        if (b200_unrepack(e.type, e.m, e.k, (const char *) data + i * mat, (char *) dst_dev + i * mat, nullptr) != 0) {
+            GGML_LOG_ERROR("ggml-b200: unrepack failed: %s\n", b200_last_error());
+            return false;
+        }
+    }
+    return true;
+}
+
+// make the bytes at `data` canonical again (caller holds bc->mu)
+void planes_demote_locked(buffer_ctx * bc, const void * data) {
+    auto it = bc->planes.find(data);
+    if (it == bc->planes.end()) return;
+    const plane_entry e = it->second;
+    b200_device_synchronize(bc->device);   // kernels on backend streams may still be reading the planes
+    void * tmp = bc->stage(e.nbytes);
+    GGML_ASSERT(tmp && "ggml-b200: out of device memory while demoting a repacked tensor");
+    planes_load(e, data, tmp);
+    b200_memcpy_d2d((void *) data, tmp, e.nbytes, nullptr);
+    b200_stream_synchronize(nullptr);
+    bc->planes.erase(it);
+}
+
+// the buffer context that owns a tensor allocated in one of OUR device buffers, else nullptr
+const char * buft_get_name(ggml_backend_buffer_type_t buft);
+buffer_ctx * owner_ctx(const ggml_tensor * t) {
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    if (!buf || buf->buft->iface.get_name != buft_get_name) return nullptr;
+    return (buffer_ctx *) buf->context;
+}
+
+// Is MUL_MAT src0 `w` stored as planes right now? Demotes when a view needs canonical bytes.
+int weight_layout(const ggml_tensor * w) {
+    buffer_ctx * bc = owner_ctx(w);
+    if (!bc) return B200_LAYOUT_CANONICAL;
+    const ggml_tensor * base = w->view_src ? w->view_src : w;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    auto it = bc->planes.find(base->data);
+    if (it == bc->planes.end()) return B200_LAYOUT_CANONICAL;
+    const plane_entry & e = it->second;
+    const bool same = w->data == base->data && w->ne[0] == e.k && w->ne[1] == e.m && w->ne[2] * w->ne[3] == e.nmat &&
+                      (int) w->type == e.type && ggml_is_contiguous(w);
+    if (same) return B200_LAYOUT_PLANES;
+    planes_demote_locked(bc, base->data);
+    return B200_LAYOUT_CANONICAL;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// buffer
+// ---------------------------------------------------------------------------------------------------
+void buffer_free(ggml_backend_buffer_t buffer) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    if (bc->staging) b200_free(bc->device, bc->staging);
+    b200_free(bc->device, bc->base);
+    delete bc;
+}
+
+void * buffer_get_base(ggml_backend_buffer_t buffer) { return ((buffer_ctx *) buffer->context)->base; }
+
+enum ggml_status buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor) {
+    // (re)initialising a non-view tensor at an address forgets any plane state recorded there
+    if (tensor->view_src == nullptr && tensor->data) {
+        buffer_ctx * bc = (buffer_ctx *) buffer->context;
+        std::lock_guard<std::mutex> lock(bc->mu);
+        bc->planes.erase(tensor->data);
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    if (size == 0) return;
+    b200_set_device(bc->device);
+    const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    const bool whole = offset == 0 && size == ggml_nbytes(tensor);
+    if (whole && repack_candidate(tensor)) {
+        void * tmp = bc->stage(size);
+        if (tmp) {
+            int rc = b200_memcpy_h2d(tmp, data, size, nullptr);
+            if (rc == 0 && planes_store(bc, tensor, tmp)) {
+                b200_stream_synchronize(nullptr);
+                return;
+            }
+        }
+        bc->planes.erase(tensor->data);   // fall through to the canonical write
+    } else {
+        planes_demote_locked(bc, base->data);
+    }
+    if (b200_memcpy_h2d((char *) tensor->data + offset, data, size, nullptr) != 0 || b200_stream_synchronize(nullptr) != 0)
+        GGML_ABORT("ggml-b200: set_tensor(%s) failed: %s", tensor->name, b200_last_error());
+}
+
+void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    if (size == 0) return;
+    b200_set_device(bc->device);
+    const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    auto it = bc->planes.find(base->data);
+    const char * src = (const char *) tensor->data + offset;
+    if (it != bc->planes.end()) {
+        // hand canonical bytes back: inverse repack of the owning tensor into scratch, copy the range out
+        void * tmp = bc->stage(it->second.nbytes);
+        GGML_ASSERT(tmp && "ggml-b200: out of device memory in get_tensor");
+        planes_load(it->second, base->data, tmp);
+        src = (const char *) tmp + ((const char *) tensor->data - (const char *) base->data) + offset;
+    }
+    if (b200_memcpy_d2h(data, src, size, nullptr) != 0 || b200_stream_synchronize(nullptr) != 0)
+        GGML_ABORT("ggml-b200: get_tensor(%s) failed: %s", tensor->name, b200_last_error());
+}
+
+void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    if (size == 0) return;
+    b200_set_device(bc->device);
+    const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    planes_demote_locked(bc, base->data);
+    b200_memset((char *) tensor->data + offset, value, size, nullptr);
+    b200_stream_synchronize(nullptr);
+}
+
+bool buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_tensor * dst) {
+    // device-to-device for plain (never repacked) data of our own buffers; everything else takes the
+    // generic get_tensor + set_tensor route (ggml-backend.cpp:389-410), which keeps layouts consistent
+    buffer_ctx * dc = (buffer_ctx *) buffer->context;
+    buffer_ctx * sc = owner_ctx(src);
+    if (!sc || ggml_is_quantized(src->type) || !ggml_is_contiguous(src) || !ggml_is_contiguous(dst) || ggml_nbytes(src) != ggml_nbytes(dst))
+        return false;
+    int rc = sc->device == dc->device
+                 ? b200_memcpy_d2d(dst->data, src->data, ggml_nbytes(src), nullptr)
+                 : b200_memcpy_peer(dst->data, dc->device, src->data, sc->device, ggml_nbytes(src), nullptr);
+    if (rc != 0) return false;
+    b200_stream_synchronize(nullptr);
+    return true;
+}
+
+void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    b200_set_device(bc->device);
+    std::lock_guard<std::mutex> lock(bc->mu);
+    bc->planes.clear();
+    b200_memset(bc->base, value, bc->size, nullptr);
+    b200_stream_synchronize(nullptr);
+}
+
+void buffer_reset(ggml_backend_buffer_t buffer) {
+    buffer_ctx * bc = (buffer_ctx *) buffer->context;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    bc->planes.clear();
+}
+
+const ggml_backend_buffer_i buffer_iface = {
+    /* .free_buffer   = */ buffer_free,
+    /* .get_base      = */ buffer_get_base,
+    /* .init_tensor   = */ buffer_init_tensor,
+    /* .memset_tensor = */ buffer_memset_tensor,
+    /* .set_tensor    = */ buffer_set_tensor,
+    /* .get_tensor    = */ buffer_get_tensor,
+    /* .cpy_tensor    = */ buffer_cpy_tensor,
+    /* .clear         = */ buffer_clear,
+    /* .reset         = */ buffer_reset,
+};
+
+// ---------------------------------------------------------------------------------------------------
+// buffer types: device memory (default) and pinned host memory
+// ---------------------------------------------------------------------------------------------------
+const char * buft_get_name(ggml_backend_buffer_type_t buft) { return dev_of(buft)->buft_name.c_str(); }
+
+ggml_backend_buffer_t buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    device_ctx * dc = dev_of(buft);
+    void * p = b200_malloc(dc->index, size);
+    if (!p) {
+        GGML_LOG_ERROR("ggml-b200: allocating %.2f MiB on device %d failed: %s\n", size / 1048576.0, dc->index, b200_last_error());
+        return nullptr;
+    }
+    buffer_ctx * bc = new buffer_ctx;
+    bc->device = dc->index;
+    bc->base = p;
+    bc->size = size;
+    return ggml_backend_buffer_init(buft, buffer_iface, bc, size);
+}
+
+size_t buft_get_alignment(ggml_backend_buffer_type_t) { return B200_ALIGNMENT; }
+
+size_t buft_get_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * tensor) {
+    // quantised rows are read with 128-bit loads: keep 512 B of slack behind every quantised tensor
+    size_t n = ggml_nbytes(tensor);
+    if (ggml_is_quantized(tensor->type)) n += 512;
+    return n;
+}
+
+bool buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i buft_iface = {
+    /* .get_name       = */ buft_get_name,
+    /* .alloc_buffer   = */ buft_alloc_buffer,
+    /* .get_alignment  = */ buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ buft_get_alloc_size,
+    /* .is_host        = */ buft_is_host,
+};
+
+// pinned host memory: a CPU buffer whose storage came from b200_malloc_host (faster H2D/D2H for the
+// scheduler's input/output copies; ggml_backend_dev_host_buffer_type, ggml-backend.h:181)
+const char * host_buft_get_name(ggml_backend_buffer_type_t buft) { return dev_of(buft)->host_buft_name.c_str(); }
+
+void host_buffer_free(ggml_backend_buffer_t buffer) { b200_free_host(buffer->context); }
+
+ggml_backend_buffer_t host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    void * p = b200_malloc_host(size);
+    if (!p) {   // pinned memory exhausted: let the caller fall back to a pageable CPU buffer
+        GGML_LOG_WARN("ggml-b200: pinned host allocation of %.2f MiB failed, using pageable memory\n", size / 1048576.0);
+        return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);
+    }
+    ggml_backend_buffer_t buf = ggml_backend_cpu_buffer_from_ptr(p, size);
+    buf->buft = buft;
+    buf->iface.free_buffer = host_buffer_free;
+    return buf;
+}
+
+size_t host_buft_get_alignment(ggml_backend_buffer_type_t) { return 64; }
+bool   host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
+
+const ggml_backend_buffer_type_i host_buft_iface = {
+    /* .get_name       = */ host_buft_get_name,
+    /* .alloc_buffer   = */ host_buft_alloc_buffer,
+    /* .get_alignment  = */ host_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ nullptr,
+    /* .is_host        = */ host_buft_is_host,
+};
+
+// ---------------------------------------------------------------------------------------------------
+// op support
+// ---------------------------------------------------------------------------------------------------
+bool mul_mat_operands_ok(const ggml_tensor * w, const ggml_tensor * x, const ggml_tensor * y) {
+    if (!weight_type(w->type) || x->type != GGML_TYPE_F32 || y->type != GGML_TYPE_F32) return false;
+    if (w->nb[0] != ggml_type_size(w->type)) return false;            // quantised rows must be contiguous
+    if (x->nb[0] != sizeof(float) || y->nb[0] != sizeof(float)) return false;
+    if (x->nb[1] % sizeof(float) || x->nb[2] % sizeof(float) || x->nb[3] % sizeof(float)) return false;
+    if (w->ne[0] != x->ne[0] || w->ne[0] % ggml_blck_size(w->type) != 0) return false;
+    return true;
+}
+
+bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_VIEW:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT: {
+            const ggml_tensor * w = op->src[0], * x = op->src[1];
+            if (!w || !x || !mul_mat_operands_ok(w, x, op)) return false;
+            return x->ne[2] % w->ne[2] == 0 && x->ne[3] % w->ne[3] == 0;   // broadcast (ggml.c:3168-3174)
+        }
+        case GGML_OP_MUL_MAT_ID: {
+            const ggml_tensor * as = op->src[0], * b = op->src[1], * ids = op->src[2];
+            if (!as || !b || !ids || !mul_mat_operands_ok(as, b, op)) return false;
+            if (ids->type != GGML_TYPE_I32 || ids->nb[0] != sizeof(int32_t) || ids->nb[1] % sizeof(int32_t)) return false;
+            if (as->ne[3] != 1 || b->ne[3] != 1) return false;
+            if (as->nb[1] != ggml_row_size(as->type, as->ne[0])) return false;   // rows of one expert packed
+            return b->ne[1] == 1 || b->ne[1] == ids->ne[0];
+        }
+        default:
+            return false;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// backend (one stream)
+// ---------------------------------------------------------------------------------------------------
+const char * backend_get_name(ggml_backend_t backend) { return ((backend_ctx *) backend->context)->name.c_str(); }
+
+void backend_free(ggml_backend_t backend) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    b200_set_device(bc->device);
+    if (bc->stream) { b200_stream_synchronize(bc->stream); b200_stream_destroy(bc->stream); }
+    if (bc->workspace) b200_free(bc->device, bc->workspace);
+    delete bc;
+    delete backend;
+}
+
+void backend_synchronize(ggml_backend_t backend) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    if (b200_stream_synchronize(bc->stream) != 0) GGML_ABORT("ggml-b200: synchronize failed: %s", b200_last_error());
+}
+
+bool backend_reserve(backend_ctx * bc, size_t need) {
+    if (need <= bc->workspace_size) return true;
+    b200_stream_synchronize(bc->stream);   // kernels in flight may still read the old workspace
+    if (bc->workspace) b200_free(bc->device, bc->workspace);
+    need = (need + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+    bc->workspace = b200_malloc(bc->device, need);
+    bc->workspace_size = bc->workspace ? need : 0;
+    return bc->workspace != nullptr;
+}
+
+enum ggml_status compute_mul_mat(backend_ctx * bc, const ggml_tensor * dst) {
+    const ggml_tensor * w = dst->src[0], * x = dst->src[1];
+    const int64_t k = w->ne[0], m = w->ne[1], n = x->ne[1];
+    const int layout = weight_layout(w);
+    const size_t need = b200_mul_mat_workspace((int) w->type, n, k);
+    if (!backend_reserve(bc, need)) return GGML_STATUS_ALLOC_FAILED;
+    const int64_t r2 = x->ne[2] / w->ne[2], r3 = x->ne[3] / w->ne[3];
+    for (int64_t i13 = 0; i13 < x->ne[3]; ++i13) {
+        for (int64_t i12 = 0; i12 < x->ne[2]; ++i12) {
+            const int64_t i03 = i13 / r3, i02 = i12 / r2;
+            b200_mul_mat_args a = {};
+            a.type = (int32_t) w->type;
+            a.layout = layout;
+            a.m = m; a.n = n; a.k = k;
+            a.w = (const char *) w->data + i02 * w->nb[2] + i03 * w->nb[3];
+            a.w_row_stride = layout == B200_LAYOUT_PLANES ? 0 : (int64_t) w->nb[1];
+            a.x = (const float *) ((const char *) x->data + i12 * x->nb[2] + i13 * x->nb[3]);
+            a.x_row_stride = (int64_t) (x->nb[1] / sizeof(float));
+            a.y = (float *) ((char *) dst->data + i12 * dst->nb[2] + i13 * dst->nb[3]);
+            a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
+            a.workspace = bc->workspace;
+            a.workspace_size = bc->workspace_size;
+            a.flavour = B200_Q8_X86;
+            if (b200_mul_mat(&a, bc->stream) != 0) {
+                GGML_LOG_ERROR("ggml-b200: MUL_MAT %s failed: %s\n", dst->name, b200_last_error());
+                return GGML_STATUS_FAILED;
+            }
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
+    const ggml_tensor * as = dst->src[0], * b = dst->src[1], * ids = dst->src[2];
+    const int64_t k = as->ne[0], m = as->ne[1], n_as = as->ne[2];
+    const int64_t n_used = ids->ne[0], n_tokens = ids->ne[1], nb1 = b->ne[1];
+    const int layout = weight_layout(as);
+    const int64_t chunk = n_used > 0 ? (65535 / n_used > 0 ? 65535 / n_used : 1) : n_tokens;   // (token, slot) pairs per launch
+    const int64_t tmax = n_tokens < chunk ? n_tokens : chunk;
+    const size_t need = b200_mul_mat_id_workspace((int) as->type, k, n_used, nb1, tmax);
+    if (!backend_reserve(bc, need)) return GGML_STATUS_ALLOC_FAILED;
+    for (int64_t t0 = 0; t0 < n_tokens; t0 += chunk) {
+        const int64_t nt = n_tokens - t0 < chunk ? n_tokens - t0 : chunk;
+        b200_mul_mat_id_args a = {};
+        a.type = (int32_t) as->type; a.layout = layout;
+        a.m = m; a.k = k; a.n_as = n_as; a.n_used = n_used; a.nb1 = nb1; a.n_tokens = nt;
+        a.as = as->data; a.as_expert_stride = (int64_t) as->nb[2];
+        a.b = (const float *) ((const char *) b->data + t0 * b->nb[2]);
+        a.b_row_stride = (int64_t) (b->nb[1] / sizeof(float)); a.b_token_stride = (int64_t) (b->nb[2] / sizeof(float));
+        a.ids = (const int32_t *) ((const char *) ids->data + t0 * ids->nb[1]);
+        a.ids_row_stride = (int64_t) (ids->nb[1] / sizeof(int32_t));
+        a.y = (float *) ((char *) dst->data + t0 * dst->nb[2]);
+        a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float)); a.y_token_stride = (int64_t) (dst->nb[2] / sizeof(float));
+        a.workspace = bc->workspace; a.workspace_size = bc->workspace_size;
+        a.flavour = B200_Q8_X86;
+        if (b200_mul_mat_id(&a, bc->stream) != 0) {
+            GGML_LOG_ERROR("ggml-b200: MUL_MAT_ID %s failed: %s\n", dst->name, b200_last_error());
+            return GGML_STATUS_FAILED;
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    b200_set_device(bc->device);
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        ggml_tensor * node = cgraph->nodes[i];
+        if (ggml_is_empty(node)) continue;
+        enum ggml_status st = GGML_STATUS_SUCCESS;
+        switch (node->op) {
+            case GGML_OP_NONE:
+            case GGML_OP_VIEW:
+            case GGML_OP_RESHAPE:
+            case GGML_OP_PERMUTE:
+            case GGML_OP_TRANSPOSE:
+                break;
+            case GGML_OP_MUL_MAT:    st = compute_mul_mat(bc, node); break;
+            case GGML_OP_MUL_MAT_ID: st = compute_mul_mat_id(bc, node); break;
+            default:
+                GGML_LOG_ERROR("ggml-b200: op %s (%s) is not supported by this backend\n", ggml_op_name(node->op), node->name);
+                return GGML_STATUS_FAILED;
+        }
+        if (st != GGML_STATUS_SUCCESS) return st;
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+void backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    b200_event_record((b200_event_t) event->context, bc->stream);
+}
+
+void backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    b200_stream_wait_event(bc->stream, (b200_event_t) event->context);
+}
+
+const ggml_backend_i backend_iface = {
+    /* .get_name           = */ backend_get_name,
+    /* .free               = */ backend_free,
+    /* .set_tensor_async   = */ nullptr,   // set/get go through the buffer (repack-aware, synchronous)
+    /* .get_tensor_async   = */ nullptr,
+    /* .cpy_tensor_async   = */ nullptr,
+    /* .synchronize        = */ backend_synchronize,
+    /* .graph_plan_create  = */ nullptr,
+    /* .graph_plan_free    = */ nullptr,
+    /* .graph_plan_update  = */ nullptr,
+    /* .graph_plan_compute = */ nullptr,
+    /* .graph_compute      = */ backend_graph_compute,
+    /* .event_record       = */ backend_event_record,
+    /* .event_wait         = */ backend_event_wait,
+    /* .graph_optimize     = */ nullptr,
+};
+
+ggml_guid_t backend_guid() {
+    static ggml_guid guid = {0xb2, 0x00, 0x51, 0x00, 0xa0, 0x6d, 0x4d, 0x41, 0x54, 0x5f, 0x51, 0x34, 0x4b, 0x36, 0x4b, 0x38};
+    return &guid;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// device
+// ---------------------------------------------------------------------------------------------------
+const char * device_get_name(ggml_backend_dev_t dev) { return ((device_ctx *) dev->context)->name.c_str(); }
+const char * device_get_description(ggml_backend_dev_t dev) { return ((device_ctx *) dev->context)->description.c_str(); }
+
+void device_get_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    device_ctx * dc = (device_ctx *) dev->context;
+    size_t f = 0, t = 0;
+    b200_device_info(dc->index, nullptr, 0, &f, &t, nullptr, nullptr, nullptr);
+    *free = f; *total = t;
+}
+
+enum ggml_backend_dev_type device_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+
+void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    props->name = device_get_name(dev);
+    props->description = device_get_description(dev);
+    props->type = GGML_BACKEND_DEVICE_TYPE_GPU;
+    props->device_id = nullptr;
+    device_get_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = {
+        /* .async                = */ false,
+        /* .host_buffer          = */ true,
+        /* .buffer_from_host_ptr = */ false,
+        /* .events               = */ true,
+    };
+}
+
+ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char *) {
+    device_ctx * dc = (device_ctx *) dev->context;
+    backend_ctx * bc = new backend_ctx;
+    bc->device = dc->index;
+    bc->name = dc->name;
+    bc->stream = b200_stream_create(dc->index);
+    if (!bc->stream) {
+        GGML_LOG_ERROR("ggml-b200: cannot create a stream on device %d: %s\n", dc->index, b200_last_error());
+        delete bc;
+        return nullptr;
+    }
+    return new ggml_backend{
+        /* .guid    = */ backend_guid(),
+        /* .iface   = */ backend_iface,
+        /* .device  = */ dev,
+        /* .context = */ bc,
+    };
+}
+
+ggml_backend_buffer_type_t device_get_buffer_type(ggml_backend_dev_t dev) { return &((device_ctx *) dev->context)->buft; }
+ggml_backend_buffer_type_t device_get_host_buffer_type(ggml_backend_dev_t dev) { return &((device_ctx *) dev->context)->host_buft; }
+
+bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    // our own device memory on this device, or any host-visible buffer type is NOT enough: the kernels
+    // dereference device pointers, so only buffers of this very device qualify
+    return buft->iface.get_name == buft_get_name && buft->device == dev;
+}
+
+bool device_offload_op(ggml_backend_dev_t, const ggml_tensor *) { return false; }
+
+ggml_backend_event_t device_event_new(ggml_backend_dev_t dev) {
+    device_ctx * dc = (device_ctx *) dev->context;
+    b200_event_t ev = b200_event_create(dc->index);
+    if (!ev) return nullptr;
+    return new ggml_backend_event{ /* .device = */ dev, /* .context = */ ev };
+}
+void device_event_free(ggml_backend_dev_t, ggml_backend_event_t event) {
+    b200_event_destroy((b200_event_t) event->context);
+    delete event;
+}
+void device_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) { b200_event_synchronize((b200_event_t) event->context); }
+
+const ggml_backend_device_i device_iface = {
+    /* .get_name             = */ device_get_name,
+    /* .get_description      = */ device_get_description,
+    /* .get_memory           = */ device_get_memory,
+    /* .get_type             = */ device_get_type,
+    /* .get_props            = */ device_get_props,
+    /* .init_backend         = */ device_init_backend,
+    /* .get_buffer_type      = */ device_get_buffer_type,
+    /* .get_host_buffer_type = */ device_get_host_buffer_type,
+    /* .buffer_from_host_ptr = */ nullptr,
+    /* .supports_op          = */ device_supports_op,
+    /* .supports_buft        = */ device_supports_buft,
+    /* .offload_op           = */ device_offload_op,
+    /* .event_new            = */ device_event_new,
+    /* .event_free           = */ device_event_free,
+    /* .event_synchronize    = */ device_event_synchronize,
+};
+
+// ---------------------------------------------------------------------------------------------------
+// registry
+// ---------------------------------------------------------------------------------------------------
+struct reg_ctx {
+    std::vector<ggml_backend_device> devices;
+    std::vector<device_ctx *>        ctxs;
+};
+
+const char * reg_get_name(ggml_backend_reg_t) { return "B200"; }
+size_t reg_get_device_count(ggml_backend_reg_t reg) { return ((reg_ctx *) reg->context)->devices.size(); }
+ggml_backend_dev_t reg_get_device(ggml_backend_reg_t reg, size_t index) {
+    reg_ctx * rc = (reg_ctx *) reg->context;
+    GGML_ASSERT(index < rc->devices.size());
+    return &rc->devices[index];
+}
+
+ggml_backend_feature * reg_get_features(ggml_backend_reg_t) {
+    static ggml_backend_feature features[] = {
+        {"ARCH", "sm_100a"}, {"TCGEN05", "1"}, {"TMA", "1"}, {"REPACK", "planes"}, {nullptr, nullptr},
+    };
+    return features;
+}
+
+void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) reg_get_features;
+    return nullptr;
+}
+
+const ggml_backend_reg_i reg_iface = {
+    /* .get_name         = */ reg_get_name,
+    /* .get_device_count = */ reg_get_device_count,
+    /* .get_device       = */ reg_get_device,
+    /* .get_proc_address = */ reg_get_proc_address,
+};
+
+int usable_devices(int * idx, int cap) {
+    int n = b200_device_count(), out = 0;
+    for (int i = 0; i < n && out < cap; ++i) {
+        int major = 0, minor = 0;
+        if (b200_device_info(i, nullptr, 0, nullptr, nullptr, nullptr, &major, &minor) == 0 && major == 10) idx[out++] = i;
+    }
+    return out;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------
+// dlsym entry points (ggml-backend-reg.cpp:262-306)
+// ---------------------------------------------------------------------------------------------------
+extern "C" {
+
+GGML_B200_API int ggml_backend_score(void) {
+    int idx[B200_MAX_DEVICES];
+    return usable_devices(idx, B200_MAX_DEVICES) > 0 ? 100 : 0;
+}
+
+GGML_B200_API ggml_backend_reg_t ggml_backend_init(void) {
+    static ggml_backend_reg reg;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        reg_ctx * rc = new reg_ctx;
+        int idx[B200_MAX_DEVICES];
+        const int n = usable_devices(idx, B200_MAX_DEVICES);
+        rc->devices.reserve(n);
+        for (int i = 0; i < n; ++i) {
+            device_ctx * dc = new device_ctx;
+            char name[128] = "";
+            b200_device_info(idx[i], name, sizeof(name), nullptr, nullptr, nullptr, nullptr, nullptr);
+            dc->index = idx[i];
+            dc->name = "B200_" + std::to_string(i);
+            dc->description = name;
+            dc->buft_name = dc->name;
+            dc->host_buft_name = dc->name + "_Host";
+            rc->ctxs.push_back(dc);
+            rc->devices.push_back(ggml_backend_device{ /* .iface = */ device_iface, /* .reg = */ &reg, /* .context = */ dc });
+        }
+        for (int i = 0; i < n; ++i) {
+            device_ctx * dc = rc->ctxs[i];
+            dc->buft = ggml_backend_buffer_type{ /* .iface = */ buft_iface, /* .device = */ &rc->devices[i], /* .context = */ nullptr };
+            dc->host_buft = ggml_backend_buffer_type{ /* .iface = */ host_buft_iface, /* .device = */ &rc->devices[i], /* .context = */ nullptr };
+        }
+        reg = ggml_backend_reg{ /* .api_version = */ GGML_BACKEND_API_VERSION, /* .iface = */ reg_iface, /* .context = */ rc };
+    });
+    return &reg;
+}
+
+} // extern "C"

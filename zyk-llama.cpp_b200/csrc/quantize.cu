@@ -45,6 +45,7 @@ int b200_act_quant_planes(int act_type, int flavour, const float * x, int64_t ld
 
 extern "C" int b200_quantize_rows(int q8_type, int flavour, const float * x, int64_t x_row_stride, void * y, int64_t nrows,
                                   int64_t k, b200_stream_t stream) {
+    if (nrows == 0 || k == 0) return 0;   // empty input: nothing to do, pointers may be null
     B200_REQUIRE(x && y, "b200_quantize_rows: null pointer");
     return b200_act_quant_canonical(q8_type, flavour, x, x_row_stride, y, nrows, k, (cudaStream_t) stream);
 }
