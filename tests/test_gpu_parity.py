@@ -224,3 +224,60 @@ def test_cuda_graph_replay_and_pdl(b200, orc):
         g.launch()
     s.synchronize()
     assert nmse(y.cpu().numpy(), orc.mul_mat(Q4_K, w, x)) < DECODE_NMSE
+
+
+# ---- (2) prefill GEMM (tcgen05): within the reference's tolerance of the CPU path, and much closer to the f64 truth ------
+GEMM_VS_TRUTH = 2e-6     # fp16 operands, fp32 accumulation in TMEM: what the kernel actually achieves vs exact arithmetic
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("n", [9, 16, 33, 128, 256, 300, 512])
+def test_gemm_vs_oracle(b200, orc, t, n):
+    rng = np.random.default_rng(t * 1000 + n)
+    m, k = 256, 1024
+    w = random_blocks(t, m, k, rng)
+    x = _acts(rng, n, k)
+    wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    got = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=2).cpu().numpy()
+    assert np.isfinite(got).all()
+    assert nmse(got, orc.mul_mat(t, w, x)) < MAX_NMSE          # vs the CPU's quantised-activation arithmetic
+    assert nmse(got, orc.mul_mat_f64(t, w, x)) < GEMM_VS_TRUTH  # vs exact arithmetic on the dequantised weights
+
+
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("shape", [(131, 256, 40), (128, 2304, 17), (1000, 512, 77), (384, 4096, 512)])
+def test_gemm_ragged_shapes_and_strides(b200, orc, t, shape):
+    m, k, n = shape
+    rng = np.random.default_rng(m + k + n + t)
+    w = random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k + 32)).astype(np.float32)     # padded activation rows (row stride != k)
+    y = torch.full((n, m + 3), 7.0, device="cuda")
+    wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    b200.mul_mat(t, wp, dev(x)[:, :k], m, layout=b200.LAYOUT_PLANES, algo=2, y=y[:, :m])
+    assert nmse(y[:, :m].cpu().numpy(), orc.mul_mat_f64(t, w, x[:, :k].copy())) < GEMM_VS_TRUTH
+    assert torch.all(y[:, m:] == 7.0)                           # sentinel columns untouched
+
+
+def test_gemm_is_the_default_for_prefill_batches(b200, orc):
+    rng = np.random.default_rng(3)
+    m, k, n = 512, 2048, 64
+    w = random_blocks(Q4_K, m, k, rng)
+    x = rng.standard_normal((n, k)).astype(np.float32)
+    wd = dev(w).reshape(-1)
+    auto = b200.mul_mat(Q4_K, wd, dev(x), m).cpu().numpy()                 # canonical Q4_K is its own plane layout
+    gemv = b200.mul_mat(Q4_K, wd, dev(x), m, algo=1).cpu().numpy()
+    assert not np.array_equal(auto, gemv)                                   # different kernels ...
+    assert nmse(auto, gemv) < MAX_NMSE                                      # ... same answer within tolerance
+    assert nmse(auto, orc.mul_mat_f64(Q4_K, w, x)) < GEMM_VS_TRUTH
+
+
+def test_gemm_huge_activation_magnitudes_do_not_overflow_fp16(b200, orc):
+    rng = np.random.default_rng(4)
+    m, k, n = 128, 512, 32
+    w = random_blocks(Q6_K, m, k, rng)
+    x = (rng.standard_normal((n, k)) * np.logspace(-20, 20, n)[:, None]).astype(np.float32)
+    got = b200.mul_mat(Q6_K, b200.repack(Q6_K, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES, algo=2).cpu().numpy()
+    want = orc.mul_mat_f64(Q6_K, w, x)
+    assert np.isfinite(got).all()
+    for r in range(n):
+        assert nmse(got[r], want[r]) < GEMM_VS_TRUTH
