@@ -139,7 +139,7 @@ typedef struct b200_mul_mat_args {
     void *  workspace;     /* >= b200_mul_mat_workspace(type, n, k) bytes, 256 B aligned         */
     size_t  workspace_size;
     int32_t flavour;       /* enum b200_q8_flavour for the Q8_0 activation quantiser             */
-    int32_t algo;          /* 0 = auto, 1 = force decode GEMV, 2 = force tensor-core GEMM        */
+    int32_t algo;          /* 0 = auto, 1 = register GEMV, 2 = tensor-core GEMM, 3 = streaming GEMV */
     int32_t flags;         /* B200_MM_* bits                                                     */
     int32_t reserved;
 } b200_mul_mat_args;
@@ -154,6 +154,10 @@ enum {
 B200_API size_t b200_mul_mat_workspace(int type, int64_t n, int64_t k);
 /* replaces ggml_compute_forward_mul_mat (ggml-cpu.c:1227-1427) for a 2-D slice */
 B200_API int    b200_mul_mat(const b200_mul_mat_args * args, b200_stream_t stream);
+/* `count` MUL_MAT nodes that read the same X (wq/wk/wv, ffn_gate/ffn_up: same x, n, k, strides): issued as ONE
+ * streaming launch when n <= 4 and every matrix is in the plane layout, else as `count` b200_mul_mat calls.
+ * Counterpart of the reference's fused gate/up GEMV (ggml_cuda_should_fuse_mul_mat_vec_q, ggml-cuda.cu:2144-2180). */
+B200_API int    b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t stream);
 
 /* ---- (4) MUL_MAT_ID (ggml.c:3217-3243; CPU driver ggml-cpu.c:1500-1676) ----------------------
  *   as   : n_as expert matrices, each m rows x k, `as_expert_stride` bytes apart

@@ -281,3 +281,61 @@ def test_gemm_huge_activation_magnitudes_do_not_overflow_fp16(b200, orc):
     assert np.isfinite(got).all()
     for r in range(n):
         assert nmse(got[r], want[r]) < GEMM_VS_TRUTH
+
+
+# ---- (1) streaming decode GEMV (persistent CTAs, bulk-copy ring, fused activation quantiser) ------------------------
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("n", [1, 2, 3, 4])
+@pytest.mark.parametrize("mk", [(77, 2048), (1000, 4096), (2500, 6144)])
+def test_stream_gemv_vs_oracle(b200, orc, t, n, mk):
+    m, k = mk
+    rng = np.random.default_rng(t * 31 + n * 7 + m)
+    w = random_blocks(t, m, k, rng)
+    x = _acts(rng, n, k)
+    want = orc.mul_mat(t, w, x)
+    wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    got = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=3).cpu().numpy()
+    assert nmse(got, want) < DECODE_NMSE
+    # the register GEMV runs the same integer arithmetic: the two kernels agree to summation order
+    reg = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=1).cpu().numpy()
+    assert nmse(got, reg) < DECODE_NMSE
+
+
+def test_stream_gemv_group_mixed_types(b200, orc):
+    """wq (Q4_K) + wk (Q4_K) + wv (Q6_K) against one X in one launch, as in a Q4_K_M attention block."""
+    rng = np.random.default_rng(21)
+    k = 4096
+    ts, ms = [Q4_K, Q4_K, Q6_K], [4096, 1024, 1016]
+    ws = [random_blocks(t, m, k, rng) for t, m in zip(ts, ms)]
+    for n in (1, 3):
+        x = _acts(rng, n, k) if n > 2 else rng.standard_normal((n, k)).astype(np.float32)
+        wps = [b200.repack(t, dev(w).reshape(-1), m, k) for t, w, m in zip(ts, ws, ms)]
+        before = b200.launch_count()
+        ys = b200.mul_mat_group(ts, wps, dev(x), ms)
+        assert b200.launch_count() - before == 1          # ONE kernel for three nodes, quantiser included
+        rows = rng.choice(1016, 64, replace=False)
+        for t, w, y in zip(ts, ws, ys):
+            assert nmse(y.cpu().numpy()[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE
+
+
+def test_stream_gemv_leaves_quantised_x_for_prequantised_calls(b200, orc):
+    rng = np.random.default_rng(22)
+    m, k = 512, 4096
+    w = random_blocks(Q4_K, m, k, rng)
+    x = rng.standard_normal((1, k)).astype(np.float32)
+    wd, xd = dev(w).reshape(-1), dev(x)
+    ws = torch.zeros(b200.mul_mat_workspace(Q4_K, 1, k) + 256, dtype=torch.uint8, device="cuda")
+    y1 = b200.mul_mat(Q4_K, wd, xd, m, workspace=ws, algo=3).cpu().numpy()
+    y2 = b200.mul_mat(Q4_K, wd, xd, m, workspace=ws, algo=1, flags=b200.MM_X_PREQUANTISED).cpu().numpy()
+    want = orc.mul_mat(Q4_K, w, x)
+    assert nmse(y1, want) < DECODE_NMSE and nmse(y2, want) < DECODE_NMSE
+
+
+def test_stream_gemv_full_size_baseline_shapes(b200, orc):
+    rng = np.random.default_rng(23)
+    for t, m, k in [(Q4_K, 14336, 4096), (Q6_K, 4096, 14336), (Q6_K, 128256, 4096)]:
+        w = random_blocks(t, m, k, rng)
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        y = b200.mul_mat(t, b200.repack(t, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES, algo=3).cpu().numpy()
+        rows = np.concatenate([rng.choice(m, 40, replace=False), [0, m - 1]])
+        assert nmse(y[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE

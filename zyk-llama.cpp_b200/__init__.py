@@ -33,6 +33,7 @@ from .binding import (  # noqa: F401
     unrepack,
     mul_mat,
     mul_mat_id,
+    mul_mat_group,
     mul_mat_workspace,
     Stream,
     Event,

@@ -67,6 +67,7 @@ _sig("b200_repack", C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void
 _sig("b200_unrepack", C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p)
 _sig("b200_mul_mat_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64)
 _sig("b200_mul_mat", C.c_int, C.POINTER(MulMatArgs), C.c_void_p)
+_sig("b200_mul_mat_group", C.c_int, C.POINTER(MulMatArgs), C.c_int, C.c_void_p)
 _sig("b200_mul_mat_id_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64)
 _sig("b200_mul_mat_id", C.c_int, C.POINTER(MulMatIdArgs), C.c_void_p)
 _sig("b200_stream_create", C.c_void_p, C.c_int)
@@ -235,3 +236,20 @@ def mul_mat_id(t: int, as_: torch.Tensor, b: torch.Tensor, ids: torch.Tensor, m:
                      ws, need - (ws - workspace.data_ptr()), flavour, 0, flags, 0)
     _check(lib.b200_mul_mat_id(C.byref(a), _s(stream)))
     return y
+
+
+def mul_mat_group(ts, ws_, x: torch.Tensor, ms, *, layout=LAYOUT_PLANES, flavour=Q8_X86, flags=0, stream=None):
+    """Several weight matrices against the same X in one call (b200_mul_mat_group). Returns the list of Y tensors."""
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    n, k = x.shape
+    ys = [torch.empty((n, m), dtype=torch.float32, device=x.device) for m in ms]
+    assert len({y.stride(0) for y in ys}) >= 1
+    need = max(mul_mat_workspace(t, n, k) for t in ts) + 256
+    workspace = torch.empty(need, dtype=torch.uint8, device=x.device)
+    ws = (workspace.data_ptr() + 255) & ~255
+    arr = (MulMatArgs * len(ts))()
+    for i, (t, w, m, y) in enumerate(zip(ts, ws_, ms, ys)):
+        arr[i] = MulMatArgs(t, layout, m, n, k, _dev(w), 0, _dev(x), x.stride(0), _dev(y), y.stride(0),
+                            ws, need - (ws - workspace.data_ptr()), flavour, 0, flags, 0)
+    _check(lib.b200_mul_mat_group(arr, len(ts), _s(stream)))
+    return ys

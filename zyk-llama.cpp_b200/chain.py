@@ -22,13 +22,15 @@ from .workloads import MatMul, buffer_widths, random_weight, row_bytes
 
 class MatMulChain:
     def __init__(self, ops: list[MatMul], n: int, device: int = 0, *, seed: int = 1234, world: int = 1, rank: int = 0,
-                 gather=None, pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None):
+                 gather=None, pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None,
+                 grouping: bool = True):
         self.ops, self.n, self.device = ops, n, device
         self.world, self.rank, self.gather = world, rank, gather
         self.dev = torch.device(f"cuda:{device}")
         self.stream = stream or B.Stream(device)
         self.flags = B.MM_PDL if pdl else 0
         self.layout = layout
+        self.grouping = grouping
         gen = torch.Generator(device=self.dev)
         gen.manual_seed(seed)
 
@@ -73,13 +75,21 @@ class MatMulChain:
         self.kernels_per_step = 0
         torch.cuda.synchronize(self.dev)
 
-    # one prebuilt ctypes argument struct per node
+    # one prebuilt ctypes argument struct per node; decode nodes that read the same X (wq/wk/wv, gate/up) form a group
     def _build_calls(self):
         calls = []
-        prev_src = None
+        group: list = []
+
+        def flush():
+            if group:
+                arr = (B.MulMatArgs * len(group))(*[g[0] for g in group])
+                calls.append((B.lib.b200_mul_mat_group, arr, [g[1] for g in group], [g[2] for g in group]))
+                group.clear()
+
         for o, w, (lo, hi) in zip(self.ops, self.weights, self.rows):
             x, y = self.bufs[o.src], self.bufs[o.dst]
             if o.n_expert:
+                flush()
                 nb1 = o.n_used if o.src == "act" else 1
                 a = B.MulMatIdArgs(o.type, self.layout, hi - lo, o.k, o.n_expert, o.n_used, nb1, self.n,
                                    w.data_ptr(), (hi - lo) * row_bytes(o.type, o.k),
@@ -87,24 +97,26 @@ class MatMulChain:
                                    self.ids.data_ptr(), o.n_used,
                                    y.data_ptr() + 4 * lo, y.shape[1], o.n_used * y.shape[1],
                                    self.ws_ptr, self.ws_size, B.Q8_X86, 0, self.flags, 0)
-                calls.append((B.lib.b200_mul_mat_id, a, o, y))
-                prev_src = None
-            else:
-                flags = self.flags | (B.MM_X_PREQUANTISED if prev_src == (o.src, o.k) else 0)
-                a = B.MulMatArgs(o.type, self.layout, hi - lo, self.n, o.k, w.data_ptr(), 0, x.data_ptr(), x.shape[1],
-                                 y.data_ptr() + 4 * lo, y.shape[1], self.ws_ptr, self.ws_size, B.Q8_X86, 0, flags, 0)
-                calls.append((B.lib.b200_mul_mat, a, o, y))
-                prev_src = (o.src, o.k)
+                calls.append((B.lib.b200_mul_mat_id, a, [o], [y]))
+                continue
+            a = B.MulMatArgs(o.type, self.layout, hi - lo, self.n, o.k, w.data_ptr(), 0, x.data_ptr(), x.shape[1],
+                             y.data_ptr() + 4 * lo, y.shape[1], self.ws_ptr, self.ws_size, B.Q8_X86, 0, self.flags, 0)
+            if group and (group[0][1].src, group[0][1].k) != (o.src, o.k) or len(group) == 4 or not self.grouping:
+                flush()
+            group.append((a, o, y))
+        flush()
         return calls
 
     def issue(self):
         """enqueue one forward pass' worth of MUL_MAT nodes on self.stream (no host sync)"""
         h = self.stream.handle
-        for fn, a, o, y in self.calls:
-            if fn(C.byref(a), h) != 0:
-                raise B.B200Error(f"{o.name}: {B.lib.b200_last_error().decode()}")
+        for fn, a, ops, ys in self.calls:
+            rc = fn(a, len(ops), h) if fn is B.lib.b200_mul_mat_group else fn(C.byref(a), h)
+            if rc != 0:
+                raise B.B200Error(f"{ops[0].name}: {B.lib.b200_last_error().decode()}")
             if self.gather is not None:
-                self.gather(y, o, self.stream)
+                for o, y in zip(ops, ys):
+                    self.gather(y, o, self.stream)
 
     def capture(self):
         before = B.launch_count()

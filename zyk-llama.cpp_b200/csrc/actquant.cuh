@@ -40,6 +40,65 @@ static inline XqPlanes xq_planes_carve(void * ws, int act_type, int64_t n, int64
 
 #ifdef __CUDACC__
 
+// Quantise the warp's 256-element chunk: lane l holds elements [8l, 8l+8) in v. Returns the lane's
+// 8 quants, the scale of the lane's block as the format stores it (f32 for Q8_K, fp16-rounded for
+// Q8_0/Q8_1) and, for Q8_1, s = d * sum(q). Warp-collective (shuffles): all 32 lanes must call it.
+template <int QT, int FLAVOUR>
+__device__ __forceinline__ void quant_chunk256(const float (&v)[8], int lane, int (&q)[8], float & dval, float & sval) {
+    sval = 0.0f;
+    if (QT == B200_TYPE_Q8_K) {
+        // first element of largest magnitude, sign kept (strict '>' in the reference loop)
+        float amax = 0.0f; int idx = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float ax = fabsf(v[j]); if (ax > amax) { amax = ax; idx = lane * 8 + j; } }
+        if (amax == 0.0f) idx = 1 << 20;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+            const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (oa > amax || (oa == amax && oi < idx)) { amax = oa; idx = oi; }
+        }
+        float mine = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if ((idx & 7) == j) mine = v[j];
+        const float maxv = __shfl_sync(0xffffffffu, mine, (idx >> 3) & 31);
+        if (amax == 0.0f) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q[j] = 0;
+            dval = 0.0f;
+        } else {
+            const float iscale = __fdiv_rn(-127.0f, maxv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const int t = __float2int_rn(__fmul_rn(iscale, v[j])); q[j] = t > 127 ? 127 : t; }
+            dval = __fdiv_rn(1.0f, iscale);
+        }
+    } else {
+        float amax = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        const float d = __fdiv_rn(amax, 127.0f);
+        float id;
+        if (FLAVOUR == B200_Q8_X86) id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        else                        id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float t = __fmul_rn(v[j], id);
+            q[j] = FLAVOUR == B200_Q8_X86 ? __float2int_rn(t) : (int) roundf(t);
+        }
+        dval = __half2float(__float2half_rn(d));
+        if (QT == B200_TYPE_Q8_1) {
+            int s = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += (int)(int8_t) q[j];
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            sval = __fmul_rn((float) s, d);
+        }
+    }
+}
+
 // One warp quantises one chunk of 256 consecutive elements of one row; lane l owns elements
 // [8l, 8l+8). CANON selects canonical ggml block bytes (y) or the plane layout (pl).
 template <int QT, int FLAVOUR, bool CANON>
@@ -71,59 +130,8 @@ __global__ void __launch_bounds__(128) act_quant_kernel(const float * __restrict
         }
 
         int q[8];
-        float dval;      // the block scale as the format stores it (f32 for Q8_K, fp16-rounded for Q8_0/1)
-        float sval = 0;  // Q8_1 only
-        if (QT == B200_TYPE_Q8_K) {
-            // first element of largest magnitude, sign kept (strict '>' in the reference loop)
-            float amax = 0.0f; int idx = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) { const float ax = fabsf(v[j]); if (ax > amax) { amax = ax; idx = lane * 8 + j; } }
-            if (amax == 0.0f) idx = 1 << 20;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-                const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
-                if (oa > amax || (oa == amax && oi < idx)) { amax = oa; idx = oi; }
-            }
-            float mine = 0.0f;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if ((idx & 7) == j) mine = v[j];
-            const float maxv = __shfl_sync(0xffffffffu, mine, (idx >> 3) & 31);
-            if (amax == 0.0f) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) q[j] = 0;
-                dval = 0.0f;
-            } else {
-                const float iscale = __fdiv_rn(-127.0f, maxv);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { const int t = __float2int_rn(__fmul_rn(iscale, v[j])); q[j] = t > 127 ? 127 : t; }
-                dval = __fdiv_rn(1.0f, iscale);
-            }
-        } else {
-            float amax = 0.0f;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            const float d = __fdiv_rn(amax, 127.0f);
-            float id;
-            if (FLAVOUR == B200_Q8_X86) id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-            else                        id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float t = __fmul_rn(v[j], id);
-                q[j] = FLAVOUR == B200_Q8_X86 ? __float2int_rn(t) : (int) roundf(t);
-            }
-            dval = __half2float(__float2half_rn(d));
-            if (QT == B200_TYPE_Q8_1) {
-                int s = 0;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) s += (int)(int8_t) q[j];
-                s += __shfl_xor_sync(0xffffffffu, s, 1);
-                s += __shfl_xor_sync(0xffffffffu, s, 2);
-                sval = __fmul_rn((float) s, d);
-            }
-        }
+        float dval, sval;
+        quant_chunk256<QT, FLAVOUR>(v, lane, q, dval, sval);
 
         int s8 = 0;
 #pragma unroll

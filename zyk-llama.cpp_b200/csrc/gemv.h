@@ -1,6 +1,7 @@
 // gemv.h -- internal interface of the decode GEMV kernels (gemv.cu, gemv_generic.cu).
 #pragma once
 #include "gemv_frag.cuh"
+#include "actquant.cuh"
 
 struct GemvArgs {
     GemvW W;                 // plane pointers of ONE [m][k] matrix (expert 0 for MUL_MAT_ID)
@@ -28,3 +29,21 @@ struct GemvGenericArgs {
     int pdl;
 };
 int b200_gemv_generic_launch(int type, const GemvGenericArgs & a, int64_t pairs, cudaStream_t s);
+
+// streaming GEMV (gemv_stream.cu): up to B200_MAX_GROUP matrices that share the same f32 X (ncols <= 4 rows),
+// activation quantiser fused. xq_out (optional, qs == nullptr to skip) receives the quantised X planes.
+#define B200_MAX_GROUP 4
+struct GemvGroup {
+    int count;
+    int type[B200_MAX_GROUP];
+    const void * w[B200_MAX_GROUP];
+    int64_t m[B200_MAX_GROUP];
+    float * y[B200_MAX_GROUP];
+    int64_t k; int ncols;
+    int64_t ldy[B200_MAX_GROUP];
+    const float * x; int64_t ldx;
+    int flavour, pdl;
+    XqPlanes xq_out;
+};
+bool b200_gemv_stream_wants(const GemvGroup & g);
+int  b200_gemv_stream_launch(const GemvGroup & g, cudaStream_t s);

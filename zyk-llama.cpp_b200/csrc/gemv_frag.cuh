@@ -75,6 +75,12 @@ __device__ __forceinline__ int dot16(const uint4 & a, const uint4 & b) {
     s = __dp4a((int) a.w, (int) b.w, s);
     return s;
 }
+// unsigned bytes of a  x  signed bytes of b, accumulated into c
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 __device__ __forceinline__ uint4 and4(const uint4 & a, uint32_t m) { return make_uint4(a.x & m, a.y & m, a.z & m, a.w & m); }
 __device__ __forceinline__ uint4 shr4(const uint4 & a, int s) { return make_uint4(a.x >> s, a.y >> s, a.z >> s, a.w >> s); }
 
@@ -90,22 +96,25 @@ template <> struct WFrag<B200_TYPE_Q4_K> {
     }
     template <int NCOLS>
     __device__ __forceinline__ void dot(const XFrag (&x)[NCOLS], float (&acc)[NCOLS], int g) const {
-        // 6-bit scale/min of sub-blocks j0 = 2G (low nibbles) and j0 + 1 (high nibbles), get_scale_min_k4
-        const int j0 = g & 6;
-        int sc0, sc1, m0, m1;
-        if (j0 < 4) {
-            sc0 = byte_of(hdr, 4 + j0) & 63;      m0 = byte_of(hdr, 8 + j0) & 63;
-            sc1 = byte_of(hdr, 5 + j0) & 63;      m1 = byte_of(hdr, 9 + j0) & 63;
-        } else {
-            const uint32_t a0 = byte_of(hdr, 8 + j0), a1 = byte_of(hdr, 9 + j0);   // scales[j+4]
-            sc0 = (a0 & 0xf) | ((byte_of(hdr, j0) >> 6) << 4);      m0 = (a0 >> 4) | ((byte_of(hdr, 4 + j0) >> 6) << 4);
-            sc1 = (a1 & 0xf) | ((byte_of(hdr, 1 + j0) >> 6) << 4);  m1 = (a1 >> 4) | ((byte_of(hdr, 5 + j0) >> 6) << 4);
-        }
+        // 6-bit scale/min pairs of sub-blocks j0 = g & 6 (low nibbles) and j0 + 1 (high nibbles): get_scale_min_k4
+        // (ggml-quants.c:703-711) for two adjacent j at once, as 2 x 8-bit fields of a 16-bit value
+        const int sh = (g & 2) << 3;                                   // j0 & 3 is 0 or 2 -> bit offset 0 or 16
+        const uint32_t y16 = (hdr.y >> sh) & 0xffffu, z16 = (hdr.z >> sh) & 0xffffu, w16 = (hdr.w >> sh) & 0xffffu;
+        const bool upper = g >= 4;                                     // j0 >= 4
+        const uint32_t sc = upper ? ((w16 & 0x0f0fu) | ((y16 >> 2) & 0x3030u)) : (y16 & 0x3f3fu);
+        const uint32_t mn = upper ? (((w16 >> 4) & 0x0f0fu) | ((z16 >> 2) & 0x3030u)) : (z16 & 0x3f3fu);
+        const int sc0 = (int) (sc & 0xffu), sc1 = (int) (sc >> 8), m0 = (int) (mn & 0xffu), m1 = (int) (mn >> 8);
         const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
-        const uint4 lo = and4(q, 0x0f0f0f0fu), hi = and4(shr4(q, 4), 0x0f0f0f0fu);
+        // high nibbles stay in place (value 16 * nibble as an unsigned byte): one AND instead of shift + AND, the
+        // factor 16 leaves the int32 sum with an exact arithmetic shift
+        const uint4 lo = and4(q, 0x0f0f0f0fu), hi = and4(q, 0xf0f0f0f0u);
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
-            const int isum = sc0 * dot16(lo, x[c].x0) + sc1 * dot16(hi, x[c].x1);
+            int dhi = dp4a_us(hi.x, x[c].x1.x, 0);
+            dhi = dp4a_us(hi.y, x[c].x1.y, dhi);
+            dhi = dp4a_us(hi.z, x[c].x1.z, dhi);
+            dhi = dp4a_us(hi.w, x[c].x1.w, dhi);
+            const int isum = sc0 * dot16(lo, x[c].x0) + sc1 * (dhi >> 4);
             const int msum = m0 * x[c].bs0 + m1 * x[c].bs1;
             acc[c] += x[c].dx * (dm.x * (float) isum - dm.y * (float) msum);
         }

@@ -1,0 +1,345 @@
+// gemv_fused.cu -- (1) decode GEMV, fused version: Y[n<=4][m] = W[m][k] . X[n][k] for one or several
+// weight matrices that share X (wq/wk/wv, ffn_gate/ffn_up), activation quantiser included, ONE launch.
+//
+// Reference counterparts: ggml_compute_forward_mul_mat + ggml_vec_dot_* (ggml-cpu/ggml-cpu.c:1227-1427,
+// ggml-cpu/quants.c) and quantize_q8_1 + mul_mat_vec_q (ggml-cuda/quantize.cu:4-73, mmvq.cu:141-335).
+//
+//   * persistent grid (SMs x CTAs-per-SM), 8 warps per CTA; the row pairs of all matrices of the group form
+//     one index space that the warps of the whole grid walk interleaved (warp w takes pairs w, w + W, ...),
+//     so neighbouring warps stream neighbouring rows and there is no tail wave per matrix;
+//   * before griddepcontrol.wait every warp prefetches its first row pairs into L2 (weights do not depend on
+//     the previous kernel); after the wait the CTA quantises X into shared memory itself -- the arithmetic
+//     is quant_chunk256 (actquant.cuh), bit for bit the reference's quantize_row_q8_K / q8_0 -- so there is
+//     no separate quantiser launch and the int8 activations are read from shared memory, not L1/L2;
+//   * per row pair and 1024-element step every lane issues its 128-bit streaming loads (L1 no-allocate) for
+//     both rows and U steps before any arithmetic, then runs the integer block arithmetic of the CPU
+//     vec_dots (gemv_frag.cuh) with the activation fragment shared by the two rows; warp-shuffle reduction.
+// Algorithmic bytes per launch = sum over the group of m * row_size(type, k); HBM bound.
+#include "gemv_frag.cuh"
+#include "actquant.cuh"
+#include "gemv.h"
+#include "sm100.cuh"
+
+#include <stdlib.h>
+
+using namespace sm100;
+
+namespace {
+
+constexpr int FWARPS = 8;
+constexpr int FTHREADS = FWARPS * 32;
+constexpr int R = 2;                     // rows per warp step (share the activation fragments)
+
+struct FusedMat {
+    GemvW W;
+    int type;
+    int64_t m;
+    float * y; int64_t ldy;
+    int64_t pair_begin;                  // first row pair of this matrix in the concatenated pair space
+};
+
+struct FusedArgs {
+    FusedMat mat[B200_MAX_GROUP];
+    int nmat;
+    int64_t total_pairs;
+    int64_t k;
+    const float * x; int64_t ldx;        // f32 activations, NCOLS rows
+    int flavour;                         // enum b200_q8_flavour for the Q8_0 family
+    int act_block;                       // 256 (Q8_K) or 32 (Q8_0)
+    int pdl;
+    int ksplit;                          // 1, 2, 4 or 8 warps share a row pair (long k, few rows)
+    XqPlanes xq_out;                     // CTA 0 also leaves the quantised X here (B200_MM_X_PREQUANTISED protocol)
+};
+
+__device__ __forceinline__ uint4 lds16(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint32_t lds4(uint32_t a) { uint32_t r; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(a)); return r; }
+__device__ __forceinline__ uint16_t lds2(uint32_t a) { uint16_t r; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(a)); return r; }
+__device__ __forceinline__ void sts8(uint32_t a, uint32_t x, uint32_t y) { asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(a), "r"(x), "r"(y) : "memory"); }
+__device__ __forceinline__ void sts4(uint32_t a, uint32_t x) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(x) : "memory"); }
+__device__ __forceinline__ void sts2(uint32_t a, uint16_t x) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "h"(x) : "memory"); }
+
+__device__ __forceinline__ int plane0_bytes(int type) {   // bytes per block in plane 0 of the plane layout (repack.cu)
+    return type == B200_TYPE_Q4_K ? 144 : (type == B200_TYPE_Q6_K || type == B200_TYPE_IQ4_XS) ? 128 : type == B200_TYPE_Q8_0 ? 32 : 16;
+}
+
+// shared-memory view of the quantised activations
+struct XS { uint32_t qs, d, bs; int k; int act_block; };
+
+template <int TYPE>
+__device__ __forceinline__ void xfrag_lds(XFrag & f, const XS & xs, int col, int blk, int g) {
+    const int e0 = blk * Fmt<TYPE>::BLK + Fmt<TYPE>::off0(g);
+    const int e1 = e0 + Fmt<TYPE>::RUN1;
+    const uint32_t qc = xs.qs + (uint32_t) (col * xs.k);
+    f.x0 = lds16(qc + e0);
+    f.x1 = lds16(qc + e1);
+    const uint32_t bc = xs.bs + (uint32_t) (col * (xs.k >> 4)) * 2;
+    f.bs0 = (int) (int16_t) lds2(bc + (e0 >> 4) * 2);
+    f.bs1 = (int) (int16_t) lds2(bc + (e1 >> 4) * 2);
+    f.dx = __uint_as_float(lds4(xs.d + (uint32_t) (col * (xs.k / xs.act_block) + (xs.act_block == 256 ? (e0 >> 8) : (e0 >> 5))) * 4));
+}
+
+// rows-in-flight per lane: U steps x R rows of 128-bit loads; the thin fragments afford U = 4 (a whole k = 4096 row)
+template <int TYPE> struct Unroll { static constexpr int U = (TYPE == B200_TYPE_Q6_K || TYPE == B200_TYPE_Q8_0) ? 2 : 4; };
+
+// one warp, one row pair of matrix M: stream the two rows, U steps of loads in flight. `mid` runs after the loads of
+// the first batch have been issued and before anything is computed (the first pair of a warp passes the
+// wait-for-previous-kernel + activation quantiser there, so that phase overlaps the HBM latency of the weights).
+template <int TYPE, int NCOLS, typename Mid>
+__device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const XS & xs, int lane, int split, int ksplit, float * partial, Mid mid) {
+    constexpr int U = Unroll<TYPE>::U;
+    constexpr int BLK = Fmt<TYPE>::BLK;
+    constexpr int BPS = 1024 / BLK;
+    const int g = lane & 7;
+    const int lane_blk = BLK == 256 ? (lane >> 3) : lane;
+    const int nb = (int) M.W.nb;
+    const int nsteps = (nb + BPS - 1) / BPS;
+    const int per = (nsteps + ksplit - 1) / ksplit;      // split-K: this warp covers steps [s_begin, s_end)
+    const int s_begin = split * per, s_end = s_begin + per < nsteps ? s_begin + per : nsteps;
+    float acc[R][NCOLS];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) acc[r][c] = 0.0f;
+    bool first = true;
+    for (int s0 = s_begin; s0 < s_end || first; s0 += U) {
+        WFrag<TYPE> f[U][R];
+        bool valid[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int blk = (s0 + u) * BPS + lane_blk;
+            valid[u] = blk < nb && s0 + u < s_end;
+            const int bl = valid[u] ? blk : 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int64_t row = row0 + r < M.m ? row0 + r : M.m - 1;
+                f[u][r].load(M.W, row, bl, g);
+            }
+        }
+        if (first) { mid(); first = false; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (!valid[u]) continue;
+            const int blk = (s0 + u) * BPS + lane_blk;
+            XFrag x[NCOLS];
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) xfrag_lds<TYPE>(x[c], xs, c, blk, g);
+#pragma unroll
+            for (int r = 0; r < R; ++r) f[u][r].template dot<NCOLS>(x, acc[r], g);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const float v = warp_sum(acc[r][c]);
+            if (lane == 0) {
+                if (partial) partial[r * NCOLS + c] = v;
+                else if (row0 + r < M.m) M.y[c * M.ldy + row0 + r] = v;
+            }
+        }
+}
+
+template <int NCOLS, typename Mid>
+__device__ __forceinline__ void row_pair_any(const FusedMat & M, int64_t row0, const XS & xs, int lane, int split, int ksplit, float * partial, Mid mid) {
+    switch (M.type) {
+        case B200_TYPE_Q4_K:   row_pair<B200_TYPE_Q4_K, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+        case B200_TYPE_Q6_K:   row_pair<B200_TYPE_Q6_K, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+        case B200_TYPE_IQ4_XS: row_pair<B200_TYPE_IQ4_XS, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+        case B200_TYPE_Q4_0:   row_pair<B200_TYPE_Q4_0, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+        default:               row_pair<B200_TYPE_Q8_0, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+    }
+}
+
+// fused activation quantiser: X f32 -> int8 planes in shared memory (whole CTA; ends with __syncthreads)
+template <int NCOLS>
+__device__ __forceinline__ void quantise_x(const FusedArgs & a, const XS & xs, int warp, int lane) {
+    const int k = xs.k;
+    const int cpr = k >> 8;                          // 256-element chunks per activation row
+    constexpr int QU = 2;                            // chunks whose loads are in flight together
+    for (int c0 = warp; c0 < NCOLS * cpr; c0 += FWARPS * QU) {
+        float v[QU][8];
+#pragma unroll
+        for (int u = 0; u < QU; ++u) {
+            const int ci = c0 + u * FWARPS;
+            if (ci < NCOLS * cpr) {
+                const int col = ci / cpr, chunk = ci % cpr;
+                const float * xr = a.x + (int64_t) col * a.ldx + chunk * 256 + lane * 8;
+                if ((((uintptr_t) xr) & 15) == 0) {
+                    const float4 lo = *reinterpret_cast<const float4 *>(xr), hi = *reinterpret_cast<const float4 *>(xr + 4);
+                    v[u][0] = lo.x; v[u][1] = lo.y; v[u][2] = lo.z; v[u][3] = lo.w; v[u][4] = hi.x; v[u][5] = hi.y; v[u][6] = hi.z; v[u][7] = hi.w;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[u][j] = xr[j];
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < QU; ++u) {
+            const int ci = c0 + u * FWARPS;
+            if (ci < NCOLS * cpr) {
+                const int col = ci / cpr, chunk = ci % cpr;
+                const int e0 = chunk * 256 + lane * 8;
+                int q[8]; float dval, sval;
+                if (a.act_block == 256)                  quant_chunk256<B200_TYPE_Q8_K, B200_Q8_X86>(v[u], lane, q, dval, sval);
+                else if (a.flavour == B200_Q8_X86)       quant_chunk256<B200_TYPE_Q8_0, B200_Q8_X86>(v[u], lane, q, dval, sval);
+                else                                     quant_chunk256<B200_TYPE_Q8_0, B200_Q8_REF>(v[u], lane, q, dval, sval);
+                int s8 = 0;
+    #pragma unroll
+                for (int j = 0; j < 8; ++j) s8 += (int) (int8_t) q[j];
+                const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
+                const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) (q[3] & 0xff) << 24);
+                const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) (q[7] & 0xff) << 24);
+                sts8(xs.qs + (uint32_t) (col * k + e0), w0, w1);
+                if ((lane & 1) == 0) sts2(xs.bs + (uint32_t) (col * (k >> 4) + (e0 >> 4)) * 2, (uint16_t) (int16_t) s16);
+                if (a.act_block == 256) { if (lane == 0) sts4(xs.d + (uint32_t) (col * cpr + chunk) * 4, __float_as_uint(dval)); }
+                else if ((lane & 3) == 0) sts4(xs.d + (uint32_t) (col * (k >> 5) + (e0 >> 5)) * 4, __float_as_uint(dval));
+                if (blockIdx.x == 0 && a.xq_out.qs) {
+                    *reinterpret_cast<uint2 *>(a.xq_out.qs + col * k + e0) = make_uint2(w0, w1);
+                    if ((lane & 1) == 0) a.xq_out.bs[col * (k >> 4) + (e0 >> 4)] = (int16_t) s16;
+                    if (a.act_block == 256) { if (lane == 0) a.xq_out.d[col * cpr + chunk] = dval; }
+                    else if ((lane & 3) == 0) a.xq_out.d[col * (k >> 5) + (e0 >> 5)] = dval;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+template <int NCOLS>
+__global__ void __launch_bounds__(FTHREADS, 2) gemv_fused_kernel(const FusedArgs a) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k = (int) a.k;
+    XS xs;
+    xs.qs = smem_u32(smem_raw);                                        // int8 [NCOLS][k]
+    xs.d = xs.qs + (uint32_t) (NCOLS * k);                             // f32  [NCOLS][k / act_block]
+    xs.bs = xs.d + (uint32_t) (NCOLS * (k / a.act_block)) * 4;         // i16  [NCOLS][k / 16]
+    xs.k = k; xs.act_block = a.act_block;
+
+    const int64_t gw = (int64_t) blockIdx.x * FWARPS + warp, GW = (int64_t) gridDim.x * FWARPS;
+    if (a.pdl) pdl_launch_dependents();
+
+    // the weight loads of the warp's first row pair are issued first (they do not depend on the previous kernel);
+    // waiting for the previous kernel and quantising X happens while they are in flight
+    auto prologue = [&]() {
+        if (a.pdl) pdl_wait();
+        quantise_x<NCOLS>(a, xs, warp, lane);
+    };
+    auto nothing = []() {};
+    int g = 0;
+    if (a.ksplit == 1) {
+        if (gw >= a.total_pairs) { prologue(); return; }
+        while (gw >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+        row_pair_any<NCOLS>(a.mat[g], (gw - a.mat[g].pair_begin) * R, xs, lane, 0, 1, nullptr, prologue);
+        for (int64_t p = gw + GW; p < a.total_pairs; p += GW) {
+            while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+            row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, 0, 1, nullptr, nothing);
+        }
+        return;
+    }
+    // split-K: KS warps of the CTA share one row pair (few rows, long k: every warp gets ONE batch of loads), partial
+    // sums meet in shared memory. All warps of the CTA run the same number of iterations (barriers inside).
+    __shared__ float part[FWARPS][R * NCOLS];
+    const int KS = a.ksplit, PG = FWARPS / KS;
+    const int pg = warp / KS, split = warp % KS;
+    const int64_t groups = (a.total_pairs + PG - 1) / PG;
+    const int64_t iters = (groups + gridDim.x - 1) / gridDim.x;
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t p = (it * gridDim.x + blockIdx.x) * PG + pg;
+        const bool live = p < a.total_pairs;
+        if (live) {
+            while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+            if (it == 0) row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, split, KS, part[warp], prologue);
+            else         row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, split, KS, part[warp], nothing);
+        } else if (it == 0) prologue();
+        __syncthreads();
+        if (live && split == 0 && lane < R * NCOLS) {
+            float v = 0.0f;
+            for (int s = 0; s < KS; ++s) v += part[warp + s][lane];
+            const FusedMat & M = a.mat[g];
+            const int64_t row = (p - M.pair_begin) * R + lane / NCOLS;
+            if (row < M.m) M.y[(lane % NCOLS) * M.ldy + row] = v;
+        }
+        __syncthreads();
+    }
+}
+
+template <int NCOLS>
+int launch_fused(const FusedArgs & a, int grid, size_t smem, cudaStream_t s) {
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        configured = true;
+    }
+    B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));
+    return 0;
+}
+
+} // namespace
+
+// Can this group take the fused kernel? All matrices: plane layout (or canonical Q4_K), packed, 16 B aligned,
+// k % 256 == 0, same activation format, quantised X fits in shared memory.
+bool b200_gemv_stream_wants(const GemvGroup & g) {
+    if (g.count < 1 || g.count > B200_MAX_GROUP || g.ncols < 1 || g.ncols > 4) return false;
+    if (g.k % 256 != 0 || g.k > 65536) return false;
+    const int act = b200_act_type(g.type[0]);
+    for (int i = 0; i < g.count; ++i) {
+        if (b200_act_type(g.type[i]) != act || g.m[i] <= 0) return false;
+        if ((((uintptr_t) g.w[i]) & 15) != 0) return false;
+    }
+    const int B = act == B200_TYPE_Q8_K ? 256 : 32;
+    const size_t xbytes = (size_t) g.ncols * (g.k + g.k / B * 4 + g.k / 16 * 2);
+    return xbytes <= 96 * 1024;
+}
+
+int b200_gemv_stream_launch(const GemvGroup & g, cudaStream_t s) {
+    FusedArgs a = {};
+    a.nmat = g.count;
+    int64_t pairs = 0;
+    for (int i = 0; i < g.count; ++i) {
+        a.mat[i].W = gemv_w_make(g.type[i], g.w[i], g.m[i], g.k);
+        a.mat[i].type = g.type[i];
+        a.mat[i].m = g.m[i];
+        a.mat[i].y = g.y[i];
+        a.mat[i].ldy = g.ldy[i];
+        a.mat[i].pair_begin = pairs;
+        pairs += (g.m[i] + R - 1) / R;
+    }
+    a.total_pairs = pairs;
+    a.k = g.k; a.x = g.x; a.ldx = g.ldx;
+    a.flavour = g.flavour;
+    a.act_block = b200_act_type(g.type[0]) == B200_TYPE_Q8_K ? 256 : 32;
+    a.pdl = g.pdl;
+    a.xq_out = g.xq_out;
+
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    const size_t smem = (size_t) g.ncols * (g.k + g.k / a.act_block * 4 + g.k / 16 * 2) + 64;
+    int per_sm = 2;
+    if (const char * e = getenv("B200_FUSED_CTAS_PER_SM")) { const int v = atoi(e); if (v > 0) per_sm = v; }
+    int64_t grid = (int64_t) sms * per_sm;
+    // few row pairs and a long k: let 2..8 warps share a pair so that every warp issues one batch of loads
+    const int64_t all_warps = grid * FWARPS;
+    const int be = b200_block_elems(g.type[0]);
+    const int64_t nsteps = (g.k / be + 1024 / be - 1) / (1024 / be);
+    int max_u = 4;
+    for (int i = 0; i < g.count; ++i) if (g.type[i] == B200_TYPE_Q6_K || g.type[i] == B200_TYPE_Q8_0) max_u = 2;
+    int ks = 1;
+    (void) all_warps; (void) nsteps; (void) max_u;   // measured on B200: sharing a pair between warps does not pay, off unless forced
+    if (const char * e = getenv("B200_FUSED_KSPLIT")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) ks = v; }
+    a.ksplit = ks;
+    const int64_t need = (pairs * ks + FWARPS - 1) / FWARPS;
+    if (grid > need) grid = need;
+    switch (g.ncols) {
+        case 1: return launch_fused<1>(a, (int) grid, smem, s);
+        case 2: return launch_fused<2>(a, (int) grid, smem, s);
+        case 3: return launch_fused<3>(a, (int) grid, smem, s);
+        case 4: return launch_fused<4>(a, (int) grid, smem, s);
+    }
+    b200_set_error("gemv_fused: ncols %d out of range", g.ncols);
+    return -2;
+}

@@ -47,9 +47,22 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
     B200_REQUIRE(a->algo != 2, "b200_mul_mat: GEMM forced but shape/layout is not eligible (type %d m=%lld n=%lld k=%lld)",
                  a->type, (long long) a->m, (long long) a->n, (long long) a->k);
 
-    // (3) + (1): quantise activations into the workspace planes, then GEMV in column groups of <= 8
     const int act = b200_act_type(a->type);
     const XqPlanes pl = xq_planes_carve(a->workspace, act, a->n, a->k);
+
+    // (1) decode, streaming kernel: one launch, activation quantiser fused (quantised X also left in the workspace)
+    if (fast && a->n <= 4 && a->algo != 1 && !(a->flags & B200_MM_X_PREQUANTISED)) {
+        GemvGroup g = {};
+        g.count = 1; g.type[0] = a->type; g.w[0] = a->w; g.m[0] = a->m; g.y[0] = a->y;
+        g.ldy[0] = a->y_row_stride;
+        g.k = a->k; g.ncols = (int) a->n; g.x = a->x; g.ldx = a->x_row_stride;
+        g.flavour = a->flavour; g.pdl = pdl; g.xq_out = pl;
+        if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, s);
+    }
+    B200_REQUIRE(a->algo != 3, "b200_mul_mat: streaming GEMV forced but the call is not eligible (type %d m=%lld n=%lld k=%lld)",
+                 a->type, (long long) a->m, (long long) a->n, (long long) a->k);
+
+    // (3) + (1): quantise activations into the workspace planes, then register GEMV in column groups of <= 8
     if (!(a->flags & B200_MM_X_PREQUANTISED)) {
         int rc = b200_act_quant_planes(act, a->flavour, a->x, a->x_row_stride, pl, a->n, a->k, s, pdl);
         if (rc) return rc;
@@ -78,6 +91,46 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
             B200_REQUIRE(a->layout == B200_LAYOUT_CANONICAL, "b200_mul_mat: plane layout with unsupported stride/alignment");
             rc = b200_gemv_generic_launch(a->type, g, 1, s);
         }
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+// several MUL_MAT nodes that read the same X (Q/K/V, gate/up): one streaming launch when eligible
+int b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t stream) {
+    B200_REQUIRE(args && count >= 1, "b200_mul_mat_group: no arguments");
+    const b200_mul_mat_args & a0 = args[0];
+    bool same = count <= B200_MAX_GROUP && a0.n <= 4 && a0.workspace != nullptr;
+    for (int i = 0; i < count && same; ++i) {
+        const b200_mul_mat_args & a = args[i];
+        same = a.w && a.x && a.y && a.x == a0.x && a.n == a0.n && a.k == a0.k && a.x_row_stride == a0.x_row_stride &&
+               a.flavour == a0.flavour && a.algo == 0 && b200_type_is_weight(a.type) &&
+               a.m > 0 && a.n > 0 && a.k % b200_block_elems(a.type) == 0 && !(a.flags & B200_MM_X_PREQUANTISED) &&
+               planes_fast_path(a.type, a.layout, a.m, a.k, a.w, a.w_row_stride);
+    }
+    if (same) {
+        GemvGroup g = {};
+        g.count = count;
+        for (int i = 0; i < count; ++i) { g.type[i] = args[i].type; g.w[i] = args[i].w; g.m[i] = args[i].m; g.y[i] = args[i].y; g.ldy[i] = args[i].y_row_stride; }
+        g.k = a0.k; g.ncols = (int) a0.n; g.x = a0.x; g.ldx = a0.x_row_stride;
+        g.flavour = a0.flavour; g.pdl = (a0.flags & B200_MM_PDL) != 0;
+        const int act = b200_act_type(a0.type);
+        if (a0.workspace_size >= xq_planes_bytes(act, a0.n, a0.k) && (((uintptr_t) a0.workspace) & 255) == 0)
+            g.xq_out = xq_planes_carve(a0.workspace, act, a0.n, a0.k);
+        if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, (cudaStream_t) stream);
+    }
+    // not groupable into one launch: one call per node. Prefill nodes that all take the GEMM share the fp16 copy of X.
+    bool share_x = a0.n > 8 && a0.workspace != nullptr;
+    for (int i = 0; i < count && share_x; ++i) {
+        const b200_mul_mat_args & a = args[i];
+        share_x = a.x == a0.x && a.n == a0.n && a.k == a0.k && a.x_row_stride == a0.x_row_stride && a.workspace == a0.workspace &&
+                  a.algo == 0 && b200_type_is_weight(a.type) && planes_fast_path(a.type, a.layout, a.m, a.k, a.w, a.w_row_stride) &&
+                  b200_gemm_wants(a.type, a.m, a.n, a.k, false);
+    }
+    for (int i = 0; i < count; ++i) {
+        b200_mul_mat_args a = args[i];
+        if (share_x && i > 0) a.flags |= B200_MM_X_PREQUANTISED;
+        int rc = b200_mul_mat(&a, stream);
         if (rc) return rc;
     }
     return 0;
