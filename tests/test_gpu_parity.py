@@ -339,3 +339,18 @@ def test_stream_gemv_full_size_baseline_shapes(b200, orc):
         y = b200.mul_mat(t, b200.repack(t, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES, algo=3).cpu().numpy()
         rows = np.concatenate([rng.choice(m, 40, replace=False), [0, m - 1]])
         assert nmse(y[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE
+
+
+@pytest.mark.parametrize("ks", [2, 3, 8])
+def test_gemm_split_k(b200, orc, monkeypatch, ks):
+    """k split over gridDim.z, partial tiles reduced into a pre-zeroed Y (what small-m prefill shapes use to fill 148 SMs)."""
+    monkeypatch.setenv("B200_GEMM_KSPLIT", str(ks))
+    rng = np.random.default_rng(ks)
+    m, k, n = 200, 2048, 70
+    for t in (Q4_K, Q6_K):
+        w = random_blocks(t, m, k, rng)
+        x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+        y = torch.full((n, m + 2), 5.0, device="cuda")
+        b200.mul_mat(t, b200.repack(t, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES, algo=2, y=y[:, :m])
+        assert nmse(y[:, :m].cpu().numpy(), orc.mul_mat_f64(t, w, x)) < GEMM_VS_TRUTH
+        assert torch.all(y[:, m:] == 5.0)

@@ -28,6 +28,7 @@
 #include "sm100.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 
 using namespace sm100;
 
@@ -49,6 +50,7 @@ struct GemmArgs {
     int bn;                     // activation rows per tile (multiple of 16, <= 256)
     int stages;
     int tmem_cols;              // power of two >= max(32, bn)
+    int ksplit;                 // gridDim.z CTAs share a tile along k; partial tiles meet in Y with red.global.add (Y pre-zeroed)
 };
 
 // ---- prologue: X f32 [n][k] (row stride ldx) -> fp16 [n][k] scaled by 2^-e per row, xscale[n] = 2^e ----
@@ -87,7 +89,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant_
     const uint32_t b_stage = (uint32_t) bn * 128u;
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;      // SWIZZLE_128B tiles need 1024 B alignment
     const uint32_t smem_a = smem0, smem_b = smem0 + (uint32_t) stages * A_STAGE;
-    const int num_kb = (int) (a.k / BK);
+    const int total_kb = (int) (a.k / BK);
+    const int kb_begin = (int) ((int64_t) total_kb * blockIdx.z / a.ksplit), kb_end = (int) ((int64_t) total_kb * (blockIdx.z + 1) / a.ksplit);
+    const int num_kb = kb_end - kb_begin;   // k-blocks of this CTA; stage/phase bookkeeping runs on the local index
     const int64_t m0 = (int64_t) blockIdx.x * BM;
     const int n0 = blockIdx.y * bn;
 
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant_
                 const int s = kb % stages; const uint32_t ph = (uint32_t) (kb / stages) & 1u;
                 mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1u);
                 mbar_arrive_expect_tx(smem_u32(&bar_full[s]), b_stage);
-                tma_load_2d(smem_b + (uint32_t) s * b_stage, &tmap_x, kb * BK, n0, smem_u32(&bar_full[s]));
+                tma_load_2d(smem_b + (uint32_t) s * b_stage, &tmap_x, (kb_begin + kb) * BK, n0, smem_u32(&bar_full[s]));
             }
         }
     } else if (warp == 1) {
@@ -140,13 +144,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant_
         const int half = t >> 7, r = t & 127;
         const int64_t row = m0 + r < a.m ? m0 + r : a.m - 1;
         Deq<TYPE> cur, nxt;
-        if (half < num_kb) nxt.load(a.W, row, half);
+        if (half < num_kb) nxt.load(a.W, row, kb_begin + half);
         for (int kb = half; kb < num_kb; kb += 2) {
             cur = nxt;
-            if (kb + 2 < num_kb) nxt.load(a.W, row, kb + 2);
+            if (kb + 2 < num_kb) nxt.load(a.W, row, kb_begin + kb + 2);
             const int s = kb % stages; const uint32_t ph = (uint32_t) (kb / stages) & 1u;
             mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1u);
-            cur.store(smem_a + (uint32_t) s * A_STAGE + (uint32_t) r * 128u, r, kb);
+            cur.store(smem_a + (uint32_t) s * A_STAGE + (uint32_t) r * 128u, r, kb_begin + kb);
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&bar_full[s]));
@@ -163,7 +167,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 const int64_t n = (int64_t) n0 + c * 16 + j;
-                if (n < a.n && mrow < a.m) a.y[n * a.ldy + mrow] = __uint_as_float(v[j]) * __ldg(a.xscale + n);
+                if (n < a.n && mrow < a.m) {
+                    const float val = __uint_as_float(v[j]) * __ldg(a.xscale + n);
+                    if (a.ksplit == 1) a.y[n * a.ldy + mrow] = val;
+                    else atomicAdd(a.y + n * a.ldy + mrow, val);      // result unused -> RED.E.ADD.F32
+                }
             }
         }
     }
@@ -251,7 +259,16 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B200_REQUIRE(cr == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed (%d) for n=%lld k=%lld bn=%d", (int) cr, (long long) n, (long long) k, bn);
 
-    dim3 grid((unsigned) ((m + BM - 1) / BM), (unsigned) n_tiles);
+    // fill the machine: when the tile grid is much smaller than the SM count, split k over gridDim.z
+    const int64_t tiles = ((m + BM - 1) / BM) * n_tiles;
+    int ks = 1;
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    while (ks < 8 && tiles * ks * 2 <= sms && (k / BK) / (ks * 2) >= 4) ks *= 2;
+    if (const char * e = getenv("B200_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1 && v <= 16 && k / BK >= v) ks = v; }
+    g.ksplit = ks;
+    if (ks > 1) B200_CHECK(cudaMemset2DAsync(a->y, (size_t) a->y_row_stride * sizeof(float), 0, (size_t) m * sizeof(float), (size_t) n, s));
+    dim3 grid((unsigned) ((m + BM - 1) / BM), (unsigned) n_tiles, (unsigned) ks);
     switch (a->type) {
         case B200_TYPE_Q4_K:   return launch_gemm<B200_TYPE_Q4_K>(tm, g, grid, smem, s, pdl);
         case B200_TYPE_Q6_K:   return launch_gemm<B200_TYPE_Q6_K>(tm, g, grid, smem, s, pdl);

@@ -35,6 +35,19 @@ __device__ __forceinline__ void emit8(uint32_t row_addr, int r, int c, uint32_t 
     st_chunk(row_addr, r, c, __hfma2(a, s, nc), __hfma2(b, s, nc), __hfma2(e, s, nc), __hfma2(f, s, nc));
 }
 
+
+// ---- raw quantised tiles staged in shared memory by TMA (gemm.cu): 128 rows x one 256-element super-block ----
+__device__ __forceinline__ uint4 raw_lds16(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint16_t raw_lds2(uint32_t a) { uint16_t r; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(a)); return r; }
+// 16-byte chunk c of row r in a TMA SWIZZLE_128B region (128-byte rows) / SWIZZLE_64B region (64-byte rows)
+__device__ __forceinline__ uint32_t sw128(uint32_t base, int r, int c) { return base + (uint32_t) (r * 128 + (((c ^ r) & 7) << 4)); }
+__device__ __forceinline__ uint32_t sw64(uint32_t base, int r, int c) { return base + (uint32_t) (r * 64 + (((c ^ (r >> 1)) & 3) << 4)); }
+
+// byte sizes of the raw stage regions per type (each region 1024-byte aligned): see RawLayout in gemm.cu
 template <int TYPE> struct Deq;
 
 // ---- Q4_K (canonical 144 B blocks) -------------------------------------------------------------------
@@ -46,6 +59,12 @@ template <> struct Deq<B200_TYPE_Q4_K> {
         q0 = ld_stream16(b + 16 + 32 * (kb & 3));
         q1 = ld_stream16(b + 32 + 32 * (kb & 3));
     }
+    // raw: [128][144] no swizzle
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+        const uint32_t b = raw + (uint32_t) (r * 144);
+        hdr = raw_lds16(b); q0 = raw_lds16(b + 16 + 32 * j); q1 = raw_lds16(b + 32 + 32 * j);
+    }
+    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const int j0 = 2 * (kb & 3);
         int sc0, sc1, m0, m1;
@@ -84,6 +103,17 @@ template <> struct Deq<B200_TYPE_Q6_K> {
         sc = ld_cached16(W.p2 + bi * 16);
         d = ld_stream2(W.p3 + bi * 2);
     }
+    // raw: ql [128][128] SW128 @0 | qh [128][64] SW64 @16384 | sc [128][16] @24576 ; d comes through aux (global load)
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t aux) {
+        const int h = j >> 1;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ql[i] = raw_lds16(sw128(raw, r, 4 * h + i));
+        qh[0] = raw_lds16(sw64(raw + 16384, r, 2 * h));
+        qh[1] = raw_lds16(sw64(raw + 16384, r, 2 * h + 1));
+        sc = raw_lds16(raw + 24576 + (uint32_t) (r * 16));
+        d = (uint16_t) aux;
+    }
+    static __device__ __forceinline__ uint32_t aux_load(const GemvW & W, int64_t row, int sb) { return ld_stream2(W.p3 + (row * W.nb + sb) * 2); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const int h = (kb >> 1) & 1, c2 = kb & 1;            // c2: 0 = low nibbles (elements 0..63 of the half), 1 = high
         const float dw = half_bits_to_float(d);
@@ -121,6 +151,15 @@ template <> struct Deq<B200_TYPE_Q8_0> {
         d[0] = ld_stream2(W.p1 + bi * 2);
         d[1] = ld_stream2(W.p1 + bi * 2 + 2);
     }
+    // raw: qs bytes 0..127 [128][128] SW128 @0 | qs bytes 128..255 [128][128] SW128 @16384 | d [128][16] @32768
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+        const uint32_t reg = raw + (uint32_t) ((j >> 1) * 16384);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) q[i] = raw_lds16(sw128(reg, r, 4 * (j & 1) + i));
+        d[0] = raw_lds2(raw + 32768 + (uint32_t) (r * 16 + (2 * j) * 2));
+        d[1] = raw_lds2(raw + 32768 + (uint32_t) (r * 16 + (2 * j + 1) * 2));
+    }
+    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int) const {
         const __half2 bias = __float2half2_rn(1024.0f + 128.0f);
         const __half2 zero = __float2half2_rn(0.0f);
@@ -144,6 +183,14 @@ template <> struct Deq<B200_TYPE_Q4_0> {
         d[0] = ld_stream2(W.p1 + bi * 2);
         d[1] = ld_stream2(W.p1 + bi * 2 + 2);
     }
+    // raw: qs [128][128] SW128 @0 (8 blocks x 16 B) | d [128][16] @16384
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+        q[0] = raw_lds16(sw128(raw, r, 2 * j));
+        q[1] = raw_lds16(sw128(raw, r, 2 * j + 1));
+        d[0] = raw_lds2(raw + 16384 + (uint32_t) (r * 16 + (2 * j) * 2));
+        d[1] = raw_lds2(raw + 16384 + (uint32_t) (r * 16 + (2 * j + 1) * 2));
+    }
+    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int) const {
         const __half2 bias = __float2half2_rn(1024.0f + 8.0f);
         const __half2 zero = __float2half2_rn(0.0f);
@@ -170,6 +217,12 @@ template <> struct Deq<B200_TYPE_IQ4_XS> {
         q[1] = ld_stream16(W.p0 + bi * 128 + 32 * (kb & 3) + 16);
         hdr = ld_stream8(W.p1 + bi * 8);
     }
+    // raw: qs [128][128] SW128 @0 ; the 8-byte header comes through two aux words (global loads)
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+        q[0] = raw_lds16(sw128(raw, r, 2 * j));
+        q[1] = raw_lds16(sw128(raw, r, 2 * j + 1));
+    }
+    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const __half2 bias = __float2half2_rn(1024.0f + 128.0f);
         const __half2 zero = __float2half2_rn(0.0f);
