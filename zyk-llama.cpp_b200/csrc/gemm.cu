@@ -38,9 +38,10 @@ constexpr int BM = 128;            // weight rows per tile = UMMA M
 constexpr int BK = 64;             // k-elements per stage = one 128-byte swizzle row of fp16
 constexpr int A_STAGE = BM * BK * 2;
 constexpr int DEQ_WARPS = 8;
-constexpr int THREADS = 128 + DEQ_WARPS * 32;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM, warp 3: spare, 4..11: producers/epilogue
+constexpr int EPI_WARPS = 4;
+constexpr int THREADS = 128 + DEQ_WARPS * 32 + EPI_WARPS * 32;   // warps 0..3: TMA X, MMA, TMEM, TMA W | 4..11: dequantisers | 12..15: epilogue
 constexpr int MAX_STAGES = 8;
-constexpr size_t SMEM_BUDGET = 200 * 1024;
+constexpr size_t SMEM_BUDGET = 224 * 1024;   // dynamic shared memory per CTA (227 KB usable minus the static barriers)
 
 struct GemmArgs {
     GemvW W;
@@ -49,8 +50,12 @@ struct GemmArgs {
     const float * xscale;       // per activation row: multiply the accumulator by this
     int bn;                     // activation rows per tile (multiple of 16, <= 256)
     int stages;
-    int tmem_cols;              // power of two >= max(32, bn)
-    int ksplit;                 // gridDim.z CTAs share a tile along k; partial tiles meet in Y with red.global.add (Y pre-zeroed)
+    int acc_cols;               // TMEM columns of one accumulator buffer: power of two >= max(32, bn); two buffers are allocated
+    int debug;                  // B200_GEMM_DEBUG bit mask (timing experiments only: results are wrong when set)
+    // work list of the persistent grid: units 0..full_tiles-1 are whole tiles (plain stores); the remaining tiles are cut
+    // `ksplit` ways along k (units full_tiles + (tile - full_tiles) * ksplit + z) and meet in pre-zeroed Y with red.global.add
+    int n_tiles;                // tiles along n; tile index = m_tile * n_tiles + n_tile (the n-tiles of one weight tile run side by side)
+    int full_tiles, ksplit, total_units;
 };
 
 // ---- prologue: X f32 [n][k] (row stride ldx) -> fp16 [n][k] scaled by 2^-e per row, xscale[n] = 2^e ----
@@ -77,107 +82,265 @@ __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict_
     if (threadIdx.x == 0) xscale[row] = ldexpf(1.0f, e);
 }
 
+// ---- raw weight staging: one stage = 128 rows x one 256-element super-block, in the plane layout ----------
+// Each region is what one cp.async.bulk.tensor box writes: [128 rows][box bytes]; 128-byte boxes use
+// SWIZZLE_128B and the 64-byte box SWIZZLE_64B so that 32 lanes reading 16 bytes of 32 consecutive rows
+// hit distinct banks (gemm_dequant.cuh sw128/sw64); 144- and 16-byte rows are conflict-free as they are.
+struct RawLoad { int map, smem_off, cstep, coff, bytes; };
+template <int TYPE> struct Raw;
+template <> struct Raw<B200_TYPE_Q4_K>   { static constexpr int BYTES = 18432, N = 1; static constexpr RawLoad L[3] = {{0, 0, 144, 0, 18432}, {}, {}}; };
+template <> struct Raw<B200_TYPE_Q6_K>   { static constexpr int BYTES = 26624, N = 3; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {1, 16384, 64, 0, 8192}, {2, 24576, 16, 0, 2048}}; };
+template <> struct Raw<B200_TYPE_IQ4_XS> { static constexpr int BYTES = 16384, N = 1; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {}, {}}; };
+template <> struct Raw<B200_TYPE_Q4_0>   { static constexpr int BYTES = 18432, N = 2; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {1, 16384, 16, 0, 2048}, {}}; };
+template <> struct Raw<B200_TYPE_Q8_0>   { static constexpr int BYTES = 34816, N = 3; static constexpr RawLoad L[3] = {{0, 0, 256, 0, 16384}, {0, 16384, 256, 128, 16384}, {1, 32768, 16, 0, 2048}}; };
+constexpr int RAW_STAGES = 2;
+#ifndef B200_GEMM_PAIR_DEFAULT
+#define B200_GEMM_PAIR_DEFAULT true
+#endif
+
 // ---- main kernel --------------------------------------------------------------------------------------
-template <int TYPE>
-__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const GemmArgs a) {
+// Persistent: one CTA per SM walks the unit list (unit = tile, or k-slice of a tail tile) with stride gridDim.x.
+// warp 0: TMA of the activation boxes | warp 1: MMA issuer | warp 2: TMEM allocator | warp 3: TMA of the raw weight
+// planes | warps 4..11: dequantise raw -> fp16 operand tiles | warps 12..15: epilogue. Two accumulator buffers in
+// TMEM: the epilogue of unit i (TMEM -> registers -> Y, 128 KB of stores) overlaps the MMAs of unit i + 1. All
+// rings (operand stages, raw stages, accumulators) keep running across units.
+struct StageCursor {     // ring position without a division per step
+    int s; uint32_t ph; int stages;
+    __device__ __forceinline__ StageCursor(int stages_, int start) : s(start % stages_), ph((uint32_t) (start / stages_) & 1u), stages(stages_) {}
+    __device__ __forceinline__ void advance(int n) { s += n; if (s >= stages) { s -= stages; ph ^= 1u; } }   // n <= stages
+};
+
+struct Unit { int64_t m0; int n0, sb_begin, num_sb; bool split; };
+template <bool PAIR>
+__device__ __forceinline__ Unit unit_decode(const GemmArgs & a, int u, uint32_t rank) {
+    int tile = u, z = 0, ks = 1;
+    if (u >= a.full_tiles) { const int v = u - a.full_tiles; tile = a.full_tiles + v / a.ksplit; z = v % a.ksplit; ks = a.ksplit; }
+    const int total_sb = (int) (a.k / 256);
+    Unit r;
+    r.m0 = (int64_t) (tile / a.n_tiles) * (PAIR ? 2 * BM : BM) + (int64_t) rank * BM;
+    r.n0 = (tile % a.n_tiles) * a.bn;
+    r.sb_begin = (int) ((int64_t) total_sb * z / ks);
+    r.num_sb = (int) ((int64_t) total_sb * (z + 1) / ks) - r.sb_begin;
+    r.split = ks > 1;
+    return r;
+}
+
+template <int TYPE, bool PAIR>
+__device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUtensorMap & tmap_w0, const CUtensorMap & tmap_w1, const CUtensorMap & tmap_w2,
+                                          const GemmArgs & a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], bar_acc;
+    __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], raw_full[RAW_STAGES], raw_empty[RAW_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_smem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // PAIR: the two CTAs of a cluster (one TPC) share one cta_group::2 tile of 256 weight rows: each dequantises its own 128
+    // rows and stages HALF of the activation box; the leader issues the MMAs for both and its commits release both CTAs.
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
+    const int unit0 = PAIR ? (int) (blockIdx.x >> 1) : (int) blockIdx.x, unit_step = PAIR ? (int) (gridDim.x >> 1) : (int) gridDim.x;
     const int stages = a.stages, bn = a.bn;
-    const uint32_t b_stage = (uint32_t) bn * 128u;
-    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;      // SWIZZLE_128B tiles need 1024 B alignment
-    const uint32_t smem_a = smem0, smem_b = smem0 + (uint32_t) stages * A_STAGE;
-    const int total_kb = (int) (a.k / BK);
-    const int kb_begin = (int) ((int64_t) total_kb * blockIdx.z / a.ksplit), kb_end = (int) ((int64_t) total_kb * (blockIdx.z + 1) / a.ksplit);
-    const int num_kb = kb_end - kb_begin;   // k-blocks of this CTA; stage/phase bookkeeping runs on the local index
-    const int64_t m0 = (int64_t) blockIdx.x * BM;
-    const int n0 = blockIdx.y * bn;
+    const int bn_cta = PAIR ? bn / 2 : bn;                             // activation rows this CTA stages
+    const uint32_t b_stage = (uint32_t) bn_cta * 128u;
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;      // swizzled tiles need 1024 B alignment
+    const uint32_t smem_w = smem0;
+    const uint32_t smem_a = smem0 + (uint32_t) (RAW_STAGES * Raw<TYPE>::BYTES), smem_b = smem_a + (uint32_t) stages * A_STAGE;
 
     if (warp == 0 && lane == 0) prefetch_tensormap(&tmap_x);
+    if (warp == 3 && lane == 0) {
+        prefetch_tensormap(&tmap_w0);
+        if (Raw<TYPE>::N > 1) prefetch_tensormap(&tmap_w1);
+        if (TYPE == B200_TYPE_Q6_K) prefetch_tensormap(&tmap_w2);
+    }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < stages; ++s) {
-            mbar_init(smem_u32(&bar_full[s]), 1 + DEQ_WARPS / 2);   // TMA expect_tx arrive + the 4 producer warps of one half
+            mbar_init(smem_u32(&bar_full[s]), 1 + (PAIR ? 2 : 1) * (DEQ_WARPS / 2));   // TMA expect_tx arrive + 4 producer warps (of each CTA)
             mbar_init(smem_u32(&bar_empty[s]), 1);                  // tcgen05.commit
         }
-        mbar_init(smem_u32(&bar_acc), 1);
+        for (int s = 0; s < RAW_STAGES; ++s) {
+            mbar_init(smem_u32(&raw_full[s]), 1);                   // expect_tx arrive
+            mbar_init(smem_u32(&raw_empty[s]), DEQ_WARPS);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(smem_u32(&acc_full[s]), 1);                   // tcgen05.commit after the last MMA of a unit
+            mbar_init(smem_u32(&acc_empty[s]), (PAIR ? 2 : 1) * EPI_WARPS);
+        }
         fence_barrier_init();
     }
-    if (warp == 2) { tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t) a.tmem_cols); tmem_relinquish(); }
+    if (warp == 2) {
+        if (PAIR) { tmem_alloc_pair(smem_u32(&tmem_base_smem), (uint32_t) (2 * a.acc_cols)); tmem_relinquish_pair(); }
+        else      { tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t) (2 * a.acc_cols)); tmem_relinquish(); }
+    }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all(); else __syncthreads();   // both CTAs' barriers exist before any remote arrive / multicast commit
     tc_fence_after();
     const uint32_t tmem_d = tmem_base_smem;
 
     if (warp == 0) {
         // ===== TMA producer: activation boxes (64 k x bn rows) =====
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % stages; const uint32_t ph = (uint32_t) (kb / stages) & 1u;
-                mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1u);
-                mbar_arrive_expect_tx(smem_u32(&bar_full[s]), b_stage);
-                tma_load_2d(smem_b + (uint32_t) s * b_stage, &tmap_x, (kb_begin + kb) * BK, n0, smem_u32(&bar_full[s]));
+            StageCursor c(stages, 0);
+            for (int u = unit0; u < a.total_units; u += unit_step) {
+                const Unit w = unit_decode<PAIR>(a, u, rank);
+                for (int kb = 0; kb < 4 * w.num_sb; ++kb, c.advance(1)) {
+                    mbar_wait(smem_u32(&bar_empty[c.s]), c.ph ^ 1u);
+                    if (a.debug & 1) { if (leader) mbar_arrive(smem_u32(&bar_full[c.s])); continue; }
+                    if (leader) mbar_arrive_expect_tx(smem_u32(&bar_full[c.s]), (PAIR ? 2u : 1u) * b_stage);
+                    if (PAIR) tma_load_2d_pair(smem_b + (uint32_t) c.s * b_stage, &tmap_x, (4 * w.sb_begin + kb) * BK, w.n0 + (int) rank * bn_cta, smem_u32(&bar_full[c.s]));
+                    else      tma_load_2d(smem_b + (uint32_t) c.s * b_stage, &tmap_x, (4 * w.sb_begin + kb) * BK, w.n0, smem_u32(&bar_full[c.s]));
+                }
             }
         }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
-        const uint32_t idesc = umma_idesc_f16(BM, bn);
-        for (int kb = 0; kb < num_kb; ++kb) {
-            const int s = kb % stages; const uint32_t ph = (uint32_t) (kb / stages) & 1u;
-            mbar_wait(smem_u32(&bar_full[s]), ph);
-            tc_fence_after();
-            if (lane == 0) {
-                const uint64_t adesc = umma_desc_kmajor_sw128(smem_a + (uint32_t) s * A_STAGE);
-                const uint64_t bdesc = umma_desc_kmajor_sw128(smem_b + (uint32_t) s * b_stage);
+    } else if (warp == 3) {
+        // ===== TMA producer: raw quantised planes, one super-block (256 k) of 128 rows per stage =====
+        if (lane == 0) {
+            StageCursor c(RAW_STAGES, 0);
+            for (int u = unit0; u < a.total_units; u += unit_step) {
+                const Unit w = unit_decode<PAIR>(a, u, rank);
+                for (int sb = 0; sb < w.num_sb; ++sb, c.advance(1)) {
+                    mbar_wait(smem_u32(&raw_empty[c.s]), c.ph ^ 1u);
+                    if (a.debug & 4) { mbar_arrive(smem_u32(&raw_full[c.s])); continue; }
+                    mbar_arrive_expect_tx(smem_u32(&raw_full[c.s]), (uint32_t) Raw<TYPE>::BYTES);
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k)     // 16 fp16 = 32 bytes = 2 descriptor units along K inside the swizzle atom
-                    mma_f16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t) ((kb | k) != 0));
-                mma_commit(smem_u32(&bar_empty[s]));
-                if (kb == num_kb - 1) mma_commit(smem_u32(&bar_acc));
+                    for (int i = 0; i < Raw<TYPE>::N; ++i) {
+                        constexpr RawLoad L0 = Raw<TYPE>::L[0], L1 = Raw<TYPE>::L[1], L2 = Raw<TYPE>::L[2];
+                        const RawLoad L = i == 0 ? L0 : i == 1 ? L1 : L2;
+                        const CUtensorMap * tm = L.map == 0 ? &tmap_w0 : L.map == 1 ? &tmap_w1 : &tmap_w2;
+                        tma_load_2d(smem_w + (uint32_t) (c.s * Raw<TYPE>::BYTES + L.smem_off), tm, (w.sb_begin + sb) * L.cstep + L.coff, (int) w.m0,
+                                    smem_u32(&raw_full[c.s]));
+                    }
+                }
             }
-            __syncwarp();
         }
-    } else if (warp >= 4) {
-        // ===== weight producers: dequantise 128 rows x 64 k per stage; two halves alternate k-blocks =====
+    } else if (warp == 1 && leader) {
+        // ===== MMA issuer (leader CTA only when paired) =====
+        const uint32_t idesc = umma_idesc_f16(PAIR ? 2 * BM : BM, bn);
+        StageCursor c(stages, 0);
+        int i = 0;
+        for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
+            const Unit w = unit_decode<PAIR>(a, u, rank);
+            const int num_kb = 4 * w.num_sb;
+            const int buf = i & 1;
+            const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols);
+            mbar_wait(smem_u32(&acc_empty[buf]), (uint32_t) ((i >> 1) & 1) ^ 1u);     // the epilogue has drained this buffer
+            tc_fence_after();
+            for (int kb = 0; kb < num_kb; ++kb, c.advance(1)) {
+                mbar_wait(smem_u32(&bar_full[c.s]), c.ph);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t adesc = umma_desc_kmajor_sw128(smem_a + (uint32_t) c.s * A_STAGE);
+                    const uint64_t bdesc = umma_desc_kmajor_sw128(smem_b + (uint32_t) c.s * b_stage);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {   // 16 fp16 = 32 bytes = 2 descriptor units along K inside the swizzle atom
+                        if (PAIR) mma_f16_ss_pair(tmem_acc, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t) ((kb | k) != 0));
+                        else      mma_f16_ss(tmem_acc, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t) ((kb | k) != 0));
+                    }
+                    if (PAIR) {
+                        mma_commit_pair(smem_u32(&bar_empty[c.s]), 3);
+                        if (kb == num_kb - 1) mma_commit_pair(smem_u32(&acc_full[buf]), 3);
+                    } else {
+                        mma_commit(smem_u32(&bar_empty[c.s]));
+                        if (kb == num_kb - 1) mma_commit(smem_u32(&acc_full[buf]));
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp >= 4 && warp < 4 + DEQ_WARPS) {
+        // ===== weight producers: thread = tile row; the two halves of the group alternate 64-element k-blocks =====
         const int t = threadIdx.x - 128;
         const int half = t >> 7, r = t & 127;
-        const int64_t row = m0 + r < a.m ? m0 + r : a.m - 1;
-        Deq<TYPE> cur, nxt;
-        if (half < num_kb) nxt.load(a.W, row, kb_begin + half);
-        for (int kb = half; kb < num_kb; kb += 2) {
-            cur = nxt;
-            if (kb + 2 < num_kb) nxt.load(a.W, row, kb_begin + kb + 2);
-            const int s = kb % stages; const uint32_t ph = (uint32_t) (kb / stages) & 1u;
-            mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1u);
-            cur.store(smem_a + (uint32_t) s * A_STAGE + (uint32_t) r * 128u, r, kb_begin + kb);
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&bar_full[s]));
-        }
-        // ===== epilogue: TMEM -> registers -> Y (thread = weight row, 16 activation rows per load) =====
-        mbar_wait(smem_u32(&bar_acc), 0);
-        tc_fence_after();
-        const int q = warp & 3;                                  // TMEM lane quarter this warp may touch
-        const int64_t mrow = m0 + 32 * q + lane;
-        for (int c = (warp - 4) >> 2; c * 16 < bn; c += 2) {
-            uint32_t v[16];
-            tmem_ld_32x32b_x16(tmem_d + ((uint32_t) (32 * q) << 16) + (uint32_t) (c * 16), v);
-            tmem_ld_wait();
+        StageCursor c(stages, half), rc(RAW_STAGES, 0);
+        for (int u = unit0; u < a.total_units; u += unit_step) {
+            const Unit w = unit_decode<PAIR>(a, u, rank);
+            const int64_t row = w.m0 + r < a.m ? w.m0 + r : a.m - 1;
+            uint2 aux_next = Deq<TYPE>::aux_load(a.W, row, w.sb_begin);
+            for (int sb = 0; sb < w.num_sb; ++sb, rc.advance(1)) {
+                const uint2 aux = aux_next;
+                if (sb + 1 < w.num_sb) aux_next = Deq<TYPE>::aux_load(a.W, row, w.sb_begin + sb + 1);
+                const uint32_t raw = smem_w + (uint32_t) (rc.s * Raw<TYPE>::BYTES);
+                mbar_wait(smem_u32(&raw_full[rc.s]), rc.ph);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const int64_t n = (int64_t) n0 + c * 16 + j;
-                if (n < a.n && mrow < a.m) {
-                    const float val = __uint_as_float(v[j]) * __ldg(a.xscale + n);
-                    if (a.ksplit == 1) a.y[n * a.ldy + mrow] = val;
-                    else atomicAdd(a.y + n * a.ldy + mrow, val);      // result unused -> RED.E.ADD.F32
+                for (int jj = 0; jj < 2; ++jj, c.advance(2)) {
+                    const int j = 2 * jj + half;
+                    Deq<TYPE> cur;
+                    cur.load_smem(raw, r, j, aux);
+                    mbar_wait(smem_u32(&bar_empty[c.s]), c.ph ^ 1u);
+                    if (!(a.debug & 2)) cur.store(smem_a + (uint32_t) c.s * A_STAGE + (uint32_t) r * 128u, r, j);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (PAIR && !leader) mbar_arrive_cluster(smem_u32(&bar_full[c.s]), 0);
+                        else mbar_arrive(smem_u32(&bar_full[c.s]));
+                    }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&raw_empty[rc.s]));
+            }
+        }
+    } else if (warp >= 4 + DEQ_WARPS) {
+        // ===== epilogue: TMEM -> registers -> Y (thread = weight row, 16 activation rows per load) =====
+        const int q = warp & 3;                                  // TMEM lane quarter this warp may touch
+        int i = 0;
+        for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
+            const Unit w = unit_decode<PAIR>(a, u, rank);
+            const int buf = i & 1;
+            const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols) + ((uint32_t) (32 * q) << 16);
+            const int64_t mrow = w.m0 + 32 * q + lane;
+            mbar_wait(smem_u32(&acc_full[buf]), (uint32_t) ((i >> 1) & 1));
+            tc_fence_after();
+            const bool row_ok = mrow < a.m && !(a.debug & 16);
+            float * yp = a.y + (int64_t) w.n0 * a.ldy + (row_ok ? mrow : 0);
+            const int n_left = (int) (a.n - w.n0 < bn ? a.n - w.n0 : bn);             // activation rows of this tile that exist (>= 1)
+            // lane l carries the scale of activation row 32 * cc + l of the tile, fetched one iteration ahead
+            float xs_next = __ldg(a.xscale + w.n0 + (lane < n_left ? lane : n_left - 1));
+            for (int cc = 0; cc * 32 < bn; ++cc, yp += 32 * a.ldy) {                  // columns past bn (inside acc_cols) are read and dropped
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tmem_acc + (uint32_t) (cc * 32), v);
+                const float xs_lane = xs_next;
+                const int nn = cc * 32 + 32 + lane;
+                xs_next = __ldg(a.xscale + w.n0 + (nn < n_left ? nn : n_left - 1));
+                tmem_ld_wait();
+                if (!w.split) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
+                        if (row_ok && cc * 32 + j < n_left) yp[(int64_t) j * a.ldy] = val;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
+                        if (row_ok && cc * 32 + j < n_left) atomicAdd(yp + (int64_t) j * a.ldy, val);      // result unused -> RED.E.ADD.F32
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (PAIR && !leader) mbar_arrive_cluster(smem_u32(&acc_empty[buf]), 0);
+                else mbar_arrive(smem_u32(&acc_empty[buf]));
             }
         }
     }
     tc_fence_before();
-    __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_d, (uint32_t) a.tmem_cols);
+    if (PAIR) cluster_sync_all(); else __syncthreads();   // nobody leaves while the peer may still touch its shared memory / TMEM
+    if (warp == 2) {
+        if (PAIR) tmem_dealloc_pair(tmem_d, (uint32_t) (2 * a.acc_cols)); else tmem_dealloc(tmem_d, (uint32_t) (2 * a.acc_cols));
+    }
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w0,
+                                                          const __grid_constant__ CUtensorMap tmap_w1, const __grid_constant__ CUtensorMap tmap_w2,
+                                                          const GemmArgs a) {
+    gemm_body<TYPE, false>(tmap_x, tmap_w0, tmap_w1, tmap_w2, a);
+}
+
+template <int TYPE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w0, const __grid_constant__ CUtensorMap tmap_w1,
+                 const __grid_constant__ CUtensorMap tmap_w2, const GemmArgs a) {
+    gemm_body<TYPE, true>(tmap_x, tmap_w0, tmap_w1, tmap_w2, a);
 }
 
 // ---- host side ------------------------------------------------------------------------------------------
@@ -197,15 +360,68 @@ encode_tiled_fn get_encode_tiled() {
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
+struct WMaps { CUtensorMap m[3]; };
+
+// [rows][inner_bytes] uint8 plane, boxes of box_inner bytes x 128 rows; rows past `rows` are zero-filled by the TMA unit
+bool make_plane_map(CUtensorMap * tm, const void * base, uint64_t inner_bytes, uint64_t rows, uint32_t box_inner, CUtensorMapSwizzle sw) {
+    const cuuint64_t dims[2] = {inner_bytes, rows};
+    const cuuint64_t strides[1] = {inner_bytes};
+    const cuuint32_t box[2] = {box_inner, (cuuint32_t) BM};
+    const cuuint32_t estr[2] = {1, 1};
+    return get_encode_tiled()(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+bool make_weight_maps(int type, const GemvW & W, int64_t m, WMaps & w) {
+    const uint64_t nb = (uint64_t) W.nb, rows = (uint64_t) m;
+    bool ok = true;
+    switch (type) {
+        case B200_TYPE_Q4_K:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 144, rows, 144, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q6_K:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 128, rows, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map(&w.m[1], W.p1, nb * 64, rows, 64, CU_TENSOR_MAP_SWIZZLE_64B) &&
+                 make_plane_map(&w.m[2], W.p2, nb * 16, rows, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            break;
+        case B200_TYPE_IQ4_XS:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 128, rows, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q4_0:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 16, rows, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map(&w.m[1], W.p1, nb * 2, rows, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q8_0:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 32, rows, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map(&w.m[1], W.p1, nb * 2, rows, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[2] = w.m[0]; break;
+        default: ok = false;
+    }
+    return ok;
+}
+
+template <int TYPE> constexpr int raw_ring_bytes() { return RAW_STAGES * Raw<TYPE>::BYTES; }
+int raw_ring_bytes_of(int type) {
+    switch (type) {
+        case B200_TYPE_Q4_K:   return raw_ring_bytes<B200_TYPE_Q4_K>();
+        case B200_TYPE_Q6_K:   return raw_ring_bytes<B200_TYPE_Q6_K>();
+        case B200_TYPE_Q8_0:   return raw_ring_bytes<B200_TYPE_Q8_0>();
+        case B200_TYPE_Q4_0:   return raw_ring_bytes<B200_TYPE_Q4_0>();
+        case B200_TYPE_IQ4_XS: return raw_ring_bytes<B200_TYPE_IQ4_XS>();
+    }
+    return 0;
+}
+
 template <int TYPE>
-int launch_gemm(const CUtensorMap & tm, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pdl) {
+int launch_gemm(const CUtensorMap & tm, const WMaps & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
     static bool configured = false;
     if (!configured) {
         B200_CHECK(cudaFuncSetAttribute(gemm_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
+        B200_CHECK(cudaFuncSetAttribute(gemm_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         configured = true;
     }
-    (void) pdl;
-    B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, g));
+    if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w.m[0], w.m[1], w.m[2], g));
+    else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w.m[0], w.m[1], w.m[2], g));
     return 0;
 }
 
@@ -237,44 +453,66 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
     // N tiling: equal tiles of at most 256 rows, multiple of 16
     const int n_tiles = (int) ((n + 255) / 256);
     int bn = (int) ((n + n_tiles - 1) / n_tiles);
-    bn = (bn + 15) & ~15;
+    // CTA pairs (cta_group::2, 256 weight rows per tile) when there is more than one 128-row tile; B200_GEMM_PAIR=0/1 overrides
+    static const int pair_env = [] { const char * e = getenv("B200_GEMM_PAIR"); return e ? atoi(e) : -1; }();
+    const bool pair = (pair_env < 0 ? B200_GEMM_PAIR_DEFAULT : pair_env != 0) && m > BM;
+    bn = pair ? (bn + 31) & ~31 : (bn + 15) & ~15;     // each CTA of a pair stages bn / 2 rows, a multiple of 16
+    const int bn_cta = pair ? bn / 2 : bn;
     GemmArgs g = {};
     g.W = gemv_w_make(a->type, a->w, m, k);
     g.m = m; g.n = n; g.k = k;
     g.y = a->y; g.ldy = a->y_row_stride;
     g.xscale = xscale;
     g.bn = bn;
-    g.tmem_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
-    const size_t per_stage = (size_t) A_STAGE + (size_t) bn * 128;
-    int stages = (int) ((SMEM_BUDGET - 1024) / per_stage);
+    g.n_tiles = n_tiles;
+    g.acc_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
+    const size_t per_stage = (size_t) A_STAGE + (size_t) bn_cta * 128;
+    const size_t raw_ring = (size_t) raw_ring_bytes_of(a->type);
+    int stages = (int) ((SMEM_BUDGET - raw_ring) / per_stage);
     g.stages = stages > MAX_STAGES ? MAX_STAGES : stages;
-    const size_t smem = (size_t) g.stages * per_stage + 1024;
+    const size_t smem = raw_ring + (size_t) g.stages * per_stage + 1024;
+    WMaps wm;
+    B200_REQUIRE(make_weight_maps(a->type, g.W, m, wm), "gemm: cuTensorMapEncodeTiled failed for the weight planes (type %d m=%lld k=%lld)", a->type,
+                 (long long) m, (long long) k);
 
     CUtensorMap tm;
     const cuuint64_t dims[2] = {(cuuint64_t) k, (cuuint64_t) n};
     const cuuint64_t strides[1] = {(cuuint64_t) k * sizeof(__half)};
-    const cuuint32_t box[2] = {(cuuint32_t) BK, (cuuint32_t) bn};
+    const cuuint32_t box[2] = {(cuuint32_t) BK, (cuuint32_t) bn_cta};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult cr = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, xh, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B200_REQUIRE(cr == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed (%d) for n=%lld k=%lld bn=%d", (int) cr, (long long) n, (long long) k, bn);
 
-    // fill the machine: when the tile grid is much smaller than the SM count, split k over gridDim.z
-    const int64_t tiles = ((m + BM - 1) / BM) * n_tiles;
-    int ks = 1;
+    // work list: whole waves of full tiles, then the remaining tiles cut along k so that the last wave also fills the SMs
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
-    while (ks < 8 && tiles * ks * 2 <= sms && (k / BK) / (ks * 2) >= 4) ks *= 2;
-    if (const char * e = getenv("B200_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1 && v <= 16 && k / BK >= v) ks = v; }
-    g.ksplit = ks;
-    if (ks > 1) B200_CHECK(cudaMemset2DAsync(a->y, (size_t) a->y_row_stride * sizeof(float), 0, (size_t) m * sizeof(float), (size_t) n, s));
-    dim3 grid((unsigned) ((m + BM - 1) / BM), (unsigned) n_tiles, (unsigned) ks);
+    const int tile_m = pair ? 2 * BM : BM;
+    const int workers = pair ? sms / 2 : sms;             // CTAs, or CTA pairs
+    const int64_t m_tiles = (m + tile_m - 1) / tile_m;
+    const int64_t tiles = m_tiles * n_tiles;
+    B200_REQUIRE(tiles < ((int64_t) 1 << 26), "gemm: too many tiles (%lld)", (long long) tiles);
+    const int total_sb = (int) (k / 256);
+    int64_t full = tiles / workers * workers;
+    int64_t rest = tiles - full;
+    int ks = 1;
+    while (ks < 16 && rest * ks * 2 <= workers && total_sb / (ks * 2) >= 2) ks *= 2;
+    if (const char * e = getenv("B200_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1 && v <= 16 && total_sb >= v) { ks = v; full = 0; rest = tiles; } }
+    if (ks == 1) { full = tiles; rest = 0; }
+    g.full_tiles = (int) full; g.ksplit = ks; g.total_units = (int) (full + rest * ks);
+    if (const char * e = getenv("B200_GEMM_DEBUG")) g.debug = atoi(e);
+    if (rest > 0) {     // zero the weight rows the split tiles accumulate into (full tiles of the same rows overwrite later, in stream order)
+        const int64_t m_lo = full / n_tiles * tile_m;
+        B200_CHECK(cudaMemset2DAsync(a->y + m_lo, (size_t) a->y_row_stride * sizeof(float), 0, (size_t) (m - m_lo) * sizeof(float), (size_t) n, s));
+    }
+    const unsigned nw = (unsigned) (g.total_units < workers ? g.total_units : workers);
+    dim3 grid(pair ? 2 * nw : nw);
     switch (a->type) {
-        case B200_TYPE_Q4_K:   return launch_gemm<B200_TYPE_Q4_K>(tm, g, grid, smem, s, pdl);
-        case B200_TYPE_Q6_K:   return launch_gemm<B200_TYPE_Q6_K>(tm, g, grid, smem, s, pdl);
-        case B200_TYPE_Q8_0:   return launch_gemm<B200_TYPE_Q8_0>(tm, g, grid, smem, s, pdl);
-        case B200_TYPE_Q4_0:   return launch_gemm<B200_TYPE_Q4_0>(tm, g, grid, smem, s, pdl);
-        case B200_TYPE_IQ4_XS: return launch_gemm<B200_TYPE_IQ4_XS>(tm, g, grid, smem, s, pdl);
+        case B200_TYPE_Q4_K:   return launch_gemm<B200_TYPE_Q4_K>(tm, wm, g, grid, smem, s, pair);
+        case B200_TYPE_Q6_K:   return launch_gemm<B200_TYPE_Q6_K>(tm, wm, g, grid, smem, s, pair);
+        case B200_TYPE_Q8_0:   return launch_gemm<B200_TYPE_Q8_0>(tm, wm, g, grid, smem, s, pair);
+        case B200_TYPE_Q4_0:   return launch_gemm<B200_TYPE_Q4_0>(tm, wm, g, grid, smem, s, pair);
+        case B200_TYPE_IQ4_XS: return launch_gemm<B200_TYPE_IQ4_XS>(tm, wm, g, grid, smem, s, pair);
     }
     b200_set_error("gemm: unsupported weight type %d", a->type);
     return -2;

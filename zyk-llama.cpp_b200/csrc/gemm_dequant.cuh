@@ -60,11 +60,11 @@ template <> struct Deq<B200_TYPE_Q4_K> {
         q1 = ld_stream16(b + 32 + 32 * (kb & 3));
     }
     // raw: [128][144] no swizzle
-    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2) {
         const uint32_t b = raw + (uint32_t) (r * 144);
         hdr = raw_lds16(b); q0 = raw_lds16(b + 16 + 32 * j); q1 = raw_lds16(b + 32 + 32 * j);
     }
-    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW &, int64_t, int) { return make_uint2(0u, 0u); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const int j0 = 2 * (kb & 3);
         int sc0, sc1, m0, m1;
@@ -104,16 +104,16 @@ template <> struct Deq<B200_TYPE_Q6_K> {
         d = ld_stream2(W.p3 + bi * 2);
     }
     // raw: ql [128][128] SW128 @0 | qh [128][64] SW64 @16384 | sc [128][16] @24576 ; d comes through aux (global load)
-    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t aux) {
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2 aux) {
         const int h = j >> 1;
 #pragma unroll
         for (int i = 0; i < 4; ++i) ql[i] = raw_lds16(sw128(raw, r, 4 * h + i));
         qh[0] = raw_lds16(sw64(raw + 16384, r, 2 * h));
         qh[1] = raw_lds16(sw64(raw + 16384, r, 2 * h + 1));
         sc = raw_lds16(raw + 24576 + (uint32_t) (r * 16));
-        d = (uint16_t) aux;
+        d = (uint16_t) aux.x;
     }
-    static __device__ __forceinline__ uint32_t aux_load(const GemvW & W, int64_t row, int sb) { return ld_stream2(W.p3 + (row * W.nb + sb) * 2); }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW & W, int64_t row, int sb) { return make_uint2(ld_stream2(W.p3 + (row * W.nb + sb) * 2), 0u); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const int h = (kb >> 1) & 1, c2 = kb & 1;            // c2: 0 = low nibbles (elements 0..63 of the half), 1 = high
         const float dw = half_bits_to_float(d);
@@ -152,14 +152,14 @@ template <> struct Deq<B200_TYPE_Q8_0> {
         d[1] = ld_stream2(W.p1 + bi * 2 + 2);
     }
     // raw: qs bytes 0..127 [128][128] SW128 @0 | qs bytes 128..255 [128][128] SW128 @16384 | d [128][16] @32768
-    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2) {
         const uint32_t reg = raw + (uint32_t) ((j >> 1) * 16384);
 #pragma unroll
         for (int i = 0; i < 4; ++i) q[i] = raw_lds16(sw128(reg, r, 4 * (j & 1) + i));
         d[0] = raw_lds2(raw + 32768 + (uint32_t) (r * 16 + (2 * j) * 2));
         d[1] = raw_lds2(raw + 32768 + (uint32_t) (r * 16 + (2 * j + 1) * 2));
     }
-    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW &, int64_t, int) { return make_uint2(0u, 0u); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int) const {
         const __half2 bias = __float2half2_rn(1024.0f + 128.0f);
         const __half2 zero = __float2half2_rn(0.0f);
@@ -184,13 +184,13 @@ template <> struct Deq<B200_TYPE_Q4_0> {
         d[1] = ld_stream2(W.p1 + bi * 2 + 2);
     }
     // raw: qs [128][128] SW128 @0 (8 blocks x 16 B) | d [128][16] @16384
-    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2) {
         q[0] = raw_lds16(sw128(raw, r, 2 * j));
         q[1] = raw_lds16(sw128(raw, r, 2 * j + 1));
         d[0] = raw_lds2(raw + 16384 + (uint32_t) (r * 16 + (2 * j) * 2));
         d[1] = raw_lds2(raw + 16384 + (uint32_t) (r * 16 + (2 * j + 1) * 2));
     }
-    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW &, int64_t, int) { return make_uint2(0u, 0u); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int) const {
         const __half2 bias = __float2half2_rn(1024.0f + 8.0f);
         const __half2 zero = __float2half2_rn(0.0f);
@@ -218,11 +218,12 @@ template <> struct Deq<B200_TYPE_IQ4_XS> {
         hdr = ld_stream8(W.p1 + bi * 8);
     }
     // raw: qs [128][128] SW128 @0 ; the 8-byte header comes through two aux words (global loads)
-    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint32_t) {
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2 aux) {
         q[0] = raw_lds16(sw128(raw, r, 2 * j));
         q[1] = raw_lds16(sw128(raw, r, 2 * j + 1));
+        hdr = aux;
     }
-    static __device__ __forceinline__ uint32_t aux_load(const GemvW &, int64_t, int) { return 0; }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW & W, int64_t row, int sb) { return ld_stream8(W.p1 + (row * W.nb + sb) * 8); }
     __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
         const __half2 bias = __float2half2_rn(1024.0f + 128.0f);
         const __half2 zero = __float2half2_rn(0.0f);
