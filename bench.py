@@ -76,44 +76,62 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # the reference's CPU path (oracle/_ref): cpu_baseline leg and --impl reference
 # ------------------------------------------------------------------------------------------------
+class CpuChain:
+    """The reference CPU backend's MUL_MAT (N = 1) on one matrix of every distinct (type, m, k) of the model,
+    extrapolated to a full token: t_token = sum_nodes t(type, m, k). Weights are generated and the per-shape
+    iteration counts calibrated once; every step() re-times all shapes within `budget_s` of compute."""
+
+    def __init__(self, model: str, threads: int):
+        import numpy as np
+        from oracle.oracle import Ref, Oracle, random_blocks, ref_variant   # checker / baseline only
+        self.w = _load_pkg_module("workloads")
+        self.ops = self.w.model_ops(model)
+        self.threads = threads
+        shapes: dict[tuple, int] = {}
+        for o in self.ops:
+            shapes[(o.type, o.m, o.k)] = shapes.get((o.type, o.m, o.k), 0) + (o.n_used if o.n_expert else 1)
+        rng = np.random.default_rng(1)
+        self.kind = "reference" if ref_variant() else "port"
+        self.ref = Ref() if self.kind == "reference" else None
+        self.orc = Oracle()
+        self.items = []
+        self.paths = set()
+        for (t, m, k), cnt in sorted(shapes.items(), key=lambda kv: -kv[0][1] * kv[0][2]):
+            mm = min(m, 16384)                       # bounded sample: at most 16384 rows of the matrix, scaled
+            w = random_blocks(t, mm, k, rng)
+            x = rng.standard_normal((1, k)).astype(np.float32)
+            path, s1 = "oracle-port", None
+            if self.ref is not None:
+                path = "repack"
+                try:
+                    _, s1 = self.ref.mul_mat(t, w, x, n_threads=threads, repack=True, iters=5)
+                except RuntimeError:
+                    path = "generic"
+                    _, s1 = self.ref.mul_mat(t, w, x, n_threads=threads, repack=False, iters=5)
+            self.paths.add(path)
+            self.items.append({"t": t, "m": m, "mm": mm, "k": k, "cnt": cnt, "w": w, "x": x, "path": path, "s1": s1})
+
+    def step(self, budget_s: float) -> float:
+        per_shape = budget_s / len(self.items)
+        total = 0.0
+        for it in self.items:
+            if self.ref is not None:
+                iters = max(3, min(200, int(per_shape / max(it["s1"], 1e-6))))
+                _, secs = self.ref.mul_mat(it["t"], it["w"], it["x"], n_threads=self.threads, repack=(it["path"] == "repack"), iters=iters)
+                it["s1"] = secs
+            else:
+                t0 = time.perf_counter(); self.orc.mul_mat(it["t"], it["w"], it["x"]); secs = time.perf_counter() - t0
+            total += secs * it["m"] / it["mm"] * it["cnt"]
+        return 1.0 / total
+
+    def sample(self) -> str:
+        return (f"one N=1 MUL_MAT per distinct (type,m,k) [{len(self.items)} shapes, <=16384 rows each, scaled], summed over the "
+                f"{len(self.ops)} nodes of a token; paths={sorted(self.paths)}; {self.threads} threads")
+
+
 def cpu_tokens_per_s(model: str, budget_s: float, threads: int):
-    """Time the reference CPU backend's MUL_MAT (N = 1) on one matrix of every distinct (type, m, k)
-    of the model and extrapolate to a full token: t_token = sum_nodes t(type, m, k)."""
-    import numpy as np
-    from oracle.oracle import Ref, Oracle, random_blocks, ref_variant   # checker / baseline only
-    b200w = _load_pkg_module("workloads")
-    ops = b200w.model_ops(model)
-    shapes: dict[tuple, int] = {}
-    for o in ops:
-        shapes[(o.type, o.m, o.k)] = shapes.get((o.type, o.m, o.k), 0) + (o.n_used if o.n_expert else 1)
-    rng = np.random.default_rng(1)
-    kind = "reference" if ref_variant() else "port"
-    ref = Ref() if kind == "reference" else None
-    orc = Oracle()
-    per_shape = budget_s / len(shapes)
-    total, detail, paths = 0.0, [], set()
-    for (t, m, k), cnt in sorted(shapes.items(), key=lambda kv: -kv[0][1] * kv[0][2]):
-        mm = min(m, 16384)                       # bounded sample: at most 16384 rows of the matrix, scaled
-        w = random_blocks(t, mm, k, rng)
-        x = rng.standard_normal((1, k)).astype(np.float32)
-        if ref is not None:
-            path = "repack"
-            try:
-                _, s1 = ref.mul_mat(t, w, x, n_threads=threads, repack=True, iters=1)
-            except RuntimeError:
-                path = "generic"
-                _, s1 = ref.mul_mat(t, w, x, n_threads=threads, repack=False, iters=1)
-            iters = max(2, min(200, int(per_shape / max(s1, 1e-6))))
-            _, secs = ref.mul_mat(t, w, x, n_threads=threads, repack=(path == "repack"), iters=iters)
-            paths.add(path)
-        else:
-            t0 = time.perf_counter(); orc.mul_mat(t, w, x); secs = time.perf_counter() - t0
-            paths.add("oracle-port")
-        secs *= m / mm
-        total += secs * cnt
-        detail.append(f"{b200w.BLOCK[t][1]}B-blk m={m} k={k}: {secs * 1e6:.0f}us x{cnt}")
-    return 1.0 / total, kind, f"one N=1 MUL_MAT per distinct (type,m,k) [{len(shapes)} shapes, <=16384 rows each, scaled], " \
-                              f"summed over the {len(ops)} nodes of a token; paths={sorted(paths)}; {threads} threads"
+    c = CpuChain(model, threads)
+    return c.step(budget_s), c.kind, c.sample()
 
 
 def _load_pkg_module(name):
@@ -137,15 +155,18 @@ def run_reference(args):
     if rank != 0:
         return 0
     threads = os.cpu_count() or 1
-    vals = []
+    chain = CpuChain(args.model, threads)
+    # a step = one bounded sample of the token's MUL_MATs; the whole run is sized to about two minutes of CPU work
+    budget = min(8.0, max(0.25, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
-        cpu_tokens_per_s(args.model, 2.0, threads)
+        chain.step(budget)
+    vals = []
     t0 = time.time()
     for _ in range(args.steps):
-        v, kind, sample = cpu_tokens_per_s(args.model, max(4.0, 60.0 / max(1, args.steps)), threads)
-        vals.append(v)
+        vals.append(chain.step(budget))
     dt = time.time() - t0
-    v = sum(vals) / len(vals)
+    v = len(vals) / sum(1.0 / x for x in vals)       # steps / total extrapolated seconds
+    kind, sample = chain.kind, chain.sample() + f"; {budget:.2f} s of compute per step"
     line = {"impl": "reference", "metric": "tg tokens/s (quantised MUL_MAT chain, N=1)", "value": v, "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int8 -> int32, f32 scales", "data": "synthetic",
@@ -282,7 +303,10 @@ def main():
             ms_pp /= args.pp_steps
             pp_ops = W.pp_ops(ops) * args.pp
             pp = {"value": args.pp / (ms_pp * 1e-3), "unit": "tokens/s", "n": args.pp, "ms_per_ubatch": ms_pp,
-                  "int8_tops": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "steps": args.pp_steps}
+                  "int8_tops": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "steps": args.pp_steps,
+                  # fp16 tcgen05 path: the same op count against the measured cuBLAS bf16 throughput (sustained: this is a long step)
+                  "tensor_roofline": {"bound": "tensor", "achieved": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "peak": peaks.get("bf16_tflops_sustained"),
+                                      "unit": "TFLOP/s", "frac": pp_ops / (ms_pp * 1e-3) / 1e12 / world / peaks.get("bf16_tflops_sustained", 1400.0)}}
             del chain_pp
         except Exception as e:  # noqa: BLE001
             pp = {"error": str(e)[:200]}
@@ -304,7 +328,8 @@ def main():
     tf = ROOT / "profiles" / "traffic.json"
     if tf.exists():
         try:
-            traffic = json.load(open(tf)).get("gemv_dram_bytes_per_token")
+            tj = json.load(open(tf))     # ncu dram__bytes_read.sum + dram__bytes_write.sum over the launches of one token
+            traffic = (tj["dram_bytes_read_per_token"] + tj["dram_bytes_write_per_token"]) / max(1, world)
         except Exception:  # noqa: BLE001
             pass
     line = {
@@ -319,7 +344,9 @@ def main():
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "traffic": traffic, "peak_source": peak_src, "frac_of_8tbs": achieved / 8000.0,
-                     "kernel": "gemv_kernel<type,1,R,U> (all decode nodes of the step; activation quantiser included in the time)"},
+                     "algorithmic_bytes": bytes_tok / world,
+                     "kernel": "gemv_fused_kernel<1> (+ act_quant_kernel / gemv_kernel for the k = 14336 nodes): all launches of one decode step, "
+                               "bytes and time per step (= per token); traffic from profiles/traffic.json"},
         "pp512": pp, "cpu_baseline": cpu, "clocks": clocks,
     }
     print(json.dumps(line))

@@ -13,7 +13,9 @@
 #include "ggml-backend.h"
 #include "ggml-alloc.h"
 
+#include <algorithm>
 #include <chrono>
+#include <vector>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -114,10 +116,16 @@ int ref_mul_mat(int type, int64_t m, int64_t n, int64_t k, const void * w, const
         ggml_build_forward_expand(gf, Y);
         if (ggml_backend_graph_compute(cpu, gf) != GGML_STATUS_SUCCESS) rc = -3;
         if (rc == 0 && iters > 0) {
-            auto t0 = std::chrono::steady_clock::now();
-            for (int i = 0; i < iters; ++i) ggml_backend_graph_compute(cpu, gf);
-            auto t1 = std::chrono::steady_clock::now();
-            if (secs) *secs = std::chrono::duration<double>(t1 - t0).count() / iters;
+            // median of the per-iteration times: one descheduled worker thread stalls ggml's spin barrier for tens of
+            // milliseconds on a shared host, which a mean would charge to the reference
+            std::vector<double> dt((size_t) iters);
+            for (int i = 0; i < iters; ++i) {
+                auto t0 = std::chrono::steady_clock::now();
+                ggml_backend_graph_compute(cpu, gf);
+                dt[(size_t) i] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            }
+            std::sort(dt.begin(), dt.end());
+            if (secs) *secs = dt[dt.size() / 2];
         }
         if (rc == 0) ggml_backend_tensor_get(Y, y, 0, ggml_nbytes(Y));
     }

@@ -47,7 +47,6 @@ struct FusedArgs {
     int flavour;                         // enum b200_q8_flavour for the Q8_0 family
     int act_block;                       // 256 (Q8_K) or 32 (Q8_0)
     int pdl;
-    int ksplit;                          // 1, 2, 4 or 8 warps share a row pair (long k, few rows)
     XqPlanes xq_out;                     // CTA 0 also leaves the quantised X here (B200_MM_X_PREQUANTISED protocol)
 };
 
@@ -89,7 +88,7 @@ template <int TYPE> struct Unroll { static constexpr int U = (TYPE == B200_TYPE_
 // the first batch have been issued and before anything is computed (the first pair of a warp passes the
 // wait-for-previous-kernel + activation quantiser there, so that phase overlaps the HBM latency of the weights).
 template <int TYPE, int NCOLS, typename Mid>
-__device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const XS & xs, int lane, int split, int ksplit, float * partial, Mid mid) {
+__device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const XS & xs, int lane, Mid mid) {
     constexpr int U = Unroll<TYPE>::U;
     constexpr int BLK = Fmt<TYPE>::BLK;
     constexpr int BPS = 1024 / BLK;
@@ -97,8 +96,7 @@ __device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const
     const int lane_blk = BLK == 256 ? (lane >> 3) : lane;
     const int nb = (int) M.W.nb;
     const int nsteps = (nb + BPS - 1) / BPS;
-    const int per = (nsteps + ksplit - 1) / ksplit;      // split-K: this warp covers steps [s_begin, s_end)
-    const int s_begin = split * per, s_end = s_begin + per < nsteps ? s_begin + per : nsteps;
+    const int s_begin = 0, s_end = nsteps;
     float acc[R][NCOLS];
 #pragma unroll
     for (int r = 0; r < R; ++r)
@@ -136,21 +134,18 @@ __device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
             const float v = warp_sum(acc[r][c]);
-            if (lane == 0) {
-                if (partial) partial[r * NCOLS + c] = v;
-                else if (row0 + r < M.m) M.y[c * M.ldy + row0 + r] = v;
-            }
+            if (lane == 0 && row0 + r < M.m) M.y[c * M.ldy + row0 + r] = v;
         }
 }
 
 template <int NCOLS, typename Mid>
-__device__ __forceinline__ void row_pair_any(const FusedMat & M, int64_t row0, const XS & xs, int lane, int split, int ksplit, float * partial, Mid mid) {
+__device__ __forceinline__ void row_pair_any(const FusedMat & M, int64_t row0, const XS & xs, int lane, Mid mid) {
     switch (M.type) {
-        case B200_TYPE_Q4_K:   row_pair<B200_TYPE_Q4_K, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
-        case B200_TYPE_Q6_K:   row_pair<B200_TYPE_Q6_K, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
-        case B200_TYPE_IQ4_XS: row_pair<B200_TYPE_IQ4_XS, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
-        case B200_TYPE_Q4_0:   row_pair<B200_TYPE_Q4_0, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
-        default:               row_pair<B200_TYPE_Q8_0, NCOLS>(M, row0, xs, lane, split, ksplit, partial, mid); break;
+        case B200_TYPE_Q4_K:   row_pair<B200_TYPE_Q4_K, NCOLS>(M, row0, xs, lane, mid); break;
+        case B200_TYPE_Q6_K:   row_pair<B200_TYPE_Q6_K, NCOLS>(M, row0, xs, lane, mid); break;
+        case B200_TYPE_IQ4_XS: row_pair<B200_TYPE_IQ4_XS, NCOLS>(M, row0, xs, lane, mid); break;
+        case B200_TYPE_Q4_0:   row_pair<B200_TYPE_Q4_0, NCOLS>(M, row0, xs, lane, mid); break;
+        default:               row_pair<B200_TYPE_Q8_0, NCOLS>(M, row0, xs, lane, mid); break;
     }
 }
 
@@ -231,40 +226,12 @@ __global__ void __launch_bounds__(FTHREADS, 2) gemv_fused_kernel(const FusedArgs
     };
     auto nothing = []() {};
     int g = 0;
-    if (a.ksplit == 1) {
-        if (gw >= a.total_pairs) { prologue(); return; }
-        while (gw >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
-        row_pair_any<NCOLS>(a.mat[g], (gw - a.mat[g].pair_begin) * R, xs, lane, 0, 1, nullptr, prologue);
-        for (int64_t p = gw + GW; p < a.total_pairs; p += GW) {
-            while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
-            row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, 0, 1, nullptr, nothing);
-        }
-        return;
-    }
-    // split-K: KS warps of the CTA share one row pair (few rows, long k: every warp gets ONE batch of loads), partial
-    // sums meet in shared memory. All warps of the CTA run the same number of iterations (barriers inside).
-    __shared__ float part[FWARPS][R * NCOLS];
-    const int KS = a.ksplit, PG = FWARPS / KS;
-    const int pg = warp / KS, split = warp % KS;
-    const int64_t groups = (a.total_pairs + PG - 1) / PG;
-    const int64_t iters = (groups + gridDim.x - 1) / gridDim.x;
-    for (int64_t it = 0; it < iters; ++it) {
-        const int64_t p = (it * gridDim.x + blockIdx.x) * PG + pg;
-        const bool live = p < a.total_pairs;
-        if (live) {
-            while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
-            if (it == 0) row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, split, KS, part[warp], prologue);
-            else         row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, split, KS, part[warp], nothing);
-        } else if (it == 0) prologue();
-        __syncthreads();
-        if (live && split == 0 && lane < R * NCOLS) {
-            float v = 0.0f;
-            for (int s = 0; s < KS; ++s) v += part[warp + s][lane];
-            const FusedMat & M = a.mat[g];
-            const int64_t row = (p - M.pair_begin) * R + lane / NCOLS;
-            if (row < M.m) M.y[(lane % NCOLS) * M.ldy + row] = v;
-        }
-        __syncthreads();
+    if (gw >= a.total_pairs) { prologue(); return; }
+    while (gw >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+    row_pair_any<NCOLS>(a.mat[g], (gw - a.mat[g].pair_begin) * R, xs, lane, prologue);
+    for (int64_t p = gw + GW; p < a.total_pairs; p += GW) {
+        while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+        row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, nothing);
     }
 }
 
@@ -293,6 +260,10 @@ bool b200_gemv_stream_wants(const GemvGroup & g) {
     }
     const int B = act == B200_TYPE_Q8_K ? 256 : 32;
     const size_t xbytes = (size_t) g.ncols * (g.k + g.k / B * 4 + g.k / 16 * 2);
+    // every CTA quantises the whole of X: past 8192 activation elements the separate quantiser kernel + register GEMV wins
+    // (measured on the llama-3-8B chain: 586 -> 622 tokens/s when the k = 14336 down projections take the two-kernel path)
+    static const int64_t max_x = [] { const char * e = getenv("B200_FUSED_MAX_X"); return e ? (int64_t) atoll(e) : (int64_t) 8192; }();
+    if ((int64_t) g.ncols * g.k > max_x) return false;
     return xbytes <= 96 * 1024;
 }
 
@@ -322,17 +293,8 @@ int b200_gemv_stream_launch(const GemvGroup & g, cudaStream_t s) {
     int per_sm = 2;
     if (const char * e = getenv("B200_FUSED_CTAS_PER_SM")) { const int v = atoi(e); if (v > 0) per_sm = v; }
     int64_t grid = (int64_t) sms * per_sm;
-    // few row pairs and a long k: let 2..8 warps share a pair so that every warp issues one batch of loads
-    const int64_t all_warps = grid * FWARPS;
-    const int be = b200_block_elems(g.type[0]);
-    const int64_t nsteps = (g.k / be + 1024 / be - 1) / (1024 / be);
-    int max_u = 4;
-    for (int i = 0; i < g.count; ++i) if (g.type[i] == B200_TYPE_Q6_K || g.type[i] == B200_TYPE_Q8_0) max_u = 2;
-    int ks = 1;
-    (void) all_warps; (void) nsteps; (void) max_u;   // measured on B200: sharing a pair between warps does not pay, off unless forced
-    if (const char * e = getenv("B200_FUSED_KSPLIT")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) ks = v; }
-    a.ksplit = ks;
-    const int64_t need = (pairs * ks + FWARPS - 1) / FWARPS;
+    // (sharing a row pair between 2..8 warps for long-k / few-row shapes was measured slower on B200 and removed: DESIGN.md)
+    const int64_t need = (pairs + FWARPS - 1) / FWARPS;
     if (grid > need) grid = need;
     switch (g.ncols) {
         case 1: return launch_fused<1>(a, (int) grid, smem, s);
