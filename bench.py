@@ -189,6 +189,8 @@ def main():
     ap.add_argument("--pp", type=int, default=512, help="prefill ubatch (0 = skip the pp leg)")
     ap.add_argument("--pp-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="row split (N > 1): Y slices stored into every rank's arena by the kernels, or one NCCL all-gather per node")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -217,30 +219,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- row split exchange: all-gather of the Y slices ------------------------------
-    gather = None
+    # ---- row split exchange: one all-gather of the Y slices per node (rowsplit.py) --------
+    rowsplit = None
     if world > 1:
-        def gather(y, o, stream):
-            lo, hi = b.row_split(o.m, world, rank)
-            with torch.cuda.stream(stream.torch_stream()):
-                if o.m % (128 * world) == 0:
-                    if y.shape[0] == 1:
-                        dist.all_gather_into_tensor(y.view(-1)[:o.m], y.view(-1)[lo:hi])
-                    else:
-                        parts = [torch.empty((y.shape[0], o.m // world), device=y.device) for _ in range(world)]
-                        dist.all_gather(parts, y[:, lo:hi].contiguous())
-                        y[:, :o.m].copy_(torch.cat(parts, dim=1))
-                else:
-                    for r in range(world):        # uneven tail split (m = 128256): one broadcast per owner
-                        rl, rh = b.row_split(o.m, world, r)
-                        seg = y[:, rl:rh].contiguous()
-                        dist.broadcast(seg, src=r)
-                        if r != rank:
-                            y[:, rl:rh].copy_(seg)
+        from zyk_llama_cpp_b200.rowsplit import RowSplit
+        rowsplit = RowSplit(world, rank, b.row_split)
 
     def time_chain(n, steps, wu):
-        chain = MatMulChain(ops, n, device=local, world=world, rank=rank, gather=gather)
-        if world == 1:
+        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused")
+        if chain.capturable:
             chain.capture()
         e0, e1 = b.Event(local), b.Event(local)
         for _ in range(wu):
@@ -264,6 +251,7 @@ def main():
 
     # ---- tg: device-resident ---------------------------------------------------------------------------------
     chain, ms_total, clocks = time_chain(1, args.steps, warmup)
+    graph_used = chain.graph is not None
     ms_step = ms_total / args.steps
     tg = 1e3 / ms_step
     launches = (chain.kernels_per_step or len(chain.calls) * 2) * args.steps
@@ -292,6 +280,7 @@ def main():
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_tg = args.steps / float(e2e_s.item())
+    chain.close()
     del chain
     torch.cuda.empty_cache()
 
@@ -307,6 +296,7 @@ def main():
                   # fp16 tcgen05 path: the same op count against the measured cuBLAS bf16 throughput (sustained: this is a long step)
                   "tensor_roofline": {"bound": "tensor", "achieved": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "peak": peaks.get("bf16_tflops_sustained"),
                                       "unit": "TFLOP/s", "frac": pp_ops / (ms_pp * 1e-3) / 1e12 / world / peaks.get("bf16_tflops_sustained", 1400.0)}}
+            chain_pp.close()
             del chain_pp
         except Exception as e:  # noqa: BLE001
             pp = {"error": str(e)[:200]}
@@ -339,7 +329,7 @@ def main():
         "config": {"workload": f"{args.model} tg (N=1): every quantised MUL_MAT of one token ({len(ops)} nodes)",
                    "weights": "random-init blocks, plane layout (load-time repack)", "weight_gb_per_token": bytes_tok / 1e9,
                    "l2": "inputs larger than L2 (weights streamed once per step)", "parallelism": f"row-split x{world}" if world > 1 else "single GPU",
-                   "cuda_graph": world == 1},
+                   "cuda_graph": graph_used, "exchange": (args.exchange if world > 1 else None)},
         "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],

@@ -181,9 +181,39 @@ B200_API int    b200_mul_mat_id(const b200_mul_mat_id_args * args, b200_stream_t
 
 /* ---- (e) multi-GPU row split ----------------------------------------------------------------
  * rows [*row_lo, *row_hi) of an m-row weight matrix owned by `rank` of `world` (tile rounded,
- * cf. get_row_split, ggml-cuda/ggml-cuda.cu:790-803). The exchange step itself (all-gather of the
- * Y slices) is done by the caller's communicator (NCCL via torch.distributed in bench.py). */
+ * cf. get_row_split, ggml-cuda/ggml-cuda.cu:790-803). */
 B200_API int b200_row_split(int64_t m, int world, int rank, int64_t * row_lo, int64_t * row_hi);
+
+/* The exchange step, fused into the kernels (replaces the copy-back of ggml_cuda_op_mul_mat,
+ * ggml-cuda/ggml-cuda.cu:1725-1744, and an ncclAllGather per node): every rank keeps its activations in a
+ * SYMMETRIC ARENA (same size and layout on every rank, one process per GPU, mapped into the peers with
+ * b200_ipc_import). The kernel that produces rows [lo, hi) of Y stores them into the arena of every rank over
+ * NVLink (local address + peer_delta[g]); when its last CTA is done it adds one arrival to `sync[0]` of every rank.
+ * The kernel that reads X of call (step, seq) first waits until (step * calls_per_step + seq) * world arrivals
+ * are in, i.e. every rank has finished every earlier call. No host involvement, CUDA-graph replayable: the only
+ * per-pass state is the device word `*step`, advanced by b200_row_gather_step once per pass. */
+#define B200_MAX_PEERS 8
+typedef struct b200_row_gather {
+    int32_t  world, rank;
+    int64_t  peer_delta[B200_MAX_PEERS]; /* bytes from a local arena address to the same location on rank g (0 for g == rank) */
+    uint64_t * sync;                     /* two zero-initialised words INSIDE the local arena: [0] arrivals, [1] CTA counter  */
+    const uint64_t * step;               /* local device word: passes started so far (>= 1 while a pass runs)                 */
+    int64_t  seq;                        /* index of this call among the gather calls of one pass, 0 .. calls_per_step - 1    */
+    int64_t  calls_per_step;
+} b200_row_gather;
+
+/* *step += 1, in stream order: issue once at the start of every pass (decode step / prefill ubatch) */
+B200_API int b200_row_gather_step(uint64_t * step, b200_stream_t stream);
+/* b200_mul_mat_group(args, count) on this rank's row slices (args[i].y points at column `lo` of the full Y inside the
+ * arena, args[i].m = hi - lo) + the fused exchange described above: one wait, one arrival per call. */
+B200_API int b200_mul_mat_gather(const b200_mul_mat_args * args, int count, const b200_row_gather * gather, b200_stream_t stream);
+/* block the stream until every rank has finished calls 0 .. gather->seq - 1 of the current pass (seq == calls_per_step: the
+ * whole pass): issue before the host or a foreign kernel reads a gathered Y */
+B200_API int b200_row_gather_wait(const b200_row_gather * gather, b200_stream_t stream);
+/* peer mapping of an arena allocated with b200_malloc: 64-byte handle out / in (cudaIpcMemHandle_t) */
+B200_API int b200_ipc_export(const void * dev_ptr, void * handle64);
+B200_API int b200_ipc_import(const void * handle64, void ** dev_ptr);
+B200_API int b200_ipc_close(void * dev_ptr);
 
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 B200_API uint64_t b200_launch_count(void);

@@ -312,7 +312,8 @@ def test_stream_gemv_group_mixed_types(b200, orc):
         wps = [b200.repack(t, dev(w).reshape(-1), m, k) for t, w, m in zip(ts, ws, ms)]
         before = b200.launch_count()
         ys = b200.mul_mat_group(ts, wps, dev(x), ms)
-        assert b200.launch_count() - before == 1          # ONE kernel for three nodes, quantiser included
+        # n * k <= 8192: ONE kernel for the three nodes, quantiser included; beyond that one quantiser launch shared by three GEMVs
+        assert b200.launch_count() - before == (1 if n * k <= 8192 else 4)
         rows = rng.choice(1016, 64, replace=False)
         for t, w, y in zip(ts, ws, ys):
             assert nmse(y.cpu().numpy()[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE

@@ -50,6 +50,15 @@ class MulMatIdArgs(C.Structure):
                 ("flavour", C.c_int32), ("algo", C.c_int32), ("flags", C.c_int32), ("reserved", C.c_int32)]
 
 
+MAX_PEERS = 8
+
+
+class RowGather(C.Structure):
+    """mirror of b200_row_gather (include/b200_mm.h): the exchange fused into the row-split kernels"""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("peer_delta", C.c_int64 * MAX_PEERS), ("sync", C.c_void_p),
+                ("step", C.c_void_p), ("seq", C.c_int64), ("calls_per_step", C.c_int64)]
+
+
 def _sig(name, restype, *argtypes):
     fn = getattr(lib, name)
     fn.restype = restype
@@ -86,6 +95,15 @@ _sig("b200_memcpy_h2d", C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 _sig("b200_memcpy_d2h", C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 _sig("b200_row_split", C.c_int, C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64))
 _sig("b200_device_count", C.c_int)
+_sig("b200_malloc", C.c_void_p, C.c_int, C.c_size_t)
+_sig("b200_free", C.c_int, C.c_int, C.c_void_p)
+_sig("b200_memset", C.c_int, C.c_void_p, C.c_int, C.c_size_t, C.c_void_p)
+_sig("b200_row_gather_step", C.c_int, C.c_void_p, C.c_void_p)
+_sig("b200_mul_mat_gather", C.c_int, C.POINTER(MulMatArgs), C.c_int, C.POINTER(RowGather), C.c_void_p)
+_sig("b200_row_gather_wait", C.c_int, C.POINTER(RowGather), C.c_void_p)
+_sig("b200_ipc_export", C.c_int, C.c_void_p, C.c_void_p)
+_sig("b200_ipc_import", C.c_int, C.c_void_p, C.POINTER(C.c_void_p))
+_sig("b200_ipc_close", C.c_int, C.c_void_p)
 
 
 def _check(rc: int):

@@ -8,7 +8,7 @@ MUL_MAT nodes, which is the hot path of this repository. Weights are written onc
 load-time repack (b200_repack, the set_tensor hook), activations live in HBM between nodes.
 
 Row split: with world > 1 every rank keeps rows [lo, hi) of each matrix
-(b200_row_split) and the Y slices are exchanged after each node by `gather` (an all-gather).
+(b200_row_split) and the Y slices are exchanged after each node by RowSplit.gather (one all-gather, rowsplit.py).
 """
 from __future__ import annotations
 
@@ -21,11 +21,15 @@ from .workloads import MatMul, buffer_widths, random_weight, row_bytes
 
 
 class MatMulChain:
-    def __init__(self, ops: list[MatMul], n: int, device: int = 0, *, seed: int = 1234, world: int = 1, rank: int = 0,
-                 gather=None, pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None,
-                 grouping: bool = True):
+    def __init__(self, ops: list[MatMul], n: int, device: int = 0, *, seed: int = 1234, rowsplit=None, fused_exchange: bool = True,
+                 pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None, grouping: bool = True):
         self.ops, self.n, self.device = ops, n, device
-        self.world, self.rank, self.gather = world, rank, gather
+        self.rowsplit = rowsplit                      # rowsplit.RowSplit or None (single GPU)
+        # row split: exchange fused into the kernels over a symmetric arena (b200_mul_mat_gather), or one NCCL all-gather per node
+        self.fused_exchange = fused_exchange and rowsplit is not None and rowsplit.world > 1
+        self.arena = None
+        world, rank = (rowsplit.world, rowsplit.rank) if rowsplit is not None else (1, 0)
+        self.world, self.rank = world, rank
         self.dev = torch.device(f"cuda:{device}")
         self.stream = stream or B.Stream(device)
         self.flags = B.MM_PDL if pdl else 0
@@ -38,11 +42,16 @@ class MatMulChain:
         self.weights: list[torch.Tensor] = []
         self.rows: list[tuple[int, int]] = []
         for o in ops:
-            lo, hi = B.row_split(o.m, world, rank) if world > 1 else (0, o.m)
+            lo, hi = rowsplit.mine(o.m) if world > 1 else (0, o.m)
             self.rows.append((lo, hi))
             mats = []
+            rb = row_bytes(o.type, o.k)
             for _ in range(max(1, o.n_expert)):
-                w = random_weight(o.type, hi - lo, o.k, self.dev, gen)
+                # the same seeded full matrix on every rank, then this rank's rows: a row-split chain computes exactly
+                # what the single-GPU chain computes (tools/rowsplit_check.py compares them)
+                w = random_weight(o.type, o.m, o.k, self.dev, gen)
+                if world > 1:
+                    w = w[lo * rb:hi * rb].clone()
                 if layout == B.LAYOUT_PLANES and hi > lo:
                     w = B.repack(o.type, w, hi - lo, o.k)
                 mats.append(w)
@@ -50,11 +59,23 @@ class MatMulChain:
 
         # ---- activations (f32, [n, width]) and the shared workspace -----------------------------------
         self.bufs: dict[str, torch.Tensor] = {}
+        shapes = {}
         for name, width in buffer_widths(ops).items():
             rows = n
             if any(o.n_expert and (o.dst == name or (o.src == name and o.src == "act")) for o in ops):
                 rows = n * max(o.n_used for o in ops if o.n_expert)
-            self.bufs[name] = torch.randn((rows, width), device=self.dev, generator=gen)
+            shapes[name] = (rows, width)
+        if self.fused_exchange:
+            from .rowsplit import SymmetricArena
+            total = sum(((r * w * 4 + 255) & ~255) for r, w in shapes.values())
+            self.arena = SymmetricArena(B, device, world, rank, total, group=rowsplit.group)
+        for name, (rows, width) in shapes.items():
+            init = torch.randn((rows, width), device=self.dev, generator=gen)      # same seed on every rank: same activations
+            if self.arena is not None:
+                self.bufs[name] = self.arena.tensor(rows, width)
+                self.bufs[name].copy_(init)
+            else:
+                self.bufs[name] = init
         self.ids = None
         if any(o.n_expert for o in ops):
             ne = max(o.n_expert for o in ops)
@@ -74,6 +95,11 @@ class MatMulChain:
         self.graph = None
         self.kernels_per_step = 0
         torch.cuda.synchronize(self.dev)
+        if self.fused_exchange:
+            import torch.distributed as dist
+            dist.barrier(group=rowsplit.group)        # nobody stores into a peer arena that is still being initialised
+        # a pass may be captured into a CUDA graph when every launch is ours (no NCCL call between the nodes)
+        self.capturable = world == 1 or (self.fused_exchange and all(c[0] is B.lib.b200_mul_mat_gather for c in self.calls))
 
     # one prebuilt ctypes argument struct per node; decode nodes that read the same X (wq/wk/wv, gate/up) form a group
     def _build_calls(self):
@@ -83,7 +109,8 @@ class MatMulChain:
         def flush():
             if group:
                 arr = (B.MulMatArgs * len(group))(*[g[0] for g in group])
-                calls.append((B.lib.b200_mul_mat_group, arr, [g[1] for g in group], [g[2] for g in group]))
+                fn = B.lib.b200_mul_mat_gather if self.fused_exchange else B.lib.b200_mul_mat_group
+                calls.append((fn, arr, [g[1] for g in group], [g[2] for g in group], [g[3] for g in group]))
                 group.clear()
 
         for o, w, (lo, hi) in zip(self.ops, self.weights, self.rows):
@@ -97,26 +124,40 @@ class MatMulChain:
                                    self.ids.data_ptr(), o.n_used,
                                    y.data_ptr() + 4 * lo, y.shape[1], o.n_used * y.shape[1],
                                    self.ws_ptr, self.ws_size, B.Q8_X86, 0, self.flags, 0)
-                calls.append((B.lib.b200_mul_mat_id, a, [o], [y]))
+                calls.append((B.lib.b200_mul_mat_id, a, [o], [y], [w]))
                 continue
             a = B.MulMatArgs(o.type, self.layout, hi - lo, self.n, o.k, w.data_ptr(), 0, x.data_ptr(), x.shape[1],
                              y.data_ptr() + 4 * lo, y.shape[1], self.ws_ptr, self.ws_size, B.Q8_X86, 0, self.flags, 0)
             if group and (group[0][1].src, group[0][1].k) != (o.src, o.k) or len(group) == 4 or not self.grouping:
                 flush()
-            group.append((a, o, y))
+            group.append((a, o, y, w))
         flush()
+        if self.fused_exchange:       # one exchange descriptor per gather call: its position in the pass is baked in
+            idx = [i for i, c in enumerate(calls) if c[0] is B.lib.b200_mul_mat_gather]
+            self.gather_descs = {i: self.arena.gather_desc(seq, len(idx)) for seq, i in enumerate(idx)}
+            self.gather_all = self.arena.gather_desc(len(idx), len(idx))
         return calls
 
     def issue(self):
         """enqueue one forward pass' worth of MUL_MAT nodes on self.stream (no host sync)"""
         h = self.stream.handle
-        for fn, a, ops, ys in self.calls:
-            rc = fn(a, len(ops), h) if fn is B.lib.b200_mul_mat_group else fn(C.byref(a), h)
+        if self.fused_exchange:
+            B._check(B.lib.b200_row_gather_step(self.arena.step_ptr, h))
+        for i, (fn, a, ops, ys, _ws) in enumerate(self.calls):
+            if fn is B.lib.b200_mul_mat_gather:
+                rc = fn(a, len(ops), C.byref(self.gather_descs[i]), h)
+            elif fn is B.lib.b200_mul_mat_group:
+                rc = fn(a, len(ops), h)
+            else:
+                rc = fn(C.byref(a), h)
             if rc != 0:
                 raise B.B200Error(f"{ops[0].name}: {B.lib.b200_last_error().decode()}")
-            if self.gather is not None:
-                for o, y in zip(ops, ys):
-                    self.gather(y, o, self.stream)
+            if self.world > 1 and fn is not B.lib.b200_mul_mat_gather:
+                with torch.cuda.stream(self.stream.torch_stream()):
+                    for o, y in zip(ops, ys):
+                        self.rowsplit.gather(y, o.m)
+        if self.fused_exchange:       # the last node's slices from the other ranks are in before anything after the pass reads Y
+            B._check(B.lib.b200_row_gather_wait(C.byref(self.gather_all), h))
 
     def capture(self):
         before = B.launch_count()
@@ -131,6 +172,19 @@ class MatMulChain:
             self.graph.launch()
         else:
             self.issue()
+
+    def close(self):
+        """collective: unmap and free the symmetric arena (every rank calls it)"""
+        if self.arena is not None:
+            import torch.distributed as dist
+            self.stream.synchronize()
+            torch.cuda.synchronize(self.dev)
+            dist.barrier(group=self.rowsplit.group)
+            self.graph = None
+            self.bufs.clear()
+            self.arena.close()
+            dist.barrier(group=self.rowsplit.group)
+            self.arena = None
 
     def weight_bytes_resident(self) -> int:
         return sum(w.numel() for w in self.weights)

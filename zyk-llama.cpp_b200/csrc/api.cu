@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
 

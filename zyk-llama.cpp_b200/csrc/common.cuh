@@ -69,6 +69,9 @@ __device__ __forceinline__ uint16_t ld_stream2(const void * p) {
     asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
     return r;
 }
+// kernel variants: the row-split exchange costs registers in the streaming loops (Q6_K register GEMV: 72 -> 80, one CTA less
+// per SM), so it is compiled in only where it is used
+enum { KV_PLAIN = 0, KV_PEER = 1 };
 // 128-bit cached load (activations: re-read by every warp of the SM, want them in L1)
 __device__ __forceinline__ uint4 ld_cached16(const void * p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
 
@@ -77,6 +80,53 @@ __device__ __forceinline__ void prefetch_l2(const void * p) { asm volatile("pref
 // programmatic dependent launch (PDL): let the next kernel start, wait for the previous one
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+
+// ---- fused row-split exchange (include/b200_mm.h: b200_row_gather) ---------------------------------------
+struct PeerGather {
+    int world, rank;                    // world <= 1: off
+    long long delta[8];
+    unsigned long long * sync;          // [0] arrivals (peers add), [1] CTAs of the signalling kernel that are done
+    const unsigned long long * step;
+    unsigned long long seq, calls;
+    int wait, signal;                   // this launch waits for the earlier calls / announces the end of this call
+};
+
+// one thread: block until every rank has finished every call before (step, seq). Traps after ~10 s instead of hanging the GPU.
+__device__ __forceinline__ void peer_wait(const PeerGather & p) {
+    const unsigned long long want = ((*p.step - 1ull) * p.calls + p.seq) * (unsigned long long) p.world;
+    unsigned long long t0 = 0, v;
+    for (unsigned spin = 0;; ++spin) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p.sync) : "memory");
+        if (v >= want) break;
+        __nanosleep(40);
+        if ((spin & 1023u) == 1023u) {
+            unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t; else if (t - t0 > 10000000000ull) __trap();
+        }
+    }
+}
+// the value goes to the same location of every rank's arena (delta[rank] == 0)
+__device__ __forceinline__ void peer_store(const PeerGather & p, float * addr, float v) {
+    for (int g = 0; g < p.world; ++g) *reinterpret_cast<float *>(reinterpret_cast<char *>(addr) + p.delta[g]) = v;
+}
+// ONE thread per CTA, after a CTA barrier that follows all of the CTA's peer stores (barrier + this thread's system fence order them):
+// the last CTA of the grid announces the end of the call to every rank
+__device__ __forceinline__ void peer_signal(const PeerGather & p) {
+    // release at GPU scope on the local CTA counter (cheap), one system-scope release by the last CTA: release sequences are
+    // cumulative, so every CTA's peer stores are ordered before the arrival the other ranks acquire at system scope
+    const unsigned long long n = (unsigned long long) gridDim.x * gridDim.y * gridDim.z;
+    unsigned long long old;
+    asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], 1;" : "=l"(old) : "l"(p.sync + 1) : "memory");
+    if (old == n - 1) {
+        p.sync[1] = 0;                  // the next signalling kernel on this stream starts from zero (it runs after this one)
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        for (int g = 0; g < p.world; ++g) {
+            unsigned long long * dst = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.sync) + p.delta[g]);
+            asm volatile("red.relaxed.sys.global.add.u64 [%0], 1;" :: "l"(dst) : "memory");
+        }
+    }
+}
 
 __device__ __forceinline__ float half_bits_to_float(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 

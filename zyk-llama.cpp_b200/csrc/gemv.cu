@@ -16,7 +16,15 @@
 #include "actquant.cuh"
 #include "gemv.h"
 
-template <int TYPE, int NCOLS, int R, int U>
+// fused row-split exchange: every thread of the CTA passes here exactly once, whichever way its warp leaves the kernel
+__device__ __forceinline__ void gemv_finish(const GemvArgs & a) {
+    if (a.peer.world > 1 && a.peer.signal) {
+        __syncthreads();
+        if (threadIdx.x == 0) peer_signal(a.peer);
+    }
+}
+
+template <int TYPE, int NCOLS, int R, int U, int KV>
 __global__ void __launch_bounds__(128) gemv_kernel(GemvArgs a) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -48,7 +56,7 @@ __global__ void __launch_bounds__(128) gemv_kernel(GemvArgs a) {
     }
 
     const int64_t row0 = ((int64_t) blockIdx.x * 4 + warp) * R;
-    if (row0 >= a.m) return;
+    if (row0 >= a.m) { if (KV == KV_PEER) gemv_finish(a); return; }
 
     float acc[R][NCOLS];
 #pragma unroll
@@ -94,15 +102,20 @@ __global__ void __launch_bounds__(128) gemv_kernel(GemvArgs a) {
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
             const float v = warp_sum(acc[r][c]);
-            if (lane == 0 && row0 + r < a.m) y[c * a.ldy + row0 + r] = v;
+            if (lane == 0 && row0 + r < a.m) {
+                if (KV == KV_PEER) peer_store(a.peer, y + c * a.ldy + row0 + r, v);
+                else y[c * a.ldy + row0 + r] = v;
+            }
         }
+    if (KV == KV_PEER) gemv_finish(a);
 }
 
 // ------------------------------------------------------------------------------------------------
 template <int TYPE, int NCOLS, int R, int U>
 static int launch_gemv(const GemvArgs & a, int64_t pairs, cudaStream_t s) {
     dim3 grid((unsigned) ((a.m + 4 * R - 1) / (4 * R)), (unsigned) pairs);
-    B200_CHECK(b200_launch(gemv_kernel<TYPE, NCOLS, R, U>, grid, dim3(128), 0, s, a.pdl != 0, a));
+    if (a.peer.world > 1)  B200_CHECK(b200_launch(gemv_kernel<TYPE, NCOLS, R, U, KV_PEER>, grid, dim3(128), 0, s, a.pdl != 0, a));
+    else                   B200_CHECK(b200_launch(gemv_kernel<TYPE, NCOLS, R, U, KV_PLAIN>, grid, dim3(128), 0, s, a.pdl != 0, a));
     return 0;
 }
 

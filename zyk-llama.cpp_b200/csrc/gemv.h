@@ -13,6 +13,7 @@ struct GemvArgs {
     // MUL_MAT_ID (ids == nullptr for plain MUL_MAT)
     const int32_t * ids; int64_t ids_row_stride; int64_t n_used, nb1, n_as, expert_stride, y_token_stride;
     int pdl;
+    PeerGather peer;         // fused row-split exchange: peer stores + arrival (the activation quantiser does the wait)
 };
 
 // plane-layout fast path (also canonical packed Q4_K). ncols in 1..8. `pairs` = grid.y
@@ -44,6 +45,7 @@ struct GemvGroup {
     const float * x; int64_t ldx;
     int flavour, pdl;
     XqPlanes xq_out;
+    PeerGather peer;         // fused row-split exchange (world <= 1: off)
 };
-bool b200_gemv_stream_wants(const GemvGroup & g);
+bool b200_gemv_stream_wants(const GemvGroup & g, bool force = false);   // force: caller set algo == 3
 int  b200_gemv_stream_launch(const GemvGroup & g, cudaStream_t s);

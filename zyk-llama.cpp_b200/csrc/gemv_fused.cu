@@ -48,6 +48,7 @@ struct FusedArgs {
     int act_block;                       // 256 (Q8_K) or 32 (Q8_0)
     int pdl;
     XqPlanes xq_out;                     // CTA 0 also leaves the quantised X here (B200_MM_X_PREQUANTISED protocol)
+    PeerGather peer;                     // row-split exchange fused into this launch (world <= 1: off)
 };
 
 __device__ __forceinline__ uint4 lds16(uint32_t a) {
@@ -87,8 +88,8 @@ template <int TYPE> struct Unroll { static constexpr int U = (TYPE == B200_TYPE_
 // one warp, one row pair of matrix M: stream the two rows, U steps of loads in flight. `mid` runs after the loads of
 // the first batch have been issued and before anything is computed (the first pair of a warp passes the
 // wait-for-previous-kernel + activation quantiser there, so that phase overlaps the HBM latency of the weights).
-template <int TYPE, int NCOLS, typename Mid>
-__device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const XS & xs, int lane, Mid mid) {
+template <int TYPE, int NCOLS, int KV, typename Mid>
+__device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const XS & xs, int lane, const PeerGather & peer, Mid mid) {
     constexpr int U = Unroll<TYPE>::U;
     constexpr int BLK = Fmt<TYPE>::BLK;
     constexpr int BPS = 1024 / BLK;
@@ -134,18 +135,21 @@ __device__ __forceinline__ void row_pair(const FusedMat & M, int64_t row0, const
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
             const float v = warp_sum(acc[r][c]);
-            if (lane == 0 && row0 + r < M.m) M.y[c * M.ldy + row0 + r] = v;
+            if (lane == 0 && row0 + r < M.m) {
+                if (KV == KV_PEER) peer_store(peer, M.y + c * M.ldy + row0 + r, v);
+                else M.y[c * M.ldy + row0 + r] = v;
+            }
         }
 }
 
-template <int NCOLS, typename Mid>
-__device__ __forceinline__ void row_pair_any(const FusedMat & M, int64_t row0, const XS & xs, int lane, Mid mid) {
+template <int NCOLS, int KV, typename Mid>
+__device__ __forceinline__ void row_pair_any(const FusedMat & M, int64_t row0, const XS & xs, int lane, const PeerGather & peer, Mid mid) {
     switch (M.type) {
-        case B200_TYPE_Q4_K:   row_pair<B200_TYPE_Q4_K, NCOLS>(M, row0, xs, lane, mid); break;
-        case B200_TYPE_Q6_K:   row_pair<B200_TYPE_Q6_K, NCOLS>(M, row0, xs, lane, mid); break;
-        case B200_TYPE_IQ4_XS: row_pair<B200_TYPE_IQ4_XS, NCOLS>(M, row0, xs, lane, mid); break;
-        case B200_TYPE_Q4_0:   row_pair<B200_TYPE_Q4_0, NCOLS>(M, row0, xs, lane, mid); break;
-        default:               row_pair<B200_TYPE_Q8_0, NCOLS>(M, row0, xs, lane, mid); break;
+        case B200_TYPE_Q4_K:   row_pair<B200_TYPE_Q4_K, NCOLS, KV>(M, row0, xs, lane, peer, mid); break;
+        case B200_TYPE_Q6_K:   row_pair<B200_TYPE_Q6_K, NCOLS, KV>(M, row0, xs, lane, peer, mid); break;
+        case B200_TYPE_IQ4_XS: row_pair<B200_TYPE_IQ4_XS, NCOLS, KV>(M, row0, xs, lane, peer, mid); break;
+        case B200_TYPE_Q4_0:   row_pair<B200_TYPE_Q4_0, NCOLS, KV>(M, row0, xs, lane, peer, mid); break;
+        default:               row_pair<B200_TYPE_Q8_0, NCOLS, KV>(M, row0, xs, lane, peer, mid); break;
     }
 }
 
@@ -204,7 +208,7 @@ __device__ __forceinline__ void quantise_x(const FusedArgs & a, const XS & xs, i
     __syncthreads();
 }
 
-template <int NCOLS>
+template <int NCOLS, int KV>
 __global__ void __launch_bounds__(FTHREADS, 2) gemv_fused_kernel(const FusedArgs a) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -222,16 +226,27 @@ __global__ void __launch_bounds__(FTHREADS, 2) gemv_fused_kernel(const FusedArgs
     // waiting for the previous kernel and quantising X happens while they are in flight
     auto prologue = [&]() {
         if (a.pdl) pdl_wait();
+        if (KV == KV_PEER && a.peer.wait) {          // X is complete once every rank has finished the previous call
+            if (lane == 0) peer_wait(a.peer);
+            __syncwarp();
+        }
         quantise_x<NCOLS>(a, xs, warp, lane);
     };
     auto nothing = []() {};
     int g = 0;
-    if (gw >= a.total_pairs) { prologue(); return; }
-    while (gw >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
-    row_pair_any<NCOLS>(a.mat[g], (gw - a.mat[g].pair_begin) * R, xs, lane, prologue);
-    for (int64_t p = gw + GW; p < a.total_pairs; p += GW) {
-        while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
-        row_pair_any<NCOLS>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, nothing);
+    if (gw < a.total_pairs) {
+        while (gw >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+        row_pair_any<NCOLS, KV>(a.mat[g], (gw - a.mat[g].pair_begin) * R, xs, lane, a.peer, prologue);
+        for (int64_t p = gw + GW; p < a.total_pairs; p += GW) {
+            while (p >= a.mat[g].pair_begin + (a.mat[g].m + R - 1) / R) ++g;
+            row_pair_any<NCOLS, KV>(a.mat[g], (p - a.mat[g].pair_begin) * R, xs, lane, a.peer, nothing);
+        }
+    } else {
+        prologue();
+    }
+    if (KV == KV_PEER && a.peer.signal) {            // slices are in every rank's arena: the last CTA announces it
+        __syncthreads();                             // CTA barrier, then ONE system fence per CTA (inside peer_signal) covers all warps' stores
+        if (threadIdx.x == 0) peer_signal(a.peer);
     }
 }
 
@@ -239,10 +254,12 @@ template <int NCOLS>
 int launch_fused(const FusedArgs & a, int grid, size_t smem, cudaStream_t s) {
     static bool configured = false;
     if (!configured) {
-        B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS, KV_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS, KV_PEER>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         configured = true;
     }
-    B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));
+    if (a.peer.world > 1) B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS, KV_PEER>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));
+    else                  B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS, KV_PLAIN>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));
     return 0;
 }
 
@@ -250,7 +267,7 @@ int launch_fused(const FusedArgs & a, int grid, size_t smem, cudaStream_t s) {
 
 // Can this group take the fused kernel? All matrices: plane layout (or canonical Q4_K), packed, 16 B aligned,
 // k % 256 == 0, same activation format, quantised X fits in shared memory.
-bool b200_gemv_stream_wants(const GemvGroup & g) {
+bool b200_gemv_stream_wants(const GemvGroup & g, bool force) {
     if (g.count < 1 || g.count > B200_MAX_GROUP || g.ncols < 1 || g.ncols > 4) return false;
     if (g.k % 256 != 0 || g.k > 65536) return false;
     const int act = b200_act_type(g.type[0]);
@@ -263,7 +280,7 @@ bool b200_gemv_stream_wants(const GemvGroup & g) {
     // every CTA quantises the whole of X: past 8192 activation elements the separate quantiser kernel + register GEMV wins
     // (measured on the llama-3-8B chain: 586 -> 622 tokens/s when the k = 14336 down projections take the two-kernel path)
     static const int64_t max_x = [] { const char * e = getenv("B200_FUSED_MAX_X"); return e ? (int64_t) atoll(e) : (int64_t) 8192; }();
-    if ((int64_t) g.ncols * g.k > max_x) return false;
+    if (!force && (int64_t) g.ncols * g.k > max_x) return false;
     return xbytes <= 96 * 1024;
 }
 
@@ -286,6 +303,7 @@ int b200_gemv_stream_launch(const GemvGroup & g, cudaStream_t s) {
     a.act_block = b200_act_type(g.type[0]) == B200_TYPE_Q8_K ? 256 : 32;
     a.pdl = g.pdl;
     a.xq_out = g.xq_out;
+    a.peer = g.peer;
 
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }

@@ -3,6 +3,8 @@
 #include "actquant.cuh"
 #include "gemv.h"
 #include "gemm.h"
+#include <string.h>
+#include <stdlib.h>
 
 static bool planes_fast_path(int type, int layout, int64_t m, int64_t k, const void * w, int64_t w_row_stride) {
     const bool packed = w_row_stride == 0 || w_row_stride == (int64_t) b200_row_size(type, k);
@@ -22,8 +24,37 @@ size_t b200_mul_mat_workspace(int type, int64_t n, int64_t k) {
     return (q > g ? q : g) + 256;
 }
 
-int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
-    cudaStream_t s = (cudaStream_t) stream;
+// one tiny kernel each for the two-kernel paths (quantiser + GEMV, fp16 prologue + GEMM) of the fused row-split exchange
+static __global__ void peer_wait_kernel(const PeerGather p) { if (threadIdx.x == 0) peer_wait(p); }
+static __global__ void peer_signal_kernel(const PeerGather p) { if (threadIdx.x == 0) peer_signal(p); }
+// prefill: the GEMM keeps its epilogue local (k-split tiles meet with red.global.add); this kernel then copies the finished slice
+// y[n][0..m) (row stride ldy) into every other rank's arena with 128-bit stores and, when asked, announces the end of the call
+static __global__ void __launch_bounds__(256) peer_scatter_kernel(const float * __restrict__ y, int64_t ldy, int64_t m, int64_t n, const PeerGather p) {
+    const bool vec = (m % 4 == 0) && (ldy % 4 == 0) && ((((uintptr_t) y) & 15) == 0);
+    const int64_t per_row = vec ? m / 4 : m, total = per_row * n;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t r = i / per_row, c = i % per_row;
+        if (vec) {
+            const float4 * src = reinterpret_cast<const float4 *>(y + r * ldy) + c;
+            const float4 v = *src;
+            for (int g = 0; g < p.world; ++g)
+                if (g != p.rank) *reinterpret_cast<float4 *>(reinterpret_cast<char *>(const_cast<float4 *>(src)) + p.delta[g]) = v;
+        } else {
+            const float * src = y + r * ldy + c;
+            const float v = *src;
+            for (int g = 0; g < p.world; ++g)
+                if (g != p.rank) *reinterpret_cast<float *>(reinterpret_cast<char *>(const_cast<float *>(src)) + p.delta[g]) = v;
+        }
+    }
+    if (p.signal) {
+        __syncthreads();
+        if (threadIdx.x == 0) peer_signal(p);
+    }
+}
+
+// `peer` (may be null): fused row-split exchange for this node; peer->wait / peer->signal say whether this node's first
+// kernel waits for the earlier calls and whether its last kernel announces the end of the call
+static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerGather * peer) {
     B200_REQUIRE(a && a->w && a->x && a->y, "b200_mul_mat: null pointer");
     B200_REQUIRE(b200_type_is_weight(a->type), "b200_mul_mat: unsupported weight type %d", a->type);
     const int be = b200_block_elems(a->type);
@@ -42,7 +73,13 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
 
     // (2) prefill: tensor-core GEMM on plane layout
     if (a->algo != 1 && fast && b200_gemm_wants(a->type, a->m, a->n, a->k, a->algo == 2)) {
-        return b200_gemm_launch(a, s);
+        if (peer && peer->wait) B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, s, false, *peer));
+        const int rc = b200_gemm_launch(a, s);
+        if (rc || !peer) return rc;
+        const int64_t work = (a->m % 4 == 0 ? a->m / 4 : a->m) * a->n;
+        const unsigned blocks = (unsigned) (work / 256 + 1 < 148 * 8 ? work / 256 + 1 : 148 * 8);
+        B200_CHECK(b200_launch(peer_scatter_kernel, dim3(blocks), dim3(256), 0, s, false, (const float *) a->y, a->y_row_stride, a->m, a->n, *peer));
+        return 0;
     }
     B200_REQUIRE(a->algo != 2, "b200_mul_mat: GEMM forced but shape/layout is not eligible (type %d m=%lld n=%lld k=%lld)",
                  a->type, (long long) a->m, (long long) a->n, (long long) a->k);
@@ -57,16 +94,20 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
         g.ldy[0] = a->y_row_stride;
         g.k = a->k; g.ncols = (int) a->n; g.x = a->x; g.ldx = a->x_row_stride;
         g.flavour = a->flavour; g.pdl = pdl; g.xq_out = pl;
-        if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, s);
+        if (peer) g.peer = *peer;
+        if (b200_gemv_stream_wants(g, a->algo == 3)) return b200_gemv_stream_launch(g, s);
     }
     B200_REQUIRE(a->algo != 3, "b200_mul_mat: streaming GEMV forced but the call is not eligible (type %d m=%lld n=%lld k=%lld)",
                  a->type, (long long) a->m, (long long) a->n, (long long) a->k);
 
     // (3) + (1): quantise activations into the workspace planes, then register GEMV in column groups of <= 8
+    if (peer && peer->wait) B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, s, false, *peer));
     if (!(a->flags & B200_MM_X_PREQUANTISED)) {
         int rc = b200_act_quant_planes(act, a->flavour, a->x, a->x_row_stride, pl, a->n, a->k, s, pdl);
         if (rc) return rc;
     }
+    B200_REQUIRE(!peer || fast, "b200_mul_mat_gather: the row-split exchange needs the plane layout (type %d m=%lld k=%lld)", a->type,
+                 (long long) a->m, (long long) a->k);
     for (int64_t c0 = 0; c0 < a->n; c0 += 8) {
         const int nc = (int) (a->n - c0 < 8 ? a->n - c0 : 8);
         int rc;
@@ -78,6 +119,7 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
             g.act_block = pl.block;
             g.y = a->y + c0 * a->y_row_stride; g.ldy = a->y_row_stride;
             g.pdl = pdl;
+            if (peer) { g.peer = *peer; g.peer.wait = 0; g.peer.signal = peer->signal && c0 + 8 >= a->n; }
             rc = b200_gemv_launch(a->type, g, nc, 1, a->reserved, s);
         } else {
             GemvGenericArgs g = {};
@@ -94,6 +136,32 @@ int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) {
         if (rc) return rc;
     }
     return 0;
+}
+
+int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) { return mul_mat_impl(a, (cudaStream_t) stream, nullptr); }
+
+// do `count` nodes that read the same X all take the GEMM, or all take the quantiser + register GEMV with the same activation
+// format? Then the first call converts X into the common workspace and the others reuse it (B200_MM_X_PREQUANTISED).
+static bool group_shares_x(const b200_mul_mat_args * args, int count) {
+    const b200_mul_mat_args & a0 = args[0];
+    if (!a0.workspace || count < 2) return false;
+    int path0 = -1;
+    for (int i = 0; i < count; ++i) {
+        const b200_mul_mat_args & a = args[i];
+        if (!(a.x == a0.x && a.n == a0.n && a.k == a0.k && a.x_row_stride == a0.x_row_stride && a.workspace == a0.workspace &&
+              a.flavour == a0.flavour && a.algo == 0 && b200_type_is_weight(a.type) && !(a.flags & B200_MM_X_PREQUANTISED))) return false;
+        const bool fast = planes_fast_path(a.type, a.layout, a.m, a.k, a.w, a.w_row_stride);
+        int path = 2;                                                         // quantiser + register / generic GEMV
+        if (fast && b200_gemm_wants(a.type, a.m, a.n, a.k, false)) path = 0;  // tensor-core GEMM
+        else if (fast && a.n <= 4) {
+            GemvGroup g = {};
+            g.count = 1; g.type[0] = a.type; g.w[0] = a.w; g.m[0] = a.m; g.k = a.k; g.ncols = (int) a.n;
+            if (b200_gemv_stream_wants(g)) path = 1;                          // fused kernel: quantises for itself
+        }
+        if (path == 1 || b200_act_type(a.type) != b200_act_type(a0.type)) return false;
+        if (path0 < 0) path0 = path; else if (path != path0) return false;
+    }
+    return true;
 }
 
 // several MUL_MAT nodes that read the same X (Q/K/V, gate/up): one streaming launch when eligible
@@ -119,20 +187,111 @@ int b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t 
             g.xq_out = xq_planes_carve(a0.workspace, act, a0.n, a0.k);
         if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, (cudaStream_t) stream);
     }
-    // not groupable into one launch: one call per node. Prefill nodes that all take the GEMM share the fp16 copy of X.
-    bool share_x = a0.n > 8 && a0.workspace != nullptr;
-    for (int i = 0; i < count && share_x; ++i) {
-        const b200_mul_mat_args & a = args[i];
-        share_x = a.x == a0.x && a.n == a0.n && a.k == a0.k && a.x_row_stride == a0.x_row_stride && a.workspace == a0.workspace &&
-                  a.algo == 0 && b200_type_is_weight(a.type) && planes_fast_path(a.type, a.layout, a.m, a.k, a.w, a.w_row_stride) &&
-                  b200_gemm_wants(a.type, a.m, a.n, a.k, false);
-    }
+    // not groupable into one launch: one call per node; the nodes share the converted X (fp16 copy for the GEMM, int8 planes for
+    // the register GEMV) when they all take the same of those two paths
+    const bool share_x = group_shares_x(args, count);
     for (int i = 0; i < count; ++i) {
         b200_mul_mat_args a = args[i];
         if (share_x && i > 0) a.flags |= B200_MM_X_PREQUANTISED;
-        int rc = b200_mul_mat(&a, stream);
+        int rc = mul_mat_impl(&a, (cudaStream_t) stream, nullptr);
         if (rc) return rc;
     }
+    return 0;
+}
+
+
+// B200_PEER_DEBUG (timing experiments only, results wrong): 1 = nobody waits, 2 = nobody announces
+static int peer_debug_flags() { static const int v = [] { const char * e = getenv("B200_PEER_DEBUG"); return e ? atoi(e) : 0; }(); return v; }
+
+// row slices of `count` nodes that read the same X + the exchange fused into the kernels (include/b200_mm.h)
+int b200_mul_mat_gather(const b200_mul_mat_args * args, int count, const b200_row_gather * gt, b200_stream_t stream) {
+    cudaStream_t s = (cudaStream_t) stream;
+    B200_REQUIRE(args && count >= 1 && gt, "b200_mul_mat_gather: no arguments");
+    B200_REQUIRE(gt->world >= 2 && gt->world <= B200_MAX_PEERS && gt->rank >= 0 && gt->rank < gt->world && gt->sync && gt->step &&
+                 gt->seq >= 0 && gt->seq < gt->calls_per_step && gt->peer_delta[gt->rank] == 0,
+                 "b200_mul_mat_gather: bad descriptor (world %d rank %d seq %lld/%lld)", gt->world, gt->rank, (long long) gt->seq, (long long) gt->calls_per_step);
+    PeerGather p = {};
+    p.world = gt->world; p.rank = gt->rank;
+    for (int g = 0; g < gt->world; ++g) p.delta[g] = gt->peer_delta[g];
+    p.sync = (unsigned long long *) gt->sync; p.step = (const unsigned long long *) gt->step;
+    p.seq = (unsigned long long) gt->seq; p.calls = (unsigned long long) gt->calls_per_step;
+
+    const int peer_debug = peer_debug_flags();
+    const int dbg_wait = (peer_debug & 1) ? 0 : 1, dbg_signal = (peer_debug & 2) ? 0 : 1;
+    // ranks whose slice of a matrix is empty still take part in the exchange
+    b200_mul_mat_args live[B200_MAX_GROUP];
+    int nlive = 0;
+    B200_REQUIRE(count <= B200_MAX_GROUP, "b200_mul_mat_gather: at most %d nodes per call", B200_MAX_GROUP);
+    for (int i = 0; i < count; ++i) if (args[i].m > 0 && args[i].n > 0) live[nlive++] = args[i];
+    if (nlive == 0) {
+        p.signal = 1;
+        B200_CHECK(b200_launch(peer_signal_kernel, dim3(1), dim3(32), 0, s, false, p));
+        return 0;
+    }
+    const b200_mul_mat_args & a0 = live[0];
+    bool same = a0.n <= 4 && a0.workspace != nullptr;
+    for (int i = 0; i < nlive && same; ++i) {
+        const b200_mul_mat_args & a = live[i];
+        same = a.w && a.x && a.y && a.x == a0.x && a.n == a0.n && a.k == a0.k && a.x_row_stride == a0.x_row_stride &&
+               a.flavour == a0.flavour && a.algo == 0 && b200_type_is_weight(a.type) && a.k % b200_block_elems(a.type) == 0 &&
+               !(a.flags & B200_MM_X_PREQUANTISED) && planes_fast_path(a.type, a.layout, a.m, a.k, a.w, a.w_row_stride);
+    }
+    if (same) {
+        GemvGroup g = {};
+        g.count = nlive;
+        for (int i = 0; i < nlive; ++i) { g.type[i] = live[i].type; g.w[i] = live[i].w; g.m[i] = live[i].m; g.y[i] = live[i].y; g.ldy[i] = live[i].y_row_stride; }
+        g.k = a0.k; g.ncols = (int) a0.n; g.x = a0.x; g.ldx = a0.x_row_stride;
+        g.flavour = a0.flavour; g.pdl = (a0.flags & B200_MM_PDL) != 0;
+        g.peer = p; g.peer.wait = dbg_wait; g.peer.signal = dbg_signal;
+        if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, s);
+    }
+    // one node at a time: the first waits, the last announces; the nodes share the converted X where they can
+    const bool share_x = group_shares_x(live, nlive);
+    for (int i = 0; i < nlive; ++i) {
+        b200_mul_mat_args a = live[i];
+        if (share_x && i > 0) a.flags |= B200_MM_X_PREQUANTISED;
+        PeerGather pi = p;
+        pi.wait = (i == 0) && dbg_wait; pi.signal = (i == nlive - 1) && dbg_signal;
+        int rc = mul_mat_impl(&a, s, &pi);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int b200_row_gather_wait(const b200_row_gather * gt, b200_stream_t stream) {
+    B200_REQUIRE(gt && gt->world >= 2 && gt->world <= B200_MAX_PEERS && gt->sync && gt->step && gt->seq >= 0 && gt->seq <= gt->calls_per_step,
+                 "b200_row_gather_wait: bad descriptor");
+    if (peer_debug_flags()) return 0;
+    PeerGather p = {};
+    p.world = gt->world; p.rank = gt->rank;
+    p.sync = (unsigned long long *) gt->sync; p.step = (const unsigned long long *) gt->step;
+    p.seq = (unsigned long long) gt->seq; p.calls = (unsigned long long) gt->calls_per_step;
+    B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, (cudaStream_t) stream, false, p));
+    return 0;
+}
+
+static __global__ void step_kernel(unsigned long long * step) { if (threadIdx.x == 0) *step += 1ull; }
+int b200_row_gather_step(uint64_t * step, b200_stream_t stream) {
+    B200_REQUIRE(step, "b200_row_gather_step: null pointer");
+    B200_CHECK(b200_launch(step_kernel, dim3(1), dim3(32), 0, (cudaStream_t) stream, false, (unsigned long long *) step));
+    return 0;
+}
+
+int b200_ipc_export(const void * dev_ptr, void * handle64) {
+    B200_REQUIRE(dev_ptr && handle64, "b200_ipc_export: null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    B200_CHECK(cudaIpcGetMemHandle((cudaIpcMemHandle_t *) handle64, const_cast<void *>(dev_ptr)));
+    return 0;
+}
+int b200_ipc_import(const void * handle64, void ** dev_ptr) {
+    B200_REQUIRE(dev_ptr && handle64, "b200_ipc_import: null pointer");
+    cudaIpcMemHandle_t h; memcpy(&h, handle64, sizeof h);
+    B200_CHECK(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int b200_ipc_close(void * dev_ptr) {
+    B200_REQUIRE(dev_ptr, "b200_ipc_close: null pointer");
+    B200_CHECK(cudaIpcCloseMemHandle(dev_ptr));
     return 0;
 }
 

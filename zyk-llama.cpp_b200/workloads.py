@@ -90,6 +90,9 @@ MODELS = {
                                 n_expert=8, n_used=2),
     # 70B: attn_v would be Q5_K in llama-quantize's recipe (llama-quant.cpp:305-310); the synthetic file
     # pins it to Q6_K/Q4_K via --tensor-type so that only the five named formats occur
+    # small shapes for the multi-GPU parity check (tools/rowsplit_check.py): uneven vocab split, Q6_K rows, k = 3584
+    "tiny-q4_k_m": dict(n_layer=4, n_embd=1024, n_ff=3584, n_head=8, n_kv=2, n_vocab=5000, ftype="q4_k_m"),
+    "tiny-moe-q4_k_m": dict(n_layer=2, n_embd=1024, n_ff=1792, n_head=8, n_kv=2, n_vocab=3000, ftype="q4_k_m", n_expert=8, n_used=2),
     "llama-3-70b-q4_k_m": dict(n_layer=80, n_embd=8192, n_ff=28672, n_head=64, n_kv=8, n_vocab=128256, ftype="q4_k_m"),
 }
 
