@@ -11,12 +11,12 @@
  *
  * Names obtainable through reg->iface.get_proc_address (ggml/include/ggml-backend.h:196-212):
  *     "ggml_backend_get_features"        -> ggml_backend_get_features_t
- *     "ggml_backend_split_buffer_type"   -> ggml_backend_split_buffer_type_t   (row split, -sm row)
- *     "ggml_backend_set_n_threads"       -> NULL (no host threads on this path)
+ *     anything else                      -> NULL ("ggml_backend_set_n_threads": no host threads on this path;
+ *                                           "ggml_backend_split_buffer_type": not built yet -- row split across GPUs is
+ *                                           available one process per GPU through b200_mul_mat_gather, b200_mm.h)
  *
- * Environment switches read by the plugin:
+ * Environment switch read by the plugin:
  *     GGML_B200_REPACK=0     keep weights in canonical ggml layout (default: repack whole-tensor writes)
- *     GGML_B200_GRAPHS=0     do not cache CUDA graphs in graph_compute
  */
 #ifndef GGML_B200_H
 #define GGML_B200_H

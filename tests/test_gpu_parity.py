@@ -2,6 +2,8 @@
 vectors of the reference. Bit-exact for activation quantisation and repack; MUL_MAT within the
 reference's own tolerance (NMSE <= 5e-4, tests/test-backend-ops.cpp:3716-3718, 3852-3854) -- and
 in fact ~1e-12 for the decode path, because the integer arithmetic is the CPU's."""
+from pathlib import Path
+
 import numpy as np
 import pytest
 import torch
@@ -10,6 +12,7 @@ from conftest import nmse
 from oracle.oracle import (WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q6_K, Q8_REF, Q8_X86, random_blocks)
 
 pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
 MAX_NMSE = 5e-4          # the reference's tolerance for MUL_MAT / MUL_MAT_ID
 DECODE_NMSE = 1e-10      # what the dp4a decode path actually achieves against the CPU arithmetic
 
@@ -355,3 +358,19 @@ def test_gemm_split_k(b200, orc, monkeypatch, ks):
         b200.mul_mat(t, b200.repack(t, dev(w).reshape(-1), m, k), dev(x), m, layout=b200.LAYOUT_PLANES, algo=2, y=y[:, :m])
         assert nmse(y[:, :m].cpu().numpy(), orc.mul_mat_f64(t, w, x)) < GEMM_VS_TRUTH
         assert torch.all(y[:, m:] == 5.0)
+
+
+# ------------------------------------------------------------------------------------------------
+# row split over two GPUs: only where the box has them
+# ------------------------------------------------------------------------------------------------
+def test_row_split_two_gpus_matches_single_gpu_chain(b200):
+    """tools/rowsplit_check.py under torchrun: fused exchange and NCCL all-gather, eager and graph replay, decode and prefill,
+    dense and MoE, every activation buffer against the single-GPU chain built from the same seeded weights."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", str(ROOT / "tools" / "rowsplit_check.py")],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "ROWSPLIT_CHECK OK" in r.stdout, r.stdout[-3000:]
