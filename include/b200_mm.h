@@ -159,6 +159,22 @@ B200_API int    b200_mul_mat(const b200_mul_mat_args * args, b200_stream_t strea
  * Counterpart of the reference's fused gate/up GEMV (ggml_cuda_should_fuse_mul_mat_vec_q, ggml-cuda.cu:2144-2180). */
 B200_API int    b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t stream);
 
+/* ---- (1) decode CHAIN: a sequence of DEPENDENT MUL_MAT groups in one persistent launch ----------
+ * replaces the per-node loop of graph_compute (ggml_backend_sched_compute_splits, ggml-backend.cpp:1443-1620, over
+ * ggml_compute_forward_mul_mat, ggml-cpu.c:1227-1427) for the decode case (n <= 4): `nodes` lists the MUL_MAT nodes in
+ * graph order, `group_sizes[g]` consecutive nodes form group g (they read the same X: wq/wk/wv, ffn_gate/ffn_up). Group g + 1
+ * starts only when every row of group g has been written, exactly as if the groups had been issued one after the other
+ * with b200_mul_mat_group on one stream, so a group may read what an earlier group wrote. One CTA per SM stays resident, the
+ * weight stream (bulk copies into a shared-memory ring) runs ahead across the group boundaries. Pointers, shapes and
+ * strides are baked in at create time (like a captured CUDA graph); workspace/algo/PDL fields are ignored.
+ * Requirements (b200_chain_supported): plane layout (or canonical Q4_K), k % 256 == 0, the same n <= 4 everywhere. */
+typedef struct b200_chain * b200_chain_t;
+B200_API int          b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups);
+B200_API b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups); /* NULL on failure */
+B200_API int          b200_chain_launch(b200_chain_t chain, b200_stream_t stream);   /* asynchronous, CUDA-graph capturable */
+B200_API int          b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * smem_bytes, int * n_groups);
+B200_API int          b200_chain_destroy(b200_chain_t chain);
+
 /* ---- (4) MUL_MAT_ID (ggml.c:3217-3243; CPU driver ggml-cpu.c:1500-1676) ----------------------
  *   as   : n_as expert matrices, each m rows x k, `as_expert_stride` bytes apart
  *   b    : f32 [n_tokens][nb1][k] (nb1 == n_used, or 1 = same row for every slot), strides in elements

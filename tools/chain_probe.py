@@ -1,0 +1,65 @@
+"""GPU probe: decode step (tg, N = 1) of a model's MUL_MAT chain, persistent chain kernel vs per-node launches.
+Usage: python tools/chain_probe.py [--model llama-3-8b-q4_k_m] [--steps 64] [--layers L]"""
+import argparse
+import sys
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+from __graft_entry__ import load_pkg  # noqa: E402
+
+b = load_pkg()
+from zyk_llama_cpp_b200 import workloads as W  # noqa: E402
+from zyk_llama_cpp_b200.chain import MatMulChain  # noqa: E402
+
+
+def run(ops, persistent, steps):
+    ch = MatMulChain(ops, 1, persistent=persistent)
+    ch.capture()
+    for _ in range(5):
+        ch.step()
+    ch.stream.synchronize()
+    e0, e1 = b.Event(0), b.Event(0)
+    e0.record(ch.stream)
+    for _ in range(steps):
+        ch.step()
+    e1.record(ch.stream)
+    ch.stream.synchronize()
+    ms = e0.elapsed_ms(e1) / steps
+    info = ch.decode_chain.info() if ch.decode_chain is not None else None
+    out = {k: v.clone() for k, v in ch.bufs.items()}
+    ch.close()
+    return ms, info, out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="llama-3-8b-q4_k_m")
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--layers", type=int, default=0)
+    ap.add_argument("--only", default="both", choices=["both", "chain", "nodes"])
+    a = ap.parse_args()
+    cfg = dict(W.MODELS[a.model])
+    if a.layers:
+        cfg["n_layer"] = a.layers
+    ops = W.llama_dense(**cfg)
+    gb = W.tg_bytes(ops) / 1e9
+    res = {}
+    if a.only in ("both", "chain"):
+        ms, info, o1 = run(ops, True, a.steps)
+        res["chain"] = o1
+        print(f"persistent chain : {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms:7.1f} GB/s  {info}", flush=True)
+    if a.only in ("both", "nodes"):
+        ms, _, o2 = run(ops, False, a.steps)
+        res["nodes"] = o2
+        print(f"per-node launches: {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms:7.1f} GB/s", flush=True)
+    if len(res) == 2:
+        for k in res["chain"]:
+            x, y = res["chain"][k].double(), res["nodes"][k].double()
+            print(f"  {k:7s} nmse chain vs nodes {float(((x - y) ** 2).sum() / (y ** 2).sum().clamp_min(1e-300)):.3e}")
+
+
+if __name__ == "__main__":
+    main()

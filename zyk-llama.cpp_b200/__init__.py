@@ -34,6 +34,8 @@ from .binding import (  # noqa: F401
     mul_mat,
     mul_mat_id,
     mul_mat_group,
+    MulMatArgs,
+    DecodeChain,
     mul_mat_workspace,
     Stream,
     Event,

@@ -77,6 +77,11 @@ _sig("b200_unrepack", C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_vo
 _sig("b200_mul_mat_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64)
 _sig("b200_mul_mat", C.c_int, C.POINTER(MulMatArgs), C.c_void_p)
 _sig("b200_mul_mat_group", C.c_int, C.POINTER(MulMatArgs), C.c_int, C.c_void_p)
+_sig("b200_chain_supported", C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
+_sig("b200_chain_create", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
+_sig("b200_chain_launch", C.c_int, C.c_void_p, C.c_void_p)
+_sig("b200_chain_info", C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))
+_sig("b200_chain_destroy", C.c_int, C.c_void_p)
 _sig("b200_mul_mat_id_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64)
 _sig("b200_mul_mat_id", C.c_int, C.POINTER(MulMatIdArgs), C.c_void_p)
 _sig("b200_stream_create", C.c_void_p, C.c_int)
@@ -271,3 +276,45 @@ def mul_mat_group(ts, ws_, x: torch.Tensor, ms, *, layout=LAYOUT_PLANES, flavour
                             ws, need - (ws - workspace.data_ptr()), flavour, 0, flags, 0)
     _check(lib.b200_mul_mat_group(arr, len(ts), _s(stream)))
     return ys
+
+
+class DecodeChain:
+    """b200_chain_*: a sequence of dependent MUL_MAT groups (decode, n <= 4) as ONE persistent launch.
+    `groups` is a list of lists of MulMatArgs (nodes of one group read the same X)."""
+
+    def __init__(self, device: int, groups):
+        flat = [a for g in groups for a in g]
+        self._args = (MulMatArgs * len(flat))(*flat)
+        self._sizes = (C.c_int32 * len(groups))(*[len(g) for g in groups])
+        self.n_groups = len(groups)
+        self.handle = lib.b200_chain_create(device, self._args, self._sizes, len(groups))
+        if not self.handle:
+            raise B200Error(lib.b200_last_error().decode())
+
+    @staticmethod
+    def supported(groups) -> bool:
+        flat = [a for g in groups for a in g]
+        if not flat:
+            return False
+        args = (MulMatArgs * len(flat))(*flat)
+        sizes = (C.c_int32 * len(groups))(*[len(g) for g in groups])
+        return bool(lib.b200_chain_supported(args, sizes, len(groups)))
+
+    def info(self) -> dict:
+        v = [C.c_int() for _ in range(4)]
+        _check(lib.b200_chain_info(self.handle, *[C.byref(x) for x in v]))
+        return dict(ctas=v[0].value, stage_bytes=v[1].value, smem_bytes=v[2].value, n_groups=v[3].value)
+
+    def launch(self, stream=None):
+        _check(lib.b200_chain_launch(self.handle, _s(stream)))
+
+    def close(self):
+        if self.handle:
+            lib.b200_chain_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

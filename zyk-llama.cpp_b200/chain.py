@@ -22,7 +22,8 @@ from .workloads import MatMul, buffer_widths, random_weight, row_bytes
 
 class MatMulChain:
     def __init__(self, ops: list[MatMul], n: int, device: int = 0, *, seed: int = 1234, rowsplit=None, fused_exchange: bool = True,
-                 pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None, grouping: bool = True):
+                 pdl: bool = True, layout: int = B.LAYOUT_PLANES, stream: "B.Stream | None" = None, grouping: bool = True,
+                 persistent: bool = True):
         self.ops, self.n, self.device = ops, n, device
         self.rowsplit = rowsplit                      # rowsplit.RowSplit or None (single GPU)
         # row split: exchange fused into the kernels over a symmetric arena (b200_mul_mat_gather), or one NCCL all-gather per node
@@ -92,6 +93,12 @@ class MatMulChain:
         self.ws_size = self.workspace.numel() - (self.ws_ptr - self.workspace.data_ptr())
 
         self.calls = self._build_calls()
+        # decode on one GPU: the whole pass as ONE persistent launch (b200_chain_*), when every node is eligible
+        self.decode_chain = None
+        if persistent and world == 1 and all(c[0] is B.lib.b200_mul_mat_group for c in self.calls):
+            groups = [list(c[1]) for c in self.calls]
+            if B.DecodeChain.supported(groups):
+                self.decode_chain = B.DecodeChain(device, groups)
         self.graph = None
         self.kernels_per_step = 0
         torch.cuda.synchronize(self.dev)
@@ -141,6 +148,9 @@ class MatMulChain:
     def issue(self):
         """enqueue one forward pass' worth of MUL_MAT nodes on self.stream (no host sync)"""
         h = self.stream.handle
+        if self.decode_chain is not None:
+            self.decode_chain.launch(self.stream)
+            return
         if self.fused_exchange:
             B._check(B.lib.b200_row_gather_step(self.arena.step_ptr, h))
         for i, (fn, a, ops, ys, _ws) in enumerate(self.calls):

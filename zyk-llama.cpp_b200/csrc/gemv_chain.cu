@@ -1,0 +1,668 @@
+// gemv_chain.cu -- (1) decode GEMV, chain version: a whole sequence of DEPENDENT MUL_MAT groups (every quantised matmul of
+// one decode token: wq/wk/wv -> wo -> gate/up -> down -> ... -> output) in ONE persistent launch.
+//
+// Reference counterparts: the node loop of ggml_backend_sched_compute_splits -> graph_compute (ggml-backend.cpp:1443-1620) over
+// ggml_compute_forward_mul_mat + ggml_vec_dot_* (ggml-cpu/ggml-cpu.c:1227-1427, ggml-cpu/quants.c:115-1181); on the CUDA side
+// quantize_q8_1 + mul_mat_vec_q per node (ggml-cuda/quantize.cu:4-73, mmvq.cu:141-335).
+//
+// Why: one decode token is ~130 dependent GEMVs of 1.5-10 us each at HBM speed. As separate launches every one of them pays a
+// fill (first DRAM round trip, X quantisation) and a drain (last rows) during which HBM idles, and the register-streaming
+// kernels spend ~88 warp instructions per 512 weight bytes (issue bound). Here
+//   * one CTA per SM stays resident for the whole chain. Weights do not depend on activations, so each half-CTA ("group" of
+//     8 warps = one virtual consumer, VC) keeps a ring of NS bulk copies (cp.async.bulk global -> shared, mbarrier
+//     complete_tx, L2 evict-first) in flight that runs AHEAD across node boundaries: while the grid waits for the X of node
+//     i + 1, the weights of node i + 1 are already landing in shared memory;
+//   * a node boundary is one arrival counter in global memory (red.release.gpu / ld.acquire.gpu), then every CTA quantises
+//     the new X into its own shared memory (quant_chunk256: bit for bit quantize_row_q8_K / q8_0 of the reference);
+//   * shared-memory staging frees the lane <-> data mapping from coalescing: Q4_K is processed ONE 256-BLOCK PER LANE (the 144 B
+//     block stride is bank-conflict free), so d/dmin, the 12 scale bytes and the min correction are decoded once per 256
+//     weights instead of once per 32, and the min term is 4 dp2a against per-32 activation sums; Q6_K keeps 8 lanes per block
+//     but rebuilds the 6-bit values without shifts (nibble and 2-bit fields are masked in place and the power-of-two factor is
+//     taken out of the int32 sum exactly). The integer arithmetic per block is the CPU's, value for value; only the fp32
+//     summation order differs (fixed, so results are deterministic).
+// Work split: per node the rows of the group's matrices are cut by BYTES into one contiguous share per VC (host, at create
+// time) and each share into items that fit a ring stage; an item is 1 (Q4_K) to 4 (Q6_K planes) bulk copies.
+// Algorithmic bytes per launch = sum over all nodes of m * row_size(type, k); HBM bound.
+#include "gemv_frag.cuh"
+#include "actquant.cuh"
+#include "sm100.cuh"
+
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+namespace {
+using namespace sm100;
+
+constexpr int CH_GROUPS = 2;                 // virtual consumers per CTA
+constexpr int CH_GWARPS = 8;                 // warps per group
+constexpr int CH_GTHREADS = CH_GWARPS * 32;
+constexpr int CH_THREADS = CH_GROUPS * CH_GTHREADS;
+constexpr int CH_NS = 3;                     // ring stages per group
+constexpr int XU_BYTES = 336;                // one 256-element unit of quantised X in shared memory (bank-conflict-free stride)
+constexpr int XU_BS16 = 256, XU_BS32 = 288, XU_D = 304;
+constexpr int CH_SMEM_TOTAL = 227 * 1024;
+constexpr int CH_MAX_COLS = 4;
+
+struct ChainMatD {
+    const uint8_t * w;        // plane layout (canonical for Q4_K)
+    float * y; long long ldy;
+    int m, type, upr;         // rows, weight type, 256-element units per row
+    int pad;
+};
+struct ChainNodeD {
+    const float * x; long long ldx;
+    int k, act_block, flavour, pad;
+};
+struct ChainItemD { int mat, row0, nrows, pad; };
+
+struct ChainArgs {
+    const ChainNodeD * nodes;
+    const ChainMatD * mats;
+    const ChainItemD * items;
+    const int * node_off;     // [vc][n_nodes + 1] -> index into items (items are VC-major, node-ordered)
+    unsigned * counter;       // arrivals: every CTA adds one per finished node (zeroed before the launch)
+    int n_nodes;
+    int stage_bytes;          // bytes per ring stage
+    int max_units;            // stride of the partial-sum buffers
+    int x_bytes;              // shared memory reserved for the quantised X
+};
+
+// bytes per 256-element unit in plane p of the plane layout (repack.cu); 0 terminates
+__host__ __device__ inline int plane_bytes(int type, int p) {
+    switch (type) {
+        case B200_TYPE_Q4_K:   return p == 0 ? 144 : 0;
+        case B200_TYPE_Q6_K:   return p == 0 ? 128 : p == 1 ? 64 : p == 2 ? 16 : p == 3 ? 2 : 0;
+        case B200_TYPE_IQ4_XS: return p == 0 ? 128 : p == 1 ? 8 : 0;
+        case B200_TYPE_Q4_0:   return p == 0 ? 128 : p == 1 ? 16 : 0;
+        case B200_TYPE_Q8_0:   return p == 0 ? 256 : p == 1 ? 16 : 0;
+    }
+    return 0;
+}
+__host__ __device__ inline int unit_bytes(int type) { int s = 0; for (int p = 0; p < 4; ++p) s += plane_bytes(type, p); return s; }
+
+__device__ __forceinline__ uint4 lds16(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint2 lds8(uint32_t a) { uint2 r; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(a)); return r; }
+__device__ __forceinline__ uint32_t lds4(uint32_t a) { uint32_t r; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(a)); return r; }
+__device__ __forceinline__ uint16_t lds2(uint32_t a) { uint16_t r; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(a)); return r; }
+__device__ __forceinline__ int ldss1(uint32_t a) { int r; asm volatile("ld.shared.s8 %0, [%1];" : "=r"(r) : "r"(a)); return r; }
+__device__ __forceinline__ float ldsf(uint32_t a) { float r; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(a)); return r; }
+__device__ __forceinline__ void sts8(uint32_t a, uint32_t x, uint32_t y) { asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(a), "r"(x), "r"(y) : "memory"); }
+__device__ __forceinline__ void sts2(uint32_t a, uint16_t x) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "h"(x) : "memory"); }
+__device__ __forceinline__ void stsf(uint32_t a, float x) { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(x) : "memory"); }
+
+// X changes while the kernel runs (it is the Y of an earlier node): read it at L2, never through the non-coherent path
+__device__ __forceinline__ float4 ldcg16(const float * p) {
+    float4 r;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ float ldcg4(const float * p) { float r; asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory"); return r; }
+
+__device__ __forceinline__ void group_bar(int grp) { asm volatile("bar.sync %0, %1;" :: "r"(grp + 1), "n"(CH_GTHREADS) : "memory"); }
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+// 1-D bulk copy global -> shared, completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
+
+// position of 16-byte chunk `ch` (0..15) of a unit's int8 quants: the upper half is rotated by four chunks so that the eight
+// lanes of a Q6_K block (chunks {0..3, 8..11} or {4..7, 12..15}) hit eight different bank groups
+__host__ __device__ constexpr int xpos(int ch) { return ch < 8 ? ch : 8 + ((ch + 4) & 7); }
+
+__device__ __forceinline__ int dot16_us(const uint4 & a, const uint4 & b) {
+    int s = dp4a_us(a.x, b.x, 0); s = dp4a_us(a.y, b.y, s); s = dp4a_us(a.z, b.z, s); s = dp4a_us(a.w, b.w, s); return s;
+}
+
+// ---- activation quantiser into the shared-memory unit layout ---------------------------------------------------------
+//   unit (col, u): [qs 256 B, chunks placed by xpos][bs16: 16 x i16][bs32: 8 x i16][d: 8 x f32 (Q8_K uses d[0])]
+template <int NCOLS>
+__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
+    const int upr = nd.k >> 8;
+    const int total = NCOLS * upr;
+    constexpr int NW = CH_THREADS / 32, QU = 4;
+    for (int c0 = warp; c0 < total; c0 += NW * QU) {
+        float v[QU][8];
+#pragma unroll
+        for (int q = 0; q < QU; ++q) {
+            const int ci = c0 + q * NW;
+            if (ci < total) {
+                const int col = ci / upr, u = ci - col * upr;
+                const float * xr = nd.x + (long long) col * nd.ldx + u * 256 + lane * 8;
+                if ((((uintptr_t) xr) & 15) == 0) {
+                    const float4 lo = ldcg16(xr), hi = ldcg16(xr + 4);
+                    v[q][0] = lo.x; v[q][1] = lo.y; v[q][2] = lo.z; v[q][3] = lo.w; v[q][4] = hi.x; v[q][5] = hi.y; v[q][6] = hi.z; v[q][7] = hi.w;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[q][j] = ldcg4(xr + j);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < QU; ++q) {
+            const int ci = c0 + q * NW;
+            if (ci < total) {
+                int qq[8]; float dval, sval;
+                if (nd.act_block == 256)               quant_chunk256<B200_TYPE_Q8_K, B200_Q8_X86>(v[q], lane, qq, dval, sval);
+                else if (nd.flavour == B200_Q8_X86)    quant_chunk256<B200_TYPE_Q8_0, B200_Q8_X86>(v[q], lane, qq, dval, sval);
+                else                                   quant_chunk256<B200_TYPE_Q8_0, B200_Q8_REF>(v[q], lane, qq, dval, sval);
+                int s8 = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s8 += (int) (int8_t) qq[j];
+                const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
+                const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+                const uint32_t w0 = (qq[0] & 0xff) | ((qq[1] & 0xff) << 8) | ((qq[2] & 0xff) << 16) | ((uint32_t) (qq[3] & 0xff) << 24);
+                const uint32_t w1 = (qq[4] & 0xff) | ((qq[5] & 0xff) << 8) | ((qq[6] & 0xff) << 16) | ((uint32_t) (qq[7] & 0xff) << 24);
+                const uint32_t ub = xs + (uint32_t) ci * XU_BYTES;
+                const int ch = lane >> 1;
+                const int pc = ch < 8 ? ch : 8 + ((ch + 4) & 7);
+                sts8(ub + pc * 16 + (lane & 1) * 8, w0, w1);
+                if ((lane & 1) == 0) sts2(ub + XU_BS16 + (lane >> 1) * 2, (uint16_t) (int16_t) s16);
+                if ((lane & 3) == 0) sts2(ub + XU_BS32 + (lane >> 2) * 2, (uint16_t) (int16_t) s32);
+                if (nd.act_block == 256) { if (lane == 0) stsf(ub + XU_D, dval); }
+                else if ((lane & 3) == 0) stsf(ub + XU_D + (lane >> 2) * 4, dval);
+            }
+        }
+    }
+}
+
+// ---- Q4_K: one 256-block per lane --------------------------------------------------------------------------------------
+// block bytes (ggml-common.h:295-306): d, dmin (fp16), scales[12], qs[128]; arithmetic of ggml_vec_dot_q4_K_q8_K
+// (ggml-cpu/quants.c:550-625) with get_scale_min_k4 (ggml-quants.c:703-711) done for the eight sub-blocks at once
+template <int NCOLS>
+__device__ __forceinline__ void unit_q4k(uint32_t wb, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint4 hdr = lds16(wb);
+    const uint32_t sc03 = hdr.y & 0x3f3f3f3fu, mn03 = hdr.z & 0x3f3f3f3fu;
+    const uint32_t sc47 = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+    const uint32_t mn47 = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+    const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
+    int isum[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) isum[c] = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 qa = lds16(wb + 16 + 32 * j), qb = lds16(wb + 32 + 32 * j);
+        const uint4 la = and4(qa, 0x0f0f0f0fu), lb = and4(qb, 0x0f0f0f0fu);
+        // high nibbles stay in place (16 x nibble as an unsigned byte); the factor leaves the int32 sum with an exact shift
+        const uint4 ha = and4(qa, 0xf0f0f0f0u), hb = and4(qb, 0xf0f0f0f0u);
+        const uint32_t scw = j < 2 ? sc03 : sc47;
+        const int s0 = (int) ((scw >> (16 * (j & 1))) & 0xffu), s1 = (int) ((scw >> (16 * (j & 1) + 8)) & 0xffu);
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+            const uint4 x0 = lds16(xc + xpos(4 * j) * 16), x1 = lds16(xc + xpos(4 * j + 1) * 16);
+            const uint4 x2 = lds16(xc + xpos(4 * j + 2) * 16), x3 = lds16(xc + xpos(4 * j + 3) * 16);
+            const int dlo = dot16(la, x0) + dot16(lb, x1);
+            const int dhi = dot16_us(ha, x2) + dot16_us(hb, x3);
+            isum[c] += s0 * dlo + s1 * (dhi >> 4);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+        const uint4 bs = lds16(xc + XU_BS32);              // 8 x i16: sums of 32 quants
+        int msum = __dp2a_lo((int) bs.x, (int) mn03, 0);
+        msum = __dp2a_hi((int) bs.y, (int) mn03, msum);
+        msum = __dp2a_lo((int) bs.z, (int) mn47, msum);
+        msum = __dp2a_hi((int) bs.w, (int) mn47, msum);
+        const float dx = ldsf(xc + XU_D);
+        acc[c] += dx * (dm.x * (float) isum[c] - dm.y * (float) msum);
+    }
+}
+
+// ---- Q6_K: eight lanes per 256-block, planes QL 128 | QH 64 | SC 16 | D 2 ---------------------------------------------
+// arithmetic of ggml_vec_dot_q6_K_q8_K (ggml-cpu/quants.c:705-760); lane g owns elements e0 + [0,16) and e0 + 64 + [0,16),
+// e0 = 128 (g >> 2) + 32 ((g >> 1) & 1) + 16 (g & 1) (dequantize_row_q6_K, ggml-quants.c:1762-1792)
+template <int NCOLS>
+__device__ __forceinline__ void frag_q6k(uint32_t stage, int nunits, int u, int g, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint4 ql = lds16(stage + (uint32_t) (u * 128 + 16 * g));
+    const uint4 qh = lds16(stage + (uint32_t) (nunits * 128 + u * 64 + 32 * (g >> 2) + 16 * (g & 1)));
+    const int is = 8 * (g >> 2) + (g & 3);
+    const uint32_t scb = stage + (uint32_t) (nunits * 192 + u * 16 + is);
+    const int sc0 = ldss1(scb), sc1 = ldss1(scb + 4);
+    const float dw = half_bits_to_float(lds2(stage + (uint32_t) (nunits * 208 + u * 2)));
+    const int sh = g & 2;
+    const uint32_t ma = 0x03030303u << sh, mb = ma << 4;
+    const uint4 lo = and4(ql, 0x0f0f0f0fu), hi = and4(ql, 0xf0f0f0f0u);
+    const uint4 ha = and4(qh, ma), hb = and4(qh, mb);
+    const int ch0 = is, ch1 = is + 4;
+    const int p0 = ch0 < 8 ? ch0 : 8 + ((ch0 + 4) & 7), p1 = ch1 < 8 ? ch1 : 8 + ((ch1 + 4) & 7);
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+        const uint4 x0 = lds16(xc + p0 * 16), x1 = lds16(xc + p1 * 16);
+        const int bs0 = (int) (int16_t) lds2(xc + XU_BS16 + ch0 * 2), bs1 = (int) (int16_t) lds2(xc + XU_BS16 + ch1 * 2);
+        const float dx = ldsf(xc + XU_D);
+        // q6 = nibble | two bits << 4: the two-bit fields are masked in place (value h << sh resp. h << (sh + 4)) and the
+        // power of two is taken out of the int32 sums exactly
+        const int s0 = dot16(lo, x0) + (dot16(ha, x0) << (4 - sh)) - 32 * bs0;
+        const int s1 = (dot16_us(hi, x1) >> 4) + (dot16_us(hb, x1) >> sh) - 32 * bs1;
+        acc[c] += (dx * dw) * (float) (sc0 * s0 + sc1 * s1);
+    }
+}
+
+// ---- IQ4_XS / Q4_0 / Q8_0: eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ------------
+template <int TYPE> __device__ __forceinline__ void wfrag_lds(WFrag<TYPE> & f, uint32_t stage, int nunits, int u, int g);
+template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_IQ4_XS>(WFrag<B200_TYPE_IQ4_XS> & f, uint32_t stage, int nunits, int u, int g) {
+    f.q = lds16(stage + (uint32_t) (u * 128 + 16 * g));
+    f.hdr = lds8(stage + (uint32_t) (nunits * 128 + u * 8));
+}
+template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_Q4_0>(WFrag<B200_TYPE_Q4_0> & f, uint32_t stage, int nunits, int u, int g) {
+    f.q = lds16(stage + (uint32_t) (u * 128 + 16 * g));
+    f.d = lds2(stage + (uint32_t) (nunits * 128 + u * 16 + 2 * g));
+}
+template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_Q8_0>(WFrag<B200_TYPE_Q8_0> & f, uint32_t stage, int nunits, int u, int g) {
+    f.q0 = lds16(stage + (uint32_t) (u * 256 + 32 * g));
+    f.q1 = lds16(stage + (uint32_t) (u * 256 + 32 * g + 16));
+    f.d = lds2(stage + (uint32_t) (nunits * 256 + u * 16 + 2 * g));
+}
+template <int TYPE, int NCOLS>
+__device__ __forceinline__ void frag_legacy(uint32_t stage, int nunits, int u, int g, uint32_t xb, int x_col_stride, int act_block, float (&acc)[NCOLS]) {
+    WFrag<TYPE> f;
+    wfrag_lds<TYPE>(f, stage, nunits, u, g);
+    XFrag x[NCOLS];
+    const int ch0 = 2 * g, ch1 = 2 * g + 1;                // elements 32 g + [0,16) and + [16,32)
+    const int p0 = ch0 < 8 ? ch0 : 8 + ((ch0 + 4) & 7), p1 = ch1 < 8 ? ch1 : 8 + ((ch1 + 4) & 7);
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+        x[c].x0 = lds16(xc + p0 * 16); x[c].x1 = lds16(xc + p1 * 16);
+        x[c].bs0 = (int) (int16_t) lds2(xc + XU_BS16 + ch0 * 2); x[c].bs1 = (int) (int16_t) lds2(xc + XU_BS16 + ch1 * 2);
+        x[c].dx = ldsf(xc + XU_D + (act_block == 256 ? 0 : 4 * g));
+    }
+    f.template dot<NCOLS>(x, acc, g);
+}
+
+// phase A of one item for the 8-lanes-per-unit formats: partial sums per unit into `part`
+template <int TYPE, int NCOLS>
+__device__ __forceinline__ void item_lanes8(uint32_t stage, int nunits, int upr, uint32_t xs, int x_col_stride, int act_block,
+                                            uint32_t part, int max_units, int gtid) {
+    const int total = nunits * 8;
+    for (int w0 = (gtid & ~31); w0 < total; w0 += CH_GTHREADS) {
+        const int w = w0 + (gtid & 31);
+        float acc[NCOLS];
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+        const int u = w >> 3, g = w & 7;
+        if (w < total) {
+            const uint32_t xb = xs + (uint32_t) ((u % upr) * XU_BYTES);
+            if constexpr (TYPE == B200_TYPE_Q6_K) frag_q6k<NCOLS>(stage, nunits, u, g, xb, x_col_stride, acc);
+            else                                  frag_legacy<TYPE, NCOLS>(stage, nunits, u, g, xb, x_col_stride, act_block, acc);
+        }
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            float v = acc[c];
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            if (g == 0 && w < total) stsf(part + (uint32_t) (c * max_units + u) * 4, v);
+        }
+    }
+}
+
+template <int NCOLS>
+__global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = tid / CH_GTHREADS, gtid = tid % CH_GTHREADS, gwarp = gtid >> 5;
+    const int vc = blockIdx.x * CH_GROUPS + grp;
+    const int NN = a.n_nodes;
+
+    // shared memory: [mbarriers 64 B][X units][partials: groups x 2 x NCOLS x max_units f32][ring: groups x NS x stage_bytes]
+    const uint32_t base = smem_u32(smem_raw);
+    const uint32_t bars = base + (uint32_t) grp * (CH_NS * 8);
+    const uint32_t xs = base + 64;
+    const uint32_t part_bytes = (uint32_t) (NCOLS * a.max_units) * 4;
+    const uint32_t part0 = xs + (uint32_t) a.x_bytes + (uint32_t) grp * 2 * part_bytes;
+    const uint32_t ring = ((xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 127u) & ~127u) + (uint32_t) grp * CH_NS * (uint32_t) a.stage_bytes;
+
+    const int * off = a.node_off + (long long) vc * (NN + 1);
+    const int it_begin = off[0], it_end = off[NN];
+    const uint64_t policy = policy_evict_first();
+
+    auto issue = [&](int it) {                 // one thread of the group: the copies of item `it` into stage (it - it_begin) % NS
+        const ChainItemD item = a.items[it];
+        const ChainMatD & M = a.mats[item.mat];
+        const int seq = it - it_begin, st = seq % CH_NS;
+        const uint32_t dst = ring + (uint32_t) st * (uint32_t) a.stage_bytes, bar = bars + st * 8;
+        const long long nunits = (long long) item.nrows * M.upr, u0 = (long long) item.row0 * M.upr, all = (long long) M.m * M.upr;
+        mbar_arrive_expect_tx(bar, (uint32_t) (nunits * unit_bytes(M.type)));
+        long long src_off = 0; uint32_t dst_off = 0;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int pb = plane_bytes(M.type, p);
+            if (pb == 0) break;
+            bulk_g2s(dst + dst_off, M.w + src_off + u0 * pb, (uint32_t) (nunits * pb), bar, policy);
+            src_off += all * pb; dst_off += (uint32_t) (nunits * pb);
+        }
+    };
+
+    if (gtid == 0) {
+        for (int s = 0; s < CH_NS; ++s) mbar_init(bars + s * 8, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (gtid == 0) for (int it = it_begin; it < it_end && it < it_begin + CH_NS; ++it) issue(it);
+
+    int pbuf = 0;
+    for (int n = 0; n < NN; ++n) {
+        const ChainNodeD nd = a.nodes[n];
+        if (n > 0 && tid == 0) {               // X of this node is complete once every CTA has finished the previous node
+            const unsigned want = (unsigned) n * gridDim.x;
+            unsigned v; unsigned long long t0 = 0;
+            for (unsigned spin = 0;; ++spin) {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.counter) : "memory");
+                if (v >= want) break;
+                if ((spin & 4095u) == 4095u) {
+                    unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
+                }
+            }
+        }
+        __syncthreads();
+        chain_quantise_x<NCOLS>(nd, xs, warp, lane);
+        __syncthreads();
+
+        const int upr = nd.k >> 8;
+        const int x_col_stride = upr * XU_BYTES;
+        for (int it = off[n]; it < off[n + 1]; ++it) {
+            const ChainItemD item = a.items[it];
+            const ChainMatD & M = a.mats[item.mat];
+            const int type = M.type;
+            const int seq = it - it_begin, st = seq % CH_NS;
+            const uint32_t stage = ring + (uint32_t) st * (uint32_t) a.stage_bytes;
+            const int nunits = item.nrows * upr;
+            const uint32_t part = part0 + (uint32_t) pbuf * part_bytes;
+            mbar_wait(bars + st * 8, (uint32_t) ((seq / CH_NS) & 1));
+
+            // phase A: partial dot products per 256-element unit
+            if (type == B200_TYPE_Q4_K) {
+                for (int u = gtid; u < nunits; u += CH_GTHREADS) {
+                    float acc[NCOLS];
+#pragma unroll
+                    for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+                    unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xs + (uint32_t) ((u % upr) * XU_BYTES), x_col_stride, acc);
+#pragma unroll
+                    for (int c = 0; c < NCOLS; ++c) stsf(part + (uint32_t) (c * a.max_units + u) * 4, acc[c]);
+                }
+            } else if (type == B200_TYPE_Q6_K) {
+                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+            } else if (type == B200_TYPE_IQ4_XS) {
+                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+            } else if (type == B200_TYPE_Q4_0) {
+                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+            } else {
+                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+            }
+            group_bar(grp);
+            // the stage is free: keep the ring full (runs ahead into the following nodes)
+            if (gtid == 0 && it + CH_NS < it_end) issue(it + CH_NS);
+
+            // phase B: one warp per (row, column) adds the row's units in a fixed order
+            for (int rc = gwarp; rc < item.nrows * NCOLS; rc += CH_GWARPS) {
+                const int c = rc / item.nrows, r = rc - c * item.nrows;
+                float v = 0.0f;
+                for (int b = lane; b < upr; b += 32) v += ldsf(part + (uint32_t) (c * a.max_units + r * upr + b) * 4);
+                v = warp_sum(v);
+                if (lane == 0) M.y[(long long) c * M.ldy + item.row0 + r] = v;
+            }
+            pbuf ^= 1;
+        }
+        __syncthreads();                       // every Y store of this CTA is done; thread 0's fence + arrival publishes them
+        if (tid == 0 && n + 1 < NN) {
+            __threadfence();
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+struct Chain {
+    int device = 0, sms = 0, ncols = 1, n_nodes = 0, n_launch_nodes = 0;
+    ChainArgs args = {};
+    void * d_blob = nullptr;
+    size_t smem = 0;
+    bool cooperative = true;
+};
+
+bool chain_type_ok(int t) { return t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0; }
+int gcd_i(int a, int b) { while (b) { int t = a % b; a = b; b = t; } return a; }
+// rows of one item must keep every plane piece a multiple of 16 bytes, in size and in source address
+int row_granule(int type, int upr) {
+    int g = 1;
+    for (int p = 0; p < 4; ++p) {
+        const int pb = plane_bytes(type, p);
+        if (!pb) break;
+        const int per_row = pb * upr;
+        const int need = 16 / gcd_i(per_row, 16);
+        g = g * need / gcd_i(g, need);
+    }
+    return g;
+}
+
+template <int NCOLS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) c.sms); cfg.blockDim = dim3(CH_THREADS); cfg.dynamicSmemBytes = c.smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative; attr[0].val.cooperative = 1;
+    cfg.attrs = attr; cfg.numAttrs = c.cooperative ? 1 : 0;
+    b200_count_launch();
+    return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS>, c.args);
+}
+
+const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
+    if (!nodes || !group_sizes || n_groups < 1) return "no nodes";
+    int idx = 0;
+    const int64_t n0 = nodes[0].n;
+    if (n0 < 1 || n0 > CH_MAX_COLS) return "n must be 1..4";
+    for (int g = 0; g < n_groups; ++g) {
+        if (group_sizes[g] < 1) return "empty group";
+        const b200_mul_mat_args & a0 = nodes[idx];
+        for (int i = 0; i < group_sizes[g]; ++i, ++idx) {
+            const b200_mul_mat_args & a = nodes[idx];
+            if (!a.w || !a.x || !a.y) return "null pointer";
+            if (!chain_type_ok(a.type)) return "weight type";
+            if (a.n != n0) return "all nodes of a chain need the same n";
+            if (a.k <= 0 || a.k % 256 != 0 || a.k > 65536) return "k must be a multiple of 256 (<= 65536)";
+            if (a.m <= 0 || a.m > (1 << 30)) return "m out of range";
+            if (a.x != a0.x || a.k != a0.k || a.x_row_stride != a0.x_row_stride || a.flavour != a0.flavour) return "nodes of a group must read the same X";
+            if (b200_act_type(a.type) != b200_act_type(a0.type)) return "nodes of a group need the same activation format";
+            if (a.layout != B200_LAYOUT_PLANES && a.type != B200_TYPE_Q4_K) return "plane layout required";
+            if (a.w_row_stride != 0 && a.w_row_stride != (int64_t) b200_row_size(a.type, a.k)) return "packed rows required";
+            if ((((uintptr_t) a.w) & 15) != 0) return "weights must be 16 B aligned";
+            if (a.m % row_granule(a.type, (int) (a.k >> 8)) != 0) return "row count incompatible with 16-byte plane pieces";
+            if (a.flags & B200_MM_X_PREQUANTISED) return "prequantised X";
+        }
+    }
+    return nullptr;
+}
+
+} // namespace
+
+extern "C" {
+
+int b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
+    return chain_check(nodes, group_sizes, n_groups) == nullptr ? 1 : 0;
+}
+
+b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
+    const char * why = chain_check(nodes, group_sizes, n_groups);
+    if (why) { b200_set_error("b200_chain_create: %s", why); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); b200_set_error("b200_chain_create: cudaSetDevice(%d) failed", device); return nullptr; }
+    int sms = 0, smem_optin = 0, coop = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+    if (sms <= 0 || smem_optin < 200 * 1024) { cudaGetLastError(); b200_set_error("b200_chain_create: no usable sm_100 device"); return nullptr; }
+    if (const char * e = getenv("B200_CHAIN_CTAS")) { const int v = atoi(e); if (v > 0 && v < sms) sms = v; }
+
+    const int ncols = (int) nodes[0].n;
+    const int VC = sms * CH_GROUPS;
+    int64_t kmax = 0;
+    { int idx = 0; for (int g = 0; g < n_groups; ++g) { kmax = nodes[idx].k > kmax ? nodes[idx].k : kmax; idx += group_sizes[g]; } }
+    const int x_bytes = (int) (((int64_t) ncols * (kmax >> 8) * XU_BYTES + 127) & ~127);
+    const int total_smem = smem_optin < CH_SMEM_TOTAL ? smem_optin : CH_SMEM_TOTAL;
+    // ring stage: what is left after X, split over groups x stages; the partial buffers depend on the stage size
+    // (max_units = stage / 136 units of 4 B x 2 buffers x ncols per group), solve by stepping the stage size down
+    int stage = 0, max_units = 0;
+    for (int st = 48 * 1024; st >= 4 * 1024; st -= 1024) {
+        const int mu = st / 136 + 1;
+        const int64_t need = 64 + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 128 + (int64_t) CH_GROUPS * CH_NS * st;
+        if (need <= total_smem) { stage = st; max_units = mu; break; }
+    }
+    if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < stage) { stage = v; } }
+    if (!stage) { b200_set_error("b200_chain_create: activations of %d x %lld do not leave room for the weight ring", ncols, (long long) kmax); return nullptr; }
+
+    std::vector<ChainNodeD> hn(n_groups);
+    std::vector<ChainMatD> hm;
+    std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
+    int idx = 0;
+    for (int g = 0; g < n_groups; ++g) {
+        const b200_mul_mat_args & a0 = nodes[idx];
+        hn[g].x = a0.x; hn[g].ldx = a0.x_row_stride; hn[g].k = (int) a0.k;
+        hn[g].act_block = b200_act_type(a0.type) == B200_TYPE_Q8_K ? 256 : 32;
+        hn[g].flavour = a0.flavour; hn[g].pad = 0;
+        const int upr = (int) (a0.k >> 8);
+        // cut the concatenated rows of the group by bytes: VC v gets bytes [v T / VC, (v + 1) T / VC), rounded to row granules
+        const int cnt = group_sizes[g];
+        std::vector<int64_t> rb(cnt), cum(cnt + 1, 0);
+        for (int i = 0; i < cnt; ++i) { rb[i] = (int64_t) unit_bytes(nodes[idx + i].type) * upr; cum[i + 1] = cum[i] + rb[i] * nodes[idx + i].m; }
+        const int64_t T = cum[cnt];
+        const int mat_base = (int) hm.size();
+        for (int i = 0; i < cnt; ++i) {
+            const b200_mul_mat_args & a = nodes[idx + i];
+            ChainMatD M; M.w = (const uint8_t *) a.w; M.y = a.y; M.ldy = a.y_row_stride; M.m = (int) a.m; M.type = a.type; M.upr = upr; M.pad = 0;
+            hm.push_back(M);
+        }
+        // cut positions as (matrix, row)
+        auto cut_of = [&](int64_t t, int & mi, int64_t & row) {
+            mi = 0;
+            while (mi + 1 < cnt && t >= cum[mi + 1]) ++mi;
+            const int gr = row_granule(nodes[idx + mi].type, upr);
+            int64_t r = ((t - cum[mi]) + rb[mi] * gr / 2) / (rb[mi] * gr) * gr;
+            if (r > nodes[idx + mi].m) r = nodes[idx + mi].m;
+            row = r;
+        };
+        int pm = 0; int64_t prow = 0;
+        // rotate the VC order from node to node so that rounding leftovers do not pile up on the same SMs
+        for (int v = 0; v < VC; ++v) {
+            int cm; int64_t crow;
+            if (v == VC - 1) { cm = cnt - 1; crow = nodes[idx + cnt - 1].m; }
+            else cut_of(T * (v + 1) / VC, cm, crow);
+            if (cm < pm || (cm == pm && crow < prow)) { cm = pm; crow = prow; }
+            const int vc = (v + g * 37) % VC;
+            std::vector<ChainItemD> & out = per_vc_node[(size_t) vc * n_groups + g];
+            for (int mi = pm; mi <= cm; ++mi) {
+                const int64_t r0 = mi == pm ? prow : 0, r1 = mi == cm ? crow : nodes[idx + mi].m;
+                if (r1 <= r0) continue;
+                const int type = nodes[idx + mi].type;
+                const int gr = row_granule(type, upr);
+                int64_t max_rows = (int64_t) stage / ((int64_t) unit_bytes(type) * upr) / gr * gr;
+                if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); return nullptr; }
+                const int64_t rows = r1 - r0;
+                const int64_t nit = (rows + max_rows - 1) / max_rows;
+                int64_t per = ((rows + nit - 1) / nit + gr - 1) / gr * gr;
+                if (per > max_rows) per = max_rows;
+                for (int64_t r = r0; r < r1; r += per) {
+                    ChainItemD it; it.mat = mat_base + mi; it.row0 = (int) r; it.nrows = (int) (r1 - r < per ? r1 - r : per); it.pad = 0;
+                    out.push_back(it);
+                }
+            }
+            pm = cm; prow = crow;
+        }
+        idx += cnt;
+    }
+    std::vector<ChainItemD> hi;
+    std::vector<int> hoff((size_t) VC * (n_groups + 1));
+    for (int vc = 0; vc < VC; ++vc) {
+        for (int g = 0; g < n_groups; ++g) {
+            hoff[(size_t) vc * (n_groups + 1) + g] = (int) hi.size();
+            const std::vector<ChainItemD> & v = per_vc_node[(size_t) vc * n_groups + g];
+            hi.insert(hi.end(), v.begin(), v.end());
+        }
+        hoff[(size_t) vc * (n_groups + 1) + n_groups] = (int) hi.size();
+    }
+
+    auto al = [](size_t v) { return (v + 255) & ~(size_t) 255; };
+    const size_t o_nodes = 256, o_mats = o_nodes + al(hn.size() * sizeof(ChainNodeD)), o_items = o_mats + al(hm.size() * sizeof(ChainMatD)),
+                 o_off = o_items + al(hi.size() * sizeof(ChainItemD) + 16), total = o_off + al(hoff.size() * sizeof(int));
+    std::vector<uint8_t> blob(total, 0);
+    memcpy(blob.data() + o_nodes, hn.data(), hn.size() * sizeof(ChainNodeD));
+    memcpy(blob.data() + o_mats, hm.data(), hm.size() * sizeof(ChainMatD));
+    if (!hi.empty()) memcpy(blob.data() + o_items, hi.data(), hi.size() * sizeof(ChainItemD));
+    memcpy(blob.data() + o_off, hoff.data(), hoff.size() * sizeof(int));
+    void * d = nullptr;
+    if (cudaMalloc(&d, total) != cudaSuccess || cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
+        b200_set_error("b200_chain_create: cudaMalloc/cudaMemcpy of %zu bytes failed: %s", total, cudaGetErrorString(cudaGetLastError()));
+        if (d) cudaFree(d);
+        return nullptr;
+    }
+    Chain * c = new Chain();
+    c->device = device; c->sms = sms; c->ncols = ncols; c->n_nodes = n_groups; c->d_blob = d;
+    uint8_t * db = (uint8_t *) d;
+    c->args.counter = (unsigned *) db;
+    c->args.nodes = (const ChainNodeD *) (db + o_nodes);
+    c->args.mats = (const ChainMatD *) (db + o_mats);
+    c->args.items = (const ChainItemD *) (db + o_items);
+    c->args.node_off = (const int *) (db + o_off);
+    c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes;
+    c->smem = 64 + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 128 + (size_t) CH_GROUPS * CH_NS * stage;
+    c->cooperative = coop != 0 && !getenv("B200_CHAIN_NO_COOP");
+    cudaError_t e = cudaSuccess;
+    switch (ncols) {
+        case 1: e = cudaFuncSetAttribute(gemv_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        case 2: e = cudaFuncSetAttribute(gemv_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        case 3: e = cudaFuncSetAttribute(gemv_chain_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        default: e = cudaFuncSetAttribute(gemv_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+    }
+    if (e != cudaSuccess) {
+        b200_set_error("b200_chain_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        cudaGetLastError(); cudaFree(d); delete c; return nullptr;
+    }
+    return (b200_chain_t) c;
+}
+
+int b200_chain_launch(b200_chain_t chain, b200_stream_t stream) {
+    B200_REQUIRE(chain, "b200_chain_launch: null chain");
+    Chain * c = (Chain *) chain;
+    cudaStream_t s = (cudaStream_t) stream;
+    B200_CHECK(cudaMemsetAsync(c->args.counter, 0, 64, s));
+    cudaError_t e;
+    switch (c->ncols) {
+        case 1: e = chain_launch_t<1>(*c, s); break;
+        case 2: e = chain_launch_t<2>(*c, s); break;
+        case 3: e = chain_launch_t<3>(*c, s); break;
+        default: e = chain_launch_t<4>(*c, s); break;
+    }
+    B200_CHECK(e);
+    return 0;
+}
+
+int b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * smem_bytes, int * n_nodes) {
+    B200_REQUIRE(chain, "b200_chain_info: null chain");
+    Chain * c = (Chain *) chain;
+    if (ctas) *ctas = c->sms;
+    if (stage_bytes) *stage_bytes = c->args.stage_bytes;
+    if (smem_bytes) *smem_bytes = (int) c->smem;
+    if (n_nodes) *n_nodes = c->n_nodes;
+    return 0;
+}
+
+int b200_chain_destroy(b200_chain_t chain) {
+    if (!chain) return 0;
+    Chain * c = (Chain *) chain;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_blob);
+    delete c;
+    return 0;
+}
+
+} // extern "C"
