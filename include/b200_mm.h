@@ -173,6 +173,7 @@ B200_API int          b200_chain_supported(const b200_mul_mat_args * nodes, cons
 B200_API b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups); /* NULL on failure */
 B200_API int          b200_chain_launch(b200_chain_t chain, b200_stream_t stream);   /* asynchronous, CUDA-graph capturable */
 B200_API int          b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * smem_bytes, int * n_groups);
+B200_API int          b200_chain_timeline(b200_chain_t chain, long long * host, size_t count);  /* debugging aid, see gemv_chain.cu */
 B200_API int          b200_chain_destroy(b200_chain_t chain);
 
 /* ---- (4) MUL_MAT_ID (ggml.c:3217-3243; CPU driver ggml-cpu.c:1500-1676) ----------------------

@@ -1,6 +1,7 @@
 """GPU probe: decode step (tg, N = 1) of a model's MUL_MAT chain, persistent chain kernel vs per-node launches.
 Usage: python tools/chain_probe.py [--model llama-3-8b-q4_k_m] [--steps 64] [--layers L]"""
 import argparse
+import os
 import sys
 from pathlib import Path
 
@@ -13,6 +14,28 @@ from __graft_entry__ import load_pkg  # noqa: E402
 b = load_pkg()
 from zyk_llama_cpp_b200 import workloads as W  # noqa: E402
 from zyk_llama_cpp_b200.chain import MatMulChain  # noqa: E402
+
+
+def show_timeline(tl, call_ops, mhz=1965.0):
+    """tl [ctas, nodes, 8] clock64 samples (gemv_chain.cu); prints per node kind the mean over nodes of: the slowest CTA's wait /
+    quantiser / item loop, and per group the time stalled on weight copies"""
+    import numpy as np
+    us = lambda c: c / mhz
+    kinds = {}
+    for n, ops in enumerate(call_ops):
+        key = "+".join(o.name.split(".")[-1] for o in ops)
+        kinds.setdefault(key, []).append(n)
+    print(f"  {'node kind':28s} {'n':>3s} | {'node us':>8s} {'wait':>6s} {'quant':>6s} {'items':>6s} | per group: {'copy stall':>10s} {'item loop':>9s} | {'MB':>6s} {'GB/s':>6s}")
+    for key, idx in kinds.items():
+        t = tl[:, idx, :].astype(np.float64)
+        node = (t[:, :, 3] - t[:, :, 0]).mean()
+        wait = (t[:, :, 1] - t[:, :, 0]).mean()
+        quant = (t[:, :, 2] - t[:, :, 1]).mean()
+        items = (t[:, :, 3] - t[:, :, 2]).mean()
+        stall = t[:, :, [4, 6]].mean()
+        loop = t[:, :, [5, 7]].mean()
+        mb = sum(o.streamed_bytes for o in call_ops[idx[0]]) / 1e6
+        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
 
 
 def run(ops, persistent, steps):
@@ -29,6 +52,8 @@ def run(ops, persistent, steps):
     ch.stream.synchronize()
     ms = e0.elapsed_ms(e1) / steps
     info = ch.decode_chain.info() if ch.decode_chain is not None else None
+    if ch.decode_chain is not None and os.environ.get("B200_CHAIN_TIMELINE"):
+        show_timeline(ch.decode_chain.timeline(), [c[2] for c in ch.calls])
     out = {k: v.clone() for k, v in ch.bufs.items()}
     ch.close()
     return ms, info, out

@@ -82,6 +82,7 @@ _sig("b200_chain_create", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(
 _sig("b200_chain_launch", C.c_int, C.c_void_p, C.c_void_p)
 _sig("b200_chain_info", C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))
 _sig("b200_chain_destroy", C.c_int, C.c_void_p)
+_sig("b200_chain_timeline", C.c_int, C.c_void_p, C.c_void_p, C.c_size_t)
 _sig("b200_mul_mat_id_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64)
 _sig("b200_mul_mat_id", C.c_int, C.POINTER(MulMatIdArgs), C.c_void_p)
 _sig("b200_stream_create", C.c_void_p, C.c_int)
@@ -307,6 +308,14 @@ class DecodeChain:
 
     def launch(self, stream=None):
         _check(lib.b200_chain_launch(self.handle, _s(stream)))
+
+    def timeline(self):
+        """[ctas, n_groups, 8] clock64 samples of the last launch (needs B200_CHAIN_TIMELINE=1 at create time)"""
+        import numpy as np
+        i = self.info()
+        out = np.zeros((i["ctas"], i["n_groups"], 8), np.int64)
+        _check(lib.b200_chain_timeline(self.handle, out.ctypes.data_as(C.c_void_p), out.size))
+        return out
 
     def close(self):
         if self.handle:

@@ -37,7 +37,9 @@ using namespace sm100;
 constexpr int CH_GROUPS = 2;                 // virtual consumers per CTA
 constexpr int CH_GWARPS = 8;                 // warps per group
 constexpr int CH_GTHREADS = CH_GWARPS * 32;
-constexpr int CH_THREADS = CH_GROUPS * CH_GTHREADS;
+constexpr int CH_CONSUMERS = CH_GROUPS * CH_GTHREADS;      // 16 consumer warps ...
+constexpr int CH_THREADS = CH_CONSUMERS + 32;               // ... + one producer warp (one thread issues every bulk copy)
+constexpr int CH_HDR = 384;                                 // mbarriers (full, empty) + per-stage item descriptors
 constexpr int CH_NS = 3;                     // ring stages per group
 constexpr int XU_BYTES = 336;                // one 256-element unit of quantised X in shared memory (bank-conflict-free stride)
 constexpr int XU_BS16 = 256, XU_BS32 = 288, XU_D = 304;
@@ -54,11 +56,17 @@ struct ChainNodeD {
     const float * x; long long ldx;
     int k, act_block, flavour, pad;
 };
-struct ChainItemD { int mat, row0, nrows, pad; };
+// one ring stage worth of rows of one matrix, self-contained (the producer thread reads nothing else)
+struct ChainItemD {
+    const uint8_t * src[4];   // plane pieces (nullptr / 0 bytes: unused)
+    uint32_t bytes[4];
+    float * y; long long ldy; // y already points at the item's first row
+    int type, nrows;
+    int segs, S;              // how the warps share the item (plan_item)
+};
 
 struct ChainArgs {
     const ChainNodeD * nodes;
-    const ChainMatD * mats;
     const ChainItemD * items;
     const int * node_off;     // [vc][n_nodes + 1] -> index into items (items are VC-major, node-ordered)
     unsigned * counter;       // arrivals: every CTA adds one per finished node (zeroed before the launch)
@@ -66,6 +74,8 @@ struct ChainArgs {
     int stage_bytes;          // bytes per ring stage
     int max_units;            // stride of the partial-sum buffers
     int x_bytes;              // shared memory reserved for the quantised X
+    long long * timeline;     // B200_CHAIN_TIMELINE: clock64 samples per (CTA, node), see the kernel
+    int debug;                // B200_CHAIN_DEBUG (timing experiments, results wrong): 1 no node wait, 2 no dot products, 4 no X quantiser, 8 no row sums
 };
 
 // bytes per 256-element unit in plane p of the plane layout (repack.cu); 0 terminates
@@ -124,18 +134,21 @@ __device__ __forceinline__ int dot16_us(const uint4 & a, const uint4 & b) {
 
 // ---- activation quantiser into the shared-memory unit layout ---------------------------------------------------------
 //   unit (col, u): [qs 256 B, chunks placed by xpos][bs16: 16 x i16][bs32: 8 x i16][d: 8 x f32 (Q8_K uses d[0])]
-template <int NCOLS>
-__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
+template <int NCOLS, int QU>
+__device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
     const int upr = nd.k >> 8;
     const int total = NCOLS * upr;
-    constexpr int NW = CH_THREADS / 32, QU = 4;
+    constexpr int NW = CH_CONSUMERS / 32;
+    constexpr unsigned FULL = 0xffffffffu;
     for (int c0 = warp; c0 < total; c0 += NW * QU) {
         float v[QU][8];
 #pragma unroll
         for (int q = 0; q < QU; ++q) {
             const int ci = c0 + q * NW;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[q][j] = 0.0f;
             if (ci < total) {
-                const int col = ci / upr, u = ci - col * upr;
+                const int col = NCOLS == 1 ? 0 : ci / upr, u = ci - col * upr;
                 const float * xr = nd.x + (long long) col * nd.ldx + u * 256 + lane * 8;
                 if ((((uintptr_t) xr) & 15) == 0) {
                     const float4 lo = ldcg16(xr), hi = ldcg16(xr + 4);
@@ -146,32 +159,82 @@ __device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t
                 }
             }
         }
+        int qq[QU][8]; float dval[QU];
+        if (nd.act_block == 256) {
+            // quantize_row_q8_K_ref (ggml-quants.c:2555-2591), the stages of the QU chunks interleaved by hand: the node boundary
+            // waits for this. max |x| of the chunk by ONE redux on the bit patterns (order preserving for non-negative floats),
+            // then the FIRST element that has it (strict '>' in the reference loop) keeps its sign
+            uint32_t mb[QU]; float maxv[QU];
+#pragma unroll
+            for (int q = 0; q < QU; ++q) {
+                float am = 0.0f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) am = fmaxf(am, fabsf(v[q][j]));
+                mb[q] = __float_as_uint(am);
+            }
+#pragma unroll
+            for (int q = 0; q < QU; ++q) mb[q] = __reduce_max_sync(FULL, mb[q]);
+#pragma unroll
+            for (int q = 0; q < QU; ++q) {
+                float cand = 0.0f; bool have = false;
+#pragma unroll
+                for (int j = 7; j >= 0; --j) if (__float_as_uint(fabsf(v[q][j])) == mb[q]) { cand = v[q][j]; have = true; }
+                const unsigned bal = __ballot_sync(FULL, have);
+                maxv[q] = __shfl_sync(FULL, cand, (__ffs((int) bal) - 1) & 31);
+            }
+#pragma unroll
+            for (int q = 0; q < QU; ++q) {
+                if (mb[q] == 0u) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) qq[q][j] = 0;
+                    dval[q] = 0.0f;
+                } else {
+                    const float iscale = __fdiv_rn(-127.0f, maxv[q]);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { const int t = __float2int_rn(__fmul_rn(iscale, v[q][j])); qq[q][j] = t > 127 ? 127 : t; }
+                    dval[q] = __fdiv_rn(1.0f, iscale);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < QU; ++q) {
+                float sval;
+                if (nd.flavour == B200_Q8_X86) quant_chunk256<B200_TYPE_Q8_0, B200_Q8_X86>(v[q], lane, qq[q], dval[q], sval);
+                else                           quant_chunk256<B200_TYPE_Q8_0, B200_Q8_REF>(v[q], lane, qq[q], dval[q], sval);
+            }
+        }
 #pragma unroll
         for (int q = 0; q < QU; ++q) {
             const int ci = c0 + q * NW;
-            if (ci < total) {
-                int qq[8]; float dval, sval;
-                if (nd.act_block == 256)               quant_chunk256<B200_TYPE_Q8_K, B200_Q8_X86>(v[q], lane, qq, dval, sval);
-                else if (nd.flavour == B200_Q8_X86)    quant_chunk256<B200_TYPE_Q8_0, B200_Q8_X86>(v[q], lane, qq, dval, sval);
-                else                                   quant_chunk256<B200_TYPE_Q8_0, B200_Q8_REF>(v[q], lane, qq, dval, sval);
-                int s8 = 0;
+            int s8 = 0;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) s8 += (int) (int8_t) qq[j];
-                const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
-                const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
-                const uint32_t w0 = (qq[0] & 0xff) | ((qq[1] & 0xff) << 8) | ((qq[2] & 0xff) << 16) | ((uint32_t) (qq[3] & 0xff) << 24);
-                const uint32_t w1 = (qq[4] & 0xff) | ((qq[5] & 0xff) << 8) | ((qq[6] & 0xff) << 16) | ((uint32_t) (qq[7] & 0xff) << 24);
+            for (int j = 0; j < 8; ++j) s8 += (int) (int8_t) qq[q][j];
+            const int s16 = s8 + __shfl_xor_sync(FULL, s8, 1);
+            const int s32 = s16 + __shfl_xor_sync(FULL, s16, 2);
+            if (ci < total) {
+                const uint32_t w0 = (qq[q][0] & 0xff) | ((qq[q][1] & 0xff) << 8) | ((qq[q][2] & 0xff) << 16) | ((uint32_t) (qq[q][3] & 0xff) << 24);
+                const uint32_t w1 = (qq[q][4] & 0xff) | ((qq[q][5] & 0xff) << 8) | ((qq[q][6] & 0xff) << 16) | ((uint32_t) (qq[q][7] & 0xff) << 24);
                 const uint32_t ub = xs + (uint32_t) ci * XU_BYTES;
                 const int ch = lane >> 1;
                 const int pc = ch < 8 ? ch : 8 + ((ch + 4) & 7);
                 sts8(ub + pc * 16 + (lane & 1) * 8, w0, w1);
                 if ((lane & 1) == 0) sts2(ub + XU_BS16 + (lane >> 1) * 2, (uint16_t) (int16_t) s16);
                 if ((lane & 3) == 0) sts2(ub + XU_BS32 + (lane >> 2) * 2, (uint16_t) (int16_t) s32);
-                if (nd.act_block == 256) { if (lane == 0) stsf(ub + XU_D, dval); }
-                else if ((lane & 3) == 0) stsf(ub + XU_D + (lane >> 2) * 4, dval);
+                if (nd.act_block == 256) { if (lane == 0) stsf(ub + XU_D, dval[q]); }
+                else if ((lane & 3) == 0) stsf(ub + XU_D + (lane >> 2) * 4, dval[q]);
             }
         }
     }
+}
+
+// chunks per warp that are quantised together: as many as the node needs, no dead slots (every CTA runs this once per node)
+template <int NCOLS>
+__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
+    const int total = NCOLS * (nd.k >> 8);
+    constexpr int NW = CH_CONSUMERS / 32;
+    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane);
+    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane);
+    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane);
 }
 
 // ---- Q4_K: one 256-block per lane --------------------------------------------------------------------------------------
@@ -281,81 +344,179 @@ __device__ __forceinline__ void frag_legacy(uint32_t stage, int nunits, int u, i
     f.template dot<NCOLS>(x, acc, g);
 }
 
-// phase A of one item for the 8-lanes-per-unit formats: partial sums per unit into `part`
+// How the eight warps of a group share one item (nrows rows of upr units each). A TASK is what one warp reduces on its own:
+//   one block per lane (Q4_K): upr <= 32 -> a task is 32 / upr whole rows side by side (segmented shuffle reduction, Y stored
+//     straight from the warp); upr > 32 -> a task is 32 consecutive units of one row;
+//   eight lanes per block (the other formats): a task is a run of `S` units of one row, four units per warp pass.
+// Rows cut into several tasks meet in a small partial buffer and are added in a fixed order after the group barrier.
+struct ItemPlan { int segs, S; };
+inline ItemPlan plan_item(bool lane_per_unit, int nrows, int upr) {       // host, at create time
+    ItemPlan p;
+    if (lane_per_unit) { p.S = 32; p.segs = upr <= 32 ? 1 : (upr + 31) >> 5; return p; }
+    int want = (2 * CH_GWARPS + nrows - 1) / nrows;            // aim at >= 2 tasks per warp
+    const int most = (upr + 3) >> 2;
+    if (want > most) want = most;
+    if (want < 1) want = 1;
+    p.S = (((upr + want - 1) / want) + 3) & ~3;
+    p.segs = (upr + p.S - 1) / p.S;
+    return p;
+}
+
 template <int TYPE, int NCOLS>
-__device__ __forceinline__ void item_lanes8(uint32_t stage, int nunits, int upr, uint32_t xs, int x_col_stride, int act_block,
-                                            uint32_t part, int max_units, int gtid) {
-    const int total = nunits * 8;
-    for (int w0 = (gtid & ~31); w0 < total; w0 += CH_GTHREADS) {
-        const int w = w0 + (gtid & 31);
+__device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride, int act_block,
+                                            const ItemPlan pl, uint32_t part, int part_stride, float * y, long long ldy, int gwarp, int lane) {
+    const int nunits = nrows * upr;
+    const int j = lane >> 3, g = lane & 7;
+    int row = 0, seg = gwarp;
+    for (int t = gwarp; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
+        while (seg >= pl.segs) { seg -= pl.segs; ++row; }
+        const int u_end = min(upr, (seg + 1) * pl.S);
         float acc[NCOLS];
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-        const int u = w >> 3, g = w & 7;
-        if (w < total) {
-            const uint32_t xb = xs + (uint32_t) ((u % upr) * XU_BYTES);
-            if constexpr (TYPE == B200_TYPE_Q6_K) frag_q6k<NCOLS>(stage, nunits, u, g, xb, x_col_stride, acc);
-            else                                  frag_legacy<TYPE, NCOLS>(stage, nunits, u, g, xb, x_col_stride, act_block, acc);
+        for (int b = seg * pl.S + j; b < u_end; b += 4) {
+            const uint32_t xb = xs + (uint32_t) (b * XU_BYTES);
+            if constexpr (TYPE == B200_TYPE_Q6_K) frag_q6k<NCOLS>(stage, nunits, row * upr + b, g, xb, x_col_stride, acc);
+            else                                  frag_legacy<TYPE, NCOLS>(stage, nunits, row * upr + b, g, xb, x_col_stride, act_block, acc);
         }
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
-            float v = acc[c];
-            v += __shfl_xor_sync(0xffffffffu, v, 1);
-            v += __shfl_xor_sync(0xffffffffu, v, 2);
-            v += __shfl_xor_sync(0xffffffffu, v, 4);
-            if (g == 0 && w < total) stsf(part + (uint32_t) (c * max_units + u) * 4, v);
+            const float v = warp_sum(acc[c]);
+            if (lane == 0) {
+                if (pl.segs == 1) y[c * ldy + row] = v;
+                else stsf(part + (uint32_t) (c * part_stride + t) * 4, v);
+            }
         }
     }
 }
 
 template <int NCOLS>
+__device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride,
+                                         const ItemPlan pl, uint32_t part, int part_stride, float * y, long long ldy, int gwarp, int lane,
+                                         int rp, int sub, int b) {
+    if (upr <= 32) {                                           // rp rows side by side in one warp: lane = (sub, b)
+        for (int t = gwarp; t * rp < nrows; t += CH_GWARPS) {
+            const int row = t * rp + sub;
+            const bool live = sub < rp && row < nrows;
+            float acc[NCOLS];
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+            if (live) unit_q4k<NCOLS>(stage + (uint32_t) (row * upr + b) * 144, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) {
+                float v = acc[c];
+                for (int o = 1; o < upr; o <<= 1) {            // segmented: lanes of one row are consecutive, fixed order
+                    const float w = __shfl_down_sync(0xffffffffu, v, o);
+                    if (b + o < upr) v += w;
+                }
+                if (live && b == 0) y[c * ldy + row] = v;
+            }
+        }
+    } else {
+        int row = 0, seg = gwarp;
+        for (int t = gwarp; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
+            while (seg >= pl.segs) { seg -= pl.segs; ++row; }
+            const int b = seg * 32 + lane;
+            float acc[NCOLS];
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+            if (b < upr) unit_q4k<NCOLS>(stage + (uint32_t) (row * upr + b) * 144, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) {
+                const float v = warp_sum(acc[c]);
+                if (lane == 0) stsf(part + (uint32_t) (c * part_stride + t) * 4, v);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void cons_bar() { asm volatile("bar.sync 3, %0;" :: "n"(CH_CONSUMERS) : "memory"); }
+
+template <int NCOLS>
 __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int grp = tid / CH_GTHREADS, gtid = tid % CH_GTHREADS, gwarp = gtid >> 5;
-    const int vc = blockIdx.x * CH_GROUPS + grp;
     const int NN = a.n_nodes;
 
-    // shared memory: [mbarriers 64 B][X units][partials: groups x 2 x NCOLS x max_units f32][ring: groups x NS x stage_bytes]
+    // shared memory: [full / empty mbarriers, item descriptors: CH_HDR][X units][partials: groups x 2 x NCOLS x max_units f32]
+    //                [ring: groups x NS x stage_bytes]
     const uint32_t base = smem_u32(smem_raw);
-    const uint32_t bars = base + (uint32_t) grp * (CH_NS * 8);
-    const uint32_t xs = base + 64;
+    auto full_bar  = [&](int g, int st) { return base + (uint32_t) ((g * CH_NS + st) * 8); };
+    auto empty_bar = [&](int g, int st) { return base + 64u + (uint32_t) ((g * CH_NS + st) * 8); };
+    auto desc_at   = [&](int g, int st) { return base + 128u + (uint32_t) ((g * CH_NS + st) * 32); };
+    const uint32_t xs = base + CH_HDR;
     const uint32_t part_bytes = (uint32_t) (NCOLS * a.max_units) * 4;
-    const uint32_t part0 = xs + (uint32_t) a.x_bytes + (uint32_t) grp * 2 * part_bytes;
-    const uint32_t ring = ((xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 127u) & ~127u) + (uint32_t) grp * CH_NS * (uint32_t) a.stage_bytes;
+    const uint32_t ring0 = (xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 127u) & ~127u;
 
-    const int * off = a.node_off + (long long) vc * (NN + 1);
-    const int it_begin = off[0], it_end = off[NN];
-    const uint64_t policy = policy_evict_first();
-
-    auto issue = [&](int it) {                 // one thread of the group: the copies of item `it` into stage (it - it_begin) % NS
-        const ChainItemD item = a.items[it];
-        const ChainMatD & M = a.mats[item.mat];
-        const int seq = it - it_begin, st = seq % CH_NS;
-        const uint32_t dst = ring + (uint32_t) st * (uint32_t) a.stage_bytes, bar = bars + st * 8;
-        const long long nunits = (long long) item.nrows * M.upr, u0 = (long long) item.row0 * M.upr, all = (long long) M.m * M.upr;
-        mbar_arrive_expect_tx(bar, (uint32_t) (nunits * unit_bytes(M.type)));
-        long long src_off = 0; uint32_t dst_off = 0;
-#pragma unroll
-        for (int p = 0; p < 4; ++p) {
-            const int pb = plane_bytes(M.type, p);
-            if (pb == 0) break;
-            bulk_g2s(dst + dst_off, M.w + src_off + u0 * pb, (uint32_t) (nunits * pb), bar, policy);
-            src_off += all * pb; dst_off += (uint32_t) (nunits * pb);
-        }
-    };
-
-    if (gtid == 0) {
-        for (int s = 0; s < CH_NS; ++s) mbar_init(bars + s * 8, 1);
+    if (tid == 0) {
+        for (int i = 0; i < CH_GROUPS * CH_NS; ++i) { mbar_init(base + i * 8, 1); mbar_init(base + 64 + i * 8, CH_GWARPS); }
         fence_barrier_init();
     }
     __syncthreads();
-    if (gtid == 0) for (int it = it_begin; it < it_end && it < it_begin + CH_NS; ++it) issue(it);
 
-    int pbuf = 0;
+    // ---- producer: ONE thread keeps both rings full; the item list of a VC is node-ordered, so the copies run ahead of the
+    //      node the consumers are working on for as long as there are free stages
+    if (warp == CH_CONSUMERS / 32) {
+        if (lane != 0) return;
+        const uint64_t policy = policy_evict_first();
+        int nxt[CH_GROUPS], end[CH_GROUPS], seq[CH_GROUPS];
+        ChainItemD item[CH_GROUPS];
+#pragma unroll
+        for (int g = 0; g < CH_GROUPS; ++g) {
+            const int * off = a.node_off + (long long) (blockIdx.x * CH_GROUPS + g) * (NN + 1);
+            nxt[g] = off[0]; end[g] = off[NN]; seq[g] = 0;
+            if (nxt[g] < end[g]) item[g] = a.items[nxt[g]];
+        }
+        while (true) {
+            bool pending = false;
+#pragma unroll
+            for (int g = 0; g < CH_GROUPS; ++g) {
+                if (nxt[g] >= end[g]) continue;
+                pending = true;
+                const int st = seq[g] % CH_NS;
+                if (!mbar_test(empty_bar(g, st), (uint32_t) (((seq[g] / CH_NS) & 1) ^ 1))) continue;
+                const uint32_t dst = ring0 + (uint32_t) (g * CH_NS + st) * (uint32_t) a.stage_bytes, bar = full_bar(g, st), dsc = desc_at(g, st);
+                const unsigned long long yp = (unsigned long long) item[g].y, ld = (unsigned long long) item[g].ldy;
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dsc), "r"((uint32_t) yp), "r"((uint32_t) (yp >> 32)), "r"((uint32_t) ld), "r"((uint32_t) (ld >> 32)) : "memory");
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dsc + 16), "r"((uint32_t) item[g].type), "r"((uint32_t) item[g].nrows), "r"((uint32_t) item[g].segs), "r"((uint32_t) item[g].S) : "memory");
+                const uint32_t total = item[g].bytes[0] + item[g].bytes[1] + item[g].bytes[2] + item[g].bytes[3];
+                mbar_arrive_expect_tx(bar, total);                       // release: the descriptor is visible to whoever sees the phase flip
+                uint32_t o = 0;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    if (item[g].bytes[p]) bulk_g2s(dst + o, item[g].src[p], item[g].bytes[p], bar, policy);
+                    o += item[g].bytes[p];
+                }
+                ++nxt[g]; ++seq[g];
+                if (nxt[g] < end[g]) item[g] = a.items[nxt[g]];           // in flight while the ring drains
+            }
+            if (!pending) break;
+        }
+        return;
+    }
+
+    // ---- consumers ---------------------------------------------------------------------------------------------------------
+    const int grp = tid / CH_GTHREADS, gtid = tid % CH_GTHREADS, gwarp = gtid >> 5;
+    const uint32_t part0 = xs + (uint32_t) a.x_bytes + (uint32_t) grp * 2 * part_bytes;
+    const int * off = a.node_off + (long long) (blockIdx.x * CH_GROUPS + grp) * (NN + 1);
+
+    // B200_CHAIN_TIMELINE: per (CTA, node) eight clock64 values: node start, after the wait, after the X quantiser, node end;
+    // then per group: cycles waiting for weight copies, cycles in the item loop
+    long long * tl = a.timeline ? a.timeline + ((long long) blockIdx.x * NN) * 8 : nullptr;
+
+    int pbuf = 0, seq = 0;
+    ChainNodeD nd = a.nodes[0];
+    int cnt = off[1] - off[0];
     for (int n = 0; n < NN; ++n) {
-        const ChainNodeD nd = a.nodes[n];
-        if (n > 0 && tid == 0) {               // X of this node is complete once every CTA has finished the previous node
+        ChainNodeD nd_next = nd; int cnt_next = 0;
+        if (n + 1 < NN) { nd_next = a.nodes[n + 1]; cnt_next = off[n + 2] - off[n + 1]; }   // lands while this node runs
+        if (tl && tid == 0) tl[n * 8 + 0] = clock64();
+        if (n > 0 && tid == 0 && !(a.debug & 1)) {               // X of this node is complete once every CTA has finished the previous node
             const unsigned want = (unsigned) n * gridDim.x;
             unsigned v; unsigned long long t0 = 0;
             for (unsigned spin = 0;; ++spin) {
@@ -367,60 +528,65 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 }
             }
         }
-        __syncthreads();
-        chain_quantise_x<NCOLS>(nd, xs, warp, lane);
-        __syncthreads();
+        cons_bar();
+        if (tl && tid == 0) tl[n * 8 + 1] = clock64();
+        if (!(a.debug & 4)) chain_quantise_x<NCOLS>(nd, xs, warp, lane);
+        cons_bar();
+        if (tl && tid == 0) tl[n * 8 + 2] = clock64();
 
         const int upr = nd.k >> 8;
         const int x_col_stride = upr * XU_BYTES;
-        for (int it = off[n]; it < off[n + 1]; ++it) {
-            const ChainItemD item = a.items[it];
-            const ChainMatD & M = a.mats[item.mat];
-            const int type = M.type;
-            const int seq = it - it_begin, st = seq % CH_NS;
-            const uint32_t stage = ring + (uint32_t) st * (uint32_t) a.stage_bytes;
-            const int nunits = item.nrows * upr;
+        const int q4_rp = upr <= 32 ? 32 / upr : 1, q4_sub = upr <= 32 ? lane / upr : 0, q4_b = lane - q4_sub * upr;
+        long long c_wait = 0, c_loop = tl ? clock64() : 0;
+        for (int i = 0; i < cnt; ++i, ++seq) {
+            const int st = seq % CH_NS;
+            const uint32_t stage = ring0 + (uint32_t) (grp * CH_NS + st) * (uint32_t) a.stage_bytes;
             const uint32_t part = part0 + (uint32_t) pbuf * part_bytes;
-            mbar_wait(bars + st * 8, (uint32_t) ((seq / CH_NS) & 1));
+            const long long w0 = tl ? clock64() : 0;
+            mbar_wait(full_bar(grp, st), (uint32_t) ((seq / CH_NS) & 1));
+            if (tl) c_wait += clock64() - w0;
+            const uint4 d0 = lds16(desc_at(grp, st));
+            const uint4 d1 = lds16(desc_at(grp, st) + 16);
+            float * y = (float *) (((unsigned long long) d0.y << 32) | d0.x);
+            const long long ldy = (long long) (((unsigned long long) d0.w << 32) | d0.z);
+            const int type = (int) d1.x, nrows = (int) d1.y;
+            ItemPlan pl; pl.segs = (int) d1.z; pl.S = (int) d1.w;
 
-            // phase A: partial dot products per 256-element unit
-            if (type == B200_TYPE_Q4_K) {
-                for (int u = gtid; u < nunits; u += CH_GTHREADS) {
-                    float acc[NCOLS];
-#pragma unroll
-                    for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-                    unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xs + (uint32_t) ((u % upr) * XU_BYTES), x_col_stride, acc);
-#pragma unroll
-                    for (int c = 0; c < NCOLS; ++c) stsf(part + (uint32_t) (c * a.max_units + u) * 4, acc[c]);
-                }
+            // phase A: every warp reduces its tasks (rows, or runs of units of a row)
+            if (a.debug & 2) {
+            } else if (type == B200_TYPE_Q4_K) {
+                item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, y, ldy, gwarp, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q6_K) {
-                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
             } else if (type == B200_TYPE_IQ4_XS) {
-                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
             } else if (type == B200_TYPE_Q4_0) {
-                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
             } else {
-                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nunits, upr, xs, x_col_stride, nd.act_block, part, a.max_units, gtid);
+                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
             }
-            group_bar(grp);
-            // the stage is free: keep the ring full (runs ahead into the following nodes)
-            if (gtid == 0 && it + CH_NS < it_end) issue(it + CH_NS);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty_bar(grp, st));     // this warp is done with the stage (and its descriptor)
 
-            // phase B: one warp per (row, column) adds the row's units in a fixed order
-            for (int rc = gwarp; rc < item.nrows * NCOLS; rc += CH_GWARPS) {
-                const int c = rc / item.nrows, r = rc - c * item.nrows;
-                float v = 0.0f;
-                for (int b = lane; b < upr; b += 32) v += ldsf(part + (uint32_t) (c * a.max_units + r * upr + b) * 4);
-                v = warp_sum(v);
-                if (lane == 0) M.y[(long long) c * M.ldy + item.row0 + r] = v;
+            // phase B (rows cut into several tasks only): add the pieces of a row in a fixed order
+            if (pl.segs > 1) {
+                group_bar(grp);
+                if (!(a.debug & 8)) {
+                    for (int rc = gtid; rc < nrows * NCOLS; rc += CH_GTHREADS) {
+                        const int c = NCOLS == 1 ? 0 : rc / nrows, r = rc - c * nrows;
+                        float v = 0.0f;
+                        for (int sg = 0; sg < pl.segs; ++sg) v += ldsf(part + (uint32_t) (c * a.max_units + r * pl.segs + sg) * 4);
+                        y[c * ldy + r] = v;
+                    }
+                }
+                pbuf ^= 1;
             }
-            pbuf ^= 1;
         }
-        __syncthreads();                       // every Y store of this CTA is done; thread 0's fence + arrival publishes them
-        if (tid == 0 && n + 1 < NN) {
-            __threadfence();
-            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
-        }
+        if (tl && gtid == 0) { tl[n * 8 + 4 + 2 * grp] = c_wait; tl[n * 8 + 5 + 2 * grp] = clock64() - c_loop; }
+        cons_bar();                            // every Y store of this CTA is done; the release below publishes them (cumulativity)
+        if (tid == 0 && n + 1 < NN) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
+        if (tl && tid == 0) tl[n * 8 + 3] = clock64();
+        nd = nd_next; cnt = cnt_next;
     }
 }
 
@@ -514,15 +680,15 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     // (max_units = stage / 136 units of 4 B x 2 buffers x ncols per group), solve by stepping the stage size down
     int stage = 0, max_units = 0;
     for (int st = 48 * 1024; st >= 4 * 1024; st -= 1024) {
-        const int mu = st / 136 + 1;
-        const int64_t need = 64 + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 128 + (int64_t) CH_GROUPS * CH_NS * st;
+        const int mu = st / 136 + 64;         // partial sums: at most max(rows, 2 x warps + rows) tasks per item
+        const int64_t need = CH_HDR + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 128 + (int64_t) CH_GROUPS * CH_NS * st;
         if (need <= total_smem) { stage = st; max_units = mu; break; }
     }
     if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < stage) { stage = v; } }
     if (!stage) { b200_set_error("b200_chain_create: activations of %d x %lld do not leave room for the weight ring", ncols, (long long) kmax); return nullptr; }
 
     std::vector<ChainNodeD> hn(n_groups);
-    std::vector<ChainMatD> hm;
+    std::vector<ChainMatD> hm;       // host-side only: the items carry everything the kernel needs
     std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
     int idx = 0;
     for (int g = 0; g < n_groups; ++g) {
@@ -572,7 +738,19 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
                 int64_t per = ((rows + nit - 1) / nit + gr - 1) / gr * gr;
                 if (per > max_rows) per = max_rows;
                 for (int64_t r = r0; r < r1; r += per) {
-                    ChainItemD it; it.mat = mat_base + mi; it.row0 = (int) r; it.nrows = (int) (r1 - r < per ? r1 - r : per); it.pad = 0;
+                    const ChainMatD & M = hm[mat_base + mi];
+                    ChainItemD it = {};
+                    it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
+                    it.y = M.y + r; it.ldy = M.ldy;
+                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    int64_t plane_off = 0;
+                    for (int p = 0; p < 4; ++p) {
+                        const int pb = plane_bytes(type, p);
+                        if (!pb) break;
+                        it.src[p] = M.w + plane_off + r * upr * pb;
+                        it.bytes[p] = (uint32_t) ((int64_t) it.nrows * upr * pb);
+                        plane_off += (int64_t) M.m * upr * pb;
+                    }
                     out.push_back(it);
                 }
             }
@@ -592,11 +770,10 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     }
 
     auto al = [](size_t v) { return (v + 255) & ~(size_t) 255; };
-    const size_t o_nodes = 256, o_mats = o_nodes + al(hn.size() * sizeof(ChainNodeD)), o_items = o_mats + al(hm.size() * sizeof(ChainMatD)),
+    const size_t o_nodes = 256, o_items = o_nodes + al(hn.size() * sizeof(ChainNodeD)),
                  o_off = o_items + al(hi.size() * sizeof(ChainItemD) + 16), total = o_off + al(hoff.size() * sizeof(int));
     std::vector<uint8_t> blob(total, 0);
     memcpy(blob.data() + o_nodes, hn.data(), hn.size() * sizeof(ChainNodeD));
-    memcpy(blob.data() + o_mats, hm.data(), hm.size() * sizeof(ChainMatD));
     if (!hi.empty()) memcpy(blob.data() + o_items, hi.data(), hi.size() * sizeof(ChainItemD));
     memcpy(blob.data() + o_off, hoff.data(), hoff.size() * sizeof(int));
     void * d = nullptr;
@@ -610,11 +787,15 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     uint8_t * db = (uint8_t *) d;
     c->args.counter = (unsigned *) db;
     c->args.nodes = (const ChainNodeD *) (db + o_nodes);
-    c->args.mats = (const ChainMatD *) (db + o_mats);
     c->args.items = (const ChainItemD *) (db + o_items);
     c->args.node_off = (const int *) (db + o_off);
+    if (getenv("B200_CHAIN_TIMELINE")) {
+        void * t = nullptr;
+        if (cudaMalloc(&t, (size_t) sms * n_groups * 64) == cudaSuccess) { cudaMemset(t, 0, (size_t) sms * n_groups * 64); c->args.timeline = (long long *) t; }
+    }
+    c->args.debug = getenv("B200_CHAIN_DEBUG") ? atoi(getenv("B200_CHAIN_DEBUG")) : 0;
     c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes;
-    c->smem = 64 + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 128 + (size_t) CH_GROUPS * CH_NS * stage;
+    c->smem = CH_HDR + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 128 + (size_t) CH_GROUPS * CH_NS * stage;
     c->cooperative = coop != 0 && !getenv("B200_CHAIN_NO_COOP");
     cudaError_t e = cudaSuccess;
     switch (ncols) {
@@ -656,11 +837,22 @@ int b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * sme
     return 0;
 }
 
+/* debugging aid (B200_CHAIN_TIMELINE=1 at create time): copies ctas x n_groups x 8 clock64 samples of the last launch */
+int b200_chain_timeline(b200_chain_t chain, long long * host, size_t count) {
+    B200_REQUIRE(chain && host, "b200_chain_timeline: null pointer");
+    Chain * c = (Chain *) chain;
+    B200_REQUIRE(c->args.timeline, "b200_chain_timeline: the chain was created without B200_CHAIN_TIMELINE");
+    const size_t have = (size_t) c->sms * c->n_nodes * 8;
+    B200_CHECK(cudaMemcpy(host, c->args.timeline, (count < have ? count : have) * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int b200_chain_destroy(b200_chain_t chain) {
     if (!chain) return 0;
     Chain * c = (Chain *) chain;
     cudaSetDevice(c->device);
     cudaFree(c->d_blob);
+    if (c->args.timeline) cudaFree(c->args.timeline);
     delete c;
     return 0;
 }
