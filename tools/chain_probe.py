@@ -32,10 +32,11 @@ def show_timeline(tl, call_ops, mhz=1965.0):
         wait = (t[:, :, 1] - t[:, :, 0]).mean()
         quant = (t[:, :, 2] - t[:, :, 1]).mean()
         items = (t[:, :, 3] - t[:, :, 2]).mean()
-        stall = t[:, :, [4, 6]].mean()
+        stall = t[:, :, 4].mean()
+        rel = t[:, :, 6].mean()
         loop = t[:, :, [5, 7]].mean()
         mb = sum(o.streamed_bytes for o in call_ops[idx[0]]) / 1e6
-        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
+        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
 
 
 def run(ops, persistent, steps):

@@ -39,7 +39,7 @@ constexpr int CH_GWARPS = 8;                 // warps per group
 constexpr int CH_GTHREADS = CH_GWARPS * 32;
 constexpr int CH_CONSUMERS = CH_GROUPS * CH_GTHREADS;      // 16 consumer warps ...
 constexpr int CH_THREADS = CH_CONSUMERS + 32;               // ... + one producer warp (one thread issues every bulk copy)
-constexpr int CH_HDR = 384;                                 // mbarriers (full, empty) + per-stage item descriptors
+constexpr int CH_HDR = 512;                                 // mbarriers (full, empty) + per-stage item descriptors
 constexpr int CH_NS = 3;                     // ring stages per group
 constexpr int XU_BYTES = 336;                // one 256-element unit of quantised X in shared memory (bank-conflict-free stride)
 constexpr int XU_BS16 = 256, XU_BS32 = 288, XU_D = 304;
@@ -52,9 +52,19 @@ struct ChainMatD {
     int m, type, upr;         // rows, weight type, 256-element units per row
     int pad;
 };
+// how a node learns that its X is complete (decided at create time from the pointers):
+enum { NB_NONE = 0,     // first node: stream order
+       NB_FENCED = 1,   // X overlaps something an earlier node wrote: arrival counter with release / acquire fences
+       NB_RELAXED = 2,  // X is written by nobody in the chain: the node is merely kept in stream order (counter, no fences)
+       NB_TAGGED = 3 }; // X is exactly the Y of a matrix of the previous node: the values arrive as 64-bit {epoch, f32} words,
+                        // each one validates itself, no counter and no fence
 struct ChainNodeD {
     const float * x; long long ldx;
-    int k, act_block, flavour, pad;
+    int k, act_block, flavour;
+    int mode;                             // NB_*
+    const unsigned long long * xtag;      // NB_TAGGED: where the previous node publishes this X
+    unsigned want;                        // counter value that means "every earlier signalling node is finished everywhere"
+    int signal;                           // what the NEXT node needs from this one: 0 nothing, 1 relaxed arrival, 2 release arrival
 };
 // one ring stage worth of rows of one matrix, self-contained (the producer thread reads nothing else)
 struct ChainItemD {
@@ -63,6 +73,8 @@ struct ChainItemD {
     float * y; long long ldy; // y already points at the item's first row
     int type, nrows;
     int segs, S;              // how the warps share the item (plan_item)
+    unsigned long long * tag; // tagged copy of the item's rows for the next node (nullptr: nobody in the chain reads them next)
+    long long pad;
 };
 
 struct ChainArgs {
@@ -75,6 +87,9 @@ struct ChainArgs {
     int max_units;            // stride of the partial-sum buffers
     int x_bytes;              // shared memory reserved for the quantised X
     long long * timeline;     // B200_CHAIN_TIMELINE: clock64 samples per (CTA, node), see the kernel
+    unsigned * epoch;         // launches so far x nodes: makes the tags of every (launch, node) unique
+    long long tag_stride;     // elements between the columns of a tagged vector
+    int inflight;             // copies per group that may be in flight (issued, not landed): bounds the queueing delay the stream adds to the node barrier
     int debug;                // B200_CHAIN_DEBUG (timing experiments, results wrong): 1 no node wait, 2 no dot products, 4 no X quantiser, 8 no row sums
 };
 
@@ -113,6 +128,16 @@ __device__ __forceinline__ float4 ldcg16(const float * p) {
 }
 __device__ __forceinline__ float ldcg4(const float * p) { float r; asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory"); return r; }
 
+__device__ __forceinline__ void st_tagged(unsigned long long * p, float v, unsigned epoch) {
+    const unsigned long long w = ((unsigned long long) epoch << 32) | (unsigned long long) __float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(p), "l"(w) : "memory");
+}
+// y and (when the next node reads these rows) the tagged copy
+struct YOut { float * y; long long ldy; unsigned long long * tag; long long tag_stride; unsigned epoch; };
+__device__ __forceinline__ void put_y(const YOut & o, int c, int row, float v) {
+    o.y[c * o.ldy + row] = v;
+    if (o.tag) st_tagged(o.tag + c * o.tag_stride + row, v, o.epoch);
+}
 __device__ __forceinline__ void group_bar(int grp) { asm volatile("bar.sync %0, %1;" :: "r"(grp + 1), "n"(CH_GTHREADS) : "memory"); }
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -135,7 +160,7 @@ __device__ __forceinline__ int dot16_us(const uint4 & a, const uint4 & b) {
 // ---- activation quantiser into the shared-memory unit layout ---------------------------------------------------------
 //   unit (col, u): [qs 256 B, chunks placed by xpos][bs16: 16 x i16][bs32: 8 x i16][d: 8 x f32 (Q8_K uses d[0])]
 template <int NCOLS, int QU>
-__device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
+__device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch) {
     const int upr = nd.k >> 8;
     const int total = NCOLS * upr;
     constexpr int NW = CH_CONSUMERS / 32;
@@ -150,7 +175,25 @@ __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32
             if (ci < total) {
                 const int col = NCOLS == 1 ? 0 : ci / upr, u = ci - col * upr;
                 const float * xr = nd.x + (long long) col * nd.ldx + u * 256 + lane * 8;
-                if ((((uintptr_t) xr) & 15) == 0) {
+                if (nd.mode == NB_TAGGED) {
+                    // the previous node publishes this X as {epoch, value} words: spin until the lane's eight carry this launch's tag
+                    const unsigned long long * tp = nd.xtag + (long long) col * tag_stride + u * 256 + lane * 8;
+                    unsigned long long t0 = 0;
+                    for (unsigned spin = 0;; ++spin) {
+                        unsigned long long w[8];
+#pragma unroll
+                        for (int j = 0; j < 8; j += 2)
+                            asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w[j]), "=l"(w[j + 1]) : "l"(tp + j) : "memory");
+                        bool ok = true;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) { ok = ok && (unsigned) (w[j] >> 32) == epoch; v[q][j] = __uint_as_float((unsigned) w[j]); }
+                        if (__all_sync(0xffffffffu, ok)) break;
+                        if ((spin & 1023u) == 1023u) {
+                            unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                            if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
+                        }
+                    }
+                } else if ((((uintptr_t) xr) & 15) == 0) {
                     const float4 lo = ldcg16(xr), hi = ldcg16(xr + 4);
                     v[q][0] = lo.x; v[q][1] = lo.y; v[q][2] = lo.z; v[q][3] = lo.w; v[q][4] = hi.x; v[q][5] = hi.y; v[q][6] = hi.z; v[q][7] = hi.w;
                 } else {
@@ -229,12 +272,12 @@ __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32
 
 // chunks per warp that are quantised together: as many as the node needs, no dead slots (every CTA runs this once per node)
 template <int NCOLS>
-__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane) {
+__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch) {
     const int total = NCOLS * (nd.k >> 8);
     constexpr int NW = CH_CONSUMERS / 32;
-    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane);
-    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane);
-    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane);
+    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane, tag_stride, epoch);
+    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane, tag_stride, epoch);
+    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane, tag_stride, epoch);
 }
 
 // ---- Q4_K: one 256-block per lane --------------------------------------------------------------------------------------
@@ -364,7 +407,7 @@ inline ItemPlan plan_item(bool lane_per_unit, int nrows, int upr) {       // hos
 
 template <int TYPE, int NCOLS>
 __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride, int act_block,
-                                            const ItemPlan pl, uint32_t part, int part_stride, float * y, long long ldy, int gwarp, int lane) {
+                                            const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane) {
     const int nunits = nrows * upr;
     const int j = lane >> 3, g = lane & 7;
     int row = 0, seg = gwarp;
@@ -383,7 +426,7 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
         for (int c = 0; c < NCOLS; ++c) {
             const float v = warp_sum(acc[c]);
             if (lane == 0) {
-                if (pl.segs == 1) y[c * ldy + row] = v;
+                if (pl.segs == 1) put_y(out, c, row, v);
                 else stsf(part + (uint32_t) (c * part_stride + t) * 4, v);
             }
         }
@@ -392,7 +435,7 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
 
 template <int NCOLS>
 __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride,
-                                         const ItemPlan pl, uint32_t part, int part_stride, float * y, long long ldy, int gwarp, int lane,
+                                         const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane,
                                          int rp, int sub, int b) {
     if (upr <= 32) {                                           // rp rows side by side in one warp: lane = (sub, b)
         for (int t = gwarp; t * rp < nrows; t += CH_GWARPS) {
@@ -409,7 +452,7 @@ __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uin
                     const float w = __shfl_down_sync(0xffffffffu, v, o);
                     if (b + o < upr) v += w;
                 }
-                if (live && b == 0) y[c * ldy + row] = v;
+                if (live && b == 0) put_y(out, c, row, v);
             }
         }
     } else {
@@ -448,7 +491,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     const uint32_t base = smem_u32(smem_raw);
     auto full_bar  = [&](int g, int st) { return base + (uint32_t) ((g * CH_NS + st) * 8); };
     auto empty_bar = [&](int g, int st) { return base + 64u + (uint32_t) ((g * CH_NS + st) * 8); };
-    auto desc_at   = [&](int g, int st) { return base + 128u + (uint32_t) ((g * CH_NS + st) * 32); };
+    auto desc_at   = [&](int g, int st) { return base + 128u + (uint32_t) ((g * CH_NS + st) * 48); };
     const uint32_t xs = base + CH_HDR;
     const uint32_t part_bytes = (uint32_t) (NCOLS * a.max_units) * 4;
     const uint32_t ring0 = (xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 127u) & ~127u;
@@ -464,12 +507,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     if (warp == CH_CONSUMERS / 32) {
         if (lane != 0) return;
         const uint64_t policy = policy_evict_first();
-        int nxt[CH_GROUPS], end[CH_GROUPS], seq[CH_GROUPS];
+        int nxt[CH_GROUPS], end[CH_GROUPS], seq[CH_GROUPS], landed[CH_GROUPS];
         ChainItemD item[CH_GROUPS];
 #pragma unroll
         for (int g = 0; g < CH_GROUPS; ++g) {
             const int * off = a.node_off + (long long) (blockIdx.x * CH_GROUPS + g) * (NN + 1);
-            nxt[g] = off[0]; end[g] = off[NN]; seq[g] = 0;
+            nxt[g] = off[0]; end[g] = off[NN]; seq[g] = 0; landed[g] = 0;
             if (nxt[g] < end[g]) item[g] = a.items[nxt[g]];
         }
         while (true) {
@@ -479,11 +522,14 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 if (nxt[g] >= end[g]) continue;
                 pending = true;
                 const int st = seq[g] % CH_NS;
+                while (landed[g] < seq[g] && mbar_test(full_bar(g, landed[g] % CH_NS), (uint32_t) ((landed[g] / CH_NS) & 1))) ++landed[g];
+                if (seq[g] - landed[g] >= a.inflight) continue;
                 if (!mbar_test(empty_bar(g, st), (uint32_t) (((seq[g] / CH_NS) & 1) ^ 1))) continue;
                 const uint32_t dst = ring0 + (uint32_t) (g * CH_NS + st) * (uint32_t) a.stage_bytes, bar = full_bar(g, st), dsc = desc_at(g, st);
                 const unsigned long long yp = (unsigned long long) item[g].y, ld = (unsigned long long) item[g].ldy;
                 asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dsc), "r"((uint32_t) yp), "r"((uint32_t) (yp >> 32)), "r"((uint32_t) ld), "r"((uint32_t) (ld >> 32)) : "memory");
                 asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dsc + 16), "r"((uint32_t) item[g].type), "r"((uint32_t) item[g].nrows), "r"((uint32_t) item[g].segs), "r"((uint32_t) item[g].S) : "memory");
+                { const unsigned long long tg = (unsigned long long) item[g].tag; sts8(dsc + 32, (uint32_t) tg, (uint32_t) (tg >> 32)); }
                 const uint32_t total = item[g].bytes[0] + item[g].bytes[1] + item[g].bytes[2] + item[g].bytes[3];
                 mbar_arrive_expect_tx(bar, total);                       // release: the descriptor is visible to whoever sees the phase flip
                 uint32_t o = 0;
@@ -508,7 +554,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     // B200_CHAIN_TIMELINE: per (CTA, node) eight clock64 values: node start, after the wait, after the X quantiser, node end;
     // then per group: cycles waiting for weight copies, cycles in the item loop
     long long * tl = a.timeline ? a.timeline + ((long long) blockIdx.x * NN) * 8 : nullptr;
+    long long c_rel = 0;
 
+    const unsigned epoch0 = *a.epoch;        // bumped by CTA 0 when it leaves: nobody can still be here by then (see the end of the kernel)
     int pbuf = 0, seq = 0;
     ChainNodeD nd = a.nodes[0];
     int cnt = off[1] - off[0];
@@ -516,12 +564,13 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         ChainNodeD nd_next = nd; int cnt_next = 0;
         if (n + 1 < NN) { nd_next = a.nodes[n + 1]; cnt_next = off[n + 2] - off[n + 1]; }   // lands while this node runs
         if (tl && tid == 0) tl[n * 8 + 0] = clock64();
-        if (n > 0 && tid == 0 && !(a.debug & 1)) {               // X of this node is complete once every CTA has finished the previous node
-            const unsigned want = (unsigned) n * gridDim.x;
+        if (nd.mode != NB_NONE && nd.mode != NB_TAGGED && tid == 0 && !(a.debug & 1)) {
+            // every CTA has finished every earlier node (their arrivals are in). NB_FENCED: X overlaps what they wrote, so the
+            // arrivals were releases and this is the acquire; NB_RELAXED: no data flows through this barrier
             unsigned v; unsigned long long t0 = 0;
             for (unsigned spin = 0;; ++spin) {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.counter) : "memory");
-                if (v >= want) break;
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.counter) : "memory");
+                if (v >= nd.want) { if (nd.mode == NB_FENCED) asm volatile("fence.acq_rel.gpu;" ::: "memory"); break; }
                 if ((spin & 4095u) == 4095u) {
                     unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                     if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
@@ -530,7 +579,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         }
         cons_bar();
         if (tl && tid == 0) tl[n * 8 + 1] = clock64();
-        if (!(a.debug & 4)) chain_quantise_x<NCOLS>(nd, xs, warp, lane);
+        if (!(a.debug & 4)) chain_quantise_x<NCOLS>(nd, xs, warp, lane, a.tag_stride, epoch0 + (unsigned) n);   // tag of node n - 1's output
         cons_bar();
         if (tl && tid == 0) tl[n * 8 + 2] = clock64();
 
@@ -547,23 +596,27 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
             if (tl) c_wait += clock64() - w0;
             const uint4 d0 = lds16(desc_at(grp, st));
             const uint4 d1 = lds16(desc_at(grp, st) + 16);
-            float * y = (float *) (((unsigned long long) d0.y << 32) | d0.x);
-            const long long ldy = (long long) (((unsigned long long) d0.w << 32) | d0.z);
+            const uint2 d2 = lds8(desc_at(grp, st) + 32);
+            YOut out;
+            out.y = (float *) (((unsigned long long) d0.y << 32) | d0.x);
+            out.ldy = (long long) (((unsigned long long) d0.w << 32) | d0.z);
+            out.tag = (unsigned long long *) (((unsigned long long) d2.y << 32) | d2.x);
+            out.tag_stride = a.tag_stride; out.epoch = epoch0 + (unsigned) n + 1u;
             const int type = (int) d1.x, nrows = (int) d1.y;
             ItemPlan pl; pl.segs = (int) d1.z; pl.S = (int) d1.w;
 
             // phase A: every warp reduces its tasks (rows, or runs of units of a row)
             if (a.debug & 2) {
             } else if (type == B200_TYPE_Q4_K) {
-                item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, y, ldy, gwarp, lane, q4_rp, q4_sub, q4_b);
+                item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q6_K) {
-                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
+                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             } else if (type == B200_TYPE_IQ4_XS) {
-                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
+                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             } else if (type == B200_TYPE_Q4_0) {
-                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
+                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             } else {
-                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, y, ldy, gwarp, lane);
+                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_bar(grp, st));     // this warp is done with the stage (and its descriptor)
@@ -576,25 +629,32 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                         const int c = NCOLS == 1 ? 0 : rc / nrows, r = rc - c * nrows;
                         float v = 0.0f;
                         for (int sg = 0; sg < pl.segs; ++sg) v += ldsf(part + (uint32_t) (c * a.max_units + r * pl.segs + sg) * 4);
-                        y[c * ldy + r] = v;
+                        put_y(out, c, r, v);
                     }
                 }
                 pbuf ^= 1;
             }
         }
-        if (tl && gtid == 0) { tl[n * 8 + 4 + 2 * grp] = c_wait; tl[n * 8 + 5 + 2 * grp] = clock64() - c_loop; }
-        cons_bar();                            // every Y store of this CTA is done; the release below publishes them (cumulativity)
-        if (tid == 0 && n + 1 < NN) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
-        if (tl && tid == 0) tl[n * 8 + 3] = clock64();
+        if (tl && gtid == 0) { if (grp == 0) tl[n * 8 + 4] = c_wait; tl[n * 8 + 5 + 2 * grp] = clock64() - c_loop; }
+        if (tl && tid == 0) c_rel = clock64();
+        cons_bar();                            // every store of this CTA is issued; a release below publishes them (cumulativity)
+        if (tid == 0 && nd.signal) {
+            if (nd.signal == 2) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
+            else                asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
+        }
+        if (tl && tid == 0) { tl[n * 8 + 3] = clock64(); tl[n * 8 + 6] = tl[n * 8 + 3] - c_rel; }   // slot 6: cycles in the release (group 1's stall is dropped)
         nd = nd_next; cnt = cnt_next;
     }
+    // next launch, new tags. CTA 0 gets here only after every CTA has passed the start of the last node (or, for a one-node
+    // chain, tags are not used at all), i.e. after everybody has read the old value
+    if (blockIdx.x == 0 && tid == 0) *a.epoch = epoch0 + (unsigned) NN + 1u;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
 struct Chain {
     int device = 0, sms = 0, ncols = 1, n_nodes = 0, n_launch_nodes = 0;
     ChainArgs args = {};
-    void * d_blob = nullptr;
+    void * d_blob = nullptr, * d_tags = nullptr;
     size_t smem = 0;
     bool cooperative = true;
 };
@@ -689,13 +749,48 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
 
     std::vector<ChainNodeD> hn(n_groups);
     std::vector<ChainMatD> hm;       // host-side only: the items carry everything the kernel needs
+
+    // ---- how each node learns that its X is complete (NB_*): from the pointers ------------------------------------------
+    std::vector<int> mode(n_groups, NB_NONE), feed(n_groups, -1), first(n_groups + 1, 0);
+    for (int g = 0; g < n_groups; ++g) first[g + 1] = first[g] + group_sizes[g];
+    int64_t tmax = 256;
+    for (int i = 0; i < first[n_groups]; ++i) tmax = nodes[i].m > tmax ? nodes[i].m : tmax;
+    tmax = (tmax + 255) & ~(int64_t) 255;
+    auto y_lo = [&](const b200_mul_mat_args & a) { return (const char *) a.y; };
+    auto y_hi = [&](const b200_mul_mat_args & a) { return (const char *) (a.y + (a.n - 1) * a.y_row_stride + a.m); };
+    const bool no_tags = getenv("B200_CHAIN_NO_TAGS") != nullptr, all_fenced = getenv("B200_CHAIN_ALL_FENCED") != nullptr;
+    for (int g = 1; g < n_groups; ++g) {
+        const b200_mul_mat_args & a0 = nodes[first[g]];
+        const char * xlo = (const char *) a0.x, * xhi = (const char *) (a0.x + (a0.n - 1) * a0.x_row_stride + a0.k);
+        bool overlap = false;
+        for (int i = 0; i < first[g] && !overlap; ++i) overlap = xlo < y_hi(nodes[i]) && y_lo(nodes[i]) < xhi;
+        mode[g] = overlap || all_fenced ? NB_FENCED : NB_RELAXED;
+        for (int i = first[g - 1]; i < first[g] && !no_tags && !all_fenced; ++i)
+            if (nodes[i].y == a0.x && nodes[i].m == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride)) { mode[g] = NB_TAGGED; feed[g - 1] = i - first[g - 1]; }
+    }
+    // a node whose X overlaps older outputs only PARTLY covered by a tagged predecessor is still fenced: exact match required above
+    unsigned long long * d_tags = nullptr;
+    const size_t tag_bytes = (size_t) 2 * ncols * tmax * 8;
+    if (cudaMalloc((void **) &d_tags, tag_bytes) != cudaSuccess || cudaMemset(d_tags, 0, tag_bytes) != cudaSuccess) {
+        cudaGetLastError(); b200_set_error("b200_chain_create: cudaMalloc of %zu bytes failed", tag_bytes); return nullptr;
+    }
+    {
+        unsigned signalling = 0;
+        for (int g = 0; g < n_groups; ++g) {
+            hn[g].mode = mode[g];
+            hn[g].xtag = mode[g] == NB_TAGGED ? d_tags + (size_t) ((g - 1) & 1) * ncols * tmax : nullptr;
+            hn[g].want = signalling * (unsigned) sms;
+            hn[g].signal = g + 1 < n_groups ? (mode[g + 1] == NB_FENCED ? 2 : mode[g + 1] == NB_RELAXED ? 1 : 0) : 0;
+            if (hn[g].signal) ++signalling;
+        }
+    }
     std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
     int idx = 0;
     for (int g = 0; g < n_groups; ++g) {
         const b200_mul_mat_args & a0 = nodes[idx];
         hn[g].x = a0.x; hn[g].ldx = a0.x_row_stride; hn[g].k = (int) a0.k;
         hn[g].act_block = b200_act_type(a0.type) == B200_TYPE_Q8_K ? 256 : 32;
-        hn[g].flavour = a0.flavour; hn[g].pad = 0;
+        hn[g].flavour = a0.flavour;
         const int upr = (int) (a0.k >> 8);
         // cut the concatenated rows of the group by bytes: VC v gets bytes [v T / VC, (v + 1) T / VC), rounded to row granules
         const int cnt = group_sizes[g];
@@ -732,7 +827,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
                 const int type = nodes[idx + mi].type;
                 const int gr = row_granule(type, upr);
                 int64_t max_rows = (int64_t) stage / ((int64_t) unit_bytes(type) * upr) / gr * gr;
-                if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); return nullptr; }
+                if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); cudaFree(d_tags); return nullptr; }
                 const int64_t rows = r1 - r0;
                 const int64_t nit = (rows + max_rows - 1) / max_rows;
                 int64_t per = ((rows + nit - 1) / nit + gr - 1) / gr * gr;
@@ -742,6 +837,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
                     ChainItemD it = {};
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
+                    it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + r : nullptr;
                     { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     int64_t plane_off = 0;
                     for (int p = 0; p < 4; ++p) {
@@ -780,12 +876,16 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     if (cudaMalloc(&d, total) != cudaSuccess || cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaMalloc/cudaMemcpy of %zu bytes failed: %s", total, cudaGetErrorString(cudaGetLastError()));
         if (d) cudaFree(d);
+        cudaFree(d_tags);
         return nullptr;
     }
     Chain * c = new Chain();
+    c->d_tags = d_tags;
     c->device = device; c->sms = sms; c->ncols = ncols; c->n_nodes = n_groups; c->d_blob = d;
     uint8_t * db = (uint8_t *) d;
     c->args.counter = (unsigned *) db;
+    c->args.epoch = (unsigned *) (db + 128);
+    c->args.tag_stride = tmax;
     c->args.nodes = (const ChainNodeD *) (db + o_nodes);
     c->args.items = (const ChainItemD *) (db + o_items);
     c->args.node_off = (const int *) (db + o_off);
@@ -793,6 +893,8 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
         void * t = nullptr;
         if (cudaMalloc(&t, (size_t) sms * n_groups * 64) == cudaSuccess) { cudaMemset(t, 0, (size_t) sms * n_groups * 64); c->args.timeline = (long long *) t; }
     }
+    c->args.inflight = getenv("B200_CHAIN_INFLIGHT") ? atoi(getenv("B200_CHAIN_INFLIGHT")) : CH_NS;
+    if (c->args.inflight < 1) c->args.inflight = 1;
     c->args.debug = getenv("B200_CHAIN_DEBUG") ? atoi(getenv("B200_CHAIN_DEBUG")) : 0;
     c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes;
     c->smem = CH_HDR + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 128 + (size_t) CH_GROUPS * CH_NS * stage;
@@ -806,7 +908,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     }
     if (e != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        cudaGetLastError(); cudaFree(d); delete c; return nullptr;
+        cudaGetLastError(); cudaFree(d); cudaFree(d_tags); delete c; return nullptr;
     }
     return (b200_chain_t) c;
 }
@@ -852,6 +954,7 @@ int b200_chain_destroy(b200_chain_t chain) {
     Chain * c = (Chain *) chain;
     cudaSetDevice(c->device);
     cudaFree(c->d_blob);
+    cudaFree(c->d_tags);
     if (c->args.timeline) cudaFree(c->args.timeline);
     delete c;
     return 0;
