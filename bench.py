@@ -192,6 +192,8 @@ def main():
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="row split (N > 1): Y slices stored into every rank's arena by the kernels, or one NCCL all-gather per node")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--per-node", action="store_true",
+                    help="tg on one GPU: one launch per MUL_MAT group (CUDA graph) instead of the persistent chain kernel (b200_chain_*)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -226,7 +228,7 @@ def main():
         rowsplit = RowSplit(world, rank, b.row_split)
 
     def time_chain(n, steps, wu):
-        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused")
+        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused", persistent=not args.per_node)
         if chain.capturable:
             chain.capture()
         e0, e1 = b.Event(local), b.Event(local)
@@ -252,6 +254,8 @@ def main():
     # ---- tg: device-resident ---------------------------------------------------------------------------------
     chain, ms_total, clocks = time_chain(1, args.steps, warmup)
     graph_used = chain.graph is not None
+    persistent = chain.decode_chain is not None
+    chain_info = chain.decode_chain.info() if persistent else None
     ms_step = ms_total / args.steps
     tg = 1e3 / ms_step
     launches = (chain.kernels_per_step or len(chain.calls) * 2) * args.steps
@@ -329,14 +333,18 @@ def main():
         "config": {"workload": f"{args.model} tg (N=1): every quantised MUL_MAT of one token ({len(ops)} nodes)",
                    "weights": "random-init blocks, plane layout (load-time repack)", "weight_gb_per_token": bytes_tok / 1e9,
                    "l2": "inputs larger than L2 (weights streamed once per step)", "parallelism": f"row-split x{world}" if world > 1 else "single GPU",
-                   "cuda_graph": graph_used, "exchange": (args.exchange if world > 1 else None)},
+                   "cuda_graph": graph_used, "exchange": (args.exchange if world > 1 else None),
+                   "decode_kernel": ("persistent chain: one launch per token, %d dependent MUL_MAT groups" % chain_info["n_groups"]) if persistent
+                                    else "one launch per MUL_MAT group"},
         "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "traffic": traffic, "peak_source": peak_src, "frac_of_8tbs": achieved / 8000.0,
                      "algorithmic_bytes": bytes_tok / world,
-                     "kernel": "gemv_fused_kernel<1> (+ act_quant_kernel / gemv_kernel for the k = 14336 nodes): all launches of one decode step, "
-                               "bytes and time per step (= per token); traffic from profiles/traffic.json"},
+                     "kernel": ("gemv_chain_kernel<1>: ONE launch = one decode step (every MUL_MAT group of the token), bytes and time per launch; "
+                                if persistent else
+                                "gemv_fused_kernel<1> (+ act_quant_kernel / gemv_kernel for the k = 14336 nodes): all launches of one decode step, "
+                                "bytes and time per step (= per token); ") + "traffic from profiles/traffic.json"},
         "pp512": pp, "cpu_baseline": cpu, "clocks": clocks,
     }
     print(json.dumps(line))
