@@ -228,7 +228,7 @@ def main():
         rowsplit = RowSplit(world, rank, b.row_split)
 
     def time_chain(n, steps, wu):
-        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused", persistent=not args.per_node)
+        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused", persistent=False if args.per_node else "auto")
         if chain.capturable:
             chain.capture()
         e0, e1 = b.Event(local), b.Event(local)
