@@ -169,8 +169,24 @@ B200_API int    b200_mul_mat_group(const b200_mul_mat_args * args, int count, b2
  * strides are baked in at create time (like a captured CUDA graph); workspace/algo/PDL fields are ignored.
  * Requirements (b200_chain_supported): plane layout (or canonical Q4_K), k % 256 == 0, the same n <= 4 everywhere. */
 typedef struct b200_chain * b200_chain_t;
+/* Row split of a chain over `world` GPUs, one process per GPU: nodes[i].m is THIS rank's row count (may be 0),
+ * nodes[i].y points at column row_lo[i] of the full Y inside the symmetric arena (as for b200_mul_mat_gather). Every finished
+ * row, every tagged word and every barrier arrival is stored into every rank's arena over NVLink by the kernel itself; the
+ * launch completes on a rank only when all ranks' stores into its arena are done. `scratch`: zero-initialised region inside
+ * the symmetric arena (same offset on every rank), 256 B aligned, >= b200_chain_scratch_bytes(max m_full, n) bytes. */
+typedef struct b200_chain_split {
+    int32_t world, rank;
+    int64_t peer_delta[8];        /* as in b200_row_gather                                   */
+    void *  scratch;
+    size_t  scratch_bytes;
+    const int64_t * row_lo;       /* per node: first row of this rank's slice                */
+    const int64_t * m_full;       /* per node: rows of the whole matrix                      */
+} b200_chain_split;
 B200_API int          b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups);
 B200_API b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups); /* NULL on failure */
+B200_API size_t       b200_chain_scratch_bytes(int64_t max_m_full, int n);
+B200_API b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups,
+                                              const b200_chain_split * split);      /* split == NULL: b200_chain_create */
 B200_API int          b200_chain_launch(b200_chain_t chain, b200_stream_t stream);   /* asynchronous, CUDA-graph capturable */
 B200_API int          b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * smem_bytes, int * n_groups);
 B200_API int          b200_chain_timeline(b200_chain_t chain, long long * host, size_t count);  /* debugging aid, see gemv_chain.cu */

@@ -28,7 +28,7 @@ def main():
     for model in ("tiny-q4_k_m", "tiny-moe-q4_k_m"):
         ops = W.model_ops(model)
         for n in (1, 64):
-            ref = MatMulChain(ops, n, device=local)
+            ref = MatMulChain(ops, n, device=local, persistent=False)      # the reference is the per-node single-GPU path
             x0 = ref.bufs["x"].clone()
             ref.step(); ref.stream.synchronize()
             want = {k: v.clone() for k, v in ref.bufs.items()}
@@ -36,8 +36,13 @@ def main():
                 if not bool(torch.isfinite(w).all()) or float(w.abs().max()) == 0.0:
                     failures += 1
                     print(f"[rank {rank}] reference buffer {name} of {model} n={n} is not finite / all zero: the check would be vacuous", flush=True)
-            for fused in (True, False):
-                ch = MatMulChain(ops, n, device=local, rowsplit=rs, fused_exchange=fused)
+            for fused, persistent in ((True, True), (True, False), (False, False)):
+                if persistent and (n > 4 or "moe" in model):
+                    continue
+                ch = MatMulChain(ops, n, device=local, rowsplit=rs, fused_exchange=fused, persistent=persistent)
+                if persistent and ch.decode_chain is None:
+                    failures += 1
+                    print(f"[rank {rank}] {model} n={n}: the persistent row-split chain was not created: {b.lib.b200_last_error().decode()}", flush=True)
                 modes = ["eager", "eager"] + (["graph", "graph", "graph"] if ch.capturable else [])
                 for i, mode in enumerate(modes):
                     if mode == "graph" and ch.graph is None:
@@ -53,7 +58,7 @@ def main():
                             err = float((got - w).abs().max())
                             print(f"[rank {rank}] MISMATCH {model} n={n} exchange={'fused' if fused else 'nccl'} pass {i} ({mode}) buffer {name}: max|d|={err:.3e}", flush=True)
                 if rank == 0:
-                    print(f"{model} n={n} exchange={'fused' if fused else 'nccl'} world={world}: {len(modes)} passes "
+                    print(f"{model} n={n} exchange={'chain' if ch.decode_chain is not None else 'fused' if fused else 'nccl'} world={world}: {len(modes)} passes "
                           f"({'graph replay included' if ch.capturable else 'eager only'}) checked", flush=True)
                 ch.close()
                 del ch

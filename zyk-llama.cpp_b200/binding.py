@@ -59,6 +59,12 @@ class RowGather(C.Structure):
                 ("step", C.c_void_p), ("seq", C.c_int64), ("calls_per_step", C.c_int64)]
 
 
+class ChainSplit(C.Structure):
+    """mirror of b200_chain_split (include/b200_mm.h): a decode chain row-split over the GPUs of one box"""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("peer_delta", C.c_int64 * MAX_PEERS), ("scratch", C.c_void_p),
+                ("scratch_bytes", C.c_size_t), ("row_lo", C.POINTER(C.c_int64)), ("m_full", C.POINTER(C.c_int64))]
+
+
 def _sig(name, restype, *argtypes):
     fn = getattr(lib, name)
     fn.restype = restype
@@ -79,6 +85,8 @@ _sig("b200_mul_mat", C.c_int, C.POINTER(MulMatArgs), C.c_void_p)
 _sig("b200_mul_mat_group", C.c_int, C.POINTER(MulMatArgs), C.c_int, C.c_void_p)
 _sig("b200_chain_supported", C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
 _sig("b200_chain_create", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
+_sig("b200_chain_create_split", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int, C.POINTER(ChainSplit))
+_sig("b200_chain_scratch_bytes", C.c_size_t, C.c_int64, C.c_int)
 _sig("b200_chain_launch", C.c_int, C.c_void_p, C.c_void_p)
 _sig("b200_chain_info", C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))
 _sig("b200_chain_destroy", C.c_int, C.c_void_p)
@@ -283,12 +291,26 @@ class DecodeChain:
     """b200_chain_*: a sequence of dependent MUL_MAT groups (decode, n <= 4) as ONE persistent launch.
     `groups` is a list of lists of MulMatArgs (nodes of one group read the same X)."""
 
-    def __init__(self, device: int, groups):
+    def __init__(self, device: int, groups, split=None):
+        """split: None, or dict(world, rank, peer_delta, scratch, scratch_bytes, row_lo, m_full) with row_lo / m_full per node in
+        the order of the flattened groups (b200_chain_create_split: row split over the GPUs of one box)"""
         flat = [a for g in groups for a in g]
         self._args = (MulMatArgs * len(flat))(*flat)
         self._sizes = (C.c_int32 * len(groups))(*[len(g) for g in groups])
         self.n_groups = len(groups)
-        self.handle = lib.b200_chain_create(device, self._args, self._sizes, len(groups))
+        self.handle = None
+        if split is None:
+            self.handle = lib.b200_chain_create(device, self._args, self._sizes, len(groups))
+        else:
+            self._lo = (C.c_int64 * len(flat))(*split["row_lo"])
+            self._mf = (C.c_int64 * len(flat))(*split["m_full"])
+            sp = ChainSplit()
+            sp.world, sp.rank = split["world"], split["rank"]
+            for r, d in enumerate(split["peer_delta"]):
+                sp.peer_delta[r] = d
+            sp.scratch, sp.scratch_bytes = split["scratch"], split["scratch_bytes"]
+            sp.row_lo, sp.m_full = self._lo, self._mf
+            self.handle = lib.b200_chain_create_split(device, self._args, self._sizes, len(groups), C.byref(sp))
         if not self.handle:
             raise B200Error(lib.b200_last_error().decode())
 

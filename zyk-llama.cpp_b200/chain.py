@@ -69,6 +69,9 @@ class MatMulChain:
         if self.fused_exchange:
             from .rowsplit import SymmetricArena
             total = sum(((r * w * 4 + 255) & ~255) for r, w in shapes.values())
+            # scratch of the persistent row-split chain (tags + counters), also inside the arena
+            self._chain_scratch_bytes = int(B.lib.b200_chain_scratch_bytes(max(o.m for o in ops), n)) if n <= 4 else 0
+            total += (self._chain_scratch_bytes + 255) & ~255
             self.arena = SymmetricArena(B, device, world, rank, total, group=rowsplit.group)
         for name, (rows, width) in shapes.items():
             init = torch.randn((rows, width), device=self.dev, generator=gen)      # same seed on every rank: same activations
@@ -103,6 +106,17 @@ class MatMulChain:
             groups = [list(c[1]) for c in self.calls]
             if B.DecodeChain.supported(groups):
                 self.decode_chain = B.DecodeChain(device, groups)
+        elif persistent and self.fused_exchange and n <= 4 and all(c[0] is B.lib.b200_mul_mat_gather for c in self.calls):
+            # row split: the same kernel, every row / tag / arrival stored into every rank's arena (b200_chain_create_split)
+            groups = [list(c[1]) for c in self.calls]
+            flat_ops = [o for c in self.calls for o in c[2]]
+            split = dict(world=world, rank=rank, peer_delta=self.arena.deltas(),
+                         scratch=self.arena.raw(self._chain_scratch_bytes), scratch_bytes=self._chain_scratch_bytes,
+                         row_lo=[rowsplit.mine(o.m)[0] for o in flat_ops], m_full=[o.m for o in flat_ops])
+            try:
+                self.decode_chain = B.DecodeChain(device, groups, split=split)
+            except B.B200Error:
+                self.decode_chain = None        # e.g. a shape the chain does not take: the per-node exchange path stays
         self.graph = None
         self.kernels_per_step = 0
         torch.cuda.synchronize(self.dev)
@@ -195,6 +209,9 @@ class MatMulChain:
             torch.cuda.synchronize(self.dev)
             dist.barrier(group=self.rowsplit.group)
             self.graph = None
+            if self.decode_chain is not None:
+                self.decode_chain.close()
+                self.decode_chain = None
             self.bufs.clear()
             self.arena.close()
             dist.barrier(group=self.rowsplit.group)

@@ -81,13 +81,17 @@ struct ChainArgs {
     const ChainNodeD * nodes;
     const ChainItemD * items;
     const int * node_off;     // [vc][n_nodes + 1] -> index into items (items are VC-major, node-ordered)
-    unsigned * counter;       // arrivals: every CTA adds one per finished node (zeroed before the launch)
+    unsigned long long * counter;   // arrivals of the counter barriers, never reset: targets are relative to the launch number
+    unsigned long long * done;      // row split: CTAs of all ranks that have finished the whole chain (never reset)
+    unsigned long long * launches;  // launches of this chain so far (local): base of the counter targets and of the tags
+    unsigned long long per_launch;  // arrivals one launch adds to `counter` (signalling nodes x CTAs x ranks)
+    int world, rank;                // row split over `world` GPUs (1: off): every Y row, tagged word and arrival goes to every rank,
+    long long delta[B200_MAX_PEERS];//   local address + delta[g] = the same location of rank g's symmetric arena
     int n_nodes;
     int stage_bytes;          // bytes per ring stage
     int max_units;            // stride of the partial-sum buffers
     int x_bytes;              // shared memory reserved for the quantised X
     long long * timeline;     // B200_CHAIN_TIMELINE: clock64 samples per (CTA, node), see the kernel
-    unsigned * epoch;         // launches so far x nodes: makes the tags of every (launch, node) unique
     long long tag_stride;     // elements between the columns of a tagged vector
     int inflight;             // copies per group that may be in flight (issued, not landed): bounds the queueing delay the stream adds to the node barrier
     int debug;                // B200_CHAIN_DEBUG (timing experiments, results wrong): 1 no node wait, 2 no dot products, 4 no X quantiser, 8 no row sums
@@ -128,15 +132,20 @@ __device__ __forceinline__ float4 ldcg16(const float * p) {
 }
 __device__ __forceinline__ float ldcg4(const float * p) { float r; asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory"); return r; }
 
-__device__ __forceinline__ void st_tagged(unsigned long long * p, float v, unsigned epoch) {
-    const unsigned long long w = ((unsigned long long) epoch << 32) | (unsigned long long) __float_as_uint(v);
-    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(p), "l"(w) : "memory");
-}
-// y and (when the next node reads these rows) the tagged copy
-struct YOut { float * y; long long ldy; unsigned long long * tag; long long tag_stride; unsigned epoch; };
+// y and (when the next node reads these rows) the tagged copy; row split: into every rank's arena
+struct YOut { float * y; long long ldy; unsigned long long * tag; long long tag_stride; unsigned epoch; int world; const long long * delta; };
 __device__ __forceinline__ void put_y(const YOut & o, int c, int row, float v) {
-    o.y[c * o.ldy + row] = v;
-    if (o.tag) st_tagged(o.tag + c * o.tag_stride + row, v, o.epoch);
+    float * yp = o.y + c * o.ldy + row;
+    const unsigned long long w = ((unsigned long long) o.epoch << 32) | (unsigned long long) __float_as_uint(v);
+    if (o.world <= 1) {
+        *yp = v;
+        if (o.tag) asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(o.tag + c * o.tag_stride + row), "l"(w) : "memory");
+    } else {
+        for (int g = 0; g < o.world; ++g) {
+            *reinterpret_cast<float *>(reinterpret_cast<char *>(yp) + o.delta[g]) = v;
+            if (o.tag) asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(reinterpret_cast<char *>(o.tag + c * o.tag_stride + row) + o.delta[g]), "l"(w) : "memory");
+        }
+    }
 }
 __device__ __forceinline__ void group_bar(int grp) { asm volatile("bar.sync %0, %1;" :: "r"(grp + 1), "n"(CH_GTHREADS) : "memory"); }
 
@@ -160,7 +169,7 @@ __device__ __forceinline__ int dot16_us(const uint4 & a, const uint4 & b) {
 // ---- activation quantiser into the shared-memory unit layout ---------------------------------------------------------
 //   unit (col, u): [qs 256 B, chunks placed by xpos][bs16: 16 x i16][bs32: 8 x i16][d: 8 x f32 (Q8_K uses d[0])]
 template <int NCOLS, int QU>
-__device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch) {
+__device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch, bool sys) {
     const int upr = nd.k >> 8;
     const int total = NCOLS * upr;
     constexpr int NW = CH_CONSUMERS / 32;
@@ -182,8 +191,10 @@ __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32
                     for (unsigned spin = 0;; ++spin) {
                         unsigned long long w[8];
 #pragma unroll
-                        for (int j = 0; j < 8; j += 2)
-                            asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w[j]), "=l"(w[j + 1]) : "l"(tp + j) : "memory");
+                        for (int j = 0; j < 8; j += 2) {
+                            if (sys) asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(w[j]), "=l"(w[j + 1]) : "l"(tp + j) : "memory");
+                            else     asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w[j]), "=l"(w[j + 1]) : "l"(tp + j) : "memory");
+                        }
                         bool ok = true;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) { ok = ok && (unsigned) (w[j] >> 32) == epoch; v[q][j] = __uint_as_float((unsigned) w[j]); }
@@ -272,12 +283,12 @@ __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32
 
 // chunks per warp that are quantised together: as many as the node needs, no dead slots (every CTA runs this once per node)
 template <int NCOLS>
-__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch) {
+__device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch, bool sys) {
     const int total = NCOLS * (nd.k >> 8);
     constexpr int NW = CH_CONSUMERS / 32;
-    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane, tag_stride, epoch);
-    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane, tag_stride, epoch);
-    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane, tag_stride, epoch);
+    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane, tag_stride, epoch, sys);
+    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane, tag_stride, epoch, sys);
+    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane, tag_stride, epoch, sys);
 }
 
 // ---- Q4_K: one 256-block per lane --------------------------------------------------------------------------------------
@@ -556,7 +567,10 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     long long * tl = a.timeline ? a.timeline + ((long long) blockIdx.x * NN) * 8 : nullptr;
     long long c_rel = 0;
 
-    const unsigned epoch0 = *a.epoch;        // bumped by CTA 0 when it leaves: nobody can still be here by then (see the end of the kernel)
+    // launch number: bumped by CTA 0 when it leaves; nobody can still be reading it by then (see the end of the kernel)
+    const unsigned long long launch = *a.launches;
+    const unsigned epoch0 = (unsigned) (launch * (unsigned long long) (NN + 1));      // tags of this launch: epoch0 + 1 .. epoch0 + NN
+    const unsigned long long arrivals0 = launch * a.per_launch;
     int pbuf = 0, seq = 0;
     ChainNodeD nd = a.nodes[0];
     int cnt = off[1] - off[0];
@@ -567,10 +581,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         if (nd.mode != NB_NONE && nd.mode != NB_TAGGED && tid == 0 && !(a.debug & 1)) {
             // every CTA has finished every earlier node (their arrivals are in). NB_FENCED: X overlaps what they wrote, so the
             // arrivals were releases and this is the acquire; NB_RELAXED: no data flows through this barrier
-            unsigned v; unsigned long long t0 = 0;
+            const unsigned long long want = arrivals0 + (unsigned long long) nd.want * (unsigned) a.world;
+            unsigned long long v, t0 = 0;
             for (unsigned spin = 0;; ++spin) {
-                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.counter) : "memory");
-                if (v >= nd.want) { if (nd.mode == NB_FENCED) asm volatile("fence.acq_rel.gpu;" ::: "memory"); break; }
+                if (a.world > 1) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
+                else             asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
+                if (v >= want) { if (nd.mode == NB_FENCED) asm volatile("fence.acq_rel.gpu;" ::: "memory"); break; }
                 if ((spin & 4095u) == 4095u) {
                     unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                     if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
@@ -579,7 +595,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         }
         cons_bar();
         if (tl && tid == 0) tl[n * 8 + 1] = clock64();
-        if (!(a.debug & 4)) chain_quantise_x<NCOLS>(nd, xs, warp, lane, a.tag_stride, epoch0 + (unsigned) n);   // tag of node n - 1's output
+        if (!(a.debug & 4)) chain_quantise_x<NCOLS>(nd, xs, warp, lane, a.tag_stride, epoch0 + (unsigned) n, a.world > 1);   // tag of node n - 1's output
         cons_bar();
         if (tl && tid == 0) tl[n * 8 + 2] = clock64();
 
@@ -602,6 +618,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
             out.ldy = (long long) (((unsigned long long) d0.w << 32) | d0.z);
             out.tag = (unsigned long long *) (((unsigned long long) d2.y << 32) | d2.x);
             out.tag_stride = a.tag_stride; out.epoch = epoch0 + (unsigned) n + 1u;
+            out.world = a.world; out.delta = a.delta;
             const int type = (int) d1.x, nrows = (int) d1.y;
             ItemPlan pl; pl.segs = (int) d1.z; pl.S = (int) d1.w;
 
@@ -639,15 +656,41 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         if (tl && tid == 0) c_rel = clock64();
         cons_bar();                            // every store of this CTA is issued; a release below publishes them (cumulativity)
         if (tid == 0 && nd.signal) {
-            if (nd.signal == 2) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
-            else                asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" :: "l"(a.counter) : "memory");
+            if (a.world > 1) {                  // (row split: relaxed arrivals only, checked at create time)
+                for (int g = 0; g < a.world; ++g)
+                    asm volatile("red.relaxed.sys.global.add.u64 [%0], 1;" :: "l"(reinterpret_cast<char *>(a.counter) + a.delta[g]) : "memory");
+            } else if (nd.signal == 2) asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter) : "memory");
+            else                       asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter) : "memory");
         }
         if (tl && tid == 0) { tl[n * 8 + 3] = clock64(); tl[n * 8 + 6] = tl[n * 8 + 3] - c_rel; }   // slot 6: cycles in the release (group 1's stall is dropped)
         nd = nd_next; cnt = cnt_next;
     }
-    // next launch, new tags. CTA 0 gets here only after every CTA has passed the start of the last node (or, for a one-node
-    // chain, tags are not used at all), i.e. after everybody has read the old value
-    if (blockIdx.x == 0 && tid == 0) *a.epoch = epoch0 + (unsigned) NN + 1u;
+    if (a.world > 1) {
+        // row split: this rank's kernel may only complete when every rank's stores into its arena have been performed, so that
+        // whatever follows on the stream sees the whole Y. Every CTA of every rank: system fence (covers the CTA's peer stores:
+        // the barrier above + cumulativity), then one arrival on every rank's `done`; CTA 0 waits for all of them.
+        if (tid == 0) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+            for (int g = 0; g < a.world; ++g)
+                asm volatile("red.relaxed.sys.global.add.u64 [%0], 1;" :: "l"(reinterpret_cast<char *>(a.done) + a.delta[g]) : "memory");
+            if (blockIdx.x == 0) {
+                const unsigned long long want = (launch + 1ull) * (unsigned long long) gridDim.x * (unsigned) a.world;
+                unsigned long long v, t0 = 0;
+                for (unsigned spin = 0;; ++spin) {
+                    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.done) : "memory");
+                    if (v >= want) break;
+                    __nanosleep(100);
+                    if ((spin & 1023u) == 1023u) {
+                        unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                        if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
+                    }
+                }
+            }
+        }
+    }
+    // next launch, new tags and counter targets. CTA 0 gets here only after every CTA has passed the start of the last node
+    // (a one-node chain uses neither), i.e. after everybody has read the old value
+    if (blockIdx.x == 0 && tid == 0) *a.launches = launch + 1ull;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
@@ -684,7 +727,7 @@ template <int NCOLS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s)
     return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS>, c.args);
 }
 
-const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
+const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, bool split = false) {
     if (!nodes || !group_sizes || n_groups < 1) return "no nodes";
     int idx = 0;
     const int64_t n0 = nodes[0].n;
@@ -698,7 +741,7 @@ const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_
             if (!chain_type_ok(a.type)) return "weight type";
             if (a.n != n0) return "all nodes of a chain need the same n";
             if (a.k <= 0 || a.k % 256 != 0 || a.k > 65536) return "k must be a multiple of 256 (<= 65536)";
-            if (a.m <= 0 || a.m > (1 << 30)) return "m out of range";
+            if (a.m < (split ? 0 : 1) || a.m > (1 << 30)) return "m out of range";      // a rank's slice of a small matrix may be empty
             if (a.x != a0.x || a.k != a0.k || a.x_row_stride != a0.x_row_stride || a.flavour != a0.flavour) return "nodes of a group must read the same X";
             if (b200_act_type(a.type) != b200_act_type(a0.type)) return "nodes of a group need the same activation format";
             if (a.layout != B200_LAYOUT_PLANES && a.type != B200_TYPE_Q4_K) return "plane layout required";
@@ -719,9 +762,23 @@ int b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_
     return chain_check(nodes, group_sizes, n_groups) == nullptr ? 1 : 0;
 }
 
+size_t b200_chain_scratch_bytes(int64_t max_m_full, int ncols) {
+    const int64_t tmax = ((max_m_full > 256 ? max_m_full : 256) + 255) & ~(int64_t) 255;
+    return 256 + (size_t) 2 * (size_t) (ncols > 0 ? ncols : 1) * (size_t) tmax * 8;
+}
+
 b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
-    const char * why = chain_check(nodes, group_sizes, n_groups);
+    return b200_chain_create_split(device, nodes, group_sizes, n_groups, nullptr);
+}
+
+b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, const b200_chain_split * split) {
+    const char * why = chain_check(nodes, group_sizes, n_groups, split != nullptr);
     if (why) { b200_set_error("b200_chain_create: %s", why); return nullptr; }
+    const int world = split ? split->world : 1;
+    if (split && (world < 2 || world > B200_MAX_PEERS || split->rank < 0 || split->rank >= world || !split->scratch || !split->row_lo || !split->m_full ||
+                  split->peer_delta[split->rank] != 0 || (((uintptr_t) split->scratch) & 255) != 0)) {
+        b200_set_error("b200_chain_create_split: bad descriptor (world %d rank %d)", world, split->rank); return nullptr;
+    }
     if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); b200_set_error("b200_chain_create: cudaSetDevice(%d) failed", device); return nullptr; }
     int sms = 0, smem_optin = 0, coop = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
@@ -754,26 +811,37 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     std::vector<int> mode(n_groups, NB_NONE), feed(n_groups, -1), first(n_groups + 1, 0);
     for (int g = 0; g < n_groups; ++g) first[g + 1] = first[g] + group_sizes[g];
     int64_t tmax = 256;
-    for (int i = 0; i < first[n_groups]; ++i) tmax = nodes[i].m > tmax ? nodes[i].m : tmax;
+    auto lo_of = [&](int i) { return split ? split->row_lo[i] : (int64_t) 0; };          // first row of this rank's slice
+    auto mf_of = [&](int i) { return split ? split->m_full[i] : nodes[i].m; };           // rows of the whole matrix
+    for (int i = 0; i < first[n_groups]; ++i) tmax = mf_of(i) > tmax ? mf_of(i) : tmax;
     tmax = (tmax + 255) & ~(int64_t) 255;
-    auto y_lo = [&](const b200_mul_mat_args & a) { return (const char *) a.y; };
-    auto y_hi = [&](const b200_mul_mat_args & a) { return (const char *) (a.y + (a.n - 1) * a.y_row_stride + a.m); };
+    // the whole Y of node i (every rank's rows: with the row split all of it is written into this rank's arena)
+    auto y_lo = [&](int i) { return (const char *) (nodes[i].y - lo_of(i)); };
+    auto y_hi = [&](int i) { return (const char *) (nodes[i].y - lo_of(i) + (nodes[i].n - 1) * nodes[i].y_row_stride + mf_of(i)); };
     const bool no_tags = getenv("B200_CHAIN_NO_TAGS") != nullptr, all_fenced = getenv("B200_CHAIN_ALL_FENCED") != nullptr;
     for (int g = 1; g < n_groups; ++g) {
         const b200_mul_mat_args & a0 = nodes[first[g]];
         const char * xlo = (const char *) a0.x, * xhi = (const char *) (a0.x + (a0.n - 1) * a0.x_row_stride + a0.k);
         bool overlap = false;
-        for (int i = 0; i < first[g] && !overlap; ++i) overlap = xlo < y_hi(nodes[i]) && y_lo(nodes[i]) < xhi;
+        for (int i = 0; i < first[g] && !overlap; ++i) overlap = xlo < y_hi(i) && y_lo(i) < xhi;
         mode[g] = overlap || all_fenced ? NB_FENCED : NB_RELAXED;
         for (int i = first[g - 1]; i < first[g] && !no_tags && !all_fenced; ++i)
-            if (nodes[i].y == a0.x && nodes[i].m == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride)) { mode[g] = NB_TAGGED; feed[g - 1] = i - first[g - 1]; }
+            if (nodes[i].y - lo_of(i) == a0.x && mf_of(i) == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride)) { mode[g] = NB_TAGGED; feed[g - 1] = i - first[g - 1]; }
+        if (split && mode[g] == NB_FENCED) {
+            b200_set_error("b200_chain_create_split: group %d reads rows an earlier group wrote without being its direct successor: not supported with the row split", g);
+            return nullptr;
+        }
     }
     // a node whose X overlaps older outputs only PARTLY covered by a tagged predecessor is still fenced: exact match required above
     unsigned long long * d_tags = nullptr;
     const size_t tag_bytes = (size_t) 2 * ncols * tmax * 8;
-    if (cudaMalloc((void **) &d_tags, tag_bytes) != cudaSuccess || cudaMemset(d_tags, 0, tag_bytes) != cudaSuccess) {
+    if (split) {                               // tags and counters live in the symmetric arena: every rank stores into every rank's copy
+        if (split->scratch_bytes < 256 + tag_bytes) { b200_set_error("b200_chain_create_split: scratch %zu < %zu bytes", split->scratch_bytes, 256 + tag_bytes); return nullptr; }
+        d_tags = (unsigned long long *) ((char *) split->scratch + 256);
+    } else if (cudaMalloc((void **) &d_tags, tag_bytes) != cudaSuccess || cudaMemset(d_tags, 0, tag_bytes) != cudaSuccess) {
         cudaGetLastError(); b200_set_error("b200_chain_create: cudaMalloc of %zu bytes failed", tag_bytes); return nullptr;
     }
+    unsigned signalling_total = 0;
     {
         unsigned signalling = 0;
         for (int g = 0; g < n_groups; ++g) {
@@ -783,6 +851,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
             hn[g].signal = g + 1 < n_groups ? (mode[g + 1] == NB_FENCED ? 2 : mode[g + 1] == NB_RELAXED ? 1 : 0) : 0;
             if (hn[g].signal) ++signalling;
         }
+        signalling_total = signalling;
     }
     std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
     int idx = 0;
@@ -827,7 +896,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
                 const int type = nodes[idx + mi].type;
                 const int gr = row_granule(type, upr);
                 int64_t max_rows = (int64_t) stage / ((int64_t) unit_bytes(type) * upr) / gr * gr;
-                if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); cudaFree(d_tags); return nullptr; }
+                if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); if (!split) cudaFree(d_tags); return nullptr; }
                 const int64_t rows = r1 - r0;
                 const int64_t nit = (rows + max_rows - 1) / max_rows;
                 int64_t per = ((rows + nit - 1) / nit + gr - 1) / gr * gr;
@@ -837,7 +906,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
                     ChainItemD it = {};
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
-                    it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + r : nullptr;
+                    it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
                     { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     int64_t plane_off = 0;
                     for (int p = 0; p < 4; ++p) {
@@ -876,15 +945,20 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     if (cudaMalloc(&d, total) != cudaSuccess || cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaMalloc/cudaMemcpy of %zu bytes failed: %s", total, cudaGetErrorString(cudaGetLastError()));
         if (d) cudaFree(d);
-        cudaFree(d_tags);
+        if (!split) cudaFree(d_tags);
         return nullptr;
     }
     Chain * c = new Chain();
-    c->d_tags = d_tags;
+    c->d_tags = split ? nullptr : d_tags;
     c->device = device; c->sms = sms; c->ncols = ncols; c->n_nodes = n_groups; c->d_blob = d;
     uint8_t * db = (uint8_t *) d;
-    c->args.counter = (unsigned *) db;
-    c->args.epoch = (unsigned *) (db + 128);
+    // single GPU: counters in the chain's own blob; row split: in the symmetric arena (peers add to them)
+    c->args.counter = split ? (unsigned long long *) split->scratch : (unsigned long long *) db;
+    c->args.done = split ? (unsigned long long *) split->scratch + 8 : (unsigned long long *) db + 8;
+    c->args.launches = (unsigned long long *) (db + 128);
+    c->args.world = world; c->args.rank = split ? split->rank : 0;
+    for (int g = 0; g < B200_MAX_PEERS; ++g) c->args.delta[g] = split && g < world ? split->peer_delta[g] : 0;
+    c->args.per_launch = (unsigned long long) signalling_total * (unsigned) sms * (unsigned) world;
     c->args.tag_stride = tmax;
     c->args.nodes = (const ChainNodeD *) (db + o_nodes);
     c->args.items = (const ChainItemD *) (db + o_items);
@@ -908,7 +982,7 @@ b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, cons
     }
     if (e != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        cudaGetLastError(); cudaFree(d); cudaFree(d_tags); delete c; return nullptr;
+        cudaGetLastError(); cudaFree(d); if (!split) cudaFree(d_tags); delete c; return nullptr;
     }
     return (b200_chain_t) c;
 }
@@ -917,7 +991,6 @@ int b200_chain_launch(b200_chain_t chain, b200_stream_t stream) {
     B200_REQUIRE(chain, "b200_chain_launch: null chain");
     Chain * c = (Chain *) chain;
     cudaStream_t s = (cudaStream_t) stream;
-    B200_CHECK(cudaMemsetAsync(c->args.counter, 0, 64, s));
     cudaError_t e;
     switch (c->ncols) {
         case 1: e = chain_launch_t<1>(*c, s); break;

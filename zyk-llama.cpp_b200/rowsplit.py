@@ -131,6 +131,13 @@ class SymmetricArena:
         self._keep.append(v)
         return torch.as_tensor(v, device=torch.device(f"cuda:{self.device}"))
 
+    def raw(self, nbytes: int) -> int:
+        """device address of the next slot of `nbytes` (zero-initialised like the whole arena), 256 B aligned"""
+        assert self.used + nbytes <= self.size, "arena too small"
+        ptr = self.base + self.used
+        self.used += (nbytes + 255) & ~255
+        return ptr
+
     def gather_desc(self, seq: int, calls_per_step: int):
         g = self.b.RowGather()
         g.world, g.rank = self.world, self.rank
