@@ -34,9 +34,12 @@ def show_timeline(tl, call_ops, mhz=1965.0):
         items = (t[:, :, 3] - t[:, :, 2]).mean()
         stall = t[:, :, 4].mean()
         rel = t[:, :, 6].mean()
-        loop = t[:, :, [5, 7]].mean()
+        loop = t[:, :, 5].mean()
+        gt = t[:, :, 7]                      # globaltimer at the end of the node, per CTA
+        skew = (gt.max(axis=0) - np.median(gt, axis=0)).mean() / 1e3
+        spread = (gt.max(axis=0) - gt.min(axis=0)).mean() / 1e3
         mb = sum(o.streamed_bytes for o in call_ops[idx[0]]) / 1e6
-        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
+        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} end-skew max-med {skew:5.2f} max-min {spread:5.2f} us | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
 
 
 def run(ops, persistent, steps):
