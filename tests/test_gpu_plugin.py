@@ -1,0 +1,44 @@
+"""GPU (-m gpu): the ggml backend plugin (libggml-b200.so) driven through the reference's own public API.
+
+* the reference's unmodified conformance harness (tests/test-backend-ops.cpp, built by oracle/Makefile into oracle/_ref) on a
+  slice of its MUL_MAT cases, loaded the way the reference loads any out-of-tree backend (GGML_BACKEND_PATH);
+* a multi-node decode graph ({wq,wk,wv} -> wo -> {gate,up} -> down) on the reference CPU backend and on the plugin
+  (oracle/plugin_graph_check.cpp): graph_compute's grouping (b200_mul_mat_group) and decode-chain (b200_chain_*) paths.
+Skipped where oracle/_ref was not built for the host CPU (the reference binaries need avx512_vnni)."""
+import os
+import subprocess
+from pathlib import Path
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+VAR = ROOT / "oracle" / "_ref" / "avx512vnni"
+
+
+def _need(binary):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not (VAR / binary).exists() or "avx512_vnni" not in open("/proc/cpuinfo").read():
+        pytest.skip("oracle/_ref not built for this host CPU")
+    plugin = ROOT / "zyk-llama.cpp_b200" / "lib" / "libggml-b200.so"
+    assert plugin.exists(), "the plugin is not built (no fallback)"
+    return dict(os.environ, GGML_BACKEND_PATH=str(plugin))
+
+
+@pytest.mark.parametrize("mode", [{}, {"GGML_B200_CHAIN": "0"}, {"GGML_B200_GROUP": "0"}], ids=["chain", "groups", "per-node"])
+@pytest.mark.parametrize("n", [1, 3, 64])
+def test_multi_node_graph_matches_reference_cpu_backend(mode, n):
+    env = _need("plugin_graph_check")
+    env.update(mode)
+    r = subprocess.run([str(VAR / "plugin_graph_check"), str(n)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "PLUGIN_GRAPH_CHECK OK" in r.stdout, r.stdout[-3000:]
+
+
+def test_reference_conformance_harness_q4_K_slice():
+    env = _need("test-backend-ops")
+    r = subprocess.run([str(VAR / "test-backend-ops"), "test", "-o", "MUL_MAT", "-p", "type_a=q4_K"], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    tail = r.stdout[-2000:]
+    assert r.returncode == 0 and "tests passed" in tail and "FAIL" not in tail, tail

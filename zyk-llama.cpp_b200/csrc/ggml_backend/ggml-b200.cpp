@@ -76,6 +76,10 @@ struct backend_ctx {
     b200_stream_t stream = nullptr;
     void *        workspace = nullptr;
     size_t        workspace_size = 0;
+    // decode chains built from runs of MUL_MAT groups (b200_chain_*), keyed by the exact argument list: pointers, shapes and
+    // strides are baked into a chain like into a graph plan (ggml_backend_graph_plan_create, ggml-backend-impl.h:103-110)
+    struct cached_chain { std::vector<b200_mul_mat_args> args; std::vector<int32_t> sizes; b200_chain_t chain; };
+    std::vector<cached_chain> chains;
 };
 
 bool repack_enabled() {
@@ -395,6 +399,7 @@ void backend_free(ggml_backend_t backend) {
     b200_set_device(bc->device);
     if (bc->stream) { b200_stream_synchronize(bc->stream); b200_stream_destroy(bc->stream); }
     if (bc->workspace) b200_free(bc->device, bc->workspace);
+    for (auto & c : bc->chains) b200_chain_destroy(c.chain);
     delete bc;
     delete backend;
 }
@@ -408,6 +413,8 @@ bool backend_reserve(backend_ctx * bc, size_t need) {
     if (need <= bc->workspace_size) return true;
     b200_stream_synchronize(bc->stream);   // kernels in flight may still read the old workspace
     if (bc->workspace) b200_free(bc->device, bc->workspace);
+    for (auto & c : bc->chains) b200_chain_destroy(c.chain);     // (chains do not use the workspace; dropped with it to keep one rule)
+    bc->chains.clear();
     need = (need + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
     bc->workspace = b200_malloc(bc->device, need);
     bc->workspace_size = bc->workspace ? need : 0;
@@ -477,6 +484,90 @@ enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
     return GGML_STATUS_SUCCESS;
 }
 
+// ---- decode fast paths: runs of plain 2-D MUL_MAT nodes ---------------------------------------------------------------
+// A run = consecutive MUL_MAT nodes (no-op nodes in between skipped) with n <= 4 and no batch dimensions. Nodes that read the
+// same X form a group (wq / wk / wv, ffn_gate / ffn_up): ONE launch (b200_mul_mat_group, counterpart of the reference's fused
+// mul_mat_vec_q, ggml-cuda.cu:2144-2180). Two or more consecutive groups of K-quant matrices: ONE persistent launch for all of
+// them (b200_chain_*), cached per argument list. GGML_B200_GROUP=0 / GGML_B200_CHAIN=0 switch the two off.
+bool is_noop(const ggml_tensor * t) {
+    return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_VIEW || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_PERMUTE ||
+           t->op == GGML_OP_TRANSPOSE;
+}
+bool plain_decode_mul_mat(const ggml_tensor * t) {
+    if (t->op != GGML_OP_MUL_MAT) return false;
+    const ggml_tensor * w = t->src[0], * x = t->src[1];
+    return x->ne[1] <= 4 && x->ne[2] == 1 && x->ne[3] == 1 && w->ne[2] == 1 && w->ne[3] == 1 && x->nb[0] == sizeof(float) && t->nb[0] == sizeof(float);
+}
+b200_mul_mat_args plain_args(const ggml_tensor * dst) {
+    const ggml_tensor * w = dst->src[0], * x = dst->src[1];
+    b200_mul_mat_args a = {};
+    a.type = (int32_t) w->type; a.layout = weight_layout(w);
+    a.m = w->ne[1]; a.n = x->ne[1]; a.k = w->ne[0];
+    a.w = w->data; a.w_row_stride = a.layout == B200_LAYOUT_PLANES ? 0 : (int64_t) w->nb[1];
+    a.x = (const float *) x->data; a.x_row_stride = (int64_t) (x->nb[1] / sizeof(float));
+    a.y = (float *) dst->data; a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
+    a.flavour = B200_Q8_X86;
+    return a;
+}
+bool env_on(const char * name) { const char * e = getenv(name); return !(e && e[0] == '0'); }
+
+// tries to run nodes [i, ...) as groups / a chain; returns the index of the first node NOT consumed (== i: nothing done)
+int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_status & st) {
+    static const bool group_on = env_on("GGML_B200_GROUP"), chain_on = env_on("GGML_B200_CHAIN");
+    st = GGML_STATUS_SUCCESS;
+    if (!group_on) return i;
+    std::vector<b200_mul_mat_args> args;
+    std::vector<int32_t> sizes;
+    int j = i, last = i;
+    for (; j < cgraph->n_nodes; ++j) {
+        const ggml_tensor * t = cgraph->nodes[j];
+        if (is_noop(t)) continue;
+        if (!plain_decode_mul_mat(t)) break;
+        b200_mul_mat_args a = plain_args(t);
+        if (!args.empty() && a.n != args[0].n) break;
+        const b200_mul_mat_args * head = sizes.empty() ? nullptr : &args[args.size() - (size_t) sizes.back()];
+        const bool same_x = head && head->x == a.x && head->k == a.k && head->x_row_stride == a.x_row_stride && sizes.back() < 4;
+        if (same_x) ++sizes.back(); else sizes.push_back(1);
+        args.push_back(a);
+        last = j + 1;
+    }
+    if (args.size() < 2) return i;                       // a single node: the ordinary path
+    // workspace for the group launches (the chain does not need one)
+    size_t need = 0;
+    for (const auto & a : args) { const size_t w = b200_mul_mat_workspace(a.type, a.n, a.k); need = w > need ? w : need; }
+    if (!backend_reserve(bc, need)) { st = GGML_STATUS_ALLOC_FAILED; return last; }
+    for (auto & a : args) { a.workspace = bc->workspace; a.workspace_size = bc->workspace_size; }
+
+    bool kquant = true;
+    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q6_K);
+    if (chain_on && kquant && sizes.size() >= 2 && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
+        b200_chain_t chain = nullptr;
+        for (auto & c : bc->chains)
+            if (c.args.size() == args.size() && c.sizes == sizes && memcmp(c.args.data(), args.data(), args.size() * sizeof(b200_mul_mat_args)) == 0) { chain = c.chain; break; }
+        if (!chain) {
+            chain = b200_chain_create(bc->device, args.data(), sizes.data(), (int) sizes.size());
+            if (chain) {
+                if (bc->chains.size() >= 16) { b200_stream_synchronize(bc->stream); b200_chain_destroy(bc->chains.front().chain); bc->chains.erase(bc->chains.begin()); }
+                bc->chains.push_back({args, sizes, chain});
+            }
+        }
+        if (chain) {
+            if (b200_chain_launch(chain, bc->stream) != 0) { GGML_LOG_ERROR("ggml-b200: decode chain failed: %s\n", b200_last_error()); st = GGML_STATUS_FAILED; }
+            return last;
+        }
+    }
+    size_t pos = 0;
+    for (int32_t cnt : sizes) {
+        if (b200_mul_mat_group(&args[pos], cnt, bc->stream) != 0) {
+            GGML_LOG_ERROR("ggml-b200: MUL_MAT group failed: %s\n", b200_last_error());
+            st = GGML_STATUS_FAILED;
+            return last;
+        }
+        pos += (size_t) cnt;
+    }
+    return last;
+}
+
 enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     backend_ctx * bc = (backend_ctx *) backend->context;
     b200_set_device(bc->device);
@@ -484,6 +575,11 @@ enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgr
         ggml_tensor * node = cgraph->nodes[i];
         if (ggml_is_empty(node)) continue;
         enum ggml_status st = GGML_STATUS_SUCCESS;
+        if (plain_decode_mul_mat(node)) {
+            const int next = compute_decode_run(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (next > i) { i = next - 1; continue; }
+        }
         switch (node->op) {
             case GGML_OP_NONE:
             case GGML_OP_VIEW:
