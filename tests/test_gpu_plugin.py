@@ -27,8 +27,10 @@ def _need(binary):
     return dict(os.environ, GGML_BACKEND_PATH=str(plugin))
 
 
-@pytest.mark.parametrize("mode", [{}, {"GGML_B200_CHAIN": "0"}, {"GGML_B200_GROUP": "0"}], ids=["chain", "groups", "per-node"])
-@pytest.mark.parametrize("n", [1, 3, 64])
+CASES = [({}, 1), ({}, 3), ({}, 64), ({"GGML_B200_CHAIN": "0"}, 1), ({"GGML_B200_GROUP": "0"}, 1)]
+
+
+@pytest.mark.parametrize("mode,n", CASES, ids=["chain-n1", "chain-n3", "gemm-n64", "groups-n1", "per-node-n1"])
 def test_multi_node_graph_matches_reference_cpu_backend(mode, n):
     env = _need("plugin_graph_check")
     env.update(mode)
