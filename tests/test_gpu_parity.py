@@ -322,6 +322,29 @@ def test_stream_gemv_group_mixed_types(b200, orc):
             assert nmse(y.cpu().numpy()[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE
 
 
+@pytest.mark.parametrize("n", [33, 512])
+def test_gemm_group_one_launch_per_weight_type(b200, orc, n):
+    """prefill: wq + wk (Q4_K) share ONE tensor-core GEMM launch (one tile list over both matrices), wv (Q6_K) takes its own; ragged
+    row counts (1000, 72) and a k-split tail included. Compared with the CPU arithmetic at the reference's tolerance and with
+    the one-node-per-call results."""
+    rng = np.random.default_rng(23 + n)
+    k = 2048
+    ts, ms = [Q4_K, Q4_K, Q6_K, Q4_K], [1000, 4096, 520, 72]
+    ws = [random_blocks(t, m, k, rng) for t, m in zip(ts, ms)]
+    x = _acts(rng, n, k)
+    wps = [b200.repack(t, dev(w).reshape(-1), m, k) for t, w, m in zip(ts, ws, ms)]
+    before = b200.launch_count()
+    ys = b200.mul_mat_group(ts, wps, dev(x), ms)
+    assert b200.launch_count() - before == 3          # fp16 prologue + one GEMM per weight type
+    for t, w, wp, m, y in zip(ts, ws, wps, ms, ys):
+        got = y.cpu().numpy()
+        assert np.isfinite(got).all()
+        rows = rng.choice(m, min(m, 48), replace=False)
+        assert nmse(got[:, rows], orc.mul_mat(t, w[rows], x)) < MAX_NMSE
+        single = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+        assert nmse(got, single) < 1e-10          # same tiles, same arithmetic; only the k-split partition may differ
+
+
 def test_stream_gemv_leaves_quantised_x_for_prequantised_calls(b200, orc):
     rng = np.random.default_rng(22)
     m, k = 512, 4096

@@ -42,6 +42,22 @@ def show_timeline(tl, call_ops, mhz=1965.0):
         print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} end-skew max-med {skew:5.2f} max-min {spread:5.2f} us | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
 
 
+def show_lateness(tl):
+    """which CTAs finish their nodes late: mean over nodes of (end of node on this CTA - median over CTAs), globaltimer ns"""
+    import numpy as np
+    gt = tl[:, :-1, 7].astype(np.float64)
+    late = gt - np.median(gt, axis=0, keepdims=True)
+    m = late.mean(axis=1) / 1e3
+    order = np.argsort(-m)
+    print("  CTA lateness (us, mean over nodes): max %.2f  p90 %.2f  median %.2f  min %.2f" % (m.max(), np.percentile(m, 90), np.median(m), m.min()))
+    print("  latest CTAs:", ", ".join(f"{int(c)}:{m[c]:.2f}" for c in order[:12]))
+    print("  earliest CTAs:", ", ".join(f"{int(c)}:{m[c]:.2f}" for c in order[-8:]))
+    worst = np.argmax(late, axis=0)
+    cnt = np.bincount(worst, minlength=tl.shape[0])
+    top = np.argsort(-cnt)[:10]
+    print("  how often a CTA is THE last one (of %d nodes):" % late.shape[1], ", ".join(f"{int(c)}:{int(cnt[c])}" for c in top))
+
+
 def run(ops, persistent, steps):
     ch = MatMulChain(ops, 1, persistent=persistent)
     ch.capture()
@@ -57,7 +73,9 @@ def run(ops, persistent, steps):
     ms = e0.elapsed_ms(e1) / steps
     info = ch.decode_chain.info() if ch.decode_chain is not None else None
     if ch.decode_chain is not None and os.environ.get("B200_CHAIN_TIMELINE"):
-        show_timeline(ch.decode_chain.timeline(), [c[2] for c in ch.calls])
+        tl_ = ch.decode_chain.timeline()
+        show_timeline(tl_, [c[2] for c in ch.calls])
+        show_lateness(tl_)
     out = {k: v.clone() for k, v in ch.bufs.items()}
     ch.close()
     return ms, info, out

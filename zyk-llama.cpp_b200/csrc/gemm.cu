@@ -43,10 +43,14 @@ constexpr int THREADS = 128 + DEQ_WARPS * 32 + EPI_WARPS * 32;   // warps 0..3: 
 constexpr int MAX_STAGES = 8;
 constexpr size_t SMEM_BUDGET = 224 * 1024;   // dynamic shared memory per CTA (227 KB usable minus the static barriers)
 
+constexpr int GEMM_MAX_GROUP = 3;   // weight matrices of the same type and k that read the same X in ONE launch (wq/wk/wv, ffn_gate/ffn_up)
+
 struct GemmArgs {
-    GemvW W;
-    int64_t m, n, k;
-    float * y; int64_t ldy;
+    GemvW W[GEMM_MAX_GROUP];
+    int64_t m[GEMM_MAX_GROUP], n, k;
+    float * y[GEMM_MAX_GROUP]; int64_t ldy[GEMM_MAX_GROUP];
+    int nmat;
+    int tile_begin[GEMM_MAX_GROUP + 1];   // the tiles of matrix i are tile_begin[i] .. tile_begin[i + 1] - 1 of the launch's tile list
     const float * xscale;       // per activation row: multiply the accumulator by this
     int bn;                     // activation rows per tile (multiple of 16, <= 256)
     int stages;
@@ -110,13 +114,18 @@ struct StageCursor {     // ring position without a division per step
     __device__ __forceinline__ void advance(int n) { s += n; if (s >= stages) { s -= stages; ph ^= 1u; } }   // n <= stages
 };
 
-struct Unit { int64_t m0; int n0, sb_begin, num_sb; bool split; };
+// the weight-plane tensor maps of every matrix of the launch (kernel parameter, __grid_constant__: TMA reads them in place)
+struct WMapSet { CUtensorMap m[GEMM_MAX_GROUP][3]; };
+
+struct Unit { int64_t m0; int n0, sb_begin, num_sb, mat; bool split; };
 template <bool PAIR>
 __device__ __forceinline__ Unit unit_decode(const GemmArgs & a, int u, uint32_t rank) {
     int tile = u, z = 0, ks = 1;
     if (u >= a.full_tiles) { const int v = u - a.full_tiles; tile = a.full_tiles + v / a.ksplit; z = v % a.ksplit; ks = a.ksplit; }
     const int total_sb = (int) (a.k / 256);
     Unit r;
+    r.mat = (a.nmat > 1 && tile >= a.tile_begin[1]) + (a.nmat > 2 && tile >= a.tile_begin[2]);
+    tile -= a.tile_begin[r.mat];
     r.m0 = (int64_t) (tile / a.n_tiles) * (PAIR ? 2 * BM : BM) + (int64_t) rank * BM;
     r.n0 = (tile % a.n_tiles) * a.bn;
     r.sb_begin = (int) ((int64_t) total_sb * z / ks);
@@ -126,8 +135,7 @@ __device__ __forceinline__ Unit unit_decode(const GemmArgs & a, int u, uint32_t 
 }
 
 template <int TYPE, bool PAIR>
-__device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUtensorMap & tmap_w0, const CUtensorMap & tmap_w1, const CUtensorMap & tmap_w2,
-                                          const GemmArgs & a) {
+__device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMapSet & wmaps, const GemmArgs & a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], raw_full[RAW_STAGES], raw_empty[RAW_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_smem;
@@ -147,9 +155,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
 
     if (warp == 0 && lane == 0) prefetch_tensormap(&tmap_x);
     if (warp == 3 && lane == 0) {
-        prefetch_tensormap(&tmap_w0);
-        if (Raw<TYPE>::N > 1) prefetch_tensormap(&tmap_w1);
-        if (TYPE == B200_TYPE_Q6_K) prefetch_tensormap(&tmap_w2);
+        for (int i = 0; i < a.nmat; ++i) {
+            prefetch_tensormap(&wmaps.m[i][0]);
+            if (Raw<TYPE>::N > 1) prefetch_tensormap(&wmaps.m[i][1]);
+            if (TYPE == B200_TYPE_Q6_K) prefetch_tensormap(&wmaps.m[i][2]);
+        }
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < stages; ++s) {
@@ -204,7 +214,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
                     for (int i = 0; i < Raw<TYPE>::N; ++i) {
                         constexpr RawLoad L0 = Raw<TYPE>::L[0], L1 = Raw<TYPE>::L[1], L2 = Raw<TYPE>::L[2];
                         const RawLoad L = i == 0 ? L0 : i == 1 ? L1 : L2;
-                        const CUtensorMap * tm = L.map == 0 ? &tmap_w0 : L.map == 1 ? &tmap_w1 : &tmap_w2;
+                        const CUtensorMap * tm = &wmaps.m[w.mat][L.map];
                         tma_load_2d(smem_w + (uint32_t) (c.s * Raw<TYPE>::BYTES + L.smem_off), tm, (w.sb_begin + sb) * L.cstep + L.coff, (int) w.m0,
                                     smem_u32(&raw_full[c.s]));
                     }
@@ -252,11 +262,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
         StageCursor c(stages, half), rc(RAW_STAGES, 0);
         for (int u = unit0; u < a.total_units; u += unit_step) {
             const Unit w = unit_decode<PAIR>(a, u, rank);
-            const int64_t row = w.m0 + r < a.m ? w.m0 + r : a.m - 1;
-            uint2 aux_next = Deq<TYPE>::aux_load(a.W, row, w.sb_begin);
+            const int64_t row = w.m0 + r < a.m[w.mat] ? w.m0 + r : a.m[w.mat] - 1;
+            const GemvW & W = a.W[w.mat];
+            uint2 aux_next = Deq<TYPE>::aux_load(W, row, w.sb_begin);
             for (int sb = 0; sb < w.num_sb; ++sb, rc.advance(1)) {
                 const uint2 aux = aux_next;
-                if (sb + 1 < w.num_sb) aux_next = Deq<TYPE>::aux_load(a.W, row, w.sb_begin + sb + 1);
+                if (sb + 1 < w.num_sb) aux_next = Deq<TYPE>::aux_load(W, row, w.sb_begin + sb + 1);
                 const uint32_t raw = smem_w + (uint32_t) (rc.s * Raw<TYPE>::BYTES);
                 mbar_wait(smem_u32(&raw_full[rc.s]), rc.ph);
 #pragma unroll
@@ -288,12 +299,13 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
             const int64_t mrow = w.m0 + 32 * q + lane;
             mbar_wait(smem_u32(&acc_full[buf]), (uint32_t) ((i >> 1) & 1));
             tc_fence_after();
-            const bool row_ok = mrow < a.m && !(a.debug & 16);
-            float * yp = a.y + (int64_t) w.n0 * a.ldy + (row_ok ? mrow : 0);
+            const bool row_ok = mrow < a.m[w.mat] && !(a.debug & 16);
+            const int64_t ldy = a.ldy[w.mat];
+            float * yp = a.y[w.mat] + (int64_t) w.n0 * ldy + (row_ok ? mrow : 0);
             const int n_left = (int) (a.n - w.n0 < bn ? a.n - w.n0 : bn);             // activation rows of this tile that exist (>= 1)
             // lane l carries the scale of activation row 32 * cc + l of the tile, fetched one iteration ahead
             float xs_next = __ldg(a.xscale + w.n0 + (lane < n_left ? lane : n_left - 1));
-            for (int cc = 0; cc * 32 < bn; ++cc, yp += 32 * a.ldy) {                  // columns past bn (inside acc_cols) are read and dropped
+            for (int cc = 0; cc * 32 < bn; ++cc, yp += 32 * ldy) {                  // columns past bn (inside acc_cols) are read and dropped
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(tmem_acc + (uint32_t) (cc * 32), v);
                 const float xs_lane = xs_next;
@@ -304,13 +316,13 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
-                        if (row_ok && cc * 32 + j < n_left) yp[(int64_t) j * a.ldy] = val;
+                        if (row_ok && cc * 32 + j < n_left) yp[(int64_t) j * ldy] = val;
                     }
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
-                        if (row_ok && cc * 32 + j < n_left) atomicAdd(yp + (int64_t) j * a.ldy, val);      // result unused -> RED.E.ADD.F32
+                        if (row_ok && cc * 32 + j < n_left) atomicAdd(yp + (int64_t) j * ldy, val);      // result unused -> RED.E.ADD.F32
                     }
                 }
             }
@@ -330,17 +342,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const CUte
 }
 
 template <int TYPE>
-__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w0,
-                                                          const __grid_constant__ CUtensorMap tmap_w1, const __grid_constant__ CUtensorMap tmap_w2,
-                                                          const GemmArgs a) {
-    gemm_body<TYPE, false>(tmap_x, tmap_w0, tmap_w1, tmap_w2, a);
+__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ WMapSet wmaps, const GemmArgs a) {
+    gemm_body<TYPE, false>(tmap_x, wmaps, a);
 }
 
 template <int TYPE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
-gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w0, const __grid_constant__ CUtensorMap tmap_w1,
-                 const __grid_constant__ CUtensorMap tmap_w2, const GemmArgs a) {
-    gemm_body<TYPE, true>(tmap_x, tmap_w0, tmap_w1, tmap_w2, a);
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ WMapSet wmaps, const GemmArgs a) {
+    gemm_body<TYPE, true>(tmap_x, wmaps, a);
 }
 
 // ---- host side ------------------------------------------------------------------------------------------
@@ -413,15 +422,15 @@ int raw_ring_bytes_of(int type) {
 }
 
 template <int TYPE>
-int launch_gemm(const CUtensorMap & tm, const WMaps & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
+int launch_gemm(const CUtensorMap & tm, const WMapSet & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
     static bool configured = false;
     if (!configured) {
         B200_CHECK(cudaFuncSetAttribute(gemm_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         B200_CHECK(cudaFuncSetAttribute(gemm_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         configured = true;
     }
-    if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w.m[0], w.m[1], w.m[2], g));
-    else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w.m[0], w.m[1], w.m[2], g));
+    if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
+    else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
     return 0;
 }
 
@@ -438,11 +447,29 @@ bool b200_gemm_wants(int type, int64_t m, int64_t n, int64_t k, bool force) {
     return force ? n >= 1 : n > 8;
 }
 
-int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
+int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) { return b200_gemm_launch_group(a, 1, s); }
+
+// can these nodes share ONE GEMM launch? same weight type, same X (pointer, n, k, stride) and workspace
+bool b200_gemm_groupable(const b200_mul_mat_args * args, int count) {
+    if (count < 1 || count > GEMM_MAX_GROUP) return false;
+    for (int i = 1; i < count; ++i)
+        if (args[i].type != args[0].type || args[i].x != args[0].x || args[i].n != args[0].n || args[i].k != args[0].k ||
+            args[i].x_row_stride != args[0].x_row_stride || args[i].workspace != args[0].workspace) return false;
+    return true;
+}
+
+// `count` <= GEMM_MAX_GROUP weight matrices of the same type against the same X: the tiles of all of them form one work list for
+// the persistent grid (wq/wk/wv and ffn_gate/ffn_up: 7 -> 4 launches per layer, and the 2 x 112 tiles of gate + up fill 74 CTA
+// pairs in 3.03 waves instead of 2 x 2). args[0].flags decides whether X still has to be converted.
+int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s) {
     encode_tiled_fn encode = get_encode_tiled();
     B200_REQUIRE(encode != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
-    const int64_t n = a->n, k = a->k, m = a->m;
+    B200_REQUIRE(b200_gemm_groupable(args, count), "gemm: the %d nodes of the group do not share type / X / workspace", count);
+    const b200_mul_mat_args * a = &args[0];
+    const int64_t n = a->n, k = a->k;
     const bool pdl = (a->flags & B200_MM_PDL) != 0;
+    int64_t m_max = 0;
+    for (int i = 0; i < count; ++i) m_max = args[i].m > m_max ? args[i].m : m_max;
 
     // workspace: fp16 activations [n][k] + per-row scale
     __half * xh = (__half *) a->workspace;
@@ -455,13 +482,28 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
     int bn = (int) ((n + n_tiles - 1) / n_tiles);
     // CTA pairs (cta_group::2, 256 weight rows per tile) when there is more than one 128-row tile; B200_GEMM_PAIR=0/1 overrides
     static const int pair_env = [] { const char * e = getenv("B200_GEMM_PAIR"); return e ? atoi(e) : -1; }();
-    const bool pair = (pair_env < 0 ? B200_GEMM_PAIR_DEFAULT : pair_env != 0) && m > BM;
+    const bool pair = (pair_env < 0 ? B200_GEMM_PAIR_DEFAULT : pair_env != 0) && m_max > BM;
     bn = pair ? (bn + 31) & ~31 : (bn + 15) & ~15;     // each CTA of a pair stages bn / 2 rows, a multiple of 16
     const int bn_cta = pair ? bn / 2 : bn;
+    const int tile_m = pair ? 2 * BM : BM;
     GemmArgs g = {};
-    g.W = gemv_w_make(a->type, a->w, m, k);
-    g.m = m; g.n = n; g.k = k;
-    g.y = a->y; g.ldy = a->y_row_stride;
+    WMapSet wm;
+    g.nmat = count;
+    g.n = n; g.k = k;
+    int64_t tiles = 0;
+    for (int i = 0; i < count; ++i) {
+        g.W[i] = gemv_w_make(args[i].type, args[i].w, args[i].m, k);
+        g.m[i] = args[i].m; g.y[i] = args[i].y; g.ldy[i] = args[i].y_row_stride;
+        g.tile_begin[i] = (int) tiles;
+        tiles += (args[i].m + tile_m - 1) / tile_m * n_tiles;
+        WMaps one;
+        B200_REQUIRE(make_weight_maps(args[i].type, g.W[i], args[i].m, one), "gemm: cuTensorMapEncodeTiled failed for the weight planes (type %d m=%lld k=%lld)",
+                     args[i].type, (long long) args[i].m, (long long) k);
+        for (int j = 0; j < 3; ++j) wm.m[i][j] = one.m[j];
+    }
+    for (int i = count; i <= GEMM_MAX_GROUP; ++i) g.tile_begin[i] = (int) tiles;
+    for (int i = count; i < GEMM_MAX_GROUP; ++i) { g.W[i] = g.W[0]; g.m[i] = g.m[0]; g.y[i] = g.y[0]; g.ldy[i] = g.ldy[0]; for (int j = 0; j < 3; ++j) wm.m[i][j] = wm.m[0][j]; }
+    B200_REQUIRE(tiles < ((int64_t) 1 << 26), "gemm: too many tiles (%lld)", (long long) tiles);
     g.xscale = xscale;
     g.bn = bn;
     g.n_tiles = n_tiles;
@@ -471,9 +513,6 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
     int stages = (int) ((SMEM_BUDGET - raw_ring) / per_stage);
     g.stages = stages > MAX_STAGES ? MAX_STAGES : stages;
     const size_t smem = raw_ring + (size_t) g.stages * per_stage + 1024;
-    WMaps wm;
-    B200_REQUIRE(make_weight_maps(a->type, g.W, m, wm), "gemm: cuTensorMapEncodeTiled failed for the weight planes (type %d m=%lld k=%lld)", a->type,
-                 (long long) m, (long long) k);
 
     CUtensorMap tm;
     const cuuint64_t dims[2] = {(cuuint64_t) k, (cuuint64_t) n};
@@ -487,11 +526,7 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
     // work list: whole waves of full tiles, then the remaining tiles cut along k so that the last wave also fills the SMs
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
-    const int tile_m = pair ? 2 * BM : BM;
     const int workers = pair ? sms / 2 : sms;             // CTAs, or CTA pairs
-    const int64_t m_tiles = (m + tile_m - 1) / tile_m;
-    const int64_t tiles = m_tiles * n_tiles;
-    B200_REQUIRE(tiles < ((int64_t) 1 << 26), "gemm: too many tiles (%lld)", (long long) tiles);
     const int total_sb = (int) (k / 256);
     int64_t full = tiles / workers * workers;
     int64_t rest = tiles - full;
@@ -502,8 +537,12 @@ int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) {
     g.full_tiles = (int) full; g.ksplit = ks; g.total_units = (int) (full + rest * ks);
     if (const char * e = getenv("B200_GEMM_DEBUG")) g.debug = atoi(e);
     if (rest > 0) {     // zero the weight rows the split tiles accumulate into (full tiles of the same rows overwrite later, in stream order)
-        const int64_t m_lo = full / n_tiles * tile_m;
-        B200_CHECK(cudaMemset2DAsync(a->y + m_lo, (size_t) a->y_row_stride * sizeof(float), 0, (size_t) (m - m_lo) * sizeof(float), (size_t) n, s));
+        for (int i = 0; i < count; ++i) {
+            const int64_t first = full > g.tile_begin[i] ? full - g.tile_begin[i] : 0;       // first split tile of this matrix (local index)
+            const int64_t m_lo = first / n_tiles * tile_m;
+            if (m_lo >= args[i].m) continue;
+            B200_CHECK(cudaMemset2DAsync(args[i].y + m_lo, (size_t) args[i].y_row_stride * sizeof(float), 0, (size_t) (args[i].m - m_lo) * sizeof(float), (size_t) n, s));
+        }
     }
     const unsigned nw = (unsigned) (g.total_units < workers ? g.total_units : workers);
     dim3 grid(pair ? 2 * nw : nw);

@@ -6,3 +6,6 @@ size_t b200_gemm_workspace(int type, int64_t n, int64_t k);
 // does the GEMM take this shape? (force = caller set algo == 2)
 bool   b200_gemm_wants(int type, int64_t m, int64_t n, int64_t k, bool force);
 int    b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s);
+// up to 3 nodes of the same weight type that read the same X (and share the workspace): one launch, one tile list
+bool   b200_gemm_groupable(const b200_mul_mat_args * args, int count);
+int    b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s);

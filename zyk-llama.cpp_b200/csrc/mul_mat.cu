@@ -187,6 +187,33 @@ int b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t 
             g.xq_out = xq_planes_carve(a0.workspace, act, a0.n, a0.k);
         if (b200_gemv_stream_wants(g)) return b200_gemv_stream_launch(g, (cudaStream_t) stream);
     }
+    // prefill: nodes of the same weight type share ONE tensor-core GEMM launch (one tile list over up to 3 matrices), and all of
+    // them the fp16 copy of X
+    if (group_shares_x(args, count)) {
+        bool all_gemm = true;
+        for (int i = 0; i < count && all_gemm; ++i)
+            all_gemm = planes_fast_path(args[i].type, args[i].layout, args[i].m, args[i].k, args[i].w, args[i].w_row_stride) &&
+                       b200_gemm_wants(args[i].type, args[i].m, args[i].n, args[i].k, false) && args[i].m > 0 &&
+                       args[i].workspace_size >= b200_mul_mat_workspace(args[i].type, args[i].n, args[i].k) && (((uintptr_t) args[i].workspace) & 255) == 0;
+        static const bool group_gemm = [] { const char * e = getenv("B200_GEMM_GROUP"); return !(e && e[0] == '0'); }();
+        if (all_gemm && group_gemm) {
+            bool done[16] = {false};
+            bool first = true;
+            B200_REQUIRE(count <= 16, "b200_mul_mat_group: at most 16 nodes per call");
+            for (int i = 0; i < count; ++i) {
+                if (done[i]) continue;
+                b200_mul_mat_args bucket[3];
+                int nb = 0;
+                for (int j = i; j < count && nb < 3; ++j)
+                    if (!done[j] && args[j].type == args[i].type) { bucket[nb++] = args[j]; done[j] = true; }
+                if (!first) bucket[0].flags |= B200_MM_X_PREQUANTISED;
+                first = false;
+                int rc = b200_gemm_launch_group(bucket, nb, (cudaStream_t) stream);
+                if (rc) return rc;
+            }
+            return 0;
+        }
+    }
     // not groupable into one launch: one call per node; the nodes share the converted X (fp16 copy for the GEMM, int8 planes for
     // the register GEMV) when they all take the same of those two paths
     const bool share_x = group_shares_x(args, count);
