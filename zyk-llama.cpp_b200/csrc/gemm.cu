@@ -69,8 +69,22 @@ __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict_
     const int64_t row = blockIdx.x;
     const float * xr = x + row * ldx;
     __shared__ float red[8];
+    // one pass when the row fits the registers of the CTA (k <= 16384, 16-byte aligned): 128-bit loads, the row is read once
+    constexpr int VMAX = 16;
+    const bool vec = k <= 256 * 4 * VMAX && (k & 3) == 0 && (((uintptr_t) xr) & 15) == 0;
+    float4 v[VMAX];
     float amax = 0.0f;
-    for (int64_t i = threadIdx.x; i < k; i += 256) amax = fmaxf(amax, fabsf(xr[i]));
+    if (vec) {
+        const int nv = (int) (k >> 2);
+#pragma unroll
+        for (int i = 0; i < VMAX; ++i) {
+            const int idx = threadIdx.x + i * 256;
+            v[i] = idx < nv ? __ldg(reinterpret_cast<const float4 *>(xr) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[i].x), fabsf(v[i].y)), fmaxf(fabsf(v[i].z), fabsf(v[i].w))));
+        }
+    } else {
+        for (int64_t i = threadIdx.x; i < k; i += 256) amax = fmaxf(amax, fabsf(xr[i]));
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = amax;
@@ -82,7 +96,20 @@ __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict_
     int e = 0;
     if (amax > 0.0f && amax < 3.0e38f) { (void) frexpf(amax, &e); e -= 15; }
     const float down = ldexpf(1.0f, -e);
-    for (int64_t i = threadIdx.x; i < k; i += 256) xh[row * k + i] = __float2half_rn(xr[i] * down);
+    if (vec) {
+        const int nv = (int) (k >> 2);
+        uint2 * out = reinterpret_cast<uint2 *>(xh + row * k);       // k % 4 == 0 and the workspace is 256 B aligned: 8-byte stores
+#pragma unroll
+        for (int i = 0; i < VMAX; ++i) {
+            const int idx = threadIdx.x + i * 256;
+            if (idx < nv) {
+                const __half2 lo = __floats2half2_rn(v[i].x * down, v[i].y * down), hi = __floats2half2_rn(v[i].z * down, v[i].w * down);
+                out[idx] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+            }
+        }
+    } else {
+        for (int64_t i = threadIdx.x; i < k; i += 256) xh[row * k + i] = __float2half_rn(xr[i] * down);
+    }
     if (threadIdx.x == 0) xscale[row] = ldexpf(1.0f, e);
 }
 
