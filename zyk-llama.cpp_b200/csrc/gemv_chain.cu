@@ -27,6 +27,7 @@
 #include "actquant.cuh"
 #include "sm100.cuh"
 
+#include <cuda.h>
 #include <stdlib.h>
 #include <string.h>
 #include <vector>
@@ -45,6 +46,7 @@ constexpr int XU_BYTES = 336;                // one 256-element unit of quantise
 constexpr int XU_BS16 = 256, XU_BS32 = 288, XU_D = 304;
 constexpr int CH_SMEM_TOTAL = 227 * 1024;
 constexpr int CH_MAX_COLS = 4;
+constexpr int CH_T_Q6K_SW = 0x600;        // item type: Q6_K whose QL / QH planes arrive through swizzling tensor copies (one block per lane)
 
 struct ChainMatD {
     const uint8_t * w;        // plane layout (canonical for Q4_K)
@@ -151,6 +153,11 @@ __device__ __forceinline__ void group_bar(int grp) { asm volatile("bar.sync %0, 
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
+}
+// 2-D tensor copy (box at (c0, c1)) global -> shared with an L2 policy; the tensor map lives in global memory (host-written)
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void * tmap, int c0, int c1, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on `bar`
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar, uint64_t policy) {
@@ -366,6 +373,68 @@ __device__ __forceinline__ void frag_q6k(uint32_t stage, int nunits, int u, int 
     }
 }
 
+// ---- Q6_K, one 256-block per lane (CH_T_Q6K_SW items) --------------------------------------------------------------------
+// The producer lands QL and QH with 2-D tensor copies (SWIZZLE_128B / SWIZZLE_64B: 16-byte chunk c of unit u sits at chunk
+// c ^ (u & 7) resp. c ^ ((u >> 1) & 3)), so 32 lanes reading the same chunk of 32 consecutive units hit 32 different bank
+// groups. Stage: [QL 128 B x units][pad to 512][QH 64 B x units][SC 16 B x units][D 2 B x units]. Same integer arithmetic
+// as frag_q6k; QH, the 16 scales, d and the activation scale are loaded once per block instead of once per 32 weights, and
+// the -32 offset of the 6-bit values is one dp2a chain over the per-16 activation sums (sum_j sc_j * bs16_j).
+__host__ __device__ inline int q6sw_qh0(int nunits) { return (nunits * 128 + 511) & ~511; }
+__device__ __forceinline__ int sext8(uint32_t w, int byte) { return (int) (w << (24 - 8 * byte)) >> 24; }
+template <int NCOLS>
+__device__ __forceinline__ void unit_q6k(uint32_t stage, int nunits, int u, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint32_t qh0 = stage + (uint32_t) q6sw_qh0(nunits);
+    const uint32_t qlp = (stage + (uint32_t) (u * 128)) ^ (uint32_t) ((u & 7) << 4);          // ^ (c << 4): chunk c
+    const uint32_t qhp = (qh0 + (uint32_t) (u * 64)) ^ (uint32_t) (((u >> 1) & 3) << 4);
+    const uint4 scw = lds16(qh0 + (uint32_t) (nunits * 64 + u * 16));
+    const uint32_t sc[4] = {scw.x, scw.y, scw.z, scw.w};
+    const float dw = half_bits_to_float(lds2(qh0 + (uint32_t) (nunits * 80 + u * 2)));
+    int isum[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+        const uint4 b0 = lds16(xc + XU_BS16), b1 = lds16(xc + XU_BS16 + 16);            // 16 x i16: sums of 16 quants
+        int m = __dp2a_lo((int) b0.x, (int) sc[0], 0);
+        m = __dp2a_hi((int) b0.y, (int) sc[0], m);
+        m = __dp2a_lo((int) b0.z, (int) sc[1], m);
+        m = __dp2a_hi((int) b0.w, (int) sc[1], m);
+        m = __dp2a_lo((int) b1.x, (int) sc[2], m);
+        m = __dp2a_hi((int) b1.y, (int) sc[2], m);
+        m = __dp2a_lo((int) b1.z, (int) sc[3], m);
+        m = __dp2a_hi((int) b1.w, (int) sc[3], m);
+        isum[c] = -32 * m;
+    }
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+        const uint4 qhA = lds16(qhp ^ (uint32_t) ((2 * n) << 4)), qhB = lds16(qhp ^ (uint32_t) ((2 * n + 1) << 4));
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const uint4 ql = lds16(qlp ^ (uint32_t) ((4 * n + t) << 4));
+            const uint4 qh = (t & 1) ? qhB : qhA;
+            constexpr uint32_t M3 = 0x03030303u;
+            const int sh = t & 2;
+            const uint4 lo = and4(ql, 0x0f0f0f0fu), hi = and4(ql, 0xf0f0f0f0u);
+            const uint4 ha = and4(qh, M3 << sh), hb = and4(qh, M3 << (sh + 4));
+            const int is = 8 * n + t;
+            const int sc0 = sext8(sc[is >> 2], is & 3), sc1 = sext8(sc[(is + 4) >> 2], is & 3);
+            const int p0 = xpos(is), p1 = xpos(is + 4);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) {
+                const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+                const uint4 x0 = lds16(xc + p0 * 16), x1 = lds16(xc + p1 * 16);
+                const int s0 = dot16(lo, x0) + (dot16(ha, x0) << (4 - sh));
+                const int s1 = (dot16_us(hi, x1) >> 4) + (dot16_us(hb, x1) >> sh);
+                isum[c] += sc0 * s0 + sc1 * s1;
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const float dx = ldsf(xb + (uint32_t) (c * x_col_stride) + XU_D);
+        acc[c] += (dx * dw) * (float) isum[c];
+    }
+}
+
 // ---- IQ4_XS / Q4_0 / Q8_0: eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ------------
 template <int TYPE> __device__ __forceinline__ void wfrag_lds(WFrag<TYPE> & f, uint32_t stage, int nunits, int u, int g);
 template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_IQ4_XS>(WFrag<B200_TYPE_IQ4_XS> & f, uint32_t stage, int nunits, int u, int g) {
@@ -444,7 +513,12 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
     }
 }
 
-template <int NCOLS>
+template <bool Q6, int NCOLS>
+__device__ __forceinline__ void lane_unit(uint32_t stage, int nunits, int u, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    if constexpr (Q6) unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
+    else              unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
+}
+template <int NCOLS, bool Q6 = false>
 __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride,
                                          const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane,
                                          int rp, int sub, int b) {
@@ -455,7 +529,7 @@ __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uin
             float acc[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-            if (live) unit_q4k<NCOLS>(stage + (uint32_t) (row * upr + b) * 144, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+            if (live) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) {
                 float v = acc[c];
@@ -474,7 +548,7 @@ __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uin
             float acc[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-            if (b < upr) unit_q4k<NCOLS>(stage + (uint32_t) (row * upr + b) * 144, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+            if (b < upr) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) {
                 const float v = warp_sum(acc[c]);
@@ -505,7 +579,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     auto desc_at   = [&](int g, int st) { return base + 128u + (uint32_t) ((g * CH_NS + st) * 48); };
     const uint32_t xs = base + CH_HDR;
     const uint32_t part_bytes = (uint32_t) (NCOLS * a.max_units) * 4;
-    const uint32_t ring0 = (xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 127u) & ~127u;
+    const uint32_t ring0 = (xs + (uint32_t) a.x_bytes + CH_GROUPS * 2 * part_bytes + 1023u) & ~1023u;     // swizzle patterns repeat every 1024 B
 
     if (tid == 0) {
         for (int i = 0; i < CH_GROUPS * CH_NS; ++i) { mbar_init(base + i * 8, 1); mbar_init(base + 64 + i * 8, CH_GWARPS); }
@@ -543,11 +617,29 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 { const unsigned long long tg = (unsigned long long) item[g].tag; sts8(dsc + 32, (uint32_t) tg, (uint32_t) (tg >> 32)); }
                 const uint32_t total = item[g].bytes[0] + item[g].bytes[1] + item[g].bytes[2] + item[g].bytes[3];
                 mbar_arrive_expect_tx(bar, total);                       // release: the descriptor is visible to whoever sees the phase flip
-                uint32_t o = 0;
+                if (item[g].type == CH_T_Q6K_SW) {
+                    // tensor copies of R rows (box = R x upr units x 128 / 64 bytes), single rows for the tail; SC and D as bulk copies
+                    const int nr = item[g].nrows, u0 = (int) (item[g].pad & 0xffffffffll), R = (int) (item[g].pad >> 32);
+                    const int upr_i = (int) (item[g].bytes[0] >> 7) / nr;
+                    const uint32_t qh0 = dst + (uint32_t) q6sw_qh0(nr * upr_i);
+                    int r = 0;
+                    for (; r + R <= nr; r += R) {
+                        tma_load_2d_hint(dst + (uint32_t) (r * upr_i * 128), item[g].src[0], 0, u0 + r * upr_i, bar, policy);
+                        tma_load_2d_hint(qh0 + (uint32_t) (r * upr_i * 64), item[g].src[1], 0, u0 + r * upr_i, bar, policy);
+                    }
+                    for (; r < nr; ++r) {
+                        tma_load_2d_hint(dst + (uint32_t) (r * upr_i * 128), item[g].src[0] + 2 * sizeof(CUtensorMap), 0, u0 + r * upr_i, bar, policy);
+                        tma_load_2d_hint(qh0 + (uint32_t) (r * upr_i * 64), item[g].src[1] + 2 * sizeof(CUtensorMap), 0, u0 + r * upr_i, bar, policy);
+                    }
+                    bulk_g2s(qh0 + item[g].bytes[1], item[g].src[2], item[g].bytes[2], bar, policy);
+                    bulk_g2s(qh0 + item[g].bytes[1] + item[g].bytes[2], item[g].src[3], item[g].bytes[3], bar, policy);
+                } else {
+                    uint32_t o = 0;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    if (item[g].bytes[p]) bulk_g2s(dst + o, item[g].src[p], item[g].bytes[p], bar, policy);
-                    o += item[g].bytes[p];
+                    for (int p = 0; p < 4; ++p) {
+                        if (item[g].bytes[p]) bulk_g2s(dst + o, item[g].src[p], item[g].bytes[p], bar, policy);
+                        o += item[g].bytes[p];
+                    }
                 }
                 ++nxt[g]; ++seq[g];
                 if (nxt[g] < end[g]) item[g] = a.items[nxt[g]];           // in flight while the ring drains
@@ -626,6 +718,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
             if (a.debug & 2) {
             } else if (type == B200_TYPE_Q4_K) {
                 item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+            } else if (type == CH_T_Q6K_SW) {
+                item_q4k<NCOLS, true>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q6_K) {
                 item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             } else if (type == B200_TYPE_IQ4_XS) {
@@ -727,6 +821,26 @@ template <int NCOLS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s)
     return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS>, c.args);
 }
 
+// [units][plane_bytes] uint8 plane of a Q6_K matrix; one box = the `upr` units of one weight row
+typedef CUresult (*chain_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool chain_plane_map(CUtensorMap * tm, const void * base, uint32_t plane, uint64_t units, uint32_t upr, CUtensorMapSwizzle sw) {
+    static chain_encode_fn fn = [] {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (chain_encode_fn) p;
+    }();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {plane, units};
+    const cuuint64_t strides[1] = {plane};
+    const cuuint32_t box[2] = {plane, upr};
+    const cuuint32_t estr[2] = {1, 1};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, bool split = false) {
     if (!nodes || !group_sizes || n_groups < 1) return "no nodes";
     int idx = 0;
@@ -798,7 +912,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     int stage = 0, max_units = 0;
     for (int st = 48 * 1024; st >= 4 * 1024; st -= 1024) {
         const int mu = st / 136 + 64;         // partial sums: at most max(rows, 2 x warps + rows) tasks per item
-        const int64_t need = CH_HDR + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 128 + (int64_t) CH_GROUPS * CH_NS * st;
+        const int64_t need = CH_HDR + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 1024 + (int64_t) CH_GROUPS * CH_NS * st;
         if (need <= total_smem) { stage = st; max_units = mu; break; }
     }
     if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < stage) { stage = v; } }
@@ -806,6 +920,9 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
 
     std::vector<ChainNodeD> hn(n_groups);
     std::vector<ChainMatD> hm;       // host-side only: the items carry everything the kernel needs
+    std::vector<CUtensorMap> maps;   // two per swizzled Q6_K matrix (QL, QH); copied into the blob, the items point at them
+    std::vector<int> mat_map, mat_R; // per matrix: index of its first map or -1 (four: QL, QH for R rows per copy, QL, QH for one row), R
+    const bool q6_swizzled = getenv("B200_CHAIN_Q6K_LANES8") == nullptr;
 
     // ---- how each node learns that its X is complete (NB_*): from the pointers ------------------------------------------
     std::vector<int> mode(n_groups, NB_NONE), feed(n_groups, -1), first(n_groups + 1, 0);
@@ -871,6 +988,27 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
             const b200_mul_mat_args & a = nodes[idx + i];
             ChainMatD M; M.w = (const uint8_t *) a.w; M.y = a.y; M.ldy = a.y_row_stride; M.m = (int) a.m; M.type = a.type; M.upr = upr; M.pad = 0;
             hm.push_back(M);
+            // Q6_K rows of a multiple of 8 units: QL / QH through swizzling tensor copies, one block per lane (unit_q6k)
+            int map0 = -1, R = 1;
+            if (a.type == B200_TYPE_Q6_K && q6_swizzled && upr % 8 == 0 && a.m > 0 && (int64_t) a.m * upr < (1ll << 31)) {
+                const uint8_t * w = (const uint8_t *) a.w;
+                // rows per tensor copy: as many as the box limit (256 units) and a ring stage allow, but at least two copies per full stage
+                const int fit = (int) (((int64_t) stage - 512) / ((int64_t) 210 * upr));
+                const int lim = 256 / upr < fit ? 256 / upr : fit;
+                while (2 * R <= lim) R *= 2;
+                int pf = 1; while (2 * pf <= fit) pf *= 2;
+                if (R == pf && R > 2) R /= 2;
+                CUtensorMap t4[4];
+                if (chain_plane_map(&t4[0], w, 128, (uint64_t) a.m * upr, (uint32_t) (R * upr), CU_TENSOR_MAP_SWIZZLE_128B) &&
+                    chain_plane_map(&t4[1], w + (int64_t) a.m * upr * 128, 64, (uint64_t) a.m * upr, (uint32_t) (R * upr), CU_TENSOR_MAP_SWIZZLE_64B) &&
+                    chain_plane_map(&t4[2], w, 128, (uint64_t) a.m * upr, (uint32_t) upr, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                    chain_plane_map(&t4[3], w + (int64_t) a.m * upr * 128, 64, (uint64_t) a.m * upr, (uint32_t) upr, CU_TENSOR_MAP_SWIZZLE_64B)) {
+                    map0 = (int) maps.size();
+                    for (int t = 0; t < 4; ++t) maps.push_back(t4[t]);
+                }
+            }
+            mat_R.push_back(R);
+            mat_map.push_back(map0);
         }
         // cut positions as (matrix, row)
         auto cut_of = [&](int64_t t, int & mi, int64_t & row) {
@@ -895,19 +1033,22 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                 if (r1 <= r0) continue;
                 const int type = nodes[idx + mi].type;
                 const int gr = row_granule(type, upr);
-                int64_t max_rows = (int64_t) stage / ((int64_t) unit_bytes(type) * upr) / gr * gr;
+                const int map0 = mat_map[mat_base + mi];
+                int64_t max_rows = ((int64_t) stage - (map0 >= 0 ? 512 : 0)) / ((int64_t) unit_bytes(type) * upr) / gr * gr;
                 if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); if (!split) cudaFree(d_tags); return nullptr; }
                 const int64_t rows = r1 - r0;
                 const int64_t nit = (rows + max_rows - 1) / max_rows;
-                int64_t per = ((rows + nit - 1) / nit + gr - 1) / gr * gr;
-                if (per > max_rows) per = max_rows;
+                const int R = mat_R[mat_base + mi];
+                const int64_t pg = map0 >= 0 && max_rows >= R ? (int64_t) R : (int64_t) gr;      // full items are whole tensor copies (R is a power of two, gr = 1 here)
+                int64_t per = ((rows + nit - 1) / nit + pg - 1) / pg * pg;
+                if (per > max_rows) per = max_rows / pg * pg;
                 for (int64_t r = r0; r < r1; r += per) {
                     const ChainMatD & M = hm[mat_base + mi];
                     ChainItemD it = {};
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
                     it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
-                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     int64_t plane_off = 0;
                     for (int p = 0; p < 4; ++p) {
                         const int pb = plane_bytes(type, p);
@@ -915,6 +1056,11 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                         it.src[p] = M.w + plane_off + r * upr * pb;
                         it.bytes[p] = (uint32_t) ((int64_t) it.nrows * upr * pb);
                         plane_off += (int64_t) M.m * upr * pb;
+                    }
+                    if (map0 >= 0) {              // src[0], src[1]: offsets of the tensor maps for now (blob address not known yet)
+                        it.type = CH_T_Q6K_SW; it.pad = (long long) (r * upr) | ((long long) R << 32);
+                        it.src[0] = (const uint8_t *) (uintptr_t) ((size_t) map0 * sizeof(CUtensorMap));
+                        it.src[1] = (const uint8_t *) (uintptr_t) ((size_t) (map0 + 1) * sizeof(CUtensorMap));
                     }
                     out.push_back(it);
                 }
@@ -936,13 +1082,20 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
 
     auto al = [](size_t v) { return (v + 255) & ~(size_t) 255; };
     const size_t o_nodes = 256, o_items = o_nodes + al(hn.size() * sizeof(ChainNodeD)),
-                 o_off = o_items + al(hi.size() * sizeof(ChainItemD) + 16), total = o_off + al(hoff.size() * sizeof(int));
+                 o_off = o_items + al(hi.size() * sizeof(ChainItemD) + 16), o_maps = o_off + al(hoff.size() * sizeof(int)),
+                 total = o_maps + al(maps.size() * sizeof(CUtensorMap));
     std::vector<uint8_t> blob(total, 0);
+    if (!maps.empty()) memcpy(blob.data() + o_maps, maps.data(), maps.size() * sizeof(CUtensorMap));
     memcpy(blob.data() + o_nodes, hn.data(), hn.size() * sizeof(ChainNodeD));
     if (!hi.empty()) memcpy(blob.data() + o_items, hi.data(), hi.size() * sizeof(ChainItemD));
     memcpy(blob.data() + o_off, hoff.data(), hoff.size() * sizeof(int));
     void * d = nullptr;
-    if (cudaMalloc(&d, total) != cudaSuccess || cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
+    if (cudaMalloc(&d, total) == cudaSuccess) {
+        ChainItemD * bi = (ChainItemD *) (blob.data() + o_items);
+        for (size_t t = 0; t < hi.size(); ++t)
+            if (bi[t].type == CH_T_Q6K_SW) for (int p = 0; p < 2; ++p) bi[t].src[p] = (const uint8_t *) d + o_maps + (size_t) (uintptr_t) bi[t].src[p];
+    }
+    if (!d || cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice) != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaMalloc/cudaMemcpy of %zu bytes failed: %s", total, cudaGetErrorString(cudaGetLastError()));
         if (d) cudaFree(d);
         if (!split) cudaFree(d_tags);
@@ -971,7 +1124,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     if (c->args.inflight < 1) c->args.inflight = 1;
     c->args.debug = getenv("B200_CHAIN_DEBUG") ? atoi(getenv("B200_CHAIN_DEBUG")) : 0;
     c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes;
-    c->smem = CH_HDR + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 128 + (size_t) CH_GROUPS * CH_NS * stage;
+    c->smem = CH_HDR + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 1024 + (size_t) CH_GROUPS * CH_NS * stage;
     c->cooperative = coop != 0 && !getenv("B200_CHAIN_NO_COOP");
     cudaError_t e = cudaSuccess;
     switch (ncols) {
