@@ -56,6 +56,8 @@ struct GemmArgs {
     int stages;
     int acc_cols;               // TMEM columns of one accumulator buffer: power of two >= max(32, bn); two buffers are allocated
     int debug;                  // B200_GEMM_DEBUG bit mask (timing experiments only: results are wrong when set)
+    int pdl;                    // launched with programmatic stream serialisation: weights are staged and dequantised before griddepcontrol.wait,
+                                //   the activation loads and the Y stores come after it
     // work list of the persistent grid: units 0..full_tiles-1 are whole tiles (plain stores); the remaining tiles are cut
     // `ksplit` ways along k (units full_tiles + (tile - full_tiles) * ksplit + z) and meet in pre-zeroed Y with red.global.add
     int n_tiles;                // tiles along n; tile index = m_tile * n_tiles + n_tile (the n-tiles of one weight tile run side by side)
@@ -111,6 +113,14 @@ __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict_
         for (int64_t i = threadIdx.x; i < k; i += 256) xh[row * k + i] = __float2half_rn(xr[i] * down);
     }
     if (threadIdx.x == 0) xscale[row] = ldexpf(1.0f, e);
+}
+
+// zeroes y[r][m_lo .. m) for r < n: the rows the k-split tiles accumulate into (a kernel, not a memset node, so that the
+// programmatic launch edges between prologue, this and the GEMM survive stream capture)
+__global__ void __launch_bounds__(256) zero_rows_kernel(float * __restrict__ y, int64_t ldy, int64_t m_lo, int64_t m, bool pdl) {
+    if (pdl) { pdl_launch_dependents(); pdl_wait(); }
+    float * yr = y + (int64_t) blockIdx.x * ldy;
+    for (int64_t i = m_lo + threadIdx.x; i < m; i += 256) yr[i] = 0.0f;
 }
 
 // ---- raw weight staging: one stage = 128 rows x one 256-element super-block, in the plane layout ----------
@@ -180,6 +190,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
     const uint32_t smem_w = smem0;
     const uint32_t smem_a = smem0 + (uint32_t) (RAW_STAGES * Raw<TYPE>::BYTES), smem_b = smem_a + (uint32_t) stages * A_STAGE;
 
+    if (a.pdl) pdl_launch_dependents();      // the next kernel may start its own prologue; it waits for this grid before touching memory
     if (warp == 0 && lane == 0) prefetch_tensormap(&tmap_x);
     if (warp == 3 && lane == 0) {
         for (int i = 0; i < a.nmat; ++i) {
@@ -215,6 +226,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
     if (warp == 0) {
         // ===== TMA producer: activation boxes (64 k x bn rows) =====
         if (lane == 0) {
+            if (a.pdl) pdl_wait();               // X (fp16 copy) is written by the kernel before this one
             StageCursor c(stages, 0);
             for (int u = unit0; u < a.total_units; u += unit_step) {
                 const Unit w = unit_decode<PAIR>(a, u, rank);
@@ -319,6 +331,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         // ===== epilogue: TMEM -> registers -> Y (thread = weight row, 16 activation rows per load) =====
         const int q = warp & 3;                                  // TMEM lane quarter this warp may touch
         int i = 0;
+        if (a.pdl) pdl_wait();                   // Y may still be read by earlier kernels; xscale comes from the prologue kernel
         for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
             const Unit w = unit_decode<PAIR>(a, u, rank);
             const int buf = i & 1;
@@ -456,8 +469,8 @@ int launch_gemm(const CUtensorMap & tm, const WMapSet & w, const GemmArgs & g, d
         B200_CHECK(cudaFuncSetAttribute(gemm_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         configured = true;
     }
-    if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
-    else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
+    if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, g.pdl != 0, tm, w, g));
+    else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, g.pdl != 0, tm, w, g));
     return 0;
 }
 
@@ -563,12 +576,14 @@ int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream
     if (ks == 1) { full = tiles; rest = 0; }
     g.full_tiles = (int) full; g.ksplit = ks; g.total_units = (int) (full + rest * ks);
     if (const char * e = getenv("B200_GEMM_DEBUG")) g.debug = atoi(e);
+    static const bool pdl_env = [] { const char * e = getenv("B200_GEMM_PDL"); return !e || atoi(e) != 0; }();
+    g.pdl = pdl && pdl_env ? 1 : 0;
     if (rest > 0) {     // zero the weight rows the split tiles accumulate into (full tiles of the same rows overwrite later, in stream order)
         for (int i = 0; i < count; ++i) {
             const int64_t first = full > g.tile_begin[i] ? full - g.tile_begin[i] : 0;       // first split tile of this matrix (local index)
             const int64_t m_lo = first / n_tiles * tile_m;
             if (m_lo >= args[i].m) continue;
-            B200_CHECK(cudaMemset2DAsync(args[i].y + m_lo, (size_t) args[i].y_row_stride * sizeof(float), 0, (size_t) (args[i].m - m_lo) * sizeof(float), (size_t) n, s));
+            B200_CHECK(b200_launch(zero_rows_kernel, dim3((unsigned) n), dim3(256), 0, s, pdl, args[i].y, args[i].y_row_stride, m_lo, args[i].m, pdl));
         }
     }
     const unsigned nw = (unsigned) (g.total_units < workers ? g.total_units : workers);
