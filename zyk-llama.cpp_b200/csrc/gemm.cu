@@ -29,6 +29,7 @@
 
 #include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
 
 using namespace sm100;
 
@@ -38,8 +39,8 @@ constexpr int BM = 128;            // weight rows per tile = UMMA M
 constexpr int BK = 64;             // k-elements per stage = one 128-byte swizzle row of fp16
 constexpr int A_STAGE = BM * BK * 2;
 constexpr int DEQ_WARPS = 8;
-constexpr int EPI_WARPS = 4;
-constexpr int THREADS = 128 + DEQ_WARPS * 32 + EPI_WARPS * 32;   // warps 0..3: TMA X, MMA, TMEM, TMA W | 4..11: dequantisers | 12..15: epilogue
+constexpr int EPI_WARPS = 8;              // two warps per TMEM lane quarter: they take alternate 32-column blocks of the accumulator
+constexpr int THREADS = 128 + DEQ_WARPS * 32 + EPI_WARPS * 32;   // warps 0..3: TMA X, MMA, TMEM, TMA W | 4..11: dequantisers | 12..19: epilogue
 constexpr int MAX_STAGES = 8;
 constexpr size_t SMEM_BUDGET = 224 * 1024;   // dynamic shared memory per CTA (227 KB usable minus the static barriers)
 
@@ -56,6 +57,7 @@ struct GemmArgs {
     int stages;
     int acc_cols;               // TMEM columns of one accumulator buffer: power of two >= max(32, bn); two buffers are allocated
     int debug;                  // B200_GEMM_DEBUG bit mask (timing experiments only: results are wrong when set)
+    unsigned long long * trace; // B200_GEMM_TRACE: globaltimer samples of the leader CTAs, [pair][unit < 8][8] (debugging aid)
     int pdl;                    // launched with programmatic stream serialisation: weights are staged and dequantised before griddepcontrol.wait,
                                 //   the activation loads and the Y stores come after it
     // work list of the persistent grid: units 0..full_tiles-1 are whole tiles (plain stores); the remaining tiles are cut
@@ -145,6 +147,7 @@ constexpr int RAW_STAGES = 2;
 // planes | warps 4..11: dequantise raw -> fp16 operand tiles | warps 12..15: epilogue. Two accumulator buffers in
 // TMEM: the epilogue of unit i (TMEM -> registers -> Y, 128 KB of stores) overlaps the MMAs of unit i + 1. All
 // rings (operand stages, raw stages, accumulators) keep running across units.
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 struct StageCursor {     // ring position without a division per step
     int s; uint32_t ph; int stages;
     __device__ __forceinline__ StageCursor(int stages_, int start) : s(start % stages_), ph((uint32_t) (start / stages_) & 1u), stages(stages_) {}
@@ -270,8 +273,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
             const int num_kb = 4 * w.num_sb;
             const int buf = i & 1;
             const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols);
+            unsigned long long * tr = a.trace && lane == 0 && i < 8 ? a.trace + ((size_t) (blockIdx.x >> (PAIR ? 1 : 0)) * 8 + i) * 8 : nullptr;
+            if (tr) tr[0] = gtime();
             mbar_wait(smem_u32(&acc_empty[buf]), (uint32_t) ((i >> 1) & 1) ^ 1u);     // the epilogue has drained this buffer
             tc_fence_after();
+            if (tr) tr[1] = gtime();
             for (int kb = 0; kb < num_kb; ++kb, c.advance(1)) {
                 mbar_wait(smem_u32(&bar_full[c.s]), c.ph);
                 tc_fence_after();
@@ -292,7 +298,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
                     }
                 }
                 __syncwarp();
+                if (tr && kb == 0) tr[2] = gtime();
             }
+            if (tr) tr[3] = gtime();
         }
     } else if (warp >= 4 && warp < 4 + DEQ_WARPS) {
         // ===== weight producers: thread = tile row; the two halves of the group alternate 64-element k-blocks =====
@@ -330,6 +338,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
     } else if (warp >= 4 + DEQ_WARPS) {
         // ===== epilogue: TMEM -> registers -> Y (thread = weight row, 16 activation rows per load) =====
         const int q = warp & 3;                                  // TMEM lane quarter this warp may touch
+        const int eh = (warp - 4 - DEQ_WARPS) >> 2;              // which of the quarter's two warps: column blocks eh, eh + 2, ...
         int i = 0;
         if (a.pdl) pdl_wait();                   // Y may still be read by earlier kernels; xscale comes from the prologue kernel
         for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
@@ -337,20 +346,30 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
             const int buf = i & 1;
             const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols) + ((uint32_t) (32 * q) << 16);
             const int64_t mrow = w.m0 + 32 * q + lane;
+            // lane l carries the scales of activation rows 32 * c8 + l of the tile: all loads are issued before the wait for the
+            // accumulator, so their latency hides behind the MMAs of the unit (one load per iteration, consumed by the next one,
+            // made the epilogue a chain of 8 L2 round trips: ~7 us per unit, exposed at the end of every launch)
+            const int n_left = (int) (a.n - w.n0 < bn ? a.n - w.n0 : bn);             // activation rows of this tile that exist (>= 1)
+            float xsv[8];
+#pragma unroll
+            for (int c8 = 0; c8 < 8; ++c8) {
+                const int nn = c8 * 32 + lane;
+                xsv[c8] = c8 * 32 < bn ? __ldg(a.xscale + w.n0 + (nn < n_left ? nn : n_left - 1)) : 0.0f;
+            }
+            unsigned long long * tr = a.trace && leader && q == 0 && eh == 0 && lane == 0 && i < 8 ? a.trace + ((size_t) (blockIdx.x >> (PAIR ? 1 : 0)) * 8 + i) * 8 : nullptr;
+            if (tr) tr[4] = gtime();
             mbar_wait(smem_u32(&acc_full[buf]), (uint32_t) ((i >> 1) & 1));
             tc_fence_after();
+            if (tr) tr[5] = gtime();
             const bool row_ok = mrow < a.m[w.mat] && !(a.debug & 16);
             const int64_t ldy = a.ldy[w.mat];
-            float * yp = a.y[w.mat] + (int64_t) w.n0 * ldy + (row_ok ? mrow : 0);
-            const int n_left = (int) (a.n - w.n0 < bn ? a.n - w.n0 : bn);             // activation rows of this tile that exist (>= 1)
-            // lane l carries the scale of activation row 32 * cc + l of the tile, fetched one iteration ahead
-            float xs_next = __ldg(a.xscale + w.n0 + (lane < n_left ? lane : n_left - 1));
-            for (int cc = 0; cc * 32 < bn; ++cc, yp += 32 * ldy) {                  // columns past bn (inside acc_cols) are read and dropped
+            float * yp = a.y[w.mat] + (int64_t) (w.n0 + 32 * eh) * ldy + (row_ok ? mrow : 0);
+            for (int cc = eh; cc * 32 < bn; cc += EPI_WARPS / 4, yp += (EPI_WARPS / 4) * 32 * ldy) {     // columns past bn (inside acc_cols) are read and dropped
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(tmem_acc + (uint32_t) (cc * 32), v);
-                const float xs_lane = xs_next;
-                const int nn = cc * 32 + 32 + lane;
-                xs_next = __ldg(a.xscale + w.n0 + (nn < n_left ? nn : n_left - 1));
+                float xs_lane = xsv[0];
+#pragma unroll
+                for (int c8 = 1; c8 < 8; ++c8) if (cc == c8) xs_lane = xsv[c8];
                 tmem_ld_wait();
                 if (!w.split) {
 #pragma unroll
@@ -368,6 +387,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
             }
             tc_fence_before();
             __syncwarp();
+            if (tr) tr[6] = gtime();
             if (lane == 0) {
                 if (PAIR && !leader) mbar_arrive_cluster(smem_u32(&acc_empty[buf]), 0);
                 else mbar_arrive(smem_u32(&acc_empty[buf]));
@@ -576,6 +596,26 @@ int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream
     if (ks == 1) { full = tiles; rest = 0; }
     g.full_tiles = (int) full; g.ksplit = ks; g.total_units = (int) (full + rest * ks);
     if (const char * e = getenv("B200_GEMM_DEBUG")) g.debug = atoi(e);
+    static unsigned long long * trace_buf = [] {
+        unsigned long long * p = nullptr;
+        if (getenv("B200_GEMM_TRACE") && cudaMallocManaged((void **) &p, 148 * 8 * 8 * 8) == cudaSuccess) {
+            memset(p, 0, 148 * 8 * 8 * 8);
+            static unsigned long long * keep; keep = p;
+            atexit([] {
+                cudaDeviceSynchronize();
+                unsigned long long t0 = ~0ull;
+                for (int i = 0; i < 148 * 64; ++i) if (keep[i] && keep[i] < t0) t0 = keep[i];
+                for (int pr = 0; pr < 74; pr += 24) for (int u = 0; u < 8; ++u) {
+                    const unsigned long long * r = keep + ((size_t) pr * 8 + u) * 8;
+                    if (!r[0]) continue;
+                    fprintf(stderr, "gemm trace pair %2d unit %d: mma start %7.2f  acc_empty %7.2f  first stage %7.2f  issued %7.2f | epi wait-from %7.2f  acc_full %7.2f  done %7.2f us\n", pr, u,
+                            (r[0] - t0) * 1e-3, (r[1] - t0) * 1e-3, (r[2] - t0) * 1e-3, (r[3] - t0) * 1e-3, (r[4] - t0) * 1e-3, (r[5] - t0) * 1e-3, (r[6] - t0) * 1e-3);
+                }
+            });
+        }
+        return p;
+    }();
+    g.trace = trace_buf;
     static const bool pdl_env = [] { const char * e = getenv("B200_GEMM_PDL"); return !e || atoi(e) != 0; }();
     g.pdl = pdl && pdl_env ? 1 : 0;
     if (rest > 0) {     // zero the weight rows the split tiles accumulate into (full tiles of the same rows overwrite later, in stream order)
