@@ -67,6 +67,8 @@ struct GemmArgs {
 };
 
 // ---- prologue: X f32 [n][k] (row stride ldx) -> fp16 [n][k] scaled by 2^-e per row, xscale[n] = 2^e ----
+// VMAX: 128-bit loads per thread the one-pass path may hold (k <= 1024 VMAX); small VMAX = few registers = the whole launch resident at once
+template <int VMAX>
 __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict__ x, int64_t ldx, int64_t k, __half * __restrict__ xh,
                                                        float * __restrict__ xscale, bool pdl) {
     if (pdl) { pdl_launch_dependents(); pdl_wait(); }
@@ -74,7 +76,6 @@ __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict_
     const float * xr = x + row * ldx;
     __shared__ float red[8];
     // one pass when the row fits the registers of the CTA (k <= 16384, 16-byte aligned): 128-bit loads, the row is read once
-    constexpr int VMAX = 16;
     const bool vec = k <= 256 * 4 * VMAX && (k & 3) == 0 && (((uintptr_t) xr) & 15) == 0;
     float4 v[VMAX];
     float amax = 0.0f;
@@ -535,7 +536,11 @@ int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream
     __half * xh = (__half *) a->workspace;
     float * xscale = (float *) ((uint8_t *) a->workspace + align256((size_t) n * k * sizeof(__half)));
     if (!(a->flags & B200_MM_X_PREQUANTISED))
-        B200_CHECK(b200_launch(act_half_kernel, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
+    {
+        if (k <= 4096)      B200_CHECK(b200_launch(act_half_kernel<4>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
+        else if (k <= 8192) B200_CHECK(b200_launch(act_half_kernel<8>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
+        else                B200_CHECK(b200_launch(act_half_kernel<16>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
+    }
 
     // N tiling: equal tiles of at most 256 rows, multiple of 16
     const int n_tiles = (int) ((n + 255) / 256);
