@@ -40,6 +40,7 @@ CASES = [
     # (name, k0, [(types and row counts of group 1)], m2, [(group 3)], m4)
     ("kquants", 2048, [(Q4_K, 1536), (Q4_K, 256), (Q6_K, 256)], 4096, [(Q4_K, 3584), (Q4_K, 3584)], 2048, Q6_K),
     ("q6k_k14336", 4096, [(Q6_K, 14336)], 4096, [(Q6_K, 1024), (Q4_K, 1024)], 2048, Q4_K),
+    ("q6k_70b_shapes", 8192, [(Q6_K, 1024), (Q4_K, 27648)], 2048, [(Q6_K, 512)], 256, Q4_K),      # 32 and 112 units per row: one / two rows per tensor copy
     ("iq4_xs", 1024, [(IQ4_XS, 2048), (IQ4_XS, 512), (Q6_K, 512)], 2048, [(IQ4_XS, 4096)], 1024, IQ4_XS),
     ("q4_0", 2048, [(Q4_0, 2048), (Q4_0, 512), (Q4_0, 512)], 2048, [(Q4_0, 8192), (Q4_0, 8192)], 2048, Q8_0),
     ("q8_0", 1024, [(Q8_0, 1024), (Q8_0, 256)], 512, [(Q8_0, 3072)], 1024, Q4_0),
@@ -75,6 +76,12 @@ def test_chain_matches_oracle_node_by_node(b200, orc, case, n):
     w, wp = _mk(b200, t_last, m4, h3w, rng); keep.append(wp)
     groups.append([_args(b200, t_last, wp, h3, out, m4)]); nodes.append((t_last, w, h3, out, 0, m4))
 
+    if name == "q6k_70b_shapes" and n == 4:
+        # 4 x 28672 quantised activations leave no ring stage that holds one 23 KB row: refused up front, create agrees
+        assert not b200.DecodeChain.supported(groups)
+        with pytest.raises(b200.B200Error):
+            b200.DecodeChain(0, groups)
+        return
     assert b200.DecodeChain.supported(groups)
     ch = _run_chain(b200, groups)
     info = ch.info()

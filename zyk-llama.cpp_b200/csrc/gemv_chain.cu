@@ -841,6 +841,18 @@ bool chain_plane_map(CUtensorMap * tm, const void * base, uint32_t plane, uint64
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// ring stage: what is left after X, split over groups x stages; the partial buffers depend on the stage size
+// (max_units = stage / 136 units of 4 B x 2 buffers x ncols per group), solved by stepping the stage size down. 0: no room
+int chain_stage_bytes(int ncols, int64_t kmax, int total_smem, int * max_units) {
+    const int64_t x_bytes = ((int64_t) ncols * (kmax >> 8) * XU_BYTES + 127) & ~(int64_t) 127;
+    for (int st = 48 * 1024; st >= 4 * 1024; st -= 1024) {
+        const int mu = st / 136 + 64;         // partial sums: at most max(rows, 2 x warps + rows) tasks per item
+        const int64_t need = CH_HDR + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 1024 + (int64_t) CH_GROUPS * CH_NS * st;
+        if (need <= total_smem) { if (max_units) *max_units = mu; return st; }
+    }
+    return 0;
+}
+
 const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, bool split = false) {
     if (!nodes || !group_sizes || n_groups < 1) return "no nodes";
     int idx = 0;
@@ -864,6 +876,15 @@ const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_
             if (a.m % row_granule(a.type, (int) (a.k >> 8)) != 0) return "row count incompatible with 16-byte plane pieces";
             if (a.flags & B200_MM_X_PREQUANTISED) return "prequantised X";
         }
+    }
+    // every row granule must fit one ring stage next to the quantised activations of the widest node (n x k of 4 x 28672 does not)
+    int64_t kmax = 0;
+    for (int i = 0; i < idx; ++i) kmax = nodes[i].k > kmax ? nodes[i].k : kmax;
+    const int stage = chain_stage_bytes((int) n0, kmax, CH_SMEM_TOTAL, nullptr);
+    if (!stage) return "activations leave no room for the weight ring";
+    for (int i = 0; i < idx; ++i) {
+        const int upr = (int) (nodes[i].k >> 8);
+        if ((int64_t) unit_bytes(nodes[i].type) * upr * row_granule(nodes[i].type, upr) > stage - 512) return "a weight row does not fit a ring stage next to the activations";
     }
     return nullptr;
 }
@@ -910,11 +931,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     // ring stage: what is left after X, split over groups x stages; the partial buffers depend on the stage size
     // (max_units = stage / 136 units of 4 B x 2 buffers x ncols per group), solve by stepping the stage size down
     int stage = 0, max_units = 0;
-    for (int st = 48 * 1024; st >= 4 * 1024; st -= 1024) {
-        const int mu = st / 136 + 64;         // partial sums: at most max(rows, 2 x warps + rows) tasks per item
-        const int64_t need = CH_HDR + x_bytes + (int64_t) CH_GROUPS * 2 * ncols * mu * 4 + 1024 + (int64_t) CH_GROUPS * CH_NS * st;
-        if (need <= total_smem) { stage = st; max_units = mu; break; }
-    }
+    stage = chain_stage_bytes(ncols, kmax, total_smem, &max_units);
     if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < stage) { stage = v; } }
     if (!stage) { b200_set_error("b200_chain_create: activations of %d x %lld do not leave room for the weight ring", ncols, (long long) kmax); return nullptr; }
 
