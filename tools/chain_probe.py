@@ -23,9 +23,9 @@ def show_timeline(tl, call_ops, mhz=1965.0):
     us = lambda c: c / mhz
     kinds = {}
     for n, ops in enumerate(call_ops):
-        key = "+".join(o.name.split(".")[-1] for o in ops)
+        key = "+".join(o.name.split(".")[-1] for o in ops) + " [" + "/".join(str(o.type) for o in ops) + "]"     # weight types: ffn_down is Q6_K in half of the layers
         kinds.setdefault(key, []).append(n)
-    print(f"  {'node kind':28s} {'n':>3s} | {'node us':>8s} {'wait':>6s} {'quant':>6s} {'items':>6s} | per group: {'copy stall':>10s} {'item loop':>9s} | {'MB':>6s} {'GB/s':>6s}")
+    print(f"  {'node kind':40s} {'n':>3s} | {'node us':>8s} {'wait':>6s} {'quant':>6s} {'items':>6s} | per group: {'copy stall':>10s} {'item loop':>9s} | {'MB':>6s} {'GB/s':>6s}")
     for key, idx in kinds.items():
         t = tl[:, idx, :].astype(np.float64)
         node = (t[:, :, 3] - t[:, :, 0]).mean()
@@ -39,7 +39,7 @@ def show_timeline(tl, call_ops, mhz=1965.0):
         skew = (gt.max(axis=0) - np.median(gt, axis=0)).mean() / 1e3
         spread = (gt.max(axis=0) - gt.min(axis=0)).mean() / 1e3
         mb = sum(o.streamed_bytes for o in call_ops[idx[0]]) / 1e6
-        print(f"  {key:28s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} end-skew max-med {skew:5.2f} max-min {spread:5.2f} us | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
+        print(f"  {key:40s} {len(idx):3d} | {us(node):8.2f} {us(wait):6.2f} {us(quant):6.2f} {us(items):6.2f} | {'':10s} {us(stall):10.2f} {us(loop):9.2f} rel {us(rel):5.2f} end-skew max-med {skew:5.2f} max-min {spread:5.2f} us | {mb:6.1f} {mb / us(node) * 1e3 if node else 0:6.0f}")
 
 
 def show_lateness(tl):
