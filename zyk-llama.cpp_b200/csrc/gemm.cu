@@ -522,7 +522,9 @@ bool b200_gemm_groupable(const b200_mul_mat_args * args, int count) {
 // `count` <= GEMM_MAX_GROUP weight matrices of the same type against the same X: the tiles of all of them form one work list for
 // the persistent grid (wq/wk/wv and ffn_gate/ffn_up: 7 -> 4 launches per layer, and the 2 x 112 tiles of gate + up fill 74 CTA
 // pairs in 3.03 waves instead of 2 x 2). args[0].flags decides whether X still has to be converted.
-int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s) {
+int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s) { return b200_gemm_launch_group_ev(args, count, s, nullptr); }
+
+int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStream_t s, cudaEvent_t after_prologue) {
     encode_tiled_fn encode = get_encode_tiled();
     B200_REQUIRE(encode != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
     B200_REQUIRE(b200_gemm_groupable(args, count), "gemm: the %d nodes of the group do not share type / X / workspace", count);
@@ -541,6 +543,7 @@ int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream
         else if (k <= 8192) B200_CHECK(b200_launch(act_half_kernel<8>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
         else                B200_CHECK(b200_launch(act_half_kernel<16>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
     }
+    if (after_prologue) B200_CHECK(cudaEventRecord(after_prologue, s));
 
     // N tiling: equal tiles of at most 256 rows, multiple of 16
     const int n_tiles = (int) ((n + 255) / 256);

@@ -9,3 +9,5 @@ int    b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s);
 // up to 3 nodes of the same weight type that read the same X (and share the workspace): one launch, one tile list
 bool   b200_gemm_groupable(const b200_mul_mat_args * args, int count);
 int    b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s);
+// same; `after_prologue` (may be null) is recorded on `s` once the fp16 copy of X is in the workspace (before the GEMM itself)
+int    b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStream_t s, cudaEvent_t after_prologue);

@@ -165,6 +165,24 @@ static bool group_shares_x(const b200_mul_mat_args * args, int count) {
 }
 
 // several MUL_MAT nodes that read the same X (Q/K/V, gate/up): one streaming launch when eligible
+// side stream + fork / join events of the calling thread's current device (created on first use; B200_GEMM_SIDE=0: off)
+struct SideStream { cudaStream_t s; cudaEvent_t ready, done; };
+static SideStream * side_stream() {
+    static const bool on = [] { const char * e = getenv("B200_GEMM_SIDE"); return !(e && e[0] == '0'); }();
+    if (!on) return nullptr;
+    static thread_local SideStream per_dev[16] = {};
+    static thread_local bool have[16] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+    if (!have[dev]) {
+        SideStream t = {};
+        if (cudaStreamCreateWithFlags(&t.s, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&t.ready, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        per_dev[dev] = t; have[dev] = true;
+    }
+    return &per_dev[dev];
+}
+
 int b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t stream) {
     B200_REQUIRE(args && count >= 1, "b200_mul_mat_group: no arguments");
     const b200_mul_mat_args & a0 = args[0];
@@ -198,18 +216,34 @@ int b200_mul_mat_group(const b200_mul_mat_args * args, int count, b200_stream_t 
         static const bool group_gemm = [] { const char * e = getenv("B200_GEMM_GROUP"); return !(e && e[0] == '0'); }();
         if (all_gemm && group_gemm) {
             bool done[16] = {false};
-            bool first = true;
+            bool first = true, forked = false;
             B200_REQUIRE(count <= 16, "b200_mul_mat_group: at most 16 nodes per call");
+            // the buckets after the first only need the fp16 X of the first one's prologue: they run on a side stream next to the
+            // first bucket's GEMM (wq + wk fill 80 of the 148 SMs, the Q6_K wv of every other layer takes the rest) and join at the end
+            SideStream * side = side_stream();
+            cudaStream_t main_s = (cudaStream_t) stream;
             for (int i = 0; i < count; ++i) {
                 if (done[i]) continue;
                 b200_mul_mat_args bucket[3];
-                int nb = 0;
+                int nb = 0, left = 0;
                 for (int j = i; j < count && nb < 3; ++j)
                     if (!done[j] && args[j].type == args[i].type) { bucket[nb++] = args[j]; done[j] = true; }
-                if (!first) bucket[0].flags |= B200_MM_X_PREQUANTISED;
+                for (int j = 0; j < count; ++j) left += done[j] ? 0 : 1;
+                int rc;
+                if (first) {
+                    const bool fork = side && left > 0;
+                    rc = b200_gemm_launch_group_ev(bucket, nb, main_s, fork ? side->ready : nullptr);
+                    if (!rc && fork) { B200_CHECK(cudaStreamWaitEvent(side->s, side->ready, 0)); forked = true; }
+                } else {
+                    bucket[0].flags |= B200_MM_X_PREQUANTISED;
+                    rc = b200_gemm_launch_group(bucket, nb, forked ? side->s : main_s);
+                }
                 first = false;
-                int rc = b200_gemm_launch_group(bucket, nb, (cudaStream_t) stream);
                 if (rc) return rc;
+            }
+            if (forked) {
+                B200_CHECK(cudaEventRecord(side->done, side->s));
+                B200_CHECK(cudaStreamWaitEvent(main_s, side->done, 0));
             }
             return 0;
         }
