@@ -398,3 +398,39 @@ def test_row_split_two_gpus_matches_single_gpu_chain(b200):
                         "--master-port", "29541", str(ROOT / "tools" / "rowsplit_check.py")],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert r.returncode == 0 and "ROWSPLIT_CHECK OK" in r.stdout, r.stdout[-3000:]
+
+
+def test_gemm_group_two_weight_types_captured_in_a_graph(b200, orc):
+    """prefill group with two weight types: the second bucket runs on the library's side stream (fork after the fp16 prologue,
+    join before the call returns). The call must be capturable and the replay must give what the eager call gave."""
+    rng = np.random.default_rng(77)
+    n, k = 96, 2048
+    ts, ms = [Q4_K, Q6_K, Q4_K], [640, 384, 200]
+    ws = [random_blocks(t, m, k, rng) for t, m in zip(ts, ms)]
+    x = dev(_acts(rng, n, k))
+    wps = [b200.repack(t, dev(w).reshape(-1), m, k) for t, w, m in zip(ts, ws, ms)]
+    ys = [torch.zeros((n, m), dtype=torch.float32, device="cuda") for m in ms]
+    need = max(b200.mul_mat_workspace(t, n, k) for t in ts) + 256
+    workspace = torch.empty(need, dtype=torch.uint8, device="cuda")
+    wsp = (workspace.data_ptr() + 255) & ~255
+    arr = (b200.MulMatArgs * len(ts))()
+    for i, (t, wp, m, y) in enumerate(zip(ts, wps, ms, ys)):
+        arr[i] = b200.MulMatArgs(t, b200.LAYOUT_PLANES, m, n, k, wp.data_ptr(), 0, x.data_ptr(), x.stride(0), y.data_ptr(), y.stride(0),
+                                 wsp, need - (wsp - workspace.data_ptr()), b200.Q8_X86, 0, b200.MM_PDL, 0)
+    s = b200.Stream(0)
+    torch.cuda.synchronize()
+    assert b200.lib.b200_mul_mat_group(arr, len(ts), s.handle) == 0
+    s.synchronize()
+    eager = [y.clone() for y in ys]
+    for t, w, y in zip(ts, ws, eager):
+        assert nmse(y.cpu().numpy(), orc.mul_mat(t, w, x.cpu().numpy())) < MAX_NMSE
+    with b200.Graph(s) as g:
+        assert b200.lib.b200_mul_mat_group(arr, len(ts), s.handle) == 0
+    for _ in range(2):
+        for y in ys:
+            y.zero_()
+        torch.cuda.synchronize()
+        g.launch()
+        s.synchronize()
+        for y, e in zip(ys, eager):
+            assert nmse(y.cpu().numpy(), e.cpu().numpy()) < 1e-10
