@@ -161,6 +161,16 @@ class MatMulChain:
             idx = [i for i, c in enumerate(calls) if c[0] is B.lib.b200_mul_mat_gather]
             self.gather_descs = {i: self.arena.gather_desc(seq, len(idx)) for seq, i in enumerate(idx)}
             self.gather_all = self.arena.gather_desc(len(idx), len(idx))
+            # a call that is NOT a gather call (MUL_MAT_ID: its Y goes through NCCL) does not wait for the peers' slices of its X by
+            # itself: wait for every gather call issued before it (once per run of such calls)
+            self.mid_waits = {}
+            seen = waited = 0
+            for i, c in enumerate(calls):
+                if c[0] is B.lib.b200_mul_mat_gather:
+                    seen += 1
+                elif seen > waited:
+                    self.mid_waits[i] = self.arena.gather_desc(seen, len(idx))
+                    waited = seen
         return calls
 
     def issue(self):
@@ -172,6 +182,8 @@ class MatMulChain:
         if self.fused_exchange:
             B._check(B.lib.b200_row_gather_step(self.arena.step_ptr, h))
         for i, (fn, a, ops, ys, _ws) in enumerate(self.calls):
+            if self.fused_exchange and i in self.mid_waits:
+                B._check(B.lib.b200_row_gather_wait(C.byref(self.mid_waits[i]), h))
             if fn is B.lib.b200_mul_mat_gather:
                 rc = fn(a, len(ops), C.byref(self.gather_descs[i]), h)
             elif fn is B.lib.b200_mul_mat_group:
