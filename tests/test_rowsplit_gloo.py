@@ -102,3 +102,16 @@ def test_row_split_bounds_are_tile_aligned():
                 assert lo <= hi and lo % 128 == 0, (world, m, bounds)
                 if r + 1 < world:
                     assert hi == bounds[r + 1][0]
+
+
+def test_fused_exchange_wait_plan():
+    """host logic of the fused exchange: calls that are not gather calls get one wait per run, for every gather call before them"""
+    from __graft_entry__ import load_pkg
+    load_pkg()
+    from zyk_llama_cpp_b200.rowsplit import plan_mid_waits
+    G, O = True, False
+    assert plan_mid_waits([G, G, G, G]) == {}                                  # dense model: gather calls wait by themselves
+    assert plan_mid_waits([O, O, G]) == {}                                     # nothing gathered yet: nothing to wait for
+    # MoE layer: qkv, wo | gate, up, down (MUL_MAT_ID) | next layer's qkv, wo | gate ...
+    assert plan_mid_waits([G, G, O, O, O, G, G, O, O, O]) == {2: 2, 7: 4}
+    assert plan_mid_waits([G, O, G, O]) == {1: 1, 3: 2}

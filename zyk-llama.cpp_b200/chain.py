@@ -163,14 +163,9 @@ class MatMulChain:
             self.gather_all = self.arena.gather_desc(len(idx), len(idx))
             # a call that is NOT a gather call (MUL_MAT_ID: its Y goes through NCCL) does not wait for the peers' slices of its X by
             # itself: wait for every gather call issued before it (once per run of such calls)
-            self.mid_waits = {}
-            seen = waited = 0
-            for i, c in enumerate(calls):
-                if c[0] is B.lib.b200_mul_mat_gather:
-                    seen += 1
-                elif seen > waited:
-                    self.mid_waits[i] = self.arena.gather_desc(seen, len(idx))
-                    waited = seen
+            from .rowsplit import plan_mid_waits
+            self.mid_waits = {i: self.arena.gather_desc(seq, len(idx))
+                              for i, seq in plan_mid_waits([c[0] is B.lib.b200_mul_mat_gather for c in calls]).items()}
         return calls
 
     def issue(self):

@@ -154,3 +154,19 @@ class SymmetricArena:
         if self.base:
             self.b.lib.b200_free(self.device, self.base)
             self.base = None
+
+
+def plan_mid_waits(is_gather_call: "list[bool]") -> "dict[int, int]":
+    """Fused exchange: which calls of a pass must be preceded by a b200_row_gather_wait, and with which `seq`.
+
+    Only gather calls (b200_mul_mat_gather) wait for the peers' slices of their X by themselves. A call of another kind
+    (MUL_MAT_ID, whose Y goes through NCCL) that follows gather calls needs a wait for all of them, once per run of such
+    calls. Returns {call index: number of gather calls issued before it}."""
+    waits, seen, waited = {}, 0, 0
+    for i, g in enumerate(is_gather_call):
+        if g:
+            seen += 1
+        elif seen > waited:
+            waits[i] = seen
+            waited = seen
+    return waits
