@@ -12,16 +12,20 @@
 //     8 warps = one virtual consumer, VC) keeps a ring of NS bulk copies (cp.async.bulk global -> shared, mbarrier
 //     complete_tx, L2 evict-first) in flight that runs AHEAD across node boundaries: while the grid waits for the X of node
 //     i + 1, the weights of node i + 1 are already landing in shared memory;
-//   * a node boundary is one arrival counter in global memory (red.release.gpu / ld.acquire.gpu), then every CTA quantises
-//     the new X into its own shared memory (quant_chunk256: bit for bit quantize_row_q8_K / q8_0 of the reference);
+//   * a node boundary is chosen per node from the pointers (NB_* below): tagged 64-bit {epoch, f32} words when X is exactly the
+//     previous node's Y (no counter, no fence), a relaxed arrival counter when nobody in the chain writes X, a release /
+//     acquire counter otherwise; then every CTA quantises the new X into its own shared memory (quant_chunk256: bit for bit
+//     quantize_row_q8_K / q8_0 of the reference);
 //   * shared-memory staging frees the lane <-> data mapping from coalescing: Q4_K is processed ONE 256-BLOCK PER LANE (the 144 B
 //     block stride is bank-conflict free), so d/dmin, the 12 scale bytes and the min correction are decoded once per 256
-//     weights instead of once per 32, and the min term is 4 dp2a against per-32 activation sums; Q6_K keeps 8 lanes per block
-//     but rebuilds the 6-bit values without shifts (nibble and 2-bit fields are masked in place and the power-of-two factor is
-//     taken out of the int32 sum exactly). The integer arithmetic per block is the CPU's, value for value; only the fp32
+//     weights instead of once per 32, and the min term is 4 dp2a against per-32 activation sums; Q6_K is one block per lane
+//     as well (its QL / QH planes land through swizzling 2-D tensor copies so that the lanes hit different banks, unit_q6k) and
+//     rebuilds the 6-bit values without shifts (nibble and 2-bit fields are masked in place and the power-of-two factor is
+//     taken out of the int32 sum exactly); the other formats keep 8 lanes per block. The integer arithmetic per block is the CPU's, value for value; only the fp32
 //     summation order differs (fixed, so results are deterministic).
 // Work split: per node the rows of the group's matrices are cut by BYTES into one contiguous share per VC (host, at create
-// time) and each share into items that fit a ring stage; an item is 1 (Q4_K) to 4 (Q6_K planes) bulk copies.
+// time) and each share into items that fit a ring stage; an item is 1 (Q4_K) to 4 (Q6_K planes) bulk copies, or for Q6_K
+// rows of a multiple of 8 units a few tensor copies (QL, QH) + 2 bulk copies (scales, d).
 // Algorithmic bytes per launch = sum over all nodes of m * row_size(type, k); HBM bound.
 #include "gemv_frag.cuh"
 #include "actquant.cuh"
