@@ -5,18 +5,23 @@
 // (ggml-cpu/ggml-cpu.c:1227-1427, ggml-cpu/repack.cpp:1037-1124) and mul_mat_q (mma.sync int8) on
 // CUDA (ggml-cuda/mmq.cuh:3459). This kernel is neither:
 //
-//   * a tile is 128 weight rows x BN <= 256 activation rows; the K loop advances 64 elements a step;
-//   * A (weights): 8 producer warps stream the quantised blocks straight from HBM (plane layout of
-//     repack.cu, 128-bit loads), dequantise in registers to fp16 and write the K-major
-//     SWIZZLE_128B operand tile into shared memory (gemm_dequant.cuh) -- every weight byte is read
-//     once per N-tile and never exists in HBM in expanded form;
-//   * B (activations): a prologue kernel rescales each f32 row by a power of two and rounds it to fp16
-//     (exact scaling, 11-bit mantissa; no int8 step), TMA (cp.async.bulk.tensor, SWIZZLE_128B) stages
-//     64 x BN boxes into shared memory;
-//   * one elected thread issues tcgen05.mma.kind::f16 (M = 128, N = BN, K = 16) four times per stage,
-//     tcgen05.commit releases the stage; fp32 accumulation over the whole K lives in TMEM;
-//   * epilogue: the producer warps read the accumulator with tcgen05.ld, multiply by the per-row
-//     power-of-two scale and store Y with coalesced 128-byte rows.
+//   * persistent CTAs (one per SM, 640 threads) walk a unit list over the tiles of up to three weight matrices of one type that read
+//     the same X (b200_gemm_launch_group); a tile is 256 weight rows x BN <= 256 activation rows on a CTA PAIR
+//     (tcgen05.mma.cta_group::2, M = 256) or 128 x BN on one CTA; the K loop advances 64 elements a stage; the tiles of the last
+//     partial wave are cut along k and meet in pre-zeroed Y with red.global.add;
+//   * A (weights): one warp issues TMA copies of the RAW quantised planes (one 256-element super-block of 128 rows per raw stage,
+//     SWIZZLE_128B / 64B so that the readers are bank-conflict free), 8 dequantiser warps turn them into the fp16 K-major
+//     SWIZZLE_128B operand tile in shared memory (gemm_dequant.cuh) -- every weight byte is read once per N-tile and never exists
+//     in HBM in expanded form;
+//   * B (activations): a prologue kernel rescales each f32 row by a power of two and rounds it to fp16 (exact scaling, 11-bit
+//     mantissa; no int8 step); TMA (cp.async.bulk.tensor, SWIZZLE_128B) stages 64 x BN boxes, each CTA of a pair half of it;
+//   * one elected thread of the leader CTA issues tcgen05.mma.kind::f16 (K = 16) four times per stage, tcgen05.commit (multicast
+//     to both CTAs) releases the stage; fp32 accumulation over the whole K lives in TMEM, TWO accumulators so that
+//   * the epilogue of unit i (8 warps, two per TMEM lane quarter: tcgen05.ld, per-row power-of-two scale, coalesced 128-byte
+//     stores) overlaps the MMAs of unit i + 1;
+//   * programmatic dependent launch: weights are staged and dequantised before griddepcontrol.wait, only the activation TMA
+//     and the Y stores come after it.
+// Measured behaviour, ablations and what bounds the kernel: DESIGN.md section 5.
 //
 // Why fp16 operands instead of int8 x int8: the block formats carry a scale per 32 (or 16) weights
 // and the CPU applies one activation scale per 32/256 elements, so an int8 MMA would need a TMEM
