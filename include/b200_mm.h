@@ -248,6 +248,19 @@ B200_API int b200_ipc_export(const void * dev_ptr, void * handle64);
 B200_API int b200_ipc_import(const void * handle64, void ** dev_ptr);
 B200_API int b200_ipc_close(void * dev_ptr);
 
+/* ---- MUL_MAT without any allocation --------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it). Same result as b200_mul_mat with
+ * algo = 1 (activation quantiser + register GEMV; meant for decode, any n is accepted while the scratch fits), but the
+ * quantised activations go into a fixed file-scope device array of b200_noalloc_scratch_max() bytes (1 MiB, held by every
+ * GPU that loads the library until exit) instead of args->workspace, which is ignored. The call allocates nothing (no
+ * cudaMalloc / cudaFree / stream or event creation). Shapes whose scratch (b200_mul_mat_noalloc_scratch(type, n, k)) exceeds
+ * the array are rejected with an error. All calls on a device share the array, which keeps the last call's contents (every
+ * byte read is written first, nothing must be cleared): calls that overlap on the GPU race; calls on one stream do not. */
+B200_API size_t b200_noalloc_scratch_max(void);
+B200_API size_t b200_mul_mat_noalloc_scratch(int type, int64_t n, int64_t k);
+B200_API int    b200_mul_mat_noalloc(const b200_mul_mat_args * args, b200_stream_t stream);
+
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 B200_API uint64_t b200_launch_count(void);
 

@@ -83,6 +83,9 @@ _sig("b200_unrepack", C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_vo
 _sig("b200_mul_mat_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64)
 _sig("b200_mul_mat", C.c_int, C.POINTER(MulMatArgs), C.c_void_p)
 _sig("b200_mul_mat_group", C.c_int, C.POINTER(MulMatArgs), C.c_int, C.c_void_p)
+_sig("b200_mul_mat_noalloc", C.c_int, C.POINTER(MulMatArgs), C.c_void_p)
+_sig("b200_mul_mat_noalloc_scratch", C.c_size_t, C.c_int, C.c_int64, C.c_int64)
+_sig("b200_noalloc_scratch_max", C.c_size_t)
 _sig("b200_chain_supported", C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
 _sig("b200_chain_create", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
 _sig("b200_chain_create_split", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int, C.POINTER(ChainSplit))
