@@ -38,9 +38,19 @@ def test_multi_node_graph_matches_reference_cpu_backend(mode, n):
     assert r.returncode == 0 and "PLUGIN_GRAPH_CHECK OK" in r.stdout, r.stdout[-3000:]
 
 
-def test_reference_conformance_harness_q4_K_slice():
+@pytest.mark.parametrize("op", ["MUL_MAT", "MUL_MAT_ID"])
+def test_reference_conformance_harness_all_types(op):
+    """The reference's unmodified test-backend-ops, every case of the op (all weight types; tests/test-backend-ops.cpp:7616-7729,
+    7768-7820): the cases supports_op declines are reported "not supported" by the harness, every case it accepts must pass."""
     env = _need("test-backend-ops")
-    r = subprocess.run([str(VAR / "test-backend-ops"), "test", "-o", "MUL_MAT", "-p", "type_a=q4_K"], env=env,
-                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    r = subprocess.run([str(VAR / "test-backend-ops"), "test", "-o", op], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
     tail = r.stdout[-2000:]
-    assert r.returncode == 0 and "tests passed" in tail and "FAIL" not in tail, tail
+    assert r.returncode == 0 and "tests passed" in tail and "FAIL" not in r.stdout, tail
+    import re
+    m = re.search(r"(\d+)/(\d+) tests passed", tail)
+    assert m and m.group(1) == m.group(2) and int(m.group(2)) >= 100, tail
+    # every one of the five block formats of the path was actually exercised (not merely declined)
+    for t in ("q4_0", "q8_0", "q4_K", "q6_K", "iq4_xs"):
+        ok = [ln for ln in r.stdout.splitlines() if f"type_a={t}," in ln and "OK" in ln]
+        assert ok, f"no passing {op} case with type_a={t}"
