@@ -187,6 +187,11 @@ B200_API b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * no
 B200_API size_t       b200_chain_scratch_bytes(int64_t max_m_full, int n);
 B200_API b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups,
                                               const b200_chain_split * split);      /* split == NULL: b200_chain_create */
+/* host-only view of the plan a chain would get on a device with `sms` SMs (no CUDA call, usable without a GPU; pointers are only
+ * compared): modes[g] = how group g learns that its X is complete -- 0 first group (stream order), 1 arrival counter with release / acquire
+ * fences, 2 relaxed arrival counter, 3 self-validating tagged words; *xreg = 1 when the activations-in-registers kernel takes the chain */
+B200_API int          b200_chain_plan(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, int sms,
+                                      const b200_chain_split * split, int32_t * modes, int32_t * xreg);
 B200_API int          b200_chain_launch(b200_chain_t chain, b200_stream_t stream);   /* asynchronous, CUDA-graph capturable */
 B200_API int          b200_chain_info(b200_chain_t chain, int * ctas, int * stage_bytes, int * smem_bytes, int * n_groups);
 B200_API int          b200_chain_timeline(b200_chain_t chain, long long * host, size_t count);  /* debugging aid, see gemv_chain.cu */

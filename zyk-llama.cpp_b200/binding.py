@@ -90,6 +90,7 @@ _sig("b200_chain_supported", C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32
 _sig("b200_chain_create", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int)
 _sig("b200_chain_create_split", C.c_void_p, C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int, C.POINTER(ChainSplit))
 _sig("b200_chain_scratch_bytes", C.c_size_t, C.c_int64, C.c_int)
+_sig("b200_chain_plan", C.c_int, C.POINTER(MulMatArgs), C.POINTER(C.c_int32), C.c_int, C.c_int, C.POINTER(ChainSplit), C.POINTER(C.c_int32), C.POINTER(C.c_int32))
 _sig("b200_chain_launch", C.c_int, C.c_void_p, C.c_void_p)
 _sig("b200_chain_info", C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))
 _sig("b200_chain_destroy", C.c_int, C.c_void_p)

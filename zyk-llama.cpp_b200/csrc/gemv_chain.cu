@@ -34,6 +34,7 @@
 #include <cuda.h>
 #include <stdlib.h>
 #include <string.h>
+#include <string>
 #include <vector>
 
 namespace {
@@ -101,6 +102,7 @@ struct ChainArgs {
     long long tag_stride;     // elements between the columns of a tagged vector
     int inflight;             // copies per group that may be in flight (issued, not landed): bounds the queueing delay the stream adds to the node barrier
     int debug;                // B200_CHAIN_DEBUG (timing experiments, results wrong): 1 no node wait, 2 no dot products, 4 no X quantiser, 8 no row sums
+    int ns;                   // gemv_chainx_kernel: ring stages per CTA
 };
 
 // bytes per 256-element unit in plane p of the plane layout (repack.cu); 0 terminates
@@ -179,11 +181,10 @@ __device__ __forceinline__ int dot16_us(const uint4 & a, const uint4 & b) {
 
 // ---- activation quantiser into the shared-memory unit layout ---------------------------------------------------------
 //   unit (col, u): [qs 256 B, chunks placed by xpos][bs16: 16 x i16][bs32: 8 x i16][d: 8 x f32 (Q8_K uses d[0])]
-template <int NCOLS, int QU>
+template <int NCOLS, int QU, int NW>
 __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch, bool sys) {
     const int upr = nd.k >> 8;
     const int total = NCOLS * upr;
-    constexpr int NW = CH_CONSUMERS / 32;
     constexpr unsigned FULL = 0xffffffffu;
     for (int c0 = warp; c0 < total; c0 += NW * QU) {
         float v[QU][8];
@@ -293,13 +294,12 @@ __device__ __forceinline__ void chain_quantise_x_t(const ChainNodeD & nd, uint32
 }
 
 // chunks per warp that are quantised together: as many as the node needs, no dead slots (every CTA runs this once per node)
-template <int NCOLS>
+template <int NCOLS, int NW = CH_CONSUMERS / 32>
 __device__ __forceinline__ void chain_quantise_x(const ChainNodeD & nd, uint32_t xs, int warp, int lane, long long tag_stride, unsigned epoch, bool sys) {
     const int total = NCOLS * (nd.k >> 8);
-    constexpr int NW = CH_CONSUMERS / 32;
-    if (total <= NW)          chain_quantise_x_t<NCOLS, 1>(nd, xs, warp, lane, tag_stride, epoch, sys);
-    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2>(nd, xs, warp, lane, tag_stride, epoch, sys);
-    else                      chain_quantise_x_t<NCOLS, 4>(nd, xs, warp, lane, tag_stride, epoch, sys);
+    if (total <= NW)          chain_quantise_x_t<NCOLS, 1, NW>(nd, xs, warp, lane, tag_stride, epoch, sys);
+    else if (total <= 2 * NW) chain_quantise_x_t<NCOLS, 2, NW>(nd, xs, warp, lane, tag_stride, epoch, sys);
+    else                      chain_quantise_x_t<NCOLS, 4, NW>(nd, xs, warp, lane, tag_stride, epoch, sys);
 }
 
 // ---- Q4_K: one 256-block per lane --------------------------------------------------------------------------------------
@@ -791,6 +791,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
     if (blockIdx.x == 0 && tid == 0) *a.launches = launch + 1ull;
 }
 
+#include "gemv_chain_xreg.cuh"
+
 // ---------------------------------------------------------------------------------------------------------------------------
 struct Chain {
     int device = 0, sms = 0, ncols = 1, n_nodes = 0, n_launch_nodes = 0;
@@ -798,7 +800,12 @@ struct Chain {
     void * d_blob = nullptr, * d_tags = nullptr;
     size_t smem = 0;
     bool cooperative = true;
+    bool xreg = false;            // gemv_chainx_kernel (activations in registers) instead of gemv_chain_kernel
 };
+
+// consumer warps of gemv_chainx_kernel (8 or 12; B200_CHAIN_NW)
+int cx_nw() { static const int v = [] { const char * e = getenv("B200_CHAIN_NW"); const int n = e ? atoi(e) : 8; return n == 12 ? 12 : 8; }(); return v; }
+#define CX_NW cx_nw()
 
 bool chain_type_ok(int t) { return t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0; }
 int gcd_i(int a, int b) { while (b) { int t = a % b; a = b; b = t; } return a; }
@@ -823,6 +830,15 @@ template <int NCOLS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s)
     cfg.attrs = attr; cfg.numAttrs = c.cooperative ? 1 : 0;
     b200_count_launch();
     return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS>, c.args);
+}
+cudaError_t chainx_launch(const Chain & c, cudaStream_t s) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) c.sms); cfg.blockDim = dim3((CX_NW + 1) * 32); cfg.dynamicSmemBytes = c.smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative; attr[0].val.cooperative = 1;
+    cfg.attrs = attr; cfg.numAttrs = c.cooperative ? 1 : 0;
+    b200_count_launch();
+    return CX_NW == 12 ? cudaLaunchKernelEx(&cfg, gemv_chainx_kernel<12>, c.args) : cudaLaunchKernelEx(&cfg, gemv_chainx_kernel<8>, c.args);
 }
 
 // [units][plane_bytes] uint8 plane of a Q6_K matrix; one box = the `upr` units of one weight row
@@ -855,6 +871,14 @@ int chain_stage_bytes(int ncols, int64_t kmax, int total_smem, int * max_units) 
         if (need <= total_smem) { if (max_units) *max_units = mu; return st; }
     }
     return 0;
+}
+// gemv_chainx_kernel: header + two X buffers + per-stage partial sums + alignment slack + ns stages (multiples of 1 KB)
+int chainx_stage_bytes(int64_t kmax, int total_smem, int ns) {
+    const int64_t x_bytes = ((kmax >> 8) * XU_BYTES + 127) & ~(int64_t) 127;
+    const int64_t left = (int64_t) total_smem - CX_HDR - 2 * x_bytes - (int64_t) ns * CX_PART_FLOATS * 4 - 1024;
+    if (left <= 0) return 0;
+    const int64_t st = left / ns / 1024 * 1024;
+    return st >= 4096 ? (int) (st > 64 * 1024 ? 64 * 1024 : st) : 0;
 }
 
 const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, bool split = false) {
@@ -893,6 +917,164 @@ const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_
     return nullptr;
 }
 
+// ---- the plan of a chain: pure host logic, no CUDA call (b200_chain_plan exposes it to the CPU tests) ------------------------------
+struct Cut { int m; int64_t row; };          // where a share ends: (matrix of the group, row)
+struct ChainPlan {
+    bool xreg = false;                       // kernel: gemv_chainx_kernel (one ring, X in registers) or gemv_chain_kernel
+    int groups = CH_GROUPS, ns = CH_NS, stage = 0, max_units = 0, x_bytes = 0, ncols = 1, VC = 0;
+    size_t smem = 0;
+    std::vector<int> mode, feed, first;      // per group: NB_*, matrix of the group whose Y the next group reads through tags (-1), first node
+    std::vector<std::vector<Cut>> cuts;      // per group: end of share v = 0 .. VC - 1 (share v belongs to virtual consumer (v + 37 g) % VC)
+    std::string error;
+};
+
+bool q6_swizzle_enabled() { return getenv("B200_CHAIN_Q6K_LANES8") == nullptr; }
+bool q6_swizzled_shape(const b200_mul_mat_args & a) {
+    const int64_t upr = a.k >> 8;
+    return a.type == B200_TYPE_Q6_K && q6_swizzle_enabled() && upr % 8 == 0 && a.m * upr < (1ll << 31);
+}
+
+// shares of one group: the concatenated rows of its matrices cut by bytes into VC contiguous pieces, rounded to row granules
+void chain_cut_group(const int64_t * m, const int * type, int cnt, int upr, int VC, std::vector<Cut> & out) {
+    std::vector<int64_t> rb(cnt), cum(cnt + 1, 0);
+    for (int i = 0; i < cnt; ++i) { rb[i] = (int64_t) unit_bytes(type[i]) * upr; cum[i + 1] = cum[i] + rb[i] * m[i]; }
+    const int64_t T = cum[cnt];
+    out.resize(VC);
+    int pm = 0; int64_t prow = 0;
+    for (int v = 0; v < VC; ++v) {
+        int cm; int64_t crow;
+        if (v == VC - 1) { cm = cnt - 1; crow = m[cnt - 1]; }
+        else {
+            const int64_t t = T * (v + 1) / VC;
+            cm = 0;
+            while (cm + 1 < cnt && t >= cum[cm + 1]) ++cm;
+            const int gr = row_granule(type[cm], upr);
+            int64_t r = ((t - cum[cm]) + rb[cm] * gr / 2) / (rb[cm] * gr) * gr;
+            if (r > m[cm]) r = m[cm];
+            crow = r;
+        }
+        if (cm < pm || (cm == pm && crow < prow)) { cm = pm; crow = prow; }
+        out[v].m = cm; out[v].row = crow;
+        pm = cm; prow = crow;
+    }
+}
+
+// `sms` CTAs; split may be null. Decides the kernel, the ring geometry, the shares and how each node learns that its X is complete.
+ChainPlan chain_plan(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, int sms, int total_smem, const b200_chain_split * split) {
+    ChainPlan P;
+    const int world = split ? split->world : 1;
+    P.ncols = (int) nodes[0].n;
+    P.first.assign(n_groups + 1, 0);
+    for (int g = 0; g < n_groups; ++g) P.first[g + 1] = P.first[g] + group_sizes[g];
+    const int n_nodes = P.first[n_groups];
+    int64_t kmax = 0;
+    for (int i = 0; i < n_nodes; ++i) kmax = nodes[i].k > kmax ? nodes[i].k : kmax;
+
+    // ---- kernel and ring geometry ------------------------------------------------------------------------------------------------
+    // measured on B200 (8B Q4_K_M token): 685-732 tokens/s against 796 for gemv_chain_kernel -- with 8 warps the per-task latency chain, not
+    // shared memory, bounds the consumers -- so the activations-in-registers kernel is opt-in: B200_CHAIN_XREG=1
+    bool xreg = P.ncols == 1 && getenv("B200_CHAIN_XREG") && getenv("B200_CHAIN_XREG")[0] == '1';
+    int ns = CX_MAX_NS < 6 ? CX_MAX_NS : 6;
+    if (const char * e = getenv("B200_CHAIN_NS")) { const int v = atoi(e); if (v >= 2 && v <= CX_MAX_NS) ns = v; }
+    int xstage = xreg ? chainx_stage_bytes(kmax, total_smem, ns) : 0;
+    if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < xstage) xstage = v; }
+    for (int i = 0; i < n_nodes && xreg; ++i) {
+        const b200_mul_mat_args & a = nodes[i];
+        const int upr = (int) (a.k >> 8);
+        const int segs = upr <= 32 ? 1 : (upr + 31) >> 5;
+        if (!(a.type == B200_TYPE_Q4_K || q6_swizzled_shape(a))) xreg = false;
+        else if (CX_NW % segs != 0 || segs > CX_PART_FLOATS) xreg = false;
+        else if ((int64_t) unit_bytes(a.type) * upr > xstage - 512) xreg = false;
+    }
+    P.xreg = xreg;
+    if (xreg) {
+        P.groups = 1; P.ns = ns; P.stage = xstage; P.max_units = 0;
+        P.x_bytes = (int) (((kmax >> 8) * XU_BYTES + 127) & ~(int64_t) 127);
+        P.smem = (size_t) CX_HDR + 2 * (size_t) P.x_bytes + (size_t) ns * CX_PART_FLOATS * 4 + 1024 + (size_t) ns * xstage;
+    } else {
+        P.groups = CH_GROUPS; P.ns = CH_NS;
+        P.stage = chain_stage_bytes(P.ncols, kmax, total_smem, &P.max_units);
+        if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < P.stage) P.stage = v; }
+        P.x_bytes = (int) (((int64_t) P.ncols * (kmax >> 8) * XU_BYTES + 127) & ~127);
+        P.smem = CH_HDR + (size_t) P.x_bytes + (size_t) CH_GROUPS * 2 * P.ncols * P.max_units * 4 + 1024 + (size_t) CH_GROUPS * CH_NS * P.stage;
+        if (!P.stage) { P.error = "activations leave no room for the weight ring"; return P; }
+    }
+    P.VC = sms * P.groups;
+
+    // ---- shares ------------------------------------------------------------------------------------------------------------------
+    P.cuts.resize(n_groups);
+    for (int g = 0; g < n_groups; ++g) {
+        const int cnt = group_sizes[g];
+        std::vector<int64_t> m(cnt); std::vector<int> type(cnt);
+        for (int i = 0; i < cnt; ++i) { m[i] = nodes[P.first[g] + i].m; type[i] = nodes[P.first[g] + i].type; }
+        chain_cut_group(m.data(), type.data(), cnt, (int) (nodes[P.first[g]].k >> 8), P.VC, P.cuts[g]);
+    }
+
+    // ---- how each node learns that its X is complete (NB_*): from the pointers -----------------------------------------------------
+    auto lo_of = [&](int i) { return split ? split->row_lo[i] : (int64_t) 0; };          // first row of this rank's slice
+    auto mf_of = [&](int i) { return split ? split->m_full[i] : nodes[i].m; };           // rows of the whole matrix
+    // the whole Y of node i (every rank's rows: with the row split all of it is written into this rank's arena)
+    auto y_lo = [&](int i) { return (const char *) (nodes[i].y - lo_of(i)); };
+    auto y_hi = [&](int i) { return (const char *) (nodes[i].y - lo_of(i) + (nodes[i].n - 1) * nodes[i].y_row_stride + mf_of(i)); };
+    auto x_lo = [&](int g) { return (const char *) nodes[P.first[g]].x; };
+    auto x_hi = [&](int g) { const b200_mul_mat_args & a = nodes[P.first[g]]; return (const char *) (a.x + (a.n - 1) * a.x_row_stride + a.k); };
+    const bool no_tags = getenv("B200_CHAIN_NO_TAGS") != nullptr, all_fenced = getenv("B200_CHAIN_ALL_FENCED") != nullptr;
+    P.mode.assign(n_groups, NB_NONE); P.feed.assign(n_groups, -1);
+    // does every CTA of every rank own rows of matrix `fm` of group g? (a CTA without any is not ordered by that matrix' tagged rows)
+    auto every_cta_feeds = [&](int g, int fm) {
+        const int cnt = group_sizes[g], upr = (int) (nodes[P.first[g]].k >> 8);
+        for (int r = 0; r < world; ++r) {
+            std::vector<int64_t> m(cnt); std::vector<int> type(cnt);
+            for (int i = 0; i < cnt; ++i) {
+                type[i] = nodes[P.first[g] + i].type;
+                m[i] = nodes[P.first[g] + i].m;
+                if (split && r != split->rank) { int64_t lo = 0, hi = 0; b200_row_split(mf_of(P.first[g] + i), world, r, &lo, &hi); m[i] = hi - lo; }
+            }
+            std::vector<Cut> cuts;
+            if (split && r != split->rank) chain_cut_group(m.data(), type.data(), cnt, upr, P.VC, cuts);
+            const std::vector<Cut> & cu = (split && r != split->rank) ? cuts : P.cuts[g];
+            std::vector<char> has(sms, 0);
+            Cut prev = {0, 0};
+            for (int v = 0; v < P.VC; ++v) {
+                const Cut end = cu[v];
+                const int64_t lo = prev.m < fm ? 0 : (prev.m == fm ? prev.row : m[fm]);
+                const int64_t hi = end.m > fm ? m[fm] : (end.m == fm ? end.row : 0);
+                if (hi > lo) has[((v + g * 37) % P.VC) / P.groups] = 1;
+                prev = end;
+            }
+            for (int c = 0; c < sms; ++c) if (!has[c]) return false;
+        }
+        return true;
+    };
+    for (int g = 1; g < n_groups; ++g) {
+        const b200_mul_mat_args & a0 = nodes[P.first[g]];
+        // read after write: X overlaps the Y of any earlier node
+        bool hazard = false;
+        for (int i = 0; i < P.first[g] && !hazard; ++i) hazard = x_lo(g) < y_hi(i) && y_lo(i) < x_hi(g);
+        // write after read / write after write against the two previous groups: with a tagged boundary CTAs of neighbouring nodes coexist,
+        // and a relaxed arrival does not order the stores of the two nodes
+        bool waw_war = false;
+        for (int h = g - 1; h >= 0 && h >= g - 2 && !waw_war; --h)
+            for (int i = P.first[g]; i < P.first[g + 1] && !waw_war; ++i) {
+                waw_war = y_lo(i) < x_hi(h) && x_lo(h) < y_hi(i);
+                for (int j = P.first[h]; j < P.first[h + 1] && !waw_war; ++j) waw_war = y_lo(i) < y_hi(j) && y_lo(j) < y_hi(i);
+            }
+        P.mode[g] = hazard || waw_war || all_fenced ? NB_FENCED : NB_RELAXED;
+        // X is exactly the Y of a matrix of the previous group, and every CTA owns rows of that matrix (so nobody can be more than one
+        // node behind a CTA that has seen all of its tagged rows): the rows validate themselves, no counter and no fence
+        for (int i = P.first[g - 1]; i < P.first[g] && !no_tags && !all_fenced && !waw_war; ++i)
+            if (nodes[i].y - lo_of(i) == a0.x && mf_of(i) == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride) &&
+                every_cta_feeds(g - 1, i - P.first[g - 1])) { P.mode[g] = NB_TAGGED; P.feed[g - 1] = i - P.first[g - 1]; }
+        if (split && P.mode[g] == NB_FENCED) {
+            char buf[200];
+            snprintf(buf, sizeof buf, "group %d needs a fenced boundary (it reads or overwrites rows of an earlier group that is not its tagged predecessor): not supported with the row split", g);
+            P.error = buf;
+            return P;
+        }
+    }
+    return P;
+}
+
 } // namespace
 
 extern "C" {
@@ -904,6 +1086,20 @@ int b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_
 size_t b200_chain_scratch_bytes(int64_t max_m_full, int ncols) {
     const int64_t tmax = ((max_m_full > 256 ? max_m_full : 256) + 255) & ~(int64_t) 255;
     return 256 + (size_t) 2 * (size_t) (ncols > 0 ? ncols : 1) * (size_t) tmax * 8;
+}
+
+// host-only view of the plan a chain would get on a device with `sms` SMs (no CUDA call; pointers are only compared):
+// modes[g] = NB_* (0 none, 1 fenced counter, 2 relaxed counter, 3 tagged words), *xreg = 1 when gemv_chainx_kernel takes the chain
+int b200_chain_plan(const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups, int sms, const b200_chain_split * split,
+                    int32_t * modes, int32_t * xreg) {
+    const char * why = chain_check(nodes, group_sizes, n_groups, split != nullptr);
+    B200_REQUIRE(!why, "b200_chain_plan: %s", why);
+    B200_REQUIRE(sms > 0 && modes, "b200_chain_plan: bad arguments");
+    const ChainPlan P = chain_plan(nodes, group_sizes, n_groups, sms, CH_SMEM_TOTAL, split);
+    B200_REQUIRE(P.error.empty(), "b200_chain_plan: %s", P.error.c_str());
+    for (int g = 0; g < n_groups; ++g) modes[g] = P.mode[g];
+    if (xreg) *xreg = P.xreg ? 1 : 0;
+    return 0;
 }
 
 b200_chain_t b200_chain_create(int device, const b200_mul_mat_args * nodes, const int32_t * group_sizes, int n_groups) {
@@ -925,52 +1121,23 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
     if (sms <= 0 || smem_optin < 200 * 1024) { cudaGetLastError(); b200_set_error("b200_chain_create: no usable sm_100 device"); return nullptr; }
     if (const char * e = getenv("B200_CHAIN_CTAS")) { const int v = atoi(e); if (v > 0 && v < sms) sms = v; }
-
-    const int ncols = (int) nodes[0].n;
-    const int VC = sms * CH_GROUPS;
-    int64_t kmax = 0;
-    { int idx = 0; for (int g = 0; g < n_groups; ++g) { kmax = nodes[idx].k > kmax ? nodes[idx].k : kmax; idx += group_sizes[g]; } }
-    const int x_bytes = (int) (((int64_t) ncols * (kmax >> 8) * XU_BYTES + 127) & ~127);
     const int total_smem = smem_optin < CH_SMEM_TOTAL ? smem_optin : CH_SMEM_TOTAL;
-    // ring stage: what is left after X, split over groups x stages; the partial buffers depend on the stage size
-    // (max_units = stage / 136 units of 4 B x 2 buffers x ncols per group), solve by stepping the stage size down
-    int stage = 0, max_units = 0;
-    stage = chain_stage_bytes(ncols, kmax, total_smem, &max_units);
-    if (const char * e = getenv("B200_CHAIN_STAGE_KB")) { const int v = atoi(e) * 1024; if (v >= 4096 && v < stage) { stage = v; } }
-    if (!stage) { b200_set_error("b200_chain_create: activations of %d x %lld do not leave room for the weight ring", ncols, (long long) kmax); return nullptr; }
+
+    const ChainPlan P = chain_plan(nodes, group_sizes, n_groups, sms, total_smem, split);
+    if (!P.error.empty()) { b200_set_error("b200_chain_create: %s", P.error.c_str()); return nullptr; }
+    const int ncols = P.ncols, VC = P.VC, stage = P.stage, max_units = P.max_units, x_bytes = P.x_bytes;
+    const std::vector<int> & mode = P.mode, & feed = P.feed, & first = P.first;
 
     std::vector<ChainNodeD> hn(n_groups);
     std::vector<ChainMatD> hm;       // host-side only: the items carry everything the kernel needs
     std::vector<CUtensorMap> maps;   // two per swizzled Q6_K matrix (QL, QH); copied into the blob, the items point at them
     std::vector<int> mat_map, mat_R; // per matrix: index of its first map or -1 (four: QL, QH for R rows per copy, QL, QH for one row), R
-    const bool q6_swizzled = getenv("B200_CHAIN_Q6K_LANES8") == nullptr;
 
-    // ---- how each node learns that its X is complete (NB_*): from the pointers ------------------------------------------
-    std::vector<int> mode(n_groups, NB_NONE), feed(n_groups, -1), first(n_groups + 1, 0);
-    for (int g = 0; g < n_groups; ++g) first[g + 1] = first[g] + group_sizes[g];
     int64_t tmax = 256;
     auto lo_of = [&](int i) { return split ? split->row_lo[i] : (int64_t) 0; };          // first row of this rank's slice
     auto mf_of = [&](int i) { return split ? split->m_full[i] : nodes[i].m; };           // rows of the whole matrix
     for (int i = 0; i < first[n_groups]; ++i) tmax = mf_of(i) > tmax ? mf_of(i) : tmax;
     tmax = (tmax + 255) & ~(int64_t) 255;
-    // the whole Y of node i (every rank's rows: with the row split all of it is written into this rank's arena)
-    auto y_lo = [&](int i) { return (const char *) (nodes[i].y - lo_of(i)); };
-    auto y_hi = [&](int i) { return (const char *) (nodes[i].y - lo_of(i) + (nodes[i].n - 1) * nodes[i].y_row_stride + mf_of(i)); };
-    const bool no_tags = getenv("B200_CHAIN_NO_TAGS") != nullptr, all_fenced = getenv("B200_CHAIN_ALL_FENCED") != nullptr;
-    for (int g = 1; g < n_groups; ++g) {
-        const b200_mul_mat_args & a0 = nodes[first[g]];
-        const char * xlo = (const char *) a0.x, * xhi = (const char *) (a0.x + (a0.n - 1) * a0.x_row_stride + a0.k);
-        bool overlap = false;
-        for (int i = 0; i < first[g] && !overlap; ++i) overlap = xlo < y_hi(i) && y_lo(i) < xhi;
-        mode[g] = overlap || all_fenced ? NB_FENCED : NB_RELAXED;
-        for (int i = first[g - 1]; i < first[g] && !no_tags && !all_fenced; ++i)
-            if (nodes[i].y - lo_of(i) == a0.x && mf_of(i) == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride)) { mode[g] = NB_TAGGED; feed[g - 1] = i - first[g - 1]; }
-        if (split && mode[g] == NB_FENCED) {
-            b200_set_error("b200_chain_create_split: group %d reads rows an earlier group wrote without being its direct successor: not supported with the row split", g);
-            return nullptr;
-        }
-    }
-    // a node whose X overlaps older outputs only PARTLY covered by a tagged predecessor is still fenced: exact match required above
     unsigned long long * d_tags = nullptr;
     const size_t tag_bytes = (size_t) 2 * ncols * tmax * 8;
     if (split) {                               // tags and counters live in the symmetric arena: every rank stores into every rank's copy
@@ -992,6 +1159,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
         signalling_total = signalling;
     }
     std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
+    std::vector<int> rot(VC, 0);     // gemv_chainx_kernel: tasks dealt to the warps so far, per virtual consumer (restarts with every node)
     int idx = 0;
     for (int g = 0; g < n_groups; ++g) {
         const b200_mul_mat_args & a0 = nodes[idx];
@@ -999,11 +1167,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
         hn[g].act_block = b200_act_type(a0.type) == B200_TYPE_Q8_K ? 256 : 32;
         hn[g].flavour = a0.flavour;
         const int upr = (int) (a0.k >> 8);
-        // cut the concatenated rows of the group by bytes: VC v gets bytes [v T / VC, (v + 1) T / VC), rounded to row granules
         const int cnt = group_sizes[g];
-        std::vector<int64_t> rb(cnt), cum(cnt + 1, 0);
-        for (int i = 0; i < cnt; ++i) { rb[i] = (int64_t) unit_bytes(nodes[idx + i].type) * upr; cum[i + 1] = cum[i] + rb[i] * nodes[idx + i].m; }
-        const int64_t T = cum[cnt];
         const int mat_base = (int) hm.size();
         for (int i = 0; i < cnt; ++i) {
             const b200_mul_mat_args & a = nodes[idx + i];
@@ -1011,7 +1175,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
             hm.push_back(M);
             // Q6_K rows of a multiple of 8 units: QL / QH through swizzling tensor copies, one block per lane (unit_q6k)
             int map0 = -1, R = 1;
-            if (a.type == B200_TYPE_Q6_K && q6_swizzled && upr % 8 == 0 && a.m > 0 && (int64_t) a.m * upr < (1ll << 31)) {
+            if (q6_swizzled_shape(a) && a.m > 0) {
                 const uint8_t * w = (const uint8_t *) a.w;
                 // rows per tensor copy: as many as the box limit (256 units) and a ring stage allow, but at least two copies per full stage
                 const int fit = (int) (((int64_t) stage - 512) / ((int64_t) 210 * upr));
@@ -1026,29 +1190,22 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     chain_plane_map(&t4[3], w + (int64_t) a.m * upr * 128, 64, (uint64_t) a.m * upr, (uint32_t) upr, CU_TENSOR_MAP_SWIZZLE_64B)) {
                     map0 = (int) maps.size();
                     for (int t = 0; t < 4; ++t) maps.push_back(t4[t]);
+                } else if (P.xreg) {
+                    b200_set_error("b200_chain_create: cuTensorMapEncodeTiled failed for a Q6_K plane (m=%lld k=%lld)", (long long) a.m, (long long) a.k);
+                    if (!split) cudaFree(d_tags);
+                    return nullptr;
                 }
             }
             mat_R.push_back(R);
             mat_map.push_back(map0);
         }
-        // cut positions as (matrix, row)
-        auto cut_of = [&](int64_t t, int & mi, int64_t & row) {
-            mi = 0;
-            while (mi + 1 < cnt && t >= cum[mi + 1]) ++mi;
-            const int gr = row_granule(nodes[idx + mi].type, upr);
-            int64_t r = ((t - cum[mi]) + rb[mi] * gr / 2) / (rb[mi] * gr) * gr;
-            if (r > nodes[idx + mi].m) r = nodes[idx + mi].m;
-            row = r;
-        };
         int pm = 0; int64_t prow = 0;
-        // rotate the VC order from node to node so that rounding leftovers do not pile up on the same SMs
+        // the VC order rotates from node to node so that rounding leftovers do not pile up on the same SMs
         for (int v = 0; v < VC; ++v) {
-            int cm; int64_t crow;
-            if (v == VC - 1) { cm = cnt - 1; crow = nodes[idx + cnt - 1].m; }
-            else cut_of(T * (v + 1) / VC, cm, crow);
-            if (cm < pm || (cm == pm && crow < prow)) { cm = pm; crow = prow; }
+            const int cm = P.cuts[g][v].m; const int64_t crow = P.cuts[g][v].row;
             const int vc = (v + g * 37) % VC;
             std::vector<ChainItemD> & out = per_vc_node[(size_t) vc * n_groups + g];
+            rot[vc] = 0;
             for (int mi = pm; mi <= cm; ++mi) {
                 const int64_t r0 = mi == pm ? prow : 0, r1 = mi == cm ? crow : nodes[idx + mi].m;
                 if (r1 <= r0) continue;
@@ -1056,6 +1213,8 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                 const int gr = row_granule(type, upr);
                 const int map0 = mat_map[mat_base + mi];
                 int64_t max_rows = ((int64_t) stage - (map0 >= 0 ? 512 : 0)) / ((int64_t) unit_bytes(type) * upr) / gr * gr;
+                const int xsegs = upr <= 32 ? 1 : (upr + 31) >> 5;
+                if (P.xreg && xsegs > 1 && max_rows > CX_PART_FLOATS / xsegs) max_rows = CX_PART_FLOATS / xsegs;      // partial sums of an item: rows x segs floats
                 if (max_rows < gr) { b200_set_error("b200_chain_create: a row granule of type %d, k=%lld does not fit a %d-byte ring stage", type, (long long) a0.k, stage); if (!split) cudaFree(d_tags); return nullptr; }
                 const int64_t rows = r1 - r0;
                 const int64_t nit = (rows + max_rows - 1) / max_rows;
@@ -1070,6 +1229,11 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     it.y = M.y + r; it.ldy = M.ldy;
                     it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
                     { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    if (P.xreg) {
+                        // `S` carries the rotation: which warp gets the item's first task, so that tasks go round the warps across items
+                        if (it.segs == 1) { const int rp = 32 / upr; it.S = rot[vc] % CX_NW; rot[vc] = (rot[vc] + (it.nrows + rp - 1) / rp) % CX_NW; }
+                        else { const int per_class = CX_NW / it.segs; it.S = rot[vc] % per_class; rot[vc] = (rot[vc] + it.nrows) % CX_NW; }
+                    }
                     int64_t plane_off = 0;
                     for (int p = 0; p < 4; ++p) {
                         const int pb = plane_bytes(type, p);
@@ -1125,6 +1289,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     Chain * c = new Chain();
     c->d_tags = split ? nullptr : d_tags;
     c->device = device; c->sms = sms; c->ncols = ncols; c->n_nodes = n_groups; c->d_blob = d;
+    c->xreg = P.xreg;
     uint8_t * db = (uint8_t *) d;
     // single GPU: counters in the chain's own blob; row split: in the symmetric arena (peers add to them)
     c->args.counter = split ? (unsigned long long *) split->scratch : (unsigned long long *) db;
@@ -1144,11 +1309,13 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     c->args.inflight = getenv("B200_CHAIN_INFLIGHT") ? atoi(getenv("B200_CHAIN_INFLIGHT")) : CH_NS;
     if (c->args.inflight < 1) c->args.inflight = 1;
     c->args.debug = getenv("B200_CHAIN_DEBUG") ? atoi(getenv("B200_CHAIN_DEBUG")) : 0;
-    c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes;
-    c->smem = CH_HDR + (size_t) x_bytes + (size_t) CH_GROUPS * 2 * ncols * max_units * 4 + 1024 + (size_t) CH_GROUPS * CH_NS * stage;
+    c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes; c->args.ns = P.ns;
+    c->smem = P.smem;
     c->cooperative = coop != 0 && !getenv("B200_CHAIN_NO_COOP");
     cudaError_t e = cudaSuccess;
-    switch (ncols) {
+    if (c->xreg) e = CX_NW == 12 ? cudaFuncSetAttribute(gemv_chainx_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
+                                 : cudaFuncSetAttribute(gemv_chainx_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem);
+    else switch (ncols) {
         case 1: e = cudaFuncSetAttribute(gemv_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
         case 2: e = cudaFuncSetAttribute(gemv_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
         case 3: e = cudaFuncSetAttribute(gemv_chain_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
@@ -1166,7 +1333,8 @@ int b200_chain_launch(b200_chain_t chain, b200_stream_t stream) {
     Chain * c = (Chain *) chain;
     cudaStream_t s = (cudaStream_t) stream;
     cudaError_t e;
-    switch (c->ncols) {
+    if (c->xreg) e = chainx_launch(*c, s);
+    else switch (c->ncols) {
         case 1: e = chain_launch_t<1>(*c, s); break;
         case 2: e = chain_launch_t<2>(*c, s); break;
         case 3: e = chain_launch_t<3>(*c, s); break;
