@@ -134,20 +134,31 @@ def cpu_tokens_per_s(model: str, budget_s: float, threads: int):
     return c.step(budget_s), c.kind, c.sample()
 
 
+def _load_workloads():
+    """workloads.py is pure host logic (shape tables): loaded BY PATH so that the reference arm never imports the product package,
+    hence never maps zyk-llama.cpp_b200/lib/libb200mm.so"""
+    import importlib.util
+    name = "_b200_workloads_by_path"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, ROOT / "zyk-llama.cpp_b200" / "workloads.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def _load_pkg_module(name):
-    import importlib
-    from __graft_entry__ import load_pkg, PKG_NAME
-    try:
-        load_pkg()
-        return importlib.import_module(f"{PKG_NAME}.{name}")
-    except ImportError:
-        # the reference arm must run even where the CUDA library is absent: workloads.py is pure host logic
-        import importlib.util
-        spec = importlib.util.spec_from_file_location(f"_b200_{name}", ROOT / "zyk-llama.cpp_b200" / f"{name}.py")
-        mod = importlib.util.module_from_spec(spec)
-        sys.modules[spec.name] = mod
-        spec.loader.exec_module(mod)
-        return mod
+    assert name == "workloads"
+    return _load_workloads()
+
+
+def workload_string(model: str, n_nodes: int) -> str:
+    """the same string in both arms' config.workload"""
+    return f"{model} tg (N=1): every quantised MUL_MAT of one token ({n_nodes} nodes)"
+
+
+METRIC = "tg tokens/s (quantised MUL_MAT chain, N=1)"
 
 
 def run_reference(args):
@@ -167,10 +178,11 @@ def run_reference(args):
     dt = time.time() - t0
     v = len(vals) / sum(1.0 / x for x in vals)       # steps / total extrapolated seconds
     kind, sample = chain.kind, chain.sample() + f"; {budget:.2f} s of compute per step"
-    line = {"impl": "reference", "metric": "tg tokens/s (quantised MUL_MAT chain, N=1)", "value": v, "unit": "tokens/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "strong",
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "ms_per_step_is": "extrapolated token time (bounded sample scaled to the 225 nodes), not a measured step",
+            "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int8 -> int32, f32 scales", "data": "synthetic",
-            "config": {"workload": f"{args.model} tg (N=1), every quantised MUL_MAT of one token", "host": "reference CPU backend (oracle/_ref)"},
+            "config": {"workload": workload_string(args.model, len(chain.ops)), "host": "reference CPU backend (oracle/_ref)"},
             "cpu_baseline": {"value": v, "unit": "tokens/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": dt}
@@ -187,13 +199,15 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="llama-3-8b-q4_k_m")
     ap.add_argument("--pp", type=int, default=512, help="prefill ubatch (0 = skip the pp leg)")
-    ap.add_argument("--pp-steps", type=int, default=3)
+    ap.add_argument("--pp-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="row split (N > 1): Y slices stored into every rank's arena by the kernels, or one NCCL all-gather per node")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--per-node", action="store_true",
                     help="tg on one GPU: one launch per MUL_MAT group (CUDA graph) instead of the persistent chain kernel (b200_chain_*)")
+    ap.add_argument("--configs", default="auto",
+                    help="extra BASELINE.json configs reported as extra keys: 'auto' (all at N = 1; 70B and Mixtral at N > 1), 'none', or a comma list of model names")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -213,30 +227,32 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     peaks, peak_src = _peaks()
-    ops = W.model_ops(args.model)
     warmup = max(3, args.warmup)
+    dev = f"cuda:{local}"
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- row split exchange: one all-gather of the Y slices per node (rowsplit.py) --------
     rowsplit = None
     if world > 1:
         from zyk_llama_cpp_b200.rowsplit import RowSplit
         rowsplit = RowSplit(world, rank, b.row_split)
 
-    def time_chain(n, steps, wu):
-        chain = MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused", persistent=False if args.per_node else "auto")
-        if chain.capturable:
+    def make_chain(ops, n, persistent="auto"):
+        return MatMulChain(ops, n, device=local, rowsplit=rowsplit, fused_exchange=args.exchange == "fused",
+                           persistent=False if args.per_node else persistent)
+
+    def time_chain(chain, steps, wu, sample_clocks=False):
+        if chain.capturable and chain.graph is None:
             chain.capture()
         e0, e1 = b.Event(local), b.Event(local)
         for _ in range(wu):
             chain.step()
         chain.stream.synchronize()
         barrier()
-        sampler = ClockSampler(local) if rank == 0 else None
+        sampler = ClockSampler(local) if (rank == 0 and sample_clocks) else None
         t0 = time.time()
         e0.record(chain.stream)
         for _ in range(steps):
@@ -245,22 +261,110 @@ def main():
         chain.stream.synchronize()
         barrier()
         t1 = time.time()
-        ms = torch.tensor([e0.elapsed_ms(e1)], device=f"cuda:{local}")
+        ms = torch.tensor([e0.elapsed_ms(e1)], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         clocks = sampler.stop(t0, t1) if sampler else None
-        return chain, float(ms.item()), clocks
+        return float(ms.item()) / steps, clocks
 
-    # ---- tg: device-resident ---------------------------------------------------------------------------------
-    chain, ms_total, clocks = time_chain(1, args.steps, warmup)
-    graph_used = chain.graph is not None
-    persistent = chain.decode_chain is not None
-    chain_info = chain.decode_chain.info() if persistent else None
-    ms_step = ms_total / args.steps
+    # ---- parity of the N-rank row split against the single-GPU per-node chain (same seeded weights and inputs) ------------------
+    def split_parity(ops, n, chain):
+        """every activation buffer after one pass, NMSE against a single-GPU chain of per-node launches built on THIS rank from the
+        same seed; max over buffers and ranks"""
+        ref = MatMulChain(ops, n, device=local, persistent=False)
+        x0 = ref.bufs["x"].clone()
+        ref.step(); ref.stream.synchronize()
+        worst, names = 0.0, []
+        chain.bufs["x"].copy_(x0)
+        barrier()
+        chain.issue(); chain.stream.synchronize()
+        barrier()
+        for name, want in ref.bufs.items():
+            got = chain.bufs[name].double(); w = want.double()
+            den = float((w * w).sum())
+            if den == 0.0 or not bool(torch.isfinite(w).all()):
+                continue                      # a buffer nobody writes (static input): nothing to compare
+            worst = max(worst, float(((got - w) ** 2).sum()) / den)
+            names.append(name)
+        ref.close()
+        del ref
+        torch.cuda.empty_cache()
+        t = torch.tensor([worst], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), names
+
+    parity = None
+    PARITY_TOL = 1e-9
+
+    def bench_model(model, steps, wu, pp_steps, headline=False):
+        """tg (N = 1) and pp (N = args.pp) of one model; returns the keys of its block"""
+        nonlocal parity
+        ops = W.model_ops(model)
+        out = {"workload": workload_string(model, len(ops)), "weight_gb_per_token": W.tg_bytes(ops) / 1e9}
+        chain = make_chain(ops, 1)
+        if world > 1:
+            nm, names = split_parity(ops, 1, chain)
+            pr = {"nmse_max": nm, "checked_buffers": names, "against": "single-GPU per-node chain, same seeded weights and x", "tolerance": PARITY_TOL, "n": 1}
+            out["parity"] = pr
+            if headline:
+                parity = {"tg": pr}
+            if nm > PARITY_TOL:
+                raise RuntimeError(f"{model}: row-split parity FAILED at world {world}: nmse {nm:.3e} > {PARITY_TOL}")
+        ms_step, clocks = time_chain(chain, steps, wu, sample_clocks=headline)
+        persistent = chain.decode_chain is not None
+        info = chain.decode_chain.info() if persistent else None
+        bytes_tok = W.tg_bytes(ops)
+        achieved = bytes_tok / world / (ms_step * 1e-3) / 1e9
+        out.update({"tg": {"value": 1e3 / ms_step, "unit": "tokens/s", "ms_per_step": ms_step, "steps": steps,
+                           "decode_kernel": ("persistent chain: one launch per token, %d dependent MUL_MAT groups" % info["n_groups"]) if persistent
+                                            else "one launch per MUL_MAT group (CUDA graph replay)" if chain.graph is not None else "one launch per MUL_MAT group (eager)"},
+                    "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                                 "frac_of_8tbs": achieved / 8000.0, "algorithmic_bytes": bytes_tok / world, "peak_source": peak_src}})
+        extra = {"chain": chain, "ops": ops, "ms_step": ms_step, "clocks": clocks, "persistent": persistent, "info": info,
+                 "launches": (chain.kernels_per_step or len(chain.calls) * 2) * steps, "graph_used": chain.graph is not None}
+        if not headline:
+            chain.close()
+            del chain
+            extra["chain"] = None
+            torch.cuda.empty_cache()
+            if args.pp > 0 and pp_steps > 0:
+                out["pp%d" % args.pp] = bench_pp(ops, model, pp_steps)
+        return out, extra
+
+    def bench_pp(ops, model, pp_steps):
+        try:
+            chain_pp = make_chain(ops, args.pp)
+            res = {}
+            if world > 1:
+                nm, names = split_parity(ops, args.pp, chain_pp)
+                res["parity"] = {"nmse_max": nm, "checked_buffers": names, "tolerance": PARITY_TOL, "n": args.pp}
+                if nm > PARITY_TOL:
+                    raise RuntimeError(f"{model}: row-split pp parity FAILED at world {world}: nmse {nm:.3e}")
+            ms_pp, _ = time_chain(chain_pp, pp_steps, 3)
+            pp_ops = W.pp_ops(ops) * args.pp
+            tf = pp_ops / (ms_pp * 1e-3) / 1e12 / world
+            res.update({"value": args.pp / (ms_pp * 1e-3), "unit": "tokens/s", "n": args.pp, "ms_per_ubatch": ms_pp, "steps": pp_steps,
+                        "dtype": "fp16 x fp16 -> f32 (tcgen05.mma.kind::f16; weights dequantised in-kernel, activations scaled per row by a power of two)",
+                        "fp16_tflops": tf,
+                        # the same op count against the measured cuBLAS bf16 throughput (sustained: this is a long step) and against the nominal peaks
+                        "tensor_roofline": {"bound": "tensor", "achieved": tf, "peak": peaks.get("bf16_tflops_sustained"), "unit": "TFLOP/s",
+                                            "frac": tf / peaks.get("bf16_tflops_sustained", 1400.0), "peak_source": peak_src + " cuBLAS bf16, sustained",
+                                            "frac_of_nominal_fp16_peak": tf / 2250.0, "frac_of_nominal_int8_peak": tf / 4500.0}})
+            chain_pp.close()
+            del chain_pp
+            torch.cuda.empty_cache()
+            return res
+        except RuntimeError:
+            raise
+        except Exception as e:  # noqa: BLE001
+            return {"error": str(e)[:200]}
+
+    # ---- headline: Llama-3-8B Q4_K_M tg, device resident -------------------------------------------------------------------------
+    head, hx = bench_model(args.model, args.steps, warmup, args.pp_steps, headline=True)
+    chain, ops, ms_step, clocks = hx["chain"], hx["ops"], hx["ms_step"], hx["clocks"]
     tg = 1e3 / ms_step
-    launches = (chain.kernels_per_step or len(chain.calls) * 2) * args.steps
     bytes_tok = W.tg_bytes(ops)
-    achieved = bytes_tok / world / (ms_step * 1e-3) / 1e9       # per-GPU GB/s of algorithmic weight bytes
 
     # ---- e2e: pinned host x -> device, chain, logits -> host, host sync per token ------------------------
     x_dev, logits_dev = chain.bufs["x"], chain.bufs["logits"]
@@ -280,30 +384,52 @@ def main():
     for _ in range(args.steps):
         e2e_step()
     barrier()
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=f"cuda:{local}")
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_tg = args.steps / float(e2e_s.item())
     chain.close()
     del chain
+    hx["chain"] = None
     torch.cuda.empty_cache()
 
+    # ---- the path a per-node caller reaches today (the ggml plugin on a real llama.cpp graph: MUL_MAT groups are never adjacent there) --
+    tg_per_group = None
+    if world == 1 and hx["persistent"]:
+        ch2 = MatMulChain(ops, 1, device=local, persistent=False)
+        ms2, _ = time_chain(ch2, args.steps, warmup)
+        ach2 = bytes_tok / (ms2 * 1e-3) / 1e9
+        tg_per_group = {"value": 1e3 / ms2, "unit": "tokens/s", "ms_per_step": ms2, "decode_kernel": "one launch per MUL_MAT group (gemv_fused_kernel / act_quant + gemv_kernel), CUDA graph replay",
+                        "roofline_frac": ach2 / peaks["hbm_gbs"], "note": "what graph_compute reaches on a real llama.cpp graph (groups separated by non-MUL_MAT ops)"}
+        ch2.close()
+        del ch2
+        torch.cuda.empty_cache()
+
     # ---- pp: N = 512 ubatch through the same nodes -----------------------------------------------------------
-    pp = None
-    if args.pp > 0:
-        try:
-            chain_pp, ms_pp, _ = time_chain(args.pp, args.pp_steps, 3)
-            ms_pp /= args.pp_steps
-            pp_ops = W.pp_ops(ops) * args.pp
-            pp = {"value": args.pp / (ms_pp * 1e-3), "unit": "tokens/s", "n": args.pp, "ms_per_ubatch": ms_pp,
-                  "int8_tops": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "steps": args.pp_steps,
-                  # fp16 tcgen05 path: the same op count against the measured cuBLAS bf16 throughput (sustained: this is a long step)
-                  "tensor_roofline": {"bound": "tensor", "achieved": pp_ops / (ms_pp * 1e-3) / 1e12 / world, "peak": peaks.get("bf16_tflops_sustained"),
-                                      "unit": "TFLOP/s", "frac": pp_ops / (ms_pp * 1e-3) / 1e12 / world / peaks.get("bf16_tflops_sustained", 1400.0)}}
-            chain_pp.close()
-            del chain_pp
-        except Exception as e:  # noqa: BLE001
-            pp = {"error": str(e)[:200]}
+    pp = bench_pp(ops, args.model, args.pp_steps) if args.pp > 0 else None
+    if world > 1 and pp and "parity" in pp:
+        parity["pp"] = pp["parity"]
+
+    # ---- the other BASELINE.json configs, each with its own roofline ---------------------------------------------------------------
+    extras = {}
+    if args.configs != "none":
+        if args.configs == "auto":
+            names = (["llama-3-70b-q4_k_m", "mixtral-8x7b-q4_k_m", "llama-3-8b-q8_0", "llama-3-8b-iq4_xs", "llama-3.2-1b-q4_0"] if world == 1
+                     else ["llama-3-70b-q4_k_m"] + (["mixtral-8x7b-q4_k_m"] if world == 2 else []))
+        else:
+            names = [n for n in args.configs.split(",") if n]
+        for name in names:
+            if name == args.model:
+                continue
+            try:
+                big = "70b" in name or "mixtral" in name
+                blk, _ = bench_model(name, 32 if big else 64, 3, 3 if big else 5)
+                extras[name] = blk
+            except RuntimeError:
+                raise
+            except Exception as e:  # noqa: BLE001
+                extras[name] = {"error": str(e)[:300]}
+            torch.cuda.empty_cache()
 
     if rank != 0:
         if world > 1:
@@ -317,35 +443,53 @@ def main():
             cpu = {"value": v, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": kind, "sample": sample}
         except Exception as e:  # noqa: BLE001
             cpu = {"value": None, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": "port", "sample": f"failed: {e}"[:200]}
+        # configs[0]: the fork's ZYK Q4_0 CPU kernels (CPU_REPACK buffer) on the 1B model, next to the GPU number of the same model
+        if "llama-3.2-1b-q4_0" in extras and "error" not in extras["llama-3.2-1b-q4_0"]:
+            try:
+                v, kind, sample = cpu_tokens_per_s("llama-3.2-1b-q4_0", 5.0, os.cpu_count() or 1)
+                extras["llama-3.2-1b-q4_0"]["cpu_baseline"] = {"value": v, "unit": "tokens/s", "cores": os.cpu_count() or 1, "kind": kind, "sample": sample}
+            except Exception as e:  # noqa: BLE001
+                extras["llama-3.2-1b-q4_0"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"[:200]}
 
-    traffic = None
+    # DRAM traffic of the dominant kernel from the ncu capture committed under profiles/ -- only when it is a capture of the kernel that ran
+    traffic, traffic_src = None, None
     tf = ROOT / "profiles" / "traffic.json"
+    kernel_name = "gemv_chain_kernel<1>" if hx["persistent"] else "gemv_fused_kernel<1>"
     if tf.exists():
         try:
             tj = json.load(open(tf))     # ncu dram__bytes_read.sum + dram__bytes_write.sum over the launches of one token
-            traffic = (tj["dram_bytes_read_per_token"] + tj["dram_bytes_write_per_token"]) / max(1, world)
+            if tj.get("kernel", "").startswith(kernel_name.split("<")[0]) and world == 1:
+                traffic = tj["dram_bytes_read_per_token"] + tj["dram_bytes_write_per_token"]
+                traffic_src = f"profiles/traffic.json (round {tj.get('round')}, commit {tj.get('commit', 'n/a')})"
         except Exception:  # noqa: BLE001
             pass
+    persistent, chain_info = hx["persistent"], hx["info"]
+    roof = head["roofline"]
+    roof.update({"traffic": traffic, "traffic_source": traffic_src,
+                 "kernel": ("gemv_chain_kernel<1>: ONE launch = one decode step (every MUL_MAT group of the token), bytes and time per launch"
+                            if persistent else
+                            "gemv_fused_kernel<1> (+ act_quant_kernel / gemv_kernel for the k = 14336 nodes): all launches of one decode step, "
+                            "bytes and time per step (= per token)")})
     line = {
-        "metric": "tg tokens/s (quantised MUL_MAT chain, N=1)", "value": tg, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+        "metric": METRIC, "value": tg, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "int8 x int8 -> int32, f32 scales", "data": "synthetic",
-        "config": {"workload": f"{args.model} tg (N=1): every quantised MUL_MAT of one token ({len(ops)} nodes)",
+        "config": {"workload": workload_string(args.model, len(ops)),
                    "weights": "random-init blocks, plane layout (load-time repack)", "weight_gb_per_token": bytes_tok / 1e9,
                    "l2": "inputs larger than L2 (weights streamed once per step)", "parallelism": f"row-split x{world}" if world > 1 else "single GPU",
-                   "cuda_graph": graph_used, "exchange": (args.exchange if world > 1 else None),
-                   "decode_kernel": ("persistent chain: one launch per token, %d dependent MUL_MAT groups" % chain_info["n_groups"]) if persistent
-                                    else "one launch per MUL_MAT group"},
-        "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                     "traffic": traffic, "peak_source": peak_src, "frac_of_8tbs": achieved / 8000.0,
-                     "algorithmic_bytes": bytes_tok / world,
-                     "kernel": ("gemv_chain_kernel<1>: ONE launch = one decode step (every MUL_MAT group of the token), bytes and time per launch; "
-                                if persistent else
-                                "gemv_fused_kernel<1> (+ act_quant_kernel / gemv_kernel for the k = 14336 nodes): all launches of one decode step, "
-                                "bytes and time per step (= per token); ") + "traffic from profiles/traffic.json"},
-        "pp512": pp, "cpu_baseline": cpu, "clocks": clocks,
+                   "cuda_graph": hx["graph_used"], "exchange": (args.exchange if world > 1 else None),
+                   "decode_kernel": head["tg"]["decode_kernel"],
+                   "value_is": ("the persistent decode chain: reachable when the caller hands over consecutive MUL_MAT groups (C ABI b200_chain_*, plugin on "
+                                "MUL_MAT-only graphs); tg_per_group is the per-node path") if persistent else "one launch per MUL_MAT group"},
+        "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "through": "C ABI (ctypes -> libb200mm.so): pinned host x in, logits out, host sync per token"},
+        "gpu_launches": hx["launches"],
+        "roofline": roof,
+        "tg_per_group": tg_per_group,
+        "pp512" if args.pp == 512 else "pp%d" % args.pp: pp,
+        "parity": parity,
+        "configs": extras,
+        "cpu_baseline": cpu, "clocks": clocks,
     }
     print(json.dumps(line))
     if world > 1:
