@@ -215,6 +215,12 @@ typedef struct b200_mul_mat_id_args {
 } b200_mul_mat_id_args;
 
 B200_API size_t b200_mul_mat_id_workspace(int type, int64_t k, int64_t n_used, int64_t nb1, int64_t n_tokens);
+/* workspace for every path b200_mul_mat_id may take for these shapes (pointers in `args` are ignored). With n_tokens * n_used >= 8 pairs per
+ * expert the call sorts the pairs by expert on the device (counterpart of mm_ids_helper, ggml-cuda/mmid.cu:28-117, and of the row grouping in
+ * ggml_compute_forward_mul_mat_id, ggml-cpu/ggml-cpu.c:1589-1602), gathers their activation rows and runs ONE tensor-core GEMM launch over
+ * (expert, tile) with the Y rows scattered back -- provided the workspace has this size; with the smaller b200_mul_mat_id_workspace() size it
+ * stays on the per-pair GEMV. args->algo: 0 auto, 1 GEMV, 2 GEMM. */
+B200_API size_t b200_mul_mat_id_workspace_ex(const b200_mul_mat_id_args * args);
 B200_API int    b200_mul_mat_id(const b200_mul_mat_id_args * args, b200_stream_t stream);
 
 /* ---- (e) multi-GPU row split ----------------------------------------------------------------

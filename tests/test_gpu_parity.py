@@ -185,11 +185,91 @@ def test_mul_mat_id_vs_oracle(b200, orc, t, cfg):
         b = rng.standard_normal((n_tok, nb1, k)).astype(np.float32)
         want = orc.mul_mat_id(t, as_, b, ids)
         flat = dev(as_).reshape(n_as, -1)
-        got = b200.mul_mat_id(t, flat, dev(b), dev(ids), m).cpu().numpy()
+        got = b200.mul_mat_id(t, flat, dev(b), dev(ids), m, algo=1).cpu().numpy()
         assert nmse(got, want) < DECODE_NMSE
         planes = torch.stack([b200.repack(t, flat[e].contiguous(), m, k) for e in range(n_as)])
-        got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+        got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES, algo=1).cpu().numpy()
         assert nmse(got, want) < DECODE_NMSE
+        # auto: the per-pair GEMV (CPU integer arithmetic) or, from eight pairs per expert on, the expert-gathered tensor-core GEMM
+        got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES).cpu().numpy()
+        gemm = n_tok * n_used > 8 and n_tok * n_used >= 8 * min(n_as, n_tok * n_used)
+        assert nmse(got, want) < (MAX_NMSE if gemm else DECODE_NMSE)
+
+
+def _id_truth(orc, t, as_, b, ids, k):
+    """exact arithmetic on the dequantised expert weights (float64)"""
+    n_tok, n_used = ids.shape
+    n_as, m = as_.shape[0], as_.shape[1]
+    wf = [orc.dequantize(t, as_[e], k).reshape(m, k).astype(np.float64) for e in range(n_as)]
+    y = np.zeros((n_tok, n_used, m))
+    for tk in range(n_tok):
+        for sl in range(n_used):
+            e = int(ids[tk, sl])
+            if 0 <= e < n_as:
+                y[tk, sl] = wf[e] @ b[tk, sl % b.shape[1]].astype(np.float64)
+    return y
+
+
+# the reference's MUL_MAT_ID matrix (tests/test-backend-ops.cpp:7781-7811: n_used 1 / 2 / 4, b with one row per token or one per slot,
+# n in 1 .. 129) plus the prefill ubatch, forced onto the expert-gathered tensor-core GEMM (algo = 2)
+@pytest.mark.parametrize("t", WEIGHT_TYPES)
+@pytest.mark.parametrize("n_used", [1, 2, 4])
+@pytest.mark.parametrize("n_tok", [1, 4, 5, 17, 32, 129, 512])
+def test_mul_mat_id_gemm_vs_oracle(b200, orc, t, n_used, n_tok):
+    n_as = 8
+    rng = np.random.default_rng(1000 * t + 10 * n_tok + n_used)
+    m, k = (300, 512) if n_tok < 512 else (136, 256)          # 300 rows: CTA pairs with a ragged last tile; 136: keeps the 2048-pair oracle run short
+    as_ = np.stack([random_blocks(t, m, k, rng) for _ in range(n_as)])
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    planes = torch.stack([b200.repack(t, dev(as_[e]).reshape(-1), m, k) for e in range(n_as)])
+    for nb1 in sorted({1, n_used}):
+        b = _acts(rng, n_tok * nb1, k).reshape(n_tok, nb1, k)
+        got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES, algo=2).cpu().numpy()
+        assert np.isfinite(got).all()
+        assert nmse(got, orc.mul_mat_id(t, as_, b, ids)) < MAX_NMSE
+        assert nmse(got, _id_truth(orc, t, as_, b, ids, k)) < GEMM_VS_TRUTH
+
+
+def test_mul_mat_id_gemm_single_cta_tiles_skewed_routing_and_invalid_ids(b200, orc):
+    """m <= 128 (no CTA pair), every token routed to the same two experts (one expert needs several n-tiles, six have no rows), ids out
+    of range (their Y rows are zero, as on the GEMV path), Y / b / ids with padded strides"""
+    t, n_as, n_used, n_tok, m, k = Q4_K, 8, 2, 300, 96, 512
+    rng = np.random.default_rng(5)
+    as_ = np.stack([random_blocks(t, m, k, rng) for _ in range(n_as)])
+    ids = np.tile(np.array([[5, 2]], np.int32), (n_tok, 1))
+    ids[7, 0] = -1; ids[11, 1] = n_as + 3; ids[299, 0] = 0
+    b = _acts(rng, n_tok * n_used, k).reshape(n_tok, n_used, k)
+    planes = torch.stack([b200.repack(t, dev(as_[e]).reshape(-1), m, k) for e in range(n_as)])
+    got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES, algo=2).cpu().numpy()
+    want = orc.mul_mat_id(t, as_, b, ids)
+    assert nmse(got, want) < MAX_NMSE
+    assert not got[7, 0].any() and not got[11, 1].any()
+    assert nmse(got, _id_truth(orc, t, as_, b, ids, k)) < GEMM_VS_TRUTH
+    # the same values whichever path computes them (up to the GEMM's rounding): GEMV vs GEMM
+    ref = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES, algo=1).cpu().numpy()
+    assert nmse(got, ref) < MAX_NMSE
+
+
+def test_mul_mat_id_gemm_full_size_mixtral_sampled_rows(b200, orc):
+    """BASELINE configs[3]: Mixtral expert matrices (8 x 14336 x 4096 Q4_K), pp512 ubatch with 2 experts per token, sampled rows vs the oracle"""
+    t, n_as, n_used, n_tok, m, k = Q4_K, 8, 2, 512, 14336, 4096
+    from zyk_llama_cpp_b200 import workloads as W
+    gen = torch.Generator(device="cuda"); gen.manual_seed(3)
+    planes = torch.stack([W.random_weight(t, m, k, torch.device("cuda"), gen) for _ in range(n_as)])     # canonical Q4_K is its own plane layout
+    rng = np.random.default_rng(9)
+    ids = np.stack([rng.permutation(n_as)[:n_used] for _ in range(n_tok)]).astype(np.int32)
+    b = rng.standard_normal((n_tok, 1, k)).astype(np.float32)
+    got = b200.mul_mat_id(t, planes, dev(b), dev(ids), m, layout=b200.LAYOUT_PLANES).cpu().numpy()          # auto: 1024 pairs over 8 experts -> GEMM
+    rows = rng.choice(m, 24, replace=False)
+    rb = k // 256 * 144
+    for e in range(n_as):
+        sub = planes[e].view(m, rb)[torch.from_numpy(rows).cuda()].cpu().numpy().reshape(-1)
+        toks, slots = np.nonzero(ids == e)
+        if len(toks) == 0:
+            continue
+        pick = slice(0, min(len(toks), 40))
+        want = orc.mul_mat_f64(t, sub, np.ascontiguousarray(b[toks[pick], 0]))
+        assert nmse(got[toks[pick], slots[pick]][:, rows], want) < GEMM_VS_TRUTH
 
 
 # ---- full-size properties (BASELINE.json shapes; the oracle would take minutes here) -----------------

@@ -97,6 +97,7 @@ _sig("b200_chain_destroy", C.c_int, C.c_void_p)
 _sig("b200_chain_timeline", C.c_int, C.c_void_p, C.c_void_p, C.c_size_t)
 _sig("b200_mul_mat_id_workspace", C.c_size_t, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64)
 _sig("b200_mul_mat_id", C.c_int, C.POINTER(MulMatIdArgs), C.c_void_p)
+_sig("b200_mul_mat_id_workspace_ex", C.c_size_t, C.POINTER(MulMatIdArgs))
 _sig("b200_stream_create", C.c_void_p, C.c_int)
 _sig("b200_stream_destroy", C.c_int, C.c_void_p)
 _sig("b200_stream_synchronize", C.c_int, C.c_void_p)
@@ -257,19 +258,21 @@ def mul_mat(t: int, w: torch.Tensor, x: torch.Tensor, m: int, *, layout=LAYOUT_C
 
 
 def mul_mat_id(t: int, as_: torch.Tensor, b: torch.Tensor, ids: torch.Tensor, m: int, *, layout=LAYOUT_CANONICAL,
-               flavour=Q8_X86, flags=0, stream=None) -> torch.Tensor:
-    """as_: uint8 [n_as, m*row_size]; b: f32 [n_tokens, nb1, k]; ids: i32 [n_tokens, n_used] -> f32 [n_tokens, n_used, m]."""
+               flavour=Q8_X86, flags=0, algo=0, stream=None) -> torch.Tensor:
+    """as_: uint8 [n_as, m*row_size]; b: f32 [n_tokens, nb1, k]; ids: i32 [n_tokens, n_used] -> f32 [n_tokens, n_used, m].
+    algo: 0 auto, 1 per-pair GEMV, 2 expert-gathered tensor-core GEMM."""
     assert b.dtype == torch.float32 and ids.dtype == torch.int32 and b.is_contiguous() and ids.is_contiguous()
     n_tokens, nb1, k = b.shape
     n_used = ids.shape[1]
     n_as = as_.shape[0]
     y = torch.empty((n_tokens, n_used, m), dtype=torch.float32, device=b.device)
-    need = int(lib.b200_mul_mat_id_workspace(t, k, n_used, nb1, n_tokens)) + 256
-    workspace = torch.empty(need, dtype=torch.uint8, device=b.device)
-    ws = (workspace.data_ptr() + 255) & ~255
     a = MulMatIdArgs(t, layout, m, k, n_as, n_used, nb1, n_tokens, _dev(as_), m * row_size(t, k),
                      _dev(b), k, nb1 * k, _dev(ids), n_used, _dev(y), m, n_used * m,
-                     ws, need - (ws - workspace.data_ptr()), flavour, 0, flags, 0)
+                     0, 0, flavour, algo, flags, 0)
+    need = int(lib.b200_mul_mat_id_workspace_ex(C.byref(a))) + 256
+    workspace = torch.empty(need, dtype=torch.uint8, device=b.device)
+    ws = (workspace.data_ptr() + 255) & ~255
+    a.workspace, a.workspace_size = ws, need - (ws - workspace.data_ptr())
     _check(lib.b200_mul_mat_id(C.byref(a), _s(stream)))
     return y
 

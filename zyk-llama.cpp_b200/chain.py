@@ -88,7 +88,9 @@ class MatMulChain:
         need = 0
         for o in ops:
             if o.n_expert:
-                need = max(need, int(B.lib.b200_mul_mat_id_workspace(o.type, o.k, o.n_used, o.n_used, n)))
+                lo, hi = rowsplit.mine(o.m) if world > 1 else (0, o.m)
+                probe = B.MulMatIdArgs(o.type, layout, hi - lo, o.k, o.n_expert, o.n_used, o.n_used, n, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, B.Q8_X86, 0, 0, 0)
+                need = max(need, int(B.lib.b200_mul_mat_id_workspace_ex(C.byref(probe))))
             else:
                 need = max(need, B.mul_mat_workspace(o.type, n, o.k))
         self.workspace = torch.empty(need + 512, dtype=torch.uint8, device=self.dev)

@@ -33,6 +33,7 @@
 #include "sm100.cuh"
 
 #include <cuda.h>
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -69,16 +70,22 @@ struct GemmArgs {
     // `ksplit` ways along k (units full_tiles + (tile - full_tiles) * ksplit + z) and meet in pre-zeroed Y with red.global.add
     int n_tiles;                // tiles along n; tile index = m_tile * n_tiles + n_tile (the n-tiles of one weight tile run side by side)
     int full_tiles, ksplit, total_units;
+    // MUL_MAT_ID (MOE instantiations): the unit list is built on the device by moe_plan_kernel from the expert ids
+    const int4 * moe_units;     // [*moe_total] {expert, first weight row of the tile (before the CTA's rank), first gathered X row, X rows that exist}
+    const int * moe_total;      // number of units
+    const int * moe_yoff;       // per gathered X row: element offset of its Y row (token * y_token_stride + slot * y_row_stride)
+    long long expert_stride;    // bytes between the expert matrices (each one in the plane layout)
 };
 
 // ---- prologue: X f32 [n][k] (row stride ldx) -> fp16 [n][k] scaled by 2^-e per row, xscale[n] = 2^e ----
 // VMAX: 128-bit loads per thread the one-pass path may hold (k <= 1024 VMAX); small VMAX = few registers = the whole launch resident at once
 template <int VMAX>
 __global__ void __launch_bounds__(256) act_half_kernel(const float * __restrict__ x, int64_t ldx, int64_t k, __half * __restrict__ xh,
-                                                       float * __restrict__ xscale, bool pdl) {
+                                                       float * __restrict__ xscale, bool pdl, const long long * __restrict__ src_off) {
     if (pdl) { pdl_launch_dependents(); pdl_wait(); }
     const int64_t row = blockIdx.x;
-    const float * xr = x + row * ldx;
+    // src_off (MUL_MAT_ID): output row `row` is the activation row at element offset src_off[row] (rows gathered by expert)
+    const float * xr = src_off ? x + src_off[row] : x + row * ldx;
     __shared__ float red[8];
     // one pass when the row fits the registers of the CTA (k <= 16384, 16-byte aligned): 128-bit loads, the row is read once
     const bool vec = k <= 256 * 4 * VMAX && (k & 3) == 0 && (((uintptr_t) xr) & 15) == 0;
@@ -163,9 +170,16 @@ struct StageCursor {     // ring position without a division per step
 // the weight-plane tensor maps of every matrix of the launch (kernel parameter, __grid_constant__: TMA reads them in place)
 struct WMapSet { CUtensorMap m[GEMM_MAX_GROUP][3]; };
 
-struct Unit { int64_t m0; int n0, sb_begin, num_sb, mat; bool split; };
-template <bool PAIR>
+struct Unit { int64_t m0; int n0, sb_begin, num_sb, mat, n_left; bool split; };
+template <bool PAIR, bool MOE = false>
 __device__ __forceinline__ Unit unit_decode(const GemmArgs & a, int u, uint32_t rank) {
+    if (MOE) {
+        const int4 d = __ldg(a.moe_units + u);
+        Unit r;
+        r.mat = d.x; r.m0 = (int64_t) d.y + (int64_t) rank * BM; r.n0 = d.z; r.n_left = d.w;
+        r.sb_begin = 0; r.num_sb = (int) (a.k / 256); r.split = false;
+        return r;
+    }
     int tile = u, z = 0, ks = 1;
     if (u >= a.full_tiles) { const int v = u - a.full_tiles; tile = a.full_tiles + v / a.ksplit; z = v % a.ksplit; ks = a.ksplit; }
     const int total_sb = (int) (a.k / 256);
@@ -177,11 +191,20 @@ __device__ __forceinline__ Unit unit_decode(const GemmArgs & a, int u, uint32_t 
     r.sb_begin = (int) ((int64_t) total_sb * z / ks);
     r.num_sb = (int) ((int64_t) total_sb * (z + 1) / ks) - r.sb_begin;
     r.split = ks > 1;
+    r.n_left = (int) (a.n - r.n0 < a.bn ? a.n - r.n0 : a.bn);
     return r;
 }
 
-template <int TYPE, bool PAIR>
+// 3-D tiled load (MUL_MAT_ID weight planes: [expert][row][bytes])
+__device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void * tmap, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 :: "r"(smem_dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+template <int TYPE, bool PAIR, bool MOE = false>
 __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMapSet & wmaps, const GemmArgs & a) {
+    // MOE: the number of units comes from the plan kernel that ran before this one (plain stream order, no programmatic launch)
+    const int total_units = MOE ? *a.moe_total : a.total_units;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bar_full[MAX_STAGES], bar_empty[MAX_STAGES], raw_full[RAW_STAGES], raw_empty[RAW_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_smem;
@@ -237,8 +260,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         if (lane == 0) {
             if (a.pdl) pdl_wait();               // X (fp16 copy) is written by the kernel before this one
             StageCursor c(stages, 0);
-            for (int u = unit0; u < a.total_units; u += unit_step) {
-                const Unit w = unit_decode<PAIR>(a, u, rank);
+            for (int u = unit0; u < total_units; u += unit_step) {
+                const Unit w = unit_decode<PAIR, MOE>(a, u, rank);
                 for (int kb = 0; kb < 4 * w.num_sb; ++kb, c.advance(1)) {
                     mbar_wait(smem_u32(&bar_empty[c.s]), c.ph ^ 1u);
                     if (a.debug & 1) { if (leader) mbar_arrive(smem_u32(&bar_full[c.s])); continue; }
@@ -252,8 +275,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         // ===== TMA producer: raw quantised planes, one super-block (256 k) of 128 rows per stage =====
         if (lane == 0) {
             StageCursor c(RAW_STAGES, 0);
-            for (int u = unit0; u < a.total_units; u += unit_step) {
-                const Unit w = unit_decode<PAIR>(a, u, rank);
+            for (int u = unit0; u < total_units; u += unit_step) {
+                const Unit w = unit_decode<PAIR, MOE>(a, u, rank);
                 for (int sb = 0; sb < w.num_sb; ++sb, c.advance(1)) {
                     mbar_wait(smem_u32(&raw_empty[c.s]), c.ph ^ 1u);
                     if (a.debug & 4) { mbar_arrive(smem_u32(&raw_full[c.s])); continue; }
@@ -262,9 +285,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
                     for (int i = 0; i < Raw<TYPE>::N; ++i) {
                         constexpr RawLoad L0 = Raw<TYPE>::L[0], L1 = Raw<TYPE>::L[1], L2 = Raw<TYPE>::L[2];
                         const RawLoad L = i == 0 ? L0 : i == 1 ? L1 : L2;
-                        const CUtensorMap * tm = &wmaps.m[w.mat][L.map];
-                        tma_load_2d(smem_w + (uint32_t) (c.s * Raw<TYPE>::BYTES + L.smem_off), tm, (w.sb_begin + sb) * L.cstep + L.coff, (int) w.m0,
-                                    smem_u32(&raw_full[c.s]));
+                        const CUtensorMap * tm = &wmaps.m[MOE ? 0 : w.mat][L.map];
+                        if (MOE) tma_load_3d(smem_w + (uint32_t) (c.s * Raw<TYPE>::BYTES + L.smem_off), tm, (w.sb_begin + sb) * L.cstep + L.coff, (int) w.m0, w.mat,
+                                             smem_u32(&raw_full[c.s]));
+                        else     tma_load_2d(smem_w + (uint32_t) (c.s * Raw<TYPE>::BYTES + L.smem_off), tm, (w.sb_begin + sb) * L.cstep + L.coff, (int) w.m0,
+                                             smem_u32(&raw_full[c.s]));
                     }
                 }
             }
@@ -274,8 +299,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         const uint32_t idesc = umma_idesc_f16(PAIR ? 2 * BM : BM, bn);
         StageCursor c(stages, 0);
         int i = 0;
-        for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
-            const Unit w = unit_decode<PAIR>(a, u, rank);
+        for (int u = unit0; u < total_units; u += unit_step, ++i) {
+            const Unit w = unit_decode<PAIR, MOE>(a, u, rank);
             const int num_kb = 4 * w.num_sb;
             const int buf = i & 1;
             const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols);
@@ -313,10 +338,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         const int t = threadIdx.x - 128;
         const int half = t >> 7, r = t & 127;
         StageCursor c(stages, half), rc(RAW_STAGES, 0);
-        for (int u = unit0; u < a.total_units; u += unit_step) {
-            const Unit w = unit_decode<PAIR>(a, u, rank);
-            const int64_t row = w.m0 + r < a.m[w.mat] ? w.m0 + r : a.m[w.mat] - 1;
-            const GemvW & W = a.W[w.mat];
+        for (int u = unit0; u < total_units; u += unit_step) {
+            const Unit w = unit_decode<PAIR, MOE>(a, u, rank);
+            const int64_t m_rows = a.m[MOE ? 0 : w.mat];
+            const int64_t row = w.m0 + r < m_rows ? w.m0 + r : m_rows - 1;
+            GemvW W = a.W[MOE ? 0 : w.mat];
+            if (MOE) { const long long eo = (long long) w.mat * a.expert_stride; W.p0 += eo; W.p1 += eo; W.p2 += eo; W.p3 += eo; }
             uint2 aux_next = Deq<TYPE>::aux_load(W, row, w.sb_begin);
             for (int sb = 0; sb < w.num_sb; ++sb, rc.advance(1)) {
                 const uint2 aux = aux_next;
@@ -347,37 +374,47 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
         const int eh = (warp - 4 - DEQ_WARPS) >> 2;              // which of the quarter's two warps: column blocks eh, eh + 2, ...
         int i = 0;
         if (a.pdl) pdl_wait();                   // Y may still be read by earlier kernels; xscale comes from the prologue kernel
-        for (int u = unit0; u < a.total_units; u += unit_step, ++i) {
-            const Unit w = unit_decode<PAIR>(a, u, rank);
+        for (int u = unit0; u < total_units; u += unit_step, ++i) {
+            const Unit w = unit_decode<PAIR, MOE>(a, u, rank);
             const int buf = i & 1;
             const uint32_t tmem_acc = tmem_d + (uint32_t) (buf * a.acc_cols) + ((uint32_t) (32 * q) << 16);
             const int64_t mrow = w.m0 + 32 * q + lane;
             // lane l carries the scales of activation rows 32 * c8 + l of the tile: all loads are issued before the wait for the
             // accumulator, so their latency hides behind the MMAs of the unit (one load per iteration, consumed by the next one,
             // made the epilogue a chain of 8 L2 round trips: ~7 us per unit, exposed at the end of every launch)
-            const int n_left = (int) (a.n - w.n0 < bn ? a.n - w.n0 : bn);             // activation rows of this tile that exist (>= 1)
+            const int n_left = w.n_left;                                              // activation rows of this tile that exist (>= 1)
             float xsv[8];
+            int yov[MOE ? 8 : 1];                                                     // MOE: where the Y row of each gathered X row lives
 #pragma unroll
             for (int c8 = 0; c8 < 8; ++c8) {
                 const int nn = c8 * 32 + lane;
                 xsv[c8] = c8 * 32 < bn ? __ldg(a.xscale + w.n0 + (nn < n_left ? nn : n_left - 1)) : 0.0f;
+                if (MOE) yov[c8] = c8 * 32 < bn ? __ldg(a.moe_yoff + w.n0 + (nn < n_left ? nn : n_left - 1)) : 0;
             }
             unsigned long long * tr = a.trace && leader && q == 0 && eh == 0 && lane == 0 && i < 8 ? a.trace + ((size_t) (blockIdx.x >> (PAIR ? 1 : 0)) * 8 + i) * 8 : nullptr;
             if (tr) tr[4] = gtime();
             mbar_wait(smem_u32(&acc_full[buf]), (uint32_t) ((i >> 1) & 1));
             tc_fence_after();
             if (tr) tr[5] = gtime();
-            const bool row_ok = mrow < a.m[w.mat] && !(a.debug & 16);
-            const int64_t ldy = a.ldy[w.mat];
-            float * yp = a.y[w.mat] + (int64_t) (w.n0 + 32 * eh) * ldy + (row_ok ? mrow : 0);
+            const bool row_ok = mrow < a.m[MOE ? 0 : w.mat] && !(a.debug & 16);
+            const int64_t ldy = MOE ? 0 : a.ldy[w.mat];
+            float * yp = MOE ? a.y[0] + (row_ok ? mrow : 0) : a.y[w.mat] + (int64_t) (w.n0 + 32 * eh) * ldy + (row_ok ? mrow : 0);
             for (int cc = eh; cc * 32 < bn; cc += EPI_WARPS / 4, yp += (EPI_WARPS / 4) * 32 * ldy) {     // columns past bn (inside acc_cols) are read and dropped
                 uint32_t v[32];
                 tmem_ld_32x32b_x32(tmem_acc + (uint32_t) (cc * 32), v);
                 float xs_lane = xsv[0];
+                int yo_lane = MOE ? yov[0] : 0;
 #pragma unroll
-                for (int c8 = 1; c8 < 8; ++c8) if (cc == c8) xs_lane = xsv[c8];
+                for (int c8 = 1; c8 < 8; ++c8) if (cc == c8) { xs_lane = xsv[c8]; if (MOE) yo_lane = yov[c8]; }
                 tmem_ld_wait();
-                if (!w.split) {
+                if (MOE) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
+                        const int off = __shfl_sync(0xffffffffu, yo_lane, j);
+                        if (row_ok && cc * 32 + j < n_left) yp[off] = val;
+                    }
+                } else if (!w.split) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
@@ -416,6 +453,91 @@ template <int TYPE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ WMapSet wmaps, const GemmArgs a) {
     gemm_body<TYPE, true>(tmap_x, wmaps, a);
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(THREADS, 1) gemm_moe_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ WMapSet wmaps, const GemmArgs a) {
+    gemm_body<TYPE, false, true>(tmap_x, wmaps, a);
+}
+template <int TYPE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gemm_moe_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ WMapSet wmaps, const GemmArgs a) {
+    gemm_body<TYPE, true, true>(tmap_x, wmaps, a);
+}
+
+// ---- MUL_MAT_ID plan: sort the (token, slot) pairs by expert and lay out the unit list, all on the device ----------------------
+// (what mm_ids_helper does for the reference's CUDA backend, ggml-cuda/mmid.cu:28-117, and the row grouping of the CPU driver,
+// ggml-cpu/ggml-cpu.c:1589-1602; here the ids never visit the host). ONE CTA: counts per expert in shared memory, an exclusive scan,
+// then every valid pair takes the next free row of its expert's range of the gathered activation matrix. The order of the rows
+// inside an expert's range depends on the atomics, the VALUE of every output row does not (a row is one column of the MMA).
+// Pairs whose id is out of range are left out; moe_zero_invalid_kernel zeroes their Y rows (as the GEMV path does).
+struct MoePlanArgs {
+    const int32_t * ids; long long ids_row_stride; int n_tokens, n_used, n_as, nb1;
+    long long b_row_stride, b_token_stride, y_row_stride, y_token_stride;
+    int bn, tile_m, m_tiles, max_units;
+    int * row_begin;           // [n_as + 1] first gathered row of every expert
+    int * total;               // number of units
+    int4 * units;              // [max_units]
+    int * yoff;                // [pairs]
+    long long * src_off;       // [pairs]
+};
+__global__ void __launch_bounds__(1024) moe_plan_kernel(const MoePlanArgs p) {
+    extern __shared__ int sm[];           // cnt[n_as], begin[n_as + 1], ubeg[n_as + 1]
+    int * cnt = sm, * begin = sm + p.n_as, * ubeg = begin + p.n_as + 1;
+    const int pairs = p.n_tokens * p.n_used;
+    for (int e = threadIdx.x; e < p.n_as; e += blockDim.x) cnt[e] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < pairs; i += blockDim.x) {
+        const int t = i / p.n_used, sl = i - t * p.n_used;
+        const int e = p.ids[(long long) t * p.ids_row_stride + sl];
+        if (e >= 0 && e < p.n_as) atomicAdd(&cnt[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int r = 0, u = 0;
+        for (int e = 0; e < p.n_as; ++e) {
+            begin[e] = r; ubeg[e] = u;
+            r += cnt[e];
+            u += p.m_tiles * ((cnt[e] + p.bn - 1) / p.bn);
+        }
+        begin[p.n_as] = r; ubeg[p.n_as] = u;
+        *p.total = u < p.max_units ? u : p.max_units;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e <= p.n_as; e += blockDim.x) p.row_begin[e] = begin[e];
+    // unit list: expert-major, then weight tile, then the n-tiles of that weight tile side by side (they share the weight tile in L2)
+    for (int e = threadIdx.x; e < p.n_as; e += blockDim.x) {
+        const int nt = (cnt[e] + p.bn - 1) / p.bn;
+        int u = ubeg[e];
+        for (int mt = 0; mt < p.m_tiles; ++mt)
+            for (int j = 0; j < nt; ++j, ++u)
+                if (u < p.max_units) {
+                    const int left = cnt[e] - j * p.bn;
+                    p.units[u] = make_int4(e, mt * p.tile_m, begin[e] + j * p.bn, left < p.bn ? left : p.bn);
+                }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < p.n_as; e += blockDim.x) cnt[e] = 0;          // now the fill cursors
+    __syncthreads();
+    for (int i = threadIdx.x; i < pairs; i += blockDim.x) {
+        const int t = i / p.n_used, sl = i - t * p.n_used;
+        const int e = p.ids[(long long) t * p.ids_row_stride + sl];
+        if (e < 0 || e >= p.n_as) continue;
+        const int pos = begin[e] + atomicAdd(&cnt[e], 1);
+        p.yoff[pos] = (int) ((long long) t * p.y_token_stride + (long long) sl * p.y_row_stride);
+        p.src_off[pos] = (long long) t * p.b_token_stride + (p.nb1 == 1 ? 0ll : (long long) sl * p.b_row_stride);
+    }
+    // rows past the valid pairs (ids out of range): the gather still converts a row for them (nobody reads the result): row 0
+    for (int pos = begin[p.n_as] + (int) threadIdx.x; pos < pairs; pos += blockDim.x) { p.yoff[pos] = 0; p.src_off[pos] = 0; }
+}
+// one CTA per (token, slot) pair: zero the Y row of a pair whose expert id is out of range
+__global__ void __launch_bounds__(256) moe_zero_invalid_kernel(const int32_t * __restrict__ ids, long long ids_row_stride, int n_used, int n_as,
+                                                               float * __restrict__ y, long long y_row_stride, long long y_token_stride, long long m) {
+    const int i = blockIdx.x, t = i / n_used, sl = i - t * n_used;
+    const int e = ids[(long long) t * ids_row_stride + sl];
+    if (e >= 0 && e < n_as) return;
+    float * yr = y + (long long) t * y_token_stride + (long long) sl * y_row_stride;
+    for (long long j = threadIdx.x; j < m; j += 256) yr[j] = 0.0f;
 }
 
 // ---- host side ------------------------------------------------------------------------------------------
@@ -515,6 +637,181 @@ bool b200_gemm_wants(int type, int64_t m, int64_t n, int64_t k, bool force) {
 
 int b200_gemm_launch(const b200_mul_mat_args * a, cudaStream_t s) { return b200_gemm_launch_group(a, 1, s); }
 
+// ---- MUL_MAT_ID on the tensor cores: expert gather + one grouped GEMM launch ------------------------------------------------------
+namespace {
+struct MoeShape { int bn, tile_m, m_tiles, max_units; bool pair; int64_t pairs; };
+MoeShape moe_shape(int64_t m, int64_t n_as, int64_t pairs) {
+    MoeShape h;
+    h.pairs = pairs;
+    h.pair = m > BM;
+    h.tile_m = h.pair ? 2 * BM : BM;
+    h.m_tiles = (int) ((m + h.tile_m - 1) / h.tile_m);
+    // rows per n-tile: the expected rows per active expert plus four standard deviations of a uniform routing, so that most experts are ONE
+    // tile (an n-tile more costs another pass over the expert's weights); multiple of 32, at most 256
+    const double act = (double) (pairs < n_as ? pairs : n_as), avg = (double) pairs / act;
+    int bn = (int) (avg + 4.0 * sqrt(avg) + 1.0);
+    bn = (bn + 31) & ~31;
+    h.bn = bn < 32 ? 32 : bn > 256 ? 256 : bn;
+    const int64_t nt = pairs / h.bn + (pairs < n_as ? pairs : n_as);       // sum over experts of ceil(cnt / bn) <= pairs / bn + active experts
+    const int64_t mu = nt * h.m_tiles;
+    h.max_units = (int) (mu < (1 << 22) ? mu : (1 << 22));
+    return h;
+}
+struct MoeCarve { __half * xh; float * xscale; int * row_begin; int * total; int4 * units; int * yoff; long long * src_off; size_t bytes; };
+MoeCarve moe_carve(void * ws, int64_t k, int64_t n_as, const MoeShape & h) {
+    MoeCarve c;
+    uint8_t * b = (uint8_t *) ws;
+    size_t o = 0;
+    c.xh = (__half *) (b + o);           o += align256((size_t) (h.pairs + 256) * k * sizeof(__half));      // + one tile of slack rows: boxes may run past the last row
+    c.xscale = (float *) (b + o);        o += align256((size_t) h.pairs * sizeof(float));
+    c.row_begin = (int *) (b + o);       o += align256((size_t) (n_as + 1) * sizeof(int));
+    c.total = (int *) (b + o);           o += 256;
+    c.units = (int4 *) (b + o);          o += align256((size_t) h.max_units * sizeof(int4));
+    c.yoff = (int *) (b + o);            o += align256((size_t) h.pairs * sizeof(int));
+    c.src_off = (long long *) (b + o);   o += align256((size_t) h.pairs * sizeof(long long));
+    c.bytes = o;
+    return c;
+}
+template <int TYPE>
+int launch_gemm_moe(const CUtensorMap & tm, const WMapSet & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK(cudaFuncSetAttribute(gemm_moe_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
+        B200_CHECK(cudaFuncSetAttribute(gemm_moe_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
+        configured = true;
+    }
+    if (pair) B200_CHECK(b200_launch(gemm_moe_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
+    else      B200_CHECK(b200_launch(gemm_moe_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
+    return 0;
+}
+// [expert][rows][inner_bytes] uint8 plane, boxes of box_inner bytes x 128 rows x 1 expert
+bool make_plane_map3(CUtensorMap * tm, const void * base, uint64_t inner_bytes, uint64_t rows, uint64_t experts, uint64_t expert_stride, uint32_t box_inner, CUtensorMapSwizzle sw) {
+    const cuuint64_t dims[3] = {inner_bytes, rows, experts};
+    const cuuint64_t strides[2] = {inner_bytes, expert_stride};
+    const cuuint32_t box[3] = {box_inner, (cuuint32_t) BM, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return get_encode_tiled()(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+bool make_weight_maps3(int type, const GemvW & W, int64_t m, int64_t e, int64_t es, WMaps & w) {
+    const uint64_t nb = (uint64_t) W.nb, rows = (uint64_t) m, E = (uint64_t) e, S = (uint64_t) es;
+    bool ok = true;
+    switch (type) {
+        case B200_TYPE_Q4_K:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 144, rows, E, S, 144, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q6_K:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 128, rows, E, S, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map3(&w.m[1], W.p1, nb * 64, rows, E, S, 64, CU_TENSOR_MAP_SWIZZLE_64B) &&
+                 make_plane_map3(&w.m[2], W.p2, nb * 16, rows, E, S, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            break;
+        case B200_TYPE_IQ4_XS:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 128, rows, E, S, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q4_0:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 16, rows, E, S, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map3(&w.m[1], W.p1, nb * 2, rows, E, S, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q8_0:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 32, rows, E, S, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
+                 make_plane_map3(&w.m[1], W.p1, nb * 2, rows, E, S, 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[2] = w.m[0]; break;
+        default: ok = false;
+    }
+    return ok;
+}
+} // namespace
+
+size_t b200_gemm_moe_workspace(int type, int64_t m, int64_t k, int64_t n_as, int64_t pairs) {
+    if (!b200_type_is_weight(type) || k % 256 != 0 || pairs <= 0 || n_as <= 0) return 0;
+    const MoeShape h = moe_shape(m, n_as, pairs);
+    return moe_carve(nullptr, k, n_as, h).bytes + 256;
+}
+
+// is the grouped GEMM the better path? (fast = plane layout, 16-byte aligned expert stride). A pair costs the GEMV one pass over an expert
+// matrix, the GEMM costs every ACTIVE expert one dequantising pass that is several times dearer per weight (B200: 8 us vs 72 us for
+// 4096 x 14336): take the GEMM when there are at least eight pairs per expert that can be active
+bool b200_gemm_moe_wants(int type, int64_t m, int64_t k, int64_t n_as, int64_t n_used, int64_t n_tokens, int64_t y_span, bool force) {
+    if (!b200_type_is_weight(type) || k % 256 != 0 || m <= 0 || n_as <= 0 || n_as > 2048) return false;
+    const int64_t pairs = n_tokens * n_used;
+    if (pairs <= 0 || pairs >= ((int64_t) 1 << 24) || y_span >= ((int64_t) 1 << 31) || k * 2 > (int64_t) 1 << 31) return false;
+    if (force) return true;
+    const int64_t act = pairs < n_as ? pairs : n_as;
+    return pairs > 8 && pairs >= 8 * act;
+}
+
+int b200_gemm_moe_launch(const b200_mul_mat_id_args * a, cudaStream_t s) {
+    encode_tiled_fn encode = get_encode_tiled();
+    B200_REQUIRE(encode != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
+    const int64_t pairs = a->n_tokens * a->n_used, k = a->k;
+    const MoeShape h = moe_shape(a->m, a->n_as, pairs);
+    const MoeCarve c = moe_carve(a->workspace, k, a->n_as, h);
+    B200_REQUIRE(a->workspace && a->workspace_size >= c.bytes, "mul_mat_id (GEMM): workspace %zu < %zu bytes", a->workspace_size, c.bytes);
+
+    // 1. plan: pairs sorted by expert, unit list, scatter / gather offsets
+    MoePlanArgs p = {};
+    p.ids = a->ids; p.ids_row_stride = a->ids_row_stride; p.n_tokens = (int) a->n_tokens; p.n_used = (int) a->n_used; p.n_as = (int) a->n_as; p.nb1 = (int) a->nb1;
+    p.b_row_stride = a->b_row_stride; p.b_token_stride = a->b_token_stride; p.y_row_stride = a->y_row_stride; p.y_token_stride = a->y_token_stride;
+    p.bn = h.bn; p.tile_m = h.tile_m; p.m_tiles = h.m_tiles; p.max_units = h.max_units;
+    p.row_begin = c.row_begin; p.total = c.total; p.units = c.units; p.yoff = c.yoff; p.src_off = c.src_off;
+    B200_CHECK(b200_launch(moe_plan_kernel, dim3(1), dim3(1024), (size_t) (3 * a->n_as + 2) * sizeof(int), s, false, p));
+    B200_CHECK(b200_launch(moe_zero_invalid_kernel, dim3((unsigned) pairs), dim3(256), 0, s, false, a->ids, (long long) a->ids_row_stride, (int) a->n_used, (int) a->n_as,
+                           a->y, (long long) a->y_row_stride, (long long) a->y_token_stride, (long long) a->m));
+    // 2. gathered fp16 activations: row p of xh is the activation row of the p-th sorted pair. Rows past the valid pairs (invalid ids) keep
+    //    whatever the workspace held: they are only ever read into tile columns the epilogue drops
+    if (k <= 4096)      B200_CHECK(b200_launch(act_half_kernel<4>, dim3((unsigned) pairs), dim3(256), 0, s, false, a->b, (int64_t) 0, k, c.xh, c.xscale, false, (const long long *) c.src_off));
+    else if (k <= 8192) B200_CHECK(b200_launch(act_half_kernel<8>, dim3((unsigned) pairs), dim3(256), 0, s, false, a->b, (int64_t) 0, k, c.xh, c.xscale, false, (const long long *) c.src_off));
+    else                B200_CHECK(b200_launch(act_half_kernel<16>, dim3((unsigned) pairs), dim3(256), 0, s, false, a->b, (int64_t) 0, k, c.xh, c.xscale, false, (const long long *) c.src_off));
+
+    // 3. one GEMM launch over (expert, weight tile, n-tile)
+    const int bn = h.bn, bn_cta = h.pair ? bn / 2 : bn;
+    GemmArgs g = {};
+    WMapSet wm;
+    g.nmat = 1; g.n = pairs; g.k = k;
+    g.W[0] = gemv_w_make(a->type, a->as, a->m, k);
+    g.m[0] = a->m; g.y[0] = a->y; g.ldy[0] = 0;
+    for (int i = 1; i < GEMM_MAX_GROUP; ++i) { g.W[i] = g.W[0]; g.m[i] = g.m[0]; g.y[i] = g.y[0]; g.ldy[i] = 0; }
+    WMaps one;
+    B200_REQUIRE(make_weight_maps3(a->type, g.W[0], a->m, a->n_as, a->as_expert_stride, one),
+                 "mul_mat_id (GEMM): cuTensorMapEncodeTiled failed for the expert planes (type %d m=%lld k=%lld experts=%lld stride=%lld)", a->type,
+                 (long long) a->m, (long long) k, (long long) a->n_as, (long long) a->as_expert_stride);
+    for (int i = 0; i < GEMM_MAX_GROUP; ++i) for (int j = 0; j < 3; ++j) wm.m[i][j] = one.m[j];
+    g.xscale = c.xscale; g.bn = bn; g.n_tiles = 1;
+    g.acc_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
+    const size_t per_stage = (size_t) A_STAGE + (size_t) bn_cta * 128;
+    const size_t raw_ring = (size_t) raw_ring_bytes_of(a->type);
+    const int stages = (int) ((SMEM_BUDGET - raw_ring) / per_stage);
+    g.stages = stages > MAX_STAGES ? MAX_STAGES : stages;
+    const size_t smem = raw_ring + (size_t) g.stages * per_stage + 1024;
+    g.full_tiles = h.max_units; g.ksplit = 1; g.total_units = h.max_units;
+    g.moe_units = c.units; g.moe_total = c.total; g.moe_yoff = c.yoff; g.expert_stride = a->as_expert_stride;
+    if (const char * e = getenv("B200_GEMM_DEBUG")) g.debug = atoi(e);
+
+    CUtensorMap tm;
+    const cuuint64_t dims[2] = {(cuuint64_t) k, (cuuint64_t) (pairs + 256)};        // the slack rows exist in the workspace: boxes never leave it
+    const cuuint64_t strides[1] = {(cuuint64_t) k * sizeof(__half)};
+    const cuuint32_t box[2] = {(cuuint32_t) BK, (cuuint32_t) bn_cta};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult cr = encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, c.xh, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200_REQUIRE(cr == CUDA_SUCCESS, "mul_mat_id (GEMM): cuTensorMapEncodeTiled failed (%d) for pairs=%lld k=%lld bn=%d", (int) cr, (long long) pairs, (long long) k, bn);
+
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    const int workers = h.pair ? sms / 2 : sms;
+    const unsigned nw = (unsigned) (h.max_units < workers ? h.max_units : workers);
+    dim3 grid(h.pair ? 2 * nw : nw);
+    switch (a->type) {
+        case B200_TYPE_Q4_K:   return launch_gemm_moe<B200_TYPE_Q4_K>(tm, wm, g, grid, smem, s, h.pair);
+        case B200_TYPE_Q6_K:   return launch_gemm_moe<B200_TYPE_Q6_K>(tm, wm, g, grid, smem, s, h.pair);
+        case B200_TYPE_Q8_0:   return launch_gemm_moe<B200_TYPE_Q8_0>(tm, wm, g, grid, smem, s, h.pair);
+        case B200_TYPE_Q4_0:   return launch_gemm_moe<B200_TYPE_Q4_0>(tm, wm, g, grid, smem, s, h.pair);
+        case B200_TYPE_IQ4_XS: return launch_gemm_moe<B200_TYPE_IQ4_XS>(tm, wm, g, grid, smem, s, h.pair);
+    }
+    b200_set_error("mul_mat_id (GEMM): unsupported weight type %d", a->type);
+    return -2;
+}
+
 // can these nodes share ONE GEMM launch? same weight type, same X (pointer, n, k, stride) and workspace
 bool b200_gemm_groupable(const b200_mul_mat_args * args, int count) {
     if (count < 1 || count > GEMM_MAX_GROUP) return false;
@@ -544,9 +841,9 @@ int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStr
     float * xscale = (float *) ((uint8_t *) a->workspace + align256((size_t) n * k * sizeof(__half)));
     if (!(a->flags & B200_MM_X_PREQUANTISED))
     {
-        if (k <= 4096)      B200_CHECK(b200_launch(act_half_kernel<4>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
-        else if (k <= 8192) B200_CHECK(b200_launch(act_half_kernel<8>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
-        else                B200_CHECK(b200_launch(act_half_kernel<16>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl));
+        if (k <= 4096)      B200_CHECK(b200_launch(act_half_kernel<4>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl, (const long long *) nullptr));
+        else if (k <= 8192) B200_CHECK(b200_launch(act_half_kernel<8>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl, (const long long *) nullptr));
+        else                B200_CHECK(b200_launch(act_half_kernel<16>, dim3((unsigned) n), dim3(256), 0, s, pdl, a->x, a->x_row_stride, k, xh, xscale, pdl, (const long long *) nullptr));
     }
     if (after_prologue) B200_CHECK(cudaEventRecord(after_prologue, s));
 

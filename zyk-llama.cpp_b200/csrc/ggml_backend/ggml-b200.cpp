@@ -460,7 +460,10 @@ enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
     const int layout = weight_layout(as);
     const int64_t chunk = n_used > 0 ? (65535 / n_used > 0 ? 65535 / n_used : 1) : n_tokens;   // (token, slot) pairs per launch
     const int64_t tmax = n_tokens < chunk ? n_tokens : chunk;
-    const size_t need = b200_mul_mat_id_workspace((int) as->type, k, n_used, nb1, tmax);
+    // room for whichever path the call takes: per-pair GEMV (few pairs per expert) or expert gather + grouped tensor-core GEMM
+    b200_mul_mat_id_args probe = {};
+    probe.type = (int32_t) as->type; probe.layout = layout; probe.m = m; probe.k = k; probe.n_as = n_as; probe.n_used = n_used; probe.nb1 = nb1; probe.n_tokens = tmax;
+    const size_t need = b200_mul_mat_id_workspace_ex(&probe);
     if (!backend_reserve(bc, need)) return GGML_STATUS_ALLOC_FAILED;
     for (int64_t t0 = 0; t0 < n_tokens; t0 += chunk) {
         const int64_t nt = n_tokens - t0 < chunk ? n_tokens - t0 : chunk;

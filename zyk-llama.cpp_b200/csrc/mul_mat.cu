@@ -363,6 +363,13 @@ size_t b200_mul_mat_id_workspace(int type, int64_t k, int64_t n_used, int64_t nb
     return xq_planes_bytes(act, n_tokens * nb1, k) + 256;
 }
 
+size_t b200_mul_mat_id_workspace_ex(const b200_mul_mat_id_args * a) {
+    if (!a) return 0;
+    const size_t v = b200_mul_mat_id_workspace(a->type, a->k, a->n_used, a->nb1, a->n_tokens);
+    const size_t g = b200_gemm_moe_workspace(a->type, a->m, a->k, a->n_as, a->n_tokens * a->n_used);
+    return v > g ? v : g;
+}
+
 int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
     cudaStream_t s = (cudaStream_t) stream;
     B200_REQUIRE(a && a->as && a->b && a->ids && a->y, "b200_mul_mat_id: null pointer");
@@ -378,6 +385,18 @@ int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
     const bool pdl = (a->flags & B200_MM_PDL) != 0;
     const int act = b200_act_type(a->type);
     const int64_t rows = a->n_tokens * a->nb1;
+    // (4) many pairs per expert: sort the pairs by expert on the device, gather their activation rows, ONE tensor-core GEMM launch
+    //     over (expert, tile), Y rows scattered back (gemm.cu: b200_gemm_moe_launch)
+    {
+        const bool fast_id = planes_fast_path(a->type, a->layout, a->m, a->k, a->as, 0) && (a->as_expert_stride % 16) == 0;
+        const int64_t y_span = (a->n_tokens - 1) * a->y_token_stride + (a->n_used - 1) * a->y_row_stride + a->m;
+        const bool strides_ok = a->y_token_stride >= 0 && a->y_row_stride >= 0 && a->b_row_stride >= 0 && a->b_token_stride >= 0;
+        const bool want = a->algo != 1 && fast_id && strides_ok && b200_gemm_moe_wants(a->type, a->m, a->k, a->n_as, a->n_used, a->n_tokens, y_span, a->algo == 2);
+        const bool room = a->workspace_size >= b200_gemm_moe_workspace(a->type, a->m, a->k, a->n_as, a->n_tokens * a->n_used);
+        B200_REQUIRE(a->algo != 2 || (want && room), "b200_mul_mat_id: GEMM forced but the call is not eligible (layout / strides / workspace %zu bytes, see b200_mul_mat_id_workspace_ex)",
+                     a->workspace_size);
+        if (want && room) return b200_gemm_moe_launch(a, s);
+    }
     const XqPlanes pl = xq_planes_carve(a->workspace, act, rows, a->k);
 
     // quantise every b row once: token-major, nb1 rows per token (b strides may be arbitrary)
