@@ -153,6 +153,32 @@ def _load_pkg_module(name):
     return _load_workloads()
 
 
+def plugin_e2e(steps: int, warmup: int, pp: int, pp_steps: int):
+    """tg (and pp) of the headline model through libggml-b200.so driven by the reference's own ggml runtime (GGML_BACKEND_PATH), as a
+    subprocess: oracle/_ref/<variant>/plugin_bench. None where the reference libraries cannot run on this host."""
+    try:
+        from oracle.oracle import ref_dir
+        d = ref_dir()
+        exe = d / "plugin_bench" if d else None
+        plugin = ROOT / "zyk-llama.cpp_b200" / "lib" / "libggml-b200.so"
+        if exe is None or not exe.exists() or not plugin.exists():
+            return {"unavailable": "oracle/_ref/*/plugin_bench or libggml-b200.so not built for this host"}
+        env = dict(os.environ, GGML_BACKEND_PATH=str(plugin))
+        out = {}
+        for key, n, k, w in (("tg", 1, steps, warmup), ("pp%d" % pp, pp, pp_steps, 2)):
+            if n <= 0:
+                continue
+            r = subprocess.run([str(exe), "--n", str(n), "--steps", str(k), "--warmup", str(w)], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+            line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+            if r.returncode != 0 or not line:
+                out[key] = {"error": (r.stderr or r.stdout)[-300:]}
+                continue
+            out[key] = json.loads(line[-1])
+        return out
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:300]}
+
+
 def workload_string(model: str, n_nodes: int) -> str:
     """the same string in both arms' config.workload"""
     return f"{model} tg (N=1): every quantised MUL_MAT of one token ({n_nodes} nodes)"
@@ -451,6 +477,12 @@ def main():
             except Exception as e:  # noqa: BLE001
                 extras["llama-3.2-1b-q4_0"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"[:200]}
 
+    # ---- e2e through the ggml plugin: the same 225-node graph built with the reference's API (oracle/plugin_bench.cpp, linked against the
+    #      reference's libggml from oracle/_ref; the plugin is loaded through GGML_BACKEND_PATH), host buffers in and out ----------------------
+    e2e_plugin = None
+    if world == 1 and args.model == "llama-3-8b-q4_k_m":
+        e2e_plugin = plugin_e2e(args.steps, warmup, args.pp, max(3, args.pp_steps // 2))
+
     # DRAM traffic of the dominant kernel from the ncu capture committed under profiles/ -- only when it is a capture of the kernel that ran
     traffic, traffic_src = None, None
     tf = ROOT / "profiles" / "traffic.json"
@@ -483,6 +515,7 @@ def main():
                                 "MUL_MAT-only graphs); tg_per_group is the per-node path") if persistent else "one launch per MUL_MAT group"},
         "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "through": "C ABI (ctypes -> libb200mm.so): pinned host x in, logits out, host sync per token"},
+        "e2e_plugin": e2e_plugin,
         "gpu_launches": hx["launches"],
         "roofline": roof,
         "tg_per_group": tg_per_group,

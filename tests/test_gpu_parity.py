@@ -449,6 +449,44 @@ def test_stream_gemv_full_size_baseline_shapes(b200, orc):
         assert nmse(y[:, rows], orc.mul_mat(t, w[rows], x)) < DECODE_NMSE
 
 
+def test_gemm_full_size_baseline_shapes_sampled_rows(b200, orc):
+    """The launches that carry the pp512 number (BASELINE configs[1]), at full size, n = 512: ffn_gate + ffn_up as ONE grouped launch on
+    CTA pairs (2 x 14336 rows, k-split tail tiles), ffn_down (k = 14336, Q6_K), and the output matrix (128256 rows). Sampled rows and
+    activation rows against exact arithmetic on the dequantised weights and against the CPU's quantised-activation arithmetic."""
+    from zyk_llama_cpp_b200 import workloads as W
+    gen = torch.Generator(device="cuda"); gen.manual_seed(11)
+    rng = np.random.default_rng(31)
+    n = 512
+    cols = np.concatenate([rng.choice(n, 6, replace=False), [0, n - 1]])
+
+    def check(t, wdev, m, k, x, y):
+        rows = np.concatenate([rng.choice(m, 30, replace=False), [0, m - 1, (m // 256) * 256 - 1, min(m - 1, (m // 256) * 256)]])
+        rb = W.row_bytes(t, k)
+        sub = wdev.view(m, rb)[torch.from_numpy(rows).cuda()].cpu().numpy().reshape(-1)
+        got = y[torch.from_numpy(cols).cuda()][:, torch.from_numpy(rows).cuda()].cpu().numpy()
+        xs = np.ascontiguousarray(x[cols])
+        assert np.isfinite(got).all()
+        assert nmse(got, orc.mul_mat_f64(t, sub, xs)) < GEMM_VS_TRUTH, (t, m, k)
+        assert nmse(got, orc.mul_mat(t, sub, xs)) < MAX_NMSE, (t, m, k)
+
+    # gate + up grouped (the same X, one tile list over both matrices)
+    k = 4096
+    x = rng.standard_normal((n, k)).astype(np.float32)
+    wg, wu = (W.random_weight(Q4_K, 14336, k, torch.device("cuda"), gen) for _ in range(2))       # canonical Q4_K is its own plane layout
+    yg, yu = b200.mul_mat_group([Q4_K, Q4_K], [wg, wu], dev(x), [14336, 14336])
+    check(Q4_K, wg, 14336, k, x, yg)
+    check(Q4_K, wu, 14336, k, x, yu)
+    del wg, wu, yg, yu
+    # ffn_down of a use_more_bits layer, and the output matrix
+    for t, m, k in ((Q6_K, 4096, 14336), (Q6_K, 128256, 4096), (Q4_K, 4096, 14336)):
+        x = rng.standard_normal((n, k)).astype(np.float32)
+        w = W.random_weight(t, m, k, torch.device("cuda"), gen)
+        wp = b200.repack(t, w, m, k)
+        y = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES)
+        check(t, w, m, k, x, y)
+        del w, wp, y
+
+
 @pytest.mark.parametrize("ks", [2, 3, 8])
 def test_gemm_split_k(b200, orc, monkeypatch, ks):
     """k split over gridDim.z, partial tiles reduced into a pre-zeroed Y (what small-m prefill shapes use to fill 148 SMs)."""

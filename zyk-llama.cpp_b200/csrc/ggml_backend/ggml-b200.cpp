@@ -496,10 +496,13 @@ bool is_noop(const ggml_tensor * t) {
     return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_VIEW || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_PERMUTE ||
            t->op == GGML_OP_TRANSPOSE;
 }
-bool plain_decode_mul_mat(const ggml_tensor * t) {
-    if (t->op != GGML_OP_MUL_MAT) return false;
+// a node the graph does not ask for (GGML_TENSOR_FLAG_COMPUTE unset: ggml-cpu.c:2946, ggml-cuda.cu:3386 skip those as well)
+bool skipped(const ggml_tensor * t) { return (t->flags & GGML_TENSOR_FLAG_COMPUTE) == 0; }
+// a 2-D MUL_MAT without batch dimensions: decode (n <= 4) and prefill alike
+bool plain_mul_mat(const ggml_tensor * t) {
+    if (t->op != GGML_OP_MUL_MAT || skipped(t)) return false;
     const ggml_tensor * w = t->src[0], * x = t->src[1];
-    return x->ne[1] <= 4 && x->ne[2] == 1 && x->ne[3] == 1 && w->ne[2] == 1 && w->ne[3] == 1 && x->nb[0] == sizeof(float) && t->nb[0] == sizeof(float);
+    return x->ne[2] == 1 && x->ne[3] == 1 && w->ne[2] == 1 && w->ne[3] == 1 && x->nb[0] == sizeof(float) && t->nb[0] == sizeof(float);
 }
 b200_mul_mat_args plain_args(const ggml_tensor * dst) {
     const ggml_tensor * w = dst->src[0], * x = dst->src[1];
@@ -512,9 +515,21 @@ b200_mul_mat_args plain_args(const ggml_tensor * dst) {
     a.flavour = B200_Q8_X86;
     return a;
 }
+// two argument lists describe the same chain (field by field: the structs carry padding)
+bool same_args(const std::vector<b200_mul_mat_args> & a, const std::vector<b200_mul_mat_args> & b) {
+    if (a.size() != b.size()) return false;
+    for (size_t i = 0; i < a.size(); ++i) {
+        const b200_mul_mat_args & p = a[i], & q = b[i];
+        if (p.type != q.type || p.layout != q.layout || p.m != q.m || p.n != q.n || p.k != q.k || p.w != q.w || p.w_row_stride != q.w_row_stride ||
+            p.x != q.x || p.x_row_stride != q.x_row_stride || p.y != q.y || p.y_row_stride != q.y_row_stride || p.flavour != q.flavour) return false;
+    }
+    return true;
+}
 bool env_on(const char * name) { const char * e = getenv(name); return !(e && e[0] == '0'); }
 
-// tries to run nodes [i, ...) as groups / a chain; returns the index of the first node NOT consumed (== i: nothing done)
+// tries to run nodes [i, ...) as groups / a chain; returns the index of the first node NOT consumed (== i: nothing done).
+// Decode (n <= 4): groups become single launches, two or more consecutive K-quant groups ONE persistent chain launch. Prefill (n > 4):
+// the nodes that read the same X share the fp16 copy of X and, per weight type, ONE tensor-core GEMM launch (b200_mul_mat_group).
 int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_status & st) {
     static const bool group_on = env_on("GGML_B200_GROUP"), chain_on = env_on("GGML_B200_CHAIN");
     st = GGML_STATUS_SUCCESS;
@@ -524,8 +539,8 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     int j = i, last = i;
     for (; j < cgraph->n_nodes; ++j) {
         const ggml_tensor * t = cgraph->nodes[j];
-        if (is_noop(t)) continue;
-        if (!plain_decode_mul_mat(t)) break;
+        if (is_noop(t) || skipped(t) || ggml_is_empty(t)) continue;
+        if (!plain_mul_mat(t)) break;
         b200_mul_mat_args a = plain_args(t);
         if (!args.empty() && a.n != args[0].n) break;
         const b200_mul_mat_args * head = sizes.empty() ? nullptr : &args[args.size() - (size_t) sizes.back()];
@@ -543,10 +558,10 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
 
     bool kquant = true;
     for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q6_K);
-    if (chain_on && kquant && sizes.size() >= 2 && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
+    if (chain_on && kquant && args[0].n <= 4 && sizes.size() >= 2 && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
         b200_chain_t chain = nullptr;
         for (auto & c : bc->chains)
-            if (c.args.size() == args.size() && c.sizes == sizes && memcmp(c.args.data(), args.data(), args.size() * sizeof(b200_mul_mat_args)) == 0) { chain = c.chain; break; }
+            if (c.sizes == sizes && same_args(c.args, args)) { chain = c.chain; break; }
         if (!chain) {
             chain = b200_chain_create(bc->device, args.data(), sizes.data(), (int) sizes.size());
             if (chain) {
@@ -576,9 +591,9 @@ enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgr
     b200_set_device(bc->device);
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
-        if (ggml_is_empty(node)) continue;
+        if (ggml_is_empty(node) || skipped(node)) continue;
         enum ggml_status st = GGML_STATUS_SUCCESS;
-        if (plain_decode_mul_mat(node)) {
+        if (plain_mul_mat(node)) {
             const int next = compute_decode_run(bc, cgraph, i, st);
             if (st != GGML_STATUS_SUCCESS) return st;
             if (next > i) { i = next - 1; continue; }
