@@ -317,6 +317,68 @@ void orc_quantize_row_q8_2_x4(const float * x, void * vy, int64_t k) {
     }
 }
 
+/* CPU GEMM activation format of the repack path: four rows quantised to Q8_K at once and interleaved in
+ * runs of eight bytes, block_q8_Kx4 = { float d[4]; int8 qs[1024]; int16 bsums[64] } (ggml-cpu/repack.h:55-61).
+ * Follows ggml_quantize_mat_q8_K_4x8_generic (ggml-cpu/repack.cpp:180-229): per row and 256-block the signed
+ * element of largest magnitude (first one wins), iscale = -127 / max, q = nearest_int(x * iscale) WITHOUT the
+ * clamp to 127 that quantize_row_q8_K applies; qs[j] takes row (j % 32) / 8, element 8 * (j / 32) + j % 8;
+ * bsums index ((j & 31) >> 3) * 4 + (j >> 8) * 16 + ((j >> 6) & 3), i.e. four sums of 16 per row, rows interleaved. */
+void orc_quantize_mat_q8_K_4x8(const float * x, void * vy, int64_t k) {
+    const int64_t nb = k / 256;
+    uint8_t * out = (uint8_t *) vy;
+    for (int64_t i = 0; i < nb; ++i) {
+        uint8_t * blk = out + i * 1168;
+        float * d = (float *) blk; int8_t * qs = (int8_t *) (blk + 16); int16_t * bsums = (int16_t *) (blk + 16 + 1024);
+        float iscale[4];
+        for (int r = 0; r < 4; ++r) {
+            float amax = 0.0f, mx = 0.0f;
+            for (int j = 0; j < 256; ++j) {
+                const float v = x[r * k + i * 256 + j];
+                if (amax < fabsf(v)) { amax = fabsf(v); mx = v; }
+            }
+            iscale[r] = amax ? -127.f / mx : 0.0f;
+            d[r] = amax ? 1.0f / iscale[r] : 0.0f;
+        }
+        for (int j = 0; j < 64; ++j) bsums[j] = 0;
+        for (int j = 0; j < 1024; ++j) {
+            const int src_off = (j / 32) * 8 + (j % 8), src_id = (j % 32) / 8;
+            const int index = (((j & 31) >> 3) << 2) + ((j >> 8) << 4) + ((j >> 6) & 3);
+            const float v = x[src_id * k + i * 256 + src_off] * iscale[src_id] + 12582912.0f;       /* nearest_int, ggml-quants.c:444-449 */
+            qs[j] = (int8_t) ((int) (f2u(v) & 0x007fffffu) - 0x00400000);
+            bsums[index] = (int16_t) (bsums[index] + qs[j]);
+        }
+    }
+}
+
+/* The fork's ZYK Q4_0 path end to end (SURVEY 8 a9 + a16): activations to block_q8_2_x4 (above), then per weight row,
+ * block after block in order, acc = fma(d_w * d_x, (float) (sum_j u4_j * q8_j - 8 * s), acc) with the UNSIGNED nibbles 0..15
+ * and the block's int16 quant sum s as the bias -- arithmetic of ZykQ4_0_T::compute_block + mul_mat_q4_t_q8_0<.., -8, ..>
+ * (ggml-cpu/arch/x86/repack.cpp:186-243, 460-508): one lane of the 512-bit accumulators is one weight row, so the fp32 order
+ * of a row is exactly this loop. d_w is the block's fp16 scale, d_x the bf16 activation scale, their product one fp32 multiply.
+ * w: canonical block_q4_0 rows (the reference re-lays them at load time, repack_q4_0_transpose_bl; values are unchanged). */
+void orc_mul_mat_q4_0_zyk(int64_t m, int64_t n, int64_t k, const void * w, const float * x, float * y) {
+    const int64_t nb = k / QK;
+    uint8_t * xq = (uint8_t *) malloc((size_t) nb * 36 + 64);
+    for (int64_t c = 0; c < n; ++c) {
+        orc_quantize_row_q8_2_x4(x + c * k, xq, k);
+        for (int64_t r = 0; r < m; ++r) {
+            const blk_q4_0 * wr = (const blk_q4_0 *) ((const uint8_t *) w + (size_t) r * nb * sizeof(blk_q4_0));
+            float acc = 0.0f;
+            for (int64_t i = 0; i < nb; ++i) {
+                uint16_t dbits; int16_t sx; const int8_t * q;
+                if (i < 4 * (nb / 4)) { const uint8_t * g = xq + (i / 4) * 144; const int rr = (int) (i % 4); memcpy(&dbits, g + 2 * rr, 2); memcpy(&sx, g + 8 + 2 * rr, 2); q = (const int8_t *) (g + 16 + 32 * rr); }
+                else { const uint8_t * g = xq + i * 36; memcpy(&dbits, g, 2); memcpy(&sx, g + 2, 2); q = (const int8_t *) (g + 4); }
+                int isum = -8 * (int) sx;
+                for (int j = 0; j < 16; ++j) isum += (wr[i].qs[j] & 0x0f) * q[j] + (wr[i].qs[j] >> 4) * q[j + 16];
+                const float scale = orc_fp16_to_fp32(wr[i].d) * bf16_bits_to_fp32(dbits);
+                acc = fmaf(scale, (float) isum, acc);
+            }
+            y[c * m + r] = acc;
+        }
+    }
+    free(xq);
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* dot products: integer-exact inside a block, fp32 across blocks in the order of the          */
 /* reference's generic kernels (ggml-cpu/quants.c:115-150 q4_0, 305-335 q8_0, 550-625 q4_K,     */

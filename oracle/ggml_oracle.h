@@ -59,6 +59,12 @@ int  orc_cpu_repack_q4_K_8x8(int64_t m, int64_t k, const void * canonical, void 
 int  orc_cpu_repack_q4_0_zyk(int64_t m, int64_t k, const void * canonical, void * out);
 /* fork activation format block_q8_2_x4 (repack.h:88-101, repack.cpp:2324-2462) */
 void orc_quantize_row_q8_2_x4(const float * x, void * y, int64_t k);
+/* CPU GEMM activation format block_q8_Kx4: 4 rows x k f32 (row stride k) -> k / 256 blocks of 1168 bytes
+ * (repack.h:55-61, ggml_quantize_mat_q8_K_4x8_generic repack.cpp:180-229) */
+void orc_quantize_mat_q8_K_4x8(const float * x, void * y, int64_t k);
+/* the fork's ZYK Q4_0 matmul end to end: q8_2_x4 activations, unsigned nibbles with the -8 * s bias, fma per block in block
+ * order (arch/x86/repack.cpp:186-243, 460-508); w canonical block_q4_0 rows, x f32 [n][k], y f32 [n][m] */
+void orc_mul_mat_q4_0_zyk(int64_t m, int64_t n, int64_t k, const void * w, const float * x, float * y);
 
 #ifdef __cplusplus
 }

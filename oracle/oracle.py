@@ -107,6 +107,23 @@ class Oracle:
             self.lib.orc_quantize_row_q8_2_x4(_ptr(x[r]), _ptr(out[r]), k)
         return out
 
+    def quantize_mat_q8_K_4x8(self, x: np.ndarray) -> np.ndarray:
+        """x: f32 [4, k] -> block_q8_Kx4 bytes uint8 [k / 256 * 1168]"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        assert x.shape[0] == 4 and x.shape[1] % 256 == 0
+        out = np.zeros(x.shape[1] // 256 * 1168, np.uint8)
+        self.lib.orc_quantize_mat_q8_K_4x8(_ptr(x), _ptr(out), C.c_int64(x.shape[1]))
+        return out
+
+    def mul_mat_q4_0_zyk(self, w: np.ndarray, x: np.ndarray) -> np.ndarray:
+        """the fork's ZYK Q4_0 path: w canonical q4_0 bytes [m, k / 32 * 18], x f32 [n, k] -> f32 [n, m]"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        n, k = x.shape
+        w = np.ascontiguousarray(w, dtype=np.uint8).reshape(-1, k // 32 * 18)
+        y = np.empty((n, w.shape[0]), np.float32)
+        self.lib.orc_mul_mat_q4_0_zyk(C.c_int64(w.shape[0]), C.c_int64(n), C.c_int64(k), _ptr(w), _ptr(x), _ptr(y))
+        return y
+
     def vec_dot(self, t, k, w_row: np.ndarray, xq_row: np.ndarray) -> float:
         return float(self.lib.orc_vec_dot(t, k, _ptr(w_row), _ptr(xq_row)))
 
@@ -228,6 +245,17 @@ class Ref:
 
     def row_size(self, t, k):
         return int(self.lib.ref_row_size(t, k))
+
+    def quantize_mat_q8_K_4x8(self, x: np.ndarray, generic: bool = False) -> np.ndarray:
+        """the reference's own ggml_quantize_mat_q8_K_4x8 (SIMD, arch/x86/repack.cpp:774-1000) or _generic (repack.cpp:180-229),
+        called directly in its libggml-cpu.so"""
+        cpu = C.CDLL(str(ref_dir(self.variant) / "libggml-cpu.so"))
+        fn = cpu.ggml_quantize_mat_q8_K_4x8_generic if generic else cpu.ggml_quantize_mat_q8_K_4x8
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        out = np.zeros(x.shape[1] // 256 * 1168, np.uint8)
+        fn(_ptr(x), _ptr(out), x.shape[1])
+        return out
 
     def quantize_weights(self, t, w: np.ndarray) -> np.ndarray:
         """f32 [m, k] -> canonical quantised bytes uint8 [m, row_size] (ggml_quantize_chunk)."""

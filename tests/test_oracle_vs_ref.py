@@ -96,3 +96,44 @@ def test_fork_repack_kernels_agree_with_generic_path(ref, t):
     plain = ref.mul_mat(t, w, x, n_threads=4)
     repacked = ref.mul_mat(t, w, x, n_threads=4, repack=True)
     assert nmse(repacked, plain) < 5e-4   # test-backend-ops' MUL_MAT tolerance (tests/test-backend-ops.cpp:3716-3718)
+
+
+# ---- the fork's activation formats of the repack path -----------------------------------------------
+def test_q8_Kx4_interleave_bit_exact(orc, ref):
+    """block_q8_Kx4 (four rows quantised at once, 8-byte runs interleaved; repack.h:55-61): the restatement is bit for bit what the CPU
+    backend runs on x86, ggml_quantize_mat_q8_K_4x8 (arch/x86/repack.cpp:774-1000, exported by the reference's libggml-cpu). The scalar
+    ggml_quantize_mat_q8_K_4x8_generic (repack.cpp:180-229) computes nearest_int(x * iscale) in one expression, which this build of the
+    reference contracts into an fma: it differs from the SIMD variant (and from us) by one unit on a handful of exact ties."""
+    for seed, k in ((12, 256), (13, 2048), (14, 4096)):
+        x = _acts(np.random.default_rng(seed), 4, k)
+        mine = orc.quantize_mat_q8_K_4x8(x)
+        assert np.array_equal(mine, ref.quantize_mat_q8_K_4x8(x, generic=False))
+        gen = ref.quantize_mat_q8_K_4x8(x, generic=True).reshape(-1, 1168)
+        mine = mine.reshape(-1, 1168)
+        assert np.array_equal(gen[:, :16], mine[:, :16])                       # d
+        dq = gen[:, 16:16 + 1024].view(np.int8).astype(np.int32) - mine[:, 16:16 + 1024].view(np.int8).astype(np.int32)
+        assert np.abs(dq).max() <= 1 and np.count_nonzero(dq) <= 1e-3 * dq.size
+        # layout: row r, element 8 g + e of a block sits at qs[32 g + 8 r + e]
+        q = mine[0, 16:16 + 1024].view(np.int8).reshape(32, 4, 8)
+        rows = orc.quantize(Q8_K, x, Q8_X86).reshape(4, k // 256, 292)
+        for r in range(4):
+            qs_row = rows[r, 0, 4:260].view(np.int8)
+            if np.abs(qs_row.astype(np.int32)).max() < 127:                    # (the row quantiser clamps to 127, the 4x8 one does not)
+                assert np.array_equal(q[:, r, :].reshape(-1), qs_row)
+
+
+def test_zyk_q4_0_pipeline_bit_exact_and_q8_2_pinned(orc, ref):
+    """The fork's ZYK Q4_0 CPU path (q8_2_x4 activations with a bf16 scale, unsigned nibbles with the -8 * sum bias, one fma per block):
+    quantize_row_q8_2_x4 is a static function of the reference, so its restatement is pinned through the matmul that consumes it --
+    bit for bit against the reference's CPU_REPACK buffer path, which differs measurably from the generic Q8_0 path."""
+    rng = np.random.default_rng(77)
+    m, k = 256, 1024
+    w = random_blocks(Q4_0, m, k, rng)
+    for n in (1, 3):
+        x = _acts(rng, 4, k)[:n] if n <= 4 else None
+        got_ref = ref.mul_mat(Q4_0, w, x, n_threads=1, repack=True)
+        mine = orc.mul_mat_q4_0_zyk(w, x)
+        assert np.array_equal(mine.view(np.uint32), got_ref.view(np.uint32)), float(np.abs(mine - got_ref).max())
+        generic = ref.mul_mat(Q4_0, w, x, n_threads=1, repack=False)
+        assert not np.array_equal(generic, got_ref)          # bf16 activation scales: a different function from the Q8_0 path
+        assert nmse(generic, got_ref) < 1e-3
