@@ -36,6 +36,7 @@ extern "C" {
 /* ggml_type ids this path understands (ggml.h:389-430) */
 enum b200_type {
     B200_TYPE_F32 = 0,
+    B200_TYPE_F16 = 1,
     B200_TYPE_Q4_0 = 2,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
@@ -44,6 +45,7 @@ enum b200_type {
     B200_TYPE_Q8_K = 15,
     B200_TYPE_IQ4_XS = 23,
     B200_TYPE_I32 = 26,
+    B200_TYPE_I64 = 27,
 };
 
 /* how a weight matrix is stored in HBM */
@@ -258,6 +260,38 @@ B200_API int b200_row_gather_wait(const b200_row_gather * gather, b200_stream_t 
 B200_API int b200_ipc_export(const void * dev_ptr, void * handle64);
 B200_API int b200_ipc_import(const void * handle64, void ** dev_ptr);
 B200_API int b200_ipc_close(void * dev_ptr);
+
+/* ---- the other ops of a llama-arch graph: what sits between the quantised MUL_MATs of a layer, so that the reference's
+ * scheduler keeps the whole graph on this device. Semantics of the reference CPU backend (ggml/src/ggml-cpu/ops.cpp), restricted to the
+ * variants the plugin claims in supports_op. A tensor is described the way ggml describes it (ggml.h struct ggml_tensor: data, type, ne[4]
+ * elements per dimension, nb[4] strides in BYTES); all pointers are device pointers. */
+typedef struct b200_tensor {
+    void *  data;
+    int32_t type;        /* enum b200_type (= enum ggml_type) */
+    int32_t pad;
+    int64_t ne[4];
+    int64_t nb[4];
+} b200_tensor;
+/* ggml_compute_forward_get_rows: dst f32 [ne00, n...] = rows ids[i] (i32) of src0 (f32 / f16 / any of the five block formats, CANONICAL layout) */
+B200_API int b200_op_get_rows(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst, b200_stream_t stream);
+/* ggml_compute_forward_rms_norm_f32 (ops.cpp:3640-3710): y = x / sqrt(mean(x^2) + eps) per row */
+B200_API int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps, b200_stream_t stream);
+/* ggml_compute_forward_add / _mul, f32, src1 broadcast over src0 (ggml_can_repeat); op: 0 = add, 1 = mul */
+B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream);
+/* ggml_compute_forward_rope_flt (ops.cpp:5655-5790) for mode 0 (normal) and 2 (neox), ext_factor == 0; pos i32 [n_tokens], freq_factors f32 [n_dims / 2] or NULL */
+typedef struct b200_rope_params { int32_t n_dims, mode; float freq_base, freq_scale, ext_factor, attn_factor; } b200_rope_params;
+B200_API int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                          const b200_rope_params * params, b200_stream_t stream);
+/* ggml_compute_forward_set_rows: dst row idx[i] (i64 / i32) = src row i; src f32, dst f32 / f16 (KV cache writes) */
+B200_API int b200_op_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, b200_stream_t stream);
+/* ggml_compute_forward_dup (CPY / CONT / DUP) between f32 and f16, any strides */
+B200_API int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
+/* ggml_compute_forward_soft_max_f32 (ops.cpp:5160-5280): softmax(src * scale + mask) per row; mask f32 / f16 or NULL; max_bias == 0, no sinks */
+B200_API int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b200_tensor * dst, float scale, b200_stream_t stream);
+/* ggml_compute_forward_glu: dst = act(x) * g; glu_op 0 reglu, 1 geglu, 2 swiglu (enum ggml_glu_op); b == NULL: x, g are the halves of a's rows */
+B200_API int b200_op_glu(const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, int glu_op, int swapped, b200_stream_t stream);
+/* ggml_compute_forward_mul_mat for f16 / f32 src0 and f32 src1 (attention over the KV cache: K^T Q and V^T softmax), batched with broadcast */
+B200_API int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream);
 
 /* ---- MUL_MAT without any allocation --------------------------------------------------------------
  * No counterpart in the reference: added for callers that cannot call cudaMalloc

@@ -80,6 +80,12 @@ struct backend_ctx {
     // strides are baked into a chain like into a graph plan (ggml_backend_graph_plan_create, ggml-backend-impl.h:103-110)
     struct cached_chain { std::vector<b200_mul_mat_args> args; std::vector<int32_t> sizes; b200_chain_t chain; };
     std::vector<cached_chain> chains;
+    // whole-graph CUDA graphs (counterpart of GGML_CUDA_USE_GRAPHS, ggml-cuda.cu:2930-3100): a cgraph whose nodes (ops, shapes, strides,
+    // pointers, op_params) equal those of an earlier call is replayed as ONE cudaGraphLaunch; captured the second time a key is seen
+    struct cached_graph { std::vector<uint64_t> key; b200_graph_t exec = nullptr; int seen = 0; bool bad = false; uint64_t stamp = 0; };
+    std::vector<cached_graph> graphs;
+    uint64_t graph_stamp = 0;
+    bool capturing = false;        // a stream capture is open: nothing may allocate or synchronise
 };
 
 bool repack_enabled() {
@@ -363,6 +369,53 @@ bool mul_mat_operands_ok(const ggml_tensor * w, const ggml_tensor * x, const ggm
     return true;
 }
 
+// ---- the other ops of a llama-arch graph (csrc/glue_ops.cu): exactly the variants implemented there ----------------------
+bool glue_on() { static const bool on = [] { const char * e = getenv("GGML_B200_GLUE"); return !(e && e[0] == '0'); }(); return on; }
+bool f32_rows(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float); }
+bool f_any(const ggml_tensor * t) { return t && (t->type == GGML_TYPE_F32 || t->type == GGML_TYPE_F16) && t->nb[0] == ggml_type_size(t->type); }
+bool glue_supports(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    switch (op->op) {
+        case GGML_OP_GET_ROWS:
+            return a && b && b->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 && (a->type == GGML_TYPE_F32 || a->type == GGML_TYPE_F16 || weight_type(a->type)) &&
+                   a->nb[0] == ggml_type_size(a->type);
+        case GGML_OP_RMS_NORM:
+            return f32_rows(a) && f32_rows(op);
+        case GGML_OP_ADD:
+        case GGML_OP_MUL:
+            return a && b && a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ggml_can_repeat(b, a);
+        case GGML_OP_ROPE: {
+            if (!f32_rows(a) || !f32_rows(op) || !b || b->type != GGML_TYPE_I32) return false;
+            const int32_t * p = (const int32_t *) op->op_params;
+            float ext_factor; memcpy(&ext_factor, p + 7, sizeof(float));
+            const int n_dims = p[1], mode = p[2];
+            if ((mode != 0 && mode != GGML_ROPE_TYPE_NEOX) || ext_factor != 0.0f || n_dims <= 0 || n_dims % 2 || n_dims > a->ne[0] || a->ne[0] % 2) return false;
+            const ggml_tensor * ff = op->src[2];
+            return !ff || (ff->type == GGML_TYPE_F32 && ggml_is_contiguous(ff) && ff->ne[0] >= n_dims / 2);
+        }
+        case GGML_OP_SET_ROWS:
+            return a && b && a->type == GGML_TYPE_F32 && (b->type == GGML_TYPE_I64 || b->type == GGML_TYPE_I32) && (op->type == GGML_TYPE_F32 || op->type == GGML_TYPE_F16) &&
+                   op->nb[0] == ggml_type_size(op->type);
+        case GGML_OP_CPY:
+        case GGML_OP_CONT:
+        case GGML_OP_DUP:
+            return a && (a->type == GGML_TYPE_F32 || a->type == GGML_TYPE_F16) && (op->type == GGML_TYPE_F32 || op->type == GGML_TYPE_F16) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_SOFT_MAX: {
+            if (!f32_rows(a) || !f32_rows(op) || !ggml_is_contiguous(op) || op->src[2]) return false;
+            float max_bias; memcpy(&max_bias, (const float *) op->op_params + 1, sizeof(float));
+            if (max_bias != 0.0f) return false;
+            return !b || (f_any(b) && b->ne[0] >= a->ne[0] && b->ne[1] >= a->ne[1]);
+        }
+        case GGML_OP_GLU: {
+            const int glu = ggml_get_op_params_i32(op, 0);
+            if (glu != GGML_GLU_OP_REGLU && glu != GGML_GLU_OP_GEGLU && glu != GGML_GLU_OP_SWIGLU) return false;
+            return f32_rows(a) && f32_rows(op) && (!b || (f32_rows(b) && ggml_are_same_shape(a, b)));
+        }
+        default:
+            return false;
+    }
+}
+
 bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
     switch (op->op) {
         case GGML_OP_NONE:
@@ -373,7 +426,13 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
             return true;
         case GGML_OP_MUL_MAT: {
             const ggml_tensor * w = op->src[0], * x = op->src[1];
-            if (!w || !x || !mul_mat_operands_ok(w, x, op)) return false;
+            if (!w || !x) return false;
+            if (glue_on() && (w->type == GGML_TYPE_F16 || w->type == GGML_TYPE_F32)) {
+                // attention over the KV cache: f16 / f32 rows x f32 rows (b200_op_mul_mat_f)
+                return x->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && w->nb[0] == ggml_type_size(w->type) && x->nb[0] == sizeof(float) &&
+                       op->nb[0] == sizeof(float) && w->ne[0] == x->ne[0] && x->ne[2] % w->ne[2] == 0 && x->ne[3] % w->ne[3] == 0 && op->ne[2] * op->ne[3] <= 65535;
+            }
+            if (!mul_mat_operands_ok(w, x, op)) return false;
             return x->ne[2] % w->ne[2] == 0 && x->ne[3] % w->ne[3] == 0;   // broadcast (ggml.c:3168-3174)
         }
         case GGML_OP_MUL_MAT_ID: {
@@ -385,7 +444,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
             return b->ne[1] == 1 || b->ne[1] == ids->ne[0];
         }
         default:
-            return false;
+            return glue_on() && glue_supports(op);
     }
 }
 
@@ -400,6 +459,7 @@ void backend_free(ggml_backend_t backend) {
     if (bc->stream) { b200_stream_synchronize(bc->stream); b200_stream_destroy(bc->stream); }
     if (bc->workspace) b200_free(bc->device, bc->workspace);
     for (auto & c : bc->chains) b200_chain_destroy(c.chain);
+    for (auto & g : bc->graphs) if (g.exec) b200_graph_destroy(g.exec);
     delete bc;
     delete backend;
 }
@@ -411,10 +471,13 @@ void backend_synchronize(ggml_backend_t backend) {
 
 bool backend_reserve(backend_ctx * bc, size_t need) {
     if (need <= bc->workspace_size) return true;
+    if (bc->capturing) return false;       // (the eager pass before the capture sized the workspace; a larger request fails the capture, not the graph)
     b200_stream_synchronize(bc->stream);   // kernels in flight may still read the old workspace
     if (bc->workspace) b200_free(bc->device, bc->workspace);
     for (auto & c : bc->chains) b200_chain_destroy(c.chain);     // (chains do not use the workspace; dropped with it to keep one rule)
     bc->chains.clear();
+    for (auto & g : bc->graphs) if (g.exec) b200_graph_destroy(g.exec);   // captured launches carry the old workspace pointer
+    bc->graphs.clear();
     need = (need + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
     bc->workspace = b200_malloc(bc->device, need);
     bc->workspace_size = bc->workspace ? need : 0;
@@ -502,6 +565,7 @@ bool skipped(const ggml_tensor * t) { return (t->flags & GGML_TENSOR_FLAG_COMPUT
 bool plain_mul_mat(const ggml_tensor * t) {
     if (t->op != GGML_OP_MUL_MAT || skipped(t)) return false;
     const ggml_tensor * w = t->src[0], * x = t->src[1];
+    if (!weight_type(w->type)) return false;
     return x->ne[2] == 1 && x->ne[3] == 1 && w->ne[2] == 1 && w->ne[3] == 1 && x->nb[0] == sizeof(float) && t->nb[0] == sizeof(float);
 }
 b200_mul_mat_args plain_args(const ggml_tensor * dst) {
@@ -586,9 +650,133 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     return last;
 }
 
+b200_tensor bt(const ggml_tensor * t) {
+    b200_tensor r = {};
+    r.data = t->data; r.type = (int32_t) t->type;
+    for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = (int64_t) t->nb[i]; }
+    return r;
+}
+// a tensor another op reads byte for byte must hold the canonical ggml bytes (GET_ROWS on a repacked token_embd)
+void ensure_canonical(const ggml_tensor * t) {
+    buffer_ctx * bc = owner_ctx(t);
+    if (!bc) return;
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    planes_demote_locked(bc, base->data);
+}
+enum ggml_status compute_glue(backend_ctx * bc, const ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0], * b = node->src[1];
+    const b200_tensor d = bt(node);
+    int rc = 0;
+    switch (node->op) {
+        case GGML_OP_GET_ROWS: { ensure_canonical(a); const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_get_rows(&ta, &tb, &d, bc->stream); } break;
+        case GGML_OP_RMS_NORM: { float eps; memcpy(&eps, node->op_params, sizeof(float)); const b200_tensor ta = bt(a); rc = b200_op_rms_norm(&ta, &d, eps, bc->stream); } break;
+        case GGML_OP_ADD:
+        case GGML_OP_MUL: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_binary(node->op == GGML_OP_ADD ? 0 : 1, &ta, &tb, &d, bc->stream); } break;
+        case GGML_OP_ROPE: {
+            const int32_t * p = (const int32_t *) node->op_params;
+            b200_rope_params rp = {};
+            rp.n_dims = p[1]; rp.mode = p[2];
+            memcpy(&rp.freq_base, p + 5, sizeof(float)); memcpy(&rp.freq_scale, p + 6, sizeof(float));
+            memcpy(&rp.ext_factor, p + 7, sizeof(float)); memcpy(&rp.attn_factor, p + 8, sizeof(float));
+            const b200_tensor ta = bt(a), tb = bt(b);
+            b200_tensor tf = {}; if (node->src[2]) tf = bt(node->src[2]);
+            rc = b200_op_rope(&ta, &tb, node->src[2] ? &tf : nullptr, &d, &rp, bc->stream);
+        } break;
+        case GGML_OP_SET_ROWS: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_set_rows(&ta, &tb, &d, bc->stream); } break;
+        case GGML_OP_CPY:
+        case GGML_OP_CONT:
+        case GGML_OP_DUP: { const b200_tensor ta = bt(a); rc = b200_op_cpy(&ta, &d, bc->stream); } break;
+        case GGML_OP_SOFT_MAX: {
+            float scale; memcpy(&scale, node->op_params, sizeof(float));
+            const b200_tensor ta = bt(a); b200_tensor tm = {}; if (b) tm = bt(b);
+            rc = b200_op_soft_max(&ta, b ? &tm : nullptr, &d, scale, bc->stream);
+        } break;
+        case GGML_OP_GLU: {
+            const b200_tensor ta = bt(a); b200_tensor tb = {}; if (b) tb = bt(b);
+            rc = b200_op_glu(&ta, b ? &tb : nullptr, &d, ggml_get_op_params_i32(node, 0), ggml_get_op_params_i32(node, 1), bc->stream);
+        } break;
+        case GGML_OP_MUL_MAT: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_mul_mat_f(&ta, &tb, &d, bc->stream); } break;
+        default:
+            GGML_LOG_ERROR("ggml-b200: op %s (%s) is not supported by this backend\n", ggml_op_name(node->op), node->name);
+            return GGML_STATUS_FAILED;
+    }
+    if (rc != 0) {
+        GGML_LOG_ERROR("ggml-b200: %s (%s) failed: %s\n", ggml_op_name(node->op), node->name, b200_last_error());
+        return GGML_STATUS_FAILED;
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph);
+
+// one 64-bit word per node: everything a captured launch sequence depends on
+uint64_t mix64(uint64_t h, uint64_t v) { h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2); return h * 0xff51afd7ed558ccdull; }
+uint64_t tensor_sig(uint64_t h, const ggml_tensor * t) {
+    if (!t) return mix64(h, 0x1234);
+    h = mix64(h, (uint64_t) (uintptr_t) t->data); h = mix64(h, (uint64_t) t->type);
+    for (int i = 0; i < 4; ++i) { h = mix64(h, (uint64_t) t->ne[i]); h = mix64(h, (uint64_t) t->nb[i]); }
+    return h;
+}
+void graph_key(const ggml_cgraph * g, std::vector<uint64_t> & key) {
+    key.clear();
+    key.reserve((size_t) g->n_nodes);
+    for (int i = 0; i < g->n_nodes; ++i) {
+        const ggml_tensor * n = g->nodes[i];
+        uint64_t h = mix64((uint64_t) n->op, (uint64_t) n->flags);
+        h = tensor_sig(h, n);
+        for (int j = 0; j < GGML_MAX_SRC; ++j) if (n->src[j]) h = tensor_sig(mix64(h, (uint64_t) j), n->src[j]);
+        const uint64_t * p = (const uint64_t *) n->op_params;
+        for (size_t j = 0; j < sizeof(n->op_params) / 8; ++j) h = mix64(h, p[j]);
+        key.push_back(h);
+    }
+}
+
 enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     backend_ctx * bc = (backend_ctx *) backend->context;
     b200_set_device(bc->device);
+    static const bool graphs_on = env_on("GGML_B200_GRAPHS");
+    if (!graphs_on || cgraph->n_nodes < 8) return graph_issue(bc, cgraph);
+    std::vector<uint64_t> key;
+    graph_key(cgraph, key);
+    backend_ctx::cached_graph * hit = nullptr;
+    for (auto & c : bc->graphs) if (c.key == key) { hit = &c; break; }
+    if (!hit) {
+        if (bc->graphs.size() >= 8) {                              // drop the least recently used entry
+            size_t lru = 0;
+            for (size_t i = 1; i < bc->graphs.size(); ++i) if (bc->graphs[i].stamp < bc->graphs[lru].stamp) lru = i;
+            if (bc->graphs[lru].exec) { b200_stream_synchronize(bc->stream); b200_graph_destroy(bc->graphs[lru].exec); }
+            bc->graphs.erase(bc->graphs.begin() + (long) lru);
+        }
+        bc->graphs.emplace_back();
+        hit = &bc->graphs.back();
+        hit->key = std::move(key);
+    }
+    hit->stamp = ++bc->graph_stamp;
+    if (hit->exec) {
+        if (b200_graph_launch(hit->exec, bc->stream) == 0) return GGML_STATUS_SUCCESS;
+        GGML_LOG_WARN("ggml-b200: graph replay failed (%s), running the nodes one by one\n", b200_last_error());
+        b200_graph_destroy(hit->exec); hit->exec = nullptr; hit->bad = true;
+    }
+    if (hit->bad || ++hit->seen < 2) return graph_issue(bc, cgraph);      // first sight: eager (allocations, chains, layout changes happen here)
+    // second sight: capture the very same launch sequence
+    if (b200_graph_begin(bc->stream) != 0) { hit->bad = true; return graph_issue(bc, cgraph); }
+    bc->capturing = true;
+    const enum ggml_status st = graph_issue(bc, cgraph);
+    bc->capturing = false;
+    b200_graph_t exec = b200_graph_end(bc->stream);
+    if (st != GGML_STATUS_SUCCESS || !exec) {
+        if (exec) b200_graph_destroy(exec);
+        hit->bad = true;
+        GGML_LOG_WARN("ggml-b200: graph capture failed (%s), this graph stays on per-node launches\n", b200_last_error());
+        return graph_issue(bc, cgraph);
+    }
+    hit->exec = exec;
+    if (b200_graph_launch(exec, bc->stream) != 0) { hit->bad = true; b200_graph_destroy(exec); hit->exec = nullptr; return graph_issue(bc, cgraph); }
+    return GGML_STATUS_SUCCESS;
+}
+
+enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
         if (ggml_is_empty(node) || skipped(node)) continue;
@@ -605,11 +793,9 @@ enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgr
             case GGML_OP_PERMUTE:
             case GGML_OP_TRANSPOSE:
                 break;
-            case GGML_OP_MUL_MAT:    st = compute_mul_mat(bc, node); break;
+            case GGML_OP_MUL_MAT:    st = weight_type(node->src[0]->type) ? compute_mul_mat(bc, node) : compute_glue(bc, node); break;
             case GGML_OP_MUL_MAT_ID: st = compute_mul_mat_id(bc, node); break;
-            default:
-                GGML_LOG_ERROR("ggml-b200: op %s (%s) is not supported by this backend\n", ggml_op_name(node->op), node->name);
-                return GGML_STATUS_FAILED;
+            default:                 st = compute_glue(bc, node); break;
         }
         if (st != GGML_STATUS_SUCCESS) return st;
     }

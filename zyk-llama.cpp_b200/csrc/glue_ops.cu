@@ -1,0 +1,417 @@
+// glue_ops.cu -- the non-matmul ops of a llama-arch graph, so that llama.cpp / llama-bench keep a whole
+// layer on the device between the quantised MUL_MATs instead of bouncing to the CPU backend after every one of them:
+// GET_ROWS, RMS_NORM, ADD / MUL (broadcast), ROPE (normal / neox), SET_ROWS (KV cache writes), CPY / CONT, SOFT_MAX (scale + mask),
+// GLU (swiglu / geglu / reglu) and the f16 x f32 MUL_MAT of attention over the KV cache.
+//
+// Semantics follow the reference CPU backend, op by op (ggml/src/ggml-cpu/ops.cpp; cited at each entry point); the plugin claims
+// exactly the variants implemented here (supports_op) and the reference's test-backend-ops compares them with its CPU backend.
+// All kernels are HBM / L2 bound elementwise or row kernels: one thread per element or one CTA per row, no tensor cores (the
+// attention matmuls of a 512-token ubatch are the exception that would merit them).
+#include "common.cuh"
+
+#include <math.h>
+
+namespace {
+
+struct T4 { const char * data; long long ne[4], nb[4]; int type; };
+struct T4w { char * data; long long ne[4], nb[4]; int type; };
+
+T4 t4(const b200_tensor * t) { T4 r; r.data = (const char *) t->data; r.type = t->type; for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; } return r; }
+T4w t4w(const b200_tensor * t) { T4w r; r.data = (char *) t->data; r.type = t->type; for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; } return r; }
+long long nelem(const b200_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+bool contiguous_f(const b200_tensor * t, long long esz) {
+    return t->nb[0] == esz && t->nb[1] == t->nb[0] * t->ne[0] && t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
+}
+unsigned blocks_for(long long n, int per) { const long long b = (n + per - 1) / per; return (unsigned) (b < 1 ? 1 : b > 0x7fffffffll ? 0x7fffffffll : b); }
+
+// ---- dequantise ONE element of a canonical ggml row (dequantize_row_*, ggml-quants.c:307-325, 401-415, 1352-1375, 1762-1792, 2530-2551) ----
+__device__ __constant__ signed char kvalues_iq4nl_d[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+
+__device__ __forceinline__ float deq_one(int type, const uint8_t * row, long long e) {
+    switch (type) {
+        case B200_TYPE_F32: return reinterpret_cast<const float *>(row)[e];
+        case B200_TYPE_F16: return __half2float(reinterpret_cast<const __half *>(row)[e]);
+        case B200_TYPE_Q4_0: {
+            const uint8_t * b = row + (e >> 5) * 18; const int j = (int) (e & 31);
+            const float d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b));
+            const int q = j < 16 ? (b[2 + j] & 0x0f) : (b[2 + j - 16] >> 4);
+            return d * (float) (q - 8);
+        }
+        case B200_TYPE_Q8_0: {
+            const uint8_t * b = row + (e >> 5) * 34;
+            return half_bits_to_float(*reinterpret_cast<const uint16_t *>(b)) * (float) (int8_t) b[2 + (e & 31)];
+        }
+        case B200_TYPE_Q4_K: {
+            const uint8_t * b = row + (e >> 8) * 144; const int r = (int) (e & 255);
+            const int g = r >> 6, hi = (r >> 5) & 1, l = r & 31, is = 2 * g + hi;
+            const uint8_t * sc = b + 4;
+            int s, m;
+            if (is < 4) { s = sc[is] & 63; m = sc[is + 4] & 63; }
+            else { s = (sc[is + 4] & 0x0f) | ((sc[is - 4] >> 6) << 4); m = (sc[is + 4] >> 4) | ((sc[is] >> 6) << 4); }
+            const float d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b)), dmin = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b + 2));
+            const uint8_t qb = b[16 + 32 * g + l];
+            return d * (float) s * (float) (hi ? (qb >> 4) : (qb & 0x0f)) - dmin * (float) m;
+        }
+        case B200_TYPE_Q6_K: {
+            const uint8_t * b = row + (e >> 8) * 210; const int r = (int) (e & 255);
+            const int n = r >> 7, rr = r & 127, quarter = rr >> 5, l = rr & 31;
+            const uint8_t qlb = b[64 * n + l + ((quarter & 1) ? 32 : 0)];
+            const int nib = quarter < 2 ? (qlb & 0x0f) : (qlb >> 4);
+            const int h = (b[128 + 32 * n + l] >> (2 * quarter)) & 3;
+            const int scv = (int) (int8_t) b[192 + 8 * n + (l >> 4) + 2 * quarter];
+            const float d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b + 208));
+            return d * (float) scv * (float) ((nib | (h << 4)) - 32);
+        }
+        case B200_TYPE_IQ4_XS: {
+            const uint8_t * b = row + (e >> 8) * 136; const int r = (int) (e & 255);
+            const int ib = r >> 5, j = r & 31;
+            const float d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b));
+            const unsigned sh = *reinterpret_cast<const uint16_t *>(b + 2);
+            const int ls = (int) (((b[4 + (ib >> 1)] >> (4 * (ib & 1))) & 0x0f) | (((sh >> (2 * ib)) & 3u) << 4));
+            const uint8_t qb = b[8 + 16 * ib + (j & 15)];
+            return d * (float) (ls - 32) * (float) kvalues_iq4nl_d[j < 16 ? (qb & 0x0f) : (qb >> 4)];
+        }
+    }
+    return 0.0f;
+}
+
+// ---- GET_ROWS (ggml_compute_forward_get_rows, ggml-cpu/ops.cpp): dst[:, i10, i11, i12] = row src1[i10, i11, i12] of matrix (i11, i12) of src0 ----
+__global__ void __launch_bounds__(256) get_rows_kernel(const T4 a, const T4 ids, const T4w d) {
+    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long e = i % d.ne[0], i10 = (i / d.ne[0]) % d.ne[1], i11 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], i12 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
+        const int r = *reinterpret_cast<const int *>(ids.data + i10 * ids.nb[0] + i11 * ids.nb[1] + i12 * ids.nb[2]);
+        const uint8_t * row = reinterpret_cast<const uint8_t *>(a.data + (long long) r * a.nb[1] + i11 * a.nb[2] + i12 * a.nb[3]);
+        *reinterpret_cast<float *>(d.data + e * d.nb[0] + i10 * d.nb[1] + i11 * d.nb[2] + i12 * d.nb[3]) = deq_one(a.type, row, e);
+    }
+}
+
+// ---- RMS_NORM (ggml_compute_forward_rms_norm_f32): y = x / sqrt(mean(x^2) + eps), one CTA per row ----
+__global__ void __launch_bounds__(256) rms_norm_kernel(const T4 a, const T4w d, float eps) {
+    const long long row = blockIdx.x;
+    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
+    const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    float * y = reinterpret_cast<float *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    float s = 0.0f;
+    for (long long i = threadIdx.x; i < a.ne[0]; i += 256) { const float v = x[i]; s += v * v; }
+    __shared__ float red[8];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i];
+    const float scale = 1.0f / sqrtf(s / (float) a.ne[0] + eps);
+    for (long long i = threadIdx.x; i < a.ne[0]; i += 256) y[i] = x[i] * scale;
+}
+
+// ---- ADD / MUL with ggml broadcasting of src1 (ggml_compute_forward_add / _mul: src1 dims divide src0 dims) ----
+template <int OP>
+__global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, const T4w d) {
+    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long i0 = i % d.ne[0], i1 = (i / d.ne[0]) % d.ne[1], i2 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], i3 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
+        const float x = *reinterpret_cast<const float *>(a.data + i0 * a.nb[0] + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+        const float y = *reinterpret_cast<const float *>(b.data + (i0 % b.ne[0]) * b.nb[0] + (i1 % b.ne[1]) * b.nb[1] + (i2 % b.ne[2]) * b.nb[2] + (i3 % b.ne[3]) * b.nb[3]);
+        *reinterpret_cast<float *>(d.data + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = OP == 0 ? x + y : x * y;
+    }
+}
+
+// ---- ROPE, modes normal (0) and neox (2), ext_factor == 0 (ggml_compute_forward_rope_flt + ggml_rope_cache_init + rope_yarn, ops.cpp:5524-5790) ----
+struct RopeP { int n_dims, mode; float freq_base, freq_scale, attn_factor; };
+__global__ void __launch_bounds__(256) rope_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p) {
+    const long long half = a.ne[0] / 2, total = half * a.ne[1] * a.ne[2] * a.ne[3];
+    const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long ip = i % half, i1 = (i / half) % a.ne[1], i2 = (i / (half * a.ne[1])) % a.ne[2], i3 = i / (half * a.ne[1] * a.ne[2]);
+        const char * src = a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3];
+        char * dst = d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3];
+        if (2 * ip >= p.n_dims) {                // the dimensions past n_dims are copied
+            const long long e = 2 * ip;
+            reinterpret_cast<float *>(dst)[e] = reinterpret_cast<const float *>(src)[e];
+            reinterpret_cast<float *>(dst)[e + 1] = reinterpret_cast<const float *>(src)[e + 1];
+            continue;
+        }
+        const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
+        float sn, cs;
+        sincosf(theta, &sn, &cs);
+        sn *= p.attn_factor; cs *= p.attn_factor;
+        const long long e0 = p.mode == 2 ? ip : 2 * ip, e1 = p.mode == 2 ? ip + p.n_dims / 2 : 2 * ip + 1;
+        const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
+        reinterpret_cast<float *>(dst)[e0] = x0 * cs - x1 * sn;
+        reinterpret_cast<float *>(dst)[e1] = x0 * sn + x1 * cs;
+    }
+}
+
+__device__ __forceinline__ void store_as(char * p, int type, float v) {
+    if (type == B200_TYPE_F16) *reinterpret_cast<__half *>(p) = __float2half_rn(v); else *reinterpret_cast<float *>(p) = v;
+}
+__device__ __forceinline__ float load_as(const char * p, int type) {
+    return type == B200_TYPE_F16 ? __half2float(*reinterpret_cast<const __half *>(p)) : *reinterpret_cast<const float *>(p);
+}
+
+// ---- SET_ROWS (ggml_compute_forward_set_rows_f32): dst row src1[i01, i02 % ne11, i03 % ne12] of matrix (i02, i03) = src0 row (i01, i02, i03) ----
+__global__ void __launch_bounds__(256) set_rows_kernel(const T4 a, const T4 idx, const T4w d) {
+    const long long total = a.ne[0] * a.ne[1] * a.ne[2] * a.ne[3];
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long i0 = i % a.ne[0], i1 = (i / a.ne[0]) % a.ne[1], i2 = (i / (a.ne[0] * a.ne[1])) % a.ne[2], i3 = i / (a.ne[0] * a.ne[1] * a.ne[2]);
+        const char * ip = idx.data + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2];
+        const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
+        const float v = *reinterpret_cast<const float *>(a.data + i0 * a.nb[0] + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+        store_as(d.data + i0 * d.nb[0] + r * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], d.type, v);
+    }
+}
+
+// ---- CPY / CONT / DUP between f32 and f16 (ggml_compute_forward_dup): element i of src (row-major over its shape) -> element i of dst ----
+__global__ void __launch_bounds__(256) cpy_kernel(const T4 a, const T4w d) {
+    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long s0 = i % a.ne[0], s1 = (i / a.ne[0]) % a.ne[1], s2 = (i / (a.ne[0] * a.ne[1])) % a.ne[2], s3 = i / (a.ne[0] * a.ne[1] * a.ne[2]);
+        const long long d0 = i % d.ne[0], d1 = (i / d.ne[0]) % d.ne[1], d2 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], d3 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
+        store_as(d.data + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3], d.type,
+                 load_as(a.data + s0 * a.nb[0] + s1 * a.nb[1] + s2 * a.nb[2] + s3 * a.nb[3], a.type));
+    }
+}
+
+// ---- SOFT_MAX with scale and an optional f32 / f16 mask, max_bias == 0, no sinks (ggml_compute_forward_soft_max_f32, ops.cpp:5160-5280) ----
+__global__ void __launch_bounds__(256) soft_max_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale) {
+    const long long row = blockIdx.x;
+    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
+    const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    float * y = reinterpret_cast<float *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const char * mp = has_mask ? m.data + i1 * m.nb[1] + (i2 % m.ne[2]) * m.nb[2] + (i3 % m.ne[3]) * m.nb[3] : nullptr;
+    const long long n = a.ne[0];
+    __shared__ float red[8];
+    auto val = [&](long long i) { float v = x[i] * scale; if (mp) v += m.type == B200_TYPE_F16 ? __half2float(reinterpret_cast<const __half *>(mp)[i]) : reinterpret_cast<const float *>(mp)[i]; return v; };
+    float mx = -INFINITY;
+    for (long long i = threadIdx.x; i < n; i += 256) mx = fmaxf(mx, val(i));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+    __syncthreads();
+    float s = 0.0f;
+    for (long long i = threadIdx.x; i < n; i += 256) { const float e = expf(val(i) - mx); y[i] = e; s += e; }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i];
+    const float inv = 1.0f / s;
+    for (long long i = threadIdx.x; i < n; i += 256) y[i] *= inv;
+}
+
+// ---- GLU: reglu 0, geglu 1, swiglu 2 (enum ggml_glu_op, ggml.h; ggml_compute_forward_glu, ops.cpp): dst = act(x) * g ----
+__device__ __forceinline__ float glu_act(int op, float x) {
+    if (op == 0) return x > 0.0f ? x : 0.0f;
+    if (op == 1) return 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * (1.0f + 0.044715f * x * x)));
+    return x / (1.0f + expf(-x));
+}
+__global__ void __launch_bounds__(256) glu_kernel(const T4 a, const T4 b, int split, const T4w d, int op, int swapped) {
+    const long long nc = d.ne[0], total = nc * d.ne[1] * d.ne[2] * d.ne[3];
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
+        const long long i0 = i % nc, i1 = (i / nc) % d.ne[1], i2 = (i / (nc * d.ne[1])) % d.ne[2], i3 = i / (nc * d.ne[1] * d.ne[2]);
+        const float * ar = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+        float x, g;
+        if (split) {
+            const float * br = reinterpret_cast<const float *>(b.data + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]);
+            x = ar[i0]; g = br[i0];
+        } else {
+            x = ar[swapped ? i0 + nc : i0]; g = ar[swapped ? i0 : i0 + nc];
+        }
+        *reinterpret_cast<float *>(d.data + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = glu_act(op, x) * g;
+    }
+}
+
+// ---- MUL_MAT with f16 / f32 src0 rows and f32 src1 (attention over the KV cache): dst[m, n, i2, i3] = sum_k a[k, m, i2 / r2, i3 / r3] b[k, n, i2, i3] ----
+// few activation rows: one warp per (src0 row, batch), every lane strides over k, all n columns at once (n <= 8)
+template <int NCOLS, bool AH>
+__global__ void __launch_bounds__(128) mm_rows_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long) blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (row >= a.ne[1]) return;
+    const long long i2 = blockIdx.y % d.ne[2], i3 = blockIdx.y / d.ne[2];
+    const char * ar = a.data + row * a.nb[1] + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3];
+    const char * bb = b.data + i2 * b.nb[2] + i3 * b.nb[3];
+    float acc[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+    for (long long k = lane; k < a.ne[0]; k += 32) {
+        const float w = AH ? __half2float(reinterpret_cast<const __half *>(ar)[k]) : reinterpret_cast<const float *>(ar)[k];
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) acc[c] += w * reinterpret_cast<const float *>(bb + c * b.nb[1])[k];
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const float v = warp_sum(acc[c]);
+        if (lane == 0) *reinterpret_cast<float *>(d.data + row * d.nb[0] + c * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = v;
+    }
+}
+// many activation rows: 64 x 64 output tile per CTA of 256 threads (4 x 4 per thread), k in steps of 16 through shared memory
+template <bool AH>
+__global__ void __launch_bounds__(256) mm_tile_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    __shared__ float As[16][64 + 4], Bs[16][64 + 4];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const long long m0 = (long long) blockIdx.x * 64, n0 = (long long) blockIdx.y * 64;
+    const long long i2 = blockIdx.z % d.ne[2], i3 = blockIdx.z / d.ne[2];
+    const char * ab = a.data + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3];
+    const char * bb = b.data + i2 * b.nb[2] + i3 * b.nb[3];
+    const long long K = a.ne[0], M = a.ne[1], N = b.ne[1];
+    float acc[4][4] = {};
+    for (long long k0 = 0; k0 < K; k0 += 16) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {               // 64 rows x 16 k = 1024 values per operand, 4 per thread
+            const int idx = threadIdx.x + t * 256, r = idx >> 4, kk = idx & 15;
+            const long long k = k0 + kk;
+            float va = 0.0f, vb = 0.0f;
+            if (k < K && m0 + r < M) va = AH ? __half2float(reinterpret_cast<const __half *>(ab + (m0 + r) * a.nb[1])[k]) : reinterpret_cast<const float *>(ab + (m0 + r) * a.nb[1])[k];
+            if (k < K && n0 + r < N) vb = reinterpret_cast<const float *>(bb + (n0 + r) * b.nb[1])[k];
+            As[kk][r] = va; Bs[kk][r] = vb;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            float av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { av[i] = As[kk][tx * 4 + i]; bv[i] = Bs[kk][ty * 4 + i]; }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[j][i] += av[i] * bv[j];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const long long m = m0 + tx * 4 + i, n = n0 + ty * 4 + j;
+            if (m < M && n < N) *reinterpret_cast<float *>(d.data + m * d.nb[0] + n * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = acc[j][i];
+        }
+}
+
+} // namespace
+
+extern "C" {
+
+int b200_op_get_rows(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(src0 && ids && dst && src0->data && ids->data && dst->data, "b200_op_get_rows: null tensor");
+    B200_REQUIRE(ids->type == B200_TYPE_I32 && dst->type == B200_TYPE_F32, "b200_op_get_rows: ids must be i32 and dst f32");
+    B200_REQUIRE(src0->type == B200_TYPE_F32 || src0->type == B200_TYPE_F16 || b200_type_is_weight(src0->type), "b200_op_get_rows: unsupported source type %d", src0->type);
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    B200_CHECK(b200_launch(get_rows_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src0), t4(ids), t4w(dst)));
+    return 0;
+}
+
+int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_rms_norm: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && src->nb[0] == 4 && dst->nb[0] == 4, "b200_op_rms_norm: f32 rows with unit stride only");
+    const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
+    if (rows == 0 || src->ne[0] == 0) return 0;
+    B200_CHECK(b200_launch(rms_norm_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4w(dst), eps));
+    return 0;
+}
+
+int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(a && b && dst && a->data && b->data && dst->data, "b200_op_binary: null tensor");
+    B200_REQUIRE(a->type == B200_TYPE_F32 && b->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32, "b200_op_binary: f32 only");
+    B200_REQUIRE(op == 0 || op == 1, "b200_op_binary: op %d (0 add, 1 mul)", op);
+    for (int i = 0; i < 4; ++i) B200_REQUIRE(b->ne[i] > 0 && dst->ne[i] % b->ne[i] == 0 && a->ne[i] == dst->ne[i], "b200_op_binary: src1 does not broadcast over src0");
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    if (op == 0) B200_CHECK(b200_launch(binary_kernel<0>, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), t4(b), t4w(dst)));
+    else         B200_CHECK(b200_launch(binary_kernel<1>, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), t4(b), t4w(dst)));
+    return 0;
+}
+
+int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst, const b200_rope_params * p, b200_stream_t stream) {
+    B200_REQUIRE(src && pos && dst && p && src->data && pos->data && dst->data, "b200_op_rope: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && pos->type == B200_TYPE_I32 && src->nb[0] == 4 && dst->nb[0] == 4, "b200_op_rope: f32 rows, i32 positions");
+    B200_REQUIRE((p->mode == 0 || p->mode == 2) && p->ext_factor == 0.0f && p->n_dims > 0 && p->n_dims % 2 == 0 && p->n_dims <= src->ne[0] && src->ne[0] % 2 == 0,
+                 "b200_op_rope: mode %d / ext_factor %g / n_dims %d not supported", p->mode, (double) p->ext_factor, p->n_dims);
+    B200_REQUIRE(pos->ne[0] >= src->ne[2], "b200_op_rope: %lld positions for %lld tokens", (long long) pos->ne[0], (long long) src->ne[2]);
+    const long long n = nelem(src) / 2;
+    if (n == 0) return 0;
+    RopeP rp; rp.n_dims = p->n_dims; rp.mode = p->mode; rp.freq_base = p->freq_base; rp.freq_scale = p->freq_scale; rp.attn_factor = p->attn_factor;
+    B200_CHECK(b200_launch(rope_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data,
+                           freq_factors ? (const float *) freq_factors->data : (const float *) nullptr, t4w(dst), rp));
+    return 0;
+}
+
+int b200_op_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(src && idx && dst && src->data && idx->data && dst->data, "b200_op_set_rows: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && (dst->type == B200_TYPE_F32 || dst->type == B200_TYPE_F16) && (idx->type == B200_TYPE_I64 || idx->type == B200_TYPE_I32),
+                 "b200_op_set_rows: f32 -> f32 / f16 with i64 / i32 indices only");
+    const long long n = nelem(src);
+    if (n == 0) return 0;
+    B200_CHECK(b200_launch(set_rows_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4(idx), t4w(dst)));
+    return 0;
+}
+
+int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_cpy: null tensor");
+    B200_REQUIRE((src->type == B200_TYPE_F32 || src->type == B200_TYPE_F16) && (dst->type == B200_TYPE_F32 || dst->type == B200_TYPE_F16), "b200_op_cpy: f32 / f16 only");
+    B200_REQUIRE(nelem(src) == nelem(dst), "b200_op_cpy: element counts differ");
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    if (src->type == dst->type && contiguous_f(src, src->type == B200_TYPE_F32 ? 4 : 2) && contiguous_f(dst, dst->type == B200_TYPE_F32 ? 4 : 2)) {
+        B200_CHECK(cudaMemcpyAsync(dst->data, src->data, (size_t) n * (src->type == B200_TYPE_F32 ? 4 : 2), cudaMemcpyDeviceToDevice, (cudaStream_t) stream));
+        return 0;
+    }
+    B200_CHECK(b200_launch(cpy_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4w(dst)));
+    return 0;
+}
+
+int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b200_tensor * dst, float scale, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_soft_max: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && src->nb[0] == 4 && dst->nb[0] == 4, "b200_op_soft_max: f32 rows with unit stride only");
+    B200_REQUIRE(!mask || ((mask->type == B200_TYPE_F32 || mask->type == B200_TYPE_F16) && mask->data && mask->ne[0] >= src->ne[0] && mask->ne[1] >= src->ne[1]), "b200_op_soft_max: bad mask");
+    const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
+    if (rows == 0 || src->ne[0] == 0) return 0;
+    T4 m = mask ? t4(mask) : t4(src);
+    B200_CHECK(b200_launch(soft_max_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale));
+    return 0;
+}
+
+int b200_op_glu(const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, int glu_op, int swapped, b200_stream_t stream) {
+    B200_REQUIRE(a && dst && a->data && dst->data, "b200_op_glu: null tensor");
+    B200_REQUIRE(a->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && (!b || b->type == B200_TYPE_F32) && a->nb[0] == 4 && (!b || b->nb[0] == 4), "b200_op_glu: f32 rows with unit stride only");
+    B200_REQUIRE(glu_op >= 0 && glu_op <= 2, "b200_op_glu: op %d (0 reglu, 1 geglu, 2 swiglu)", glu_op);
+    B200_REQUIRE(b ? (a->ne[0] == dst->ne[0] && b->ne[0] == dst->ne[0]) : a->ne[0] == 2 * dst->ne[0], "b200_op_glu: shapes");
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    B200_CHECK(b200_launch(glu_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), b ? t4(b) : t4(a), b ? 1 : 0, t4w(dst), glu_op, swapped));
+    return 0;
+}
+
+int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(a && b && dst && a->data && b->data && dst->data, "b200_op_mul_mat_f: null tensor");
+    B200_REQUIRE((a->type == B200_TYPE_F16 || a->type == B200_TYPE_F32) && b->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32, "b200_op_mul_mat_f: f16 / f32 x f32 -> f32 only");
+    B200_REQUIRE(a->nb[0] == (a->type == B200_TYPE_F16 ? 2 : 4) && b->nb[0] == 4 && dst->nb[0] == 4, "b200_op_mul_mat_f: rows must have unit stride");
+    B200_REQUIRE(a->ne[0] == b->ne[0] && dst->ne[0] == a->ne[1] && dst->ne[1] == b->ne[1] && dst->ne[2] == b->ne[2] && dst->ne[3] == b->ne[3] &&
+                 a->ne[2] > 0 && a->ne[3] > 0 && b->ne[2] % a->ne[2] == 0 && b->ne[3] % a->ne[3] == 0, "b200_op_mul_mat_f: shapes");
+    if (nelem(dst) == 0) return 0;
+    const long long r2 = b->ne[2] / a->ne[2], r3 = b->ne[3] / a->ne[3], batch = dst->ne[2] * dst->ne[3], n = b->ne[1];
+    B200_REQUIRE(batch <= 65535, "b200_op_mul_mat_f: %lld batches exceed one launch", batch);
+    cudaStream_t s = (cudaStream_t) stream;
+    const bool ah = a->type == B200_TYPE_F16;
+    if (n <= 8) {
+        dim3 grid(blocks_for(a->ne[1], 4), (unsigned) batch);
+#define B200_MMR(nc) case nc: if (ah) B200_CHECK(b200_launch(mm_rows_kernel<nc, true>, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3)); \
+                              else    B200_CHECK(b200_launch(mm_rows_kernel<nc, false>, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3)); break
+        switch ((int) n) { B200_MMR(1); B200_MMR(2); B200_MMR(3); B200_MMR(4); B200_MMR(5); B200_MMR(6); B200_MMR(7); B200_MMR(8); }
+#undef B200_MMR
+        return 0;
+    }
+    dim3 grid(blocks_for(a->ne[1], 64), blocks_for(n, 64), (unsigned) batch);
+    if (ah) B200_CHECK(b200_launch(mm_tile_kernel<true>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
+    else    B200_CHECK(b200_launch(mm_tile_kernel<false>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
+    return 0;
+}
+
+} // extern "C"
