@@ -276,6 +276,15 @@ typedef struct b200_tensor {
 B200_API int b200_op_get_rows(const b200_tensor * src0, const b200_tensor * ids, const b200_tensor * dst, b200_stream_t stream);
 /* ggml_compute_forward_rms_norm_f32 (ops.cpp:3640-3710): y = x / sqrt(mean(x^2) + eps) per row */
 B200_API int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps, b200_stream_t stream);
+/* fused [ADD ->] RMS_NORM -> MUL(weight): sum = a (+ b); dst = sum / sqrt(mean(sum^2) + eps) * w; `b` and `sum` may be NULL (no add / sum not kept).
+ * The residual pattern of every llama layer; the reference CUDA backend fuses the same nodes (ggml-cuda.cu ggml_cuda_can_fuse, rms_norm + mul [+ add]) */
+B200_API int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const b200_tensor * sum, const b200_tensor * w, const b200_tensor * dst,
+                                      float eps, b200_stream_t stream);
+/* fused decode attention for a few query tokens: dst[head_dim, n_head, n_tokens] = softmax(scale * K q + mask) V, replacing the
+ * MUL_MAT -> SOFT_MAX -> MUL_MAT -> PERMUTE -> CONT sequence of build_attn_mha (src/llama-graph.cpp) when flash attention is off.
+ * k: f16 [head_dim, n_kv, n_head_kv]; v: f16 [n_kv, head_dim, n_head_kv] (transposed V cache); q: f32 [head_dim, n_tokens, n_head]; n_kv <= 12000 */
+B200_API int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst,
+                                 float scale, b200_stream_t stream);
 /* ggml_compute_forward_add / _mul, f32, src1 broadcast over src0 (ggml_can_repeat); op: 0 = add, 1 = mul */
 B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream);
 /* ggml_compute_forward_rope_flt (ops.cpp:5655-5790) for mode 0 (normal) and 2 (neox), ext_factor == 0; pos i32 [n_tokens], freq_factors f32 [n_dims / 2] or NULL */

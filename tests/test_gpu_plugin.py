@@ -54,3 +54,43 @@ def test_reference_conformance_harness_all_types(op):
     for t in ("q4_0", "q8_0", "q4_K", "q6_K", "iq4_xs"):
         ok = [ln for ln in r.stdout.splitlines() if f"type_a={t}," in ln and "OK" in ln]
         assert ok, f"no passing {op} case with type_a={t}"
+
+
+# ---- a whole llama graph through the reference's loader and llama_decode: plugin vs the reference CPU backend ------------------------------
+LLAMA_MODES = [({}, "default"), ({"GGML_B200_FUSE": "0", "GGML_B200_HOIST": "0"}, "no-fusion"), ({"GGML_B200_GRAPHS": "0"}, "no-cuda-graphs")]
+
+
+@pytest.fixture(scope="module")
+def tiny_gguf(tmp_path_factory):
+    """4 layers of Llama-3.2-1B shapes (Q4_0 + Q6_K output), random-init, written by tools/make_gguf.py"""
+    import sys
+    path = tmp_path_factory.mktemp("gguf") / "tiny-1b-q4_0.gguf"
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "llama-3.2-1b-q4_0", "--layers", "4", "--out", str(path)],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:]
+    return path
+
+
+@pytest.mark.parametrize("mode,name", LLAMA_MODES, ids=[m[1] for m in LLAMA_MODES])
+def test_whole_llama_graph_logits_match_reference_cpu_backend(tiny_gguf, mode, name):
+    """oracle/llama_logits_check.cpp: prefill of 40 tokens + 6 decoded tokens, logits of every step, NMSE <= 2e-3 (the reference's own
+    whole-model tolerance). Exercises the loader into B200 buffers (repack), every glue op, the KV cache on the device, the fused norm /
+    attention kernels, the hoisted q / k / v group and the whole-graph CUDA graph replay."""
+    env = _need("llama_logits_check")
+    env.update(mode)
+    r = subprocess.run([str(VAR / "llama_logits_check"), str(tiny_gguf), "40", "6"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0 and "LLAMA_LOGITS_CHECK OK" in r.stdout, r.stdout[-3000:]
+
+
+GLUE_OPS = ["GET_ROWS", "RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "ROPE", "SET_ROWS", "CPY", "CONT", "DUP", "SOFT_MAX", "SWIGLU", "GEGLU", "REGLU"]
+
+
+@pytest.mark.parametrize("op", GLUE_OPS)
+def test_reference_conformance_harness_glue_ops(op):
+    """The ops of a llama-arch graph between the quantised matmuls (csrc/glue_ops.cu): the reference's unmodified test-backend-ops on every
+    variant supports_op claims (the others are reported "not supported" and stay with the CPU backend)."""
+    env = _need("test-backend-ops")
+    r = subprocess.run([str(VAR / "test-backend-ops"), "test", "-o", op, "-b", "B200_0"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    import re
+    m = re.search(r"(\d+)/(\d+) tests passed", r.stdout)
+    assert r.returncode == 0 and m and m.group(1) == m.group(2) and int(m.group(2)) >= 1 and "FAIL" not in r.stdout, r.stdout[-2500:]

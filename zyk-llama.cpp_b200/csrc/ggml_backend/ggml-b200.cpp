@@ -192,10 +192,14 @@ enum ggml_status buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * 
     return GGML_STATUS_SUCCESS;
 }
 
+// The buffer-level set / get / memset are SYNCHRONOUS calls of the interface and run on the device's default stream, while graph_compute is
+// asynchronous on the backend's own (non-blocking) stream -- and ggml_backend_tensor_get_async falls back to the synchronous get WITHOUT
+// synchronising the backend when a backend has no get_tensor_async (ggml-backend.cpp:267-278; llama_context::decode reads the logits that
+// way). Every one of them therefore first waits for all work queued on the device; the async variants below stay in stream order instead.
 void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
     buffer_ctx * bc = (buffer_ctx *) buffer->context;
     if (size == 0) return;
-    b200_set_device(bc->device);
+    b200_device_synchronize(bc->device);
     const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
     std::lock_guard<std::mutex> lock(bc->mu);
     const bool whole = offset == 0 && size == ggml_nbytes(tensor);
@@ -219,7 +223,7 @@ void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const
 void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
     buffer_ctx * bc = (buffer_ctx *) buffer->context;
     if (size == 0) return;
-    b200_set_device(bc->device);
+    b200_device_synchronize(bc->device);
     const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
     std::lock_guard<std::mutex> lock(bc->mu);
     auto it = bc->planes.find(base->data);
@@ -238,7 +242,7 @@ void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor,
 void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
     buffer_ctx * bc = (buffer_ctx *) buffer->context;
     if (size == 0) return;
-    b200_set_device(bc->device);
+    b200_device_synchronize(bc->device);
     const ggml_tensor * base = tensor->view_src ? tensor->view_src : tensor;
     std::lock_guard<std::mutex> lock(bc->mu);
     planes_demote_locked(bc, base->data);
@@ -247,6 +251,7 @@ void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, ui
 }
 
 bool buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_tensor * dst) {
+    b200_device_synchronize(((buffer_ctx *) buffer->context)->device);
     // device-to-device for plain (never repacked) data of our own buffers; everything else takes the
     // generic get_tensor + set_tensor route (ggml-backend.cpp:389-410), which keeps layouts consistent
     buffer_ctx * dc = (buffer_ctx *) buffer->context;
@@ -263,7 +268,7 @@ bool buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, gg
 
 void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     buffer_ctx * bc = (buffer_ctx *) buffer->context;
-    b200_set_device(bc->device);
+    b200_device_synchronize(bc->device);
     std::lock_guard<std::mutex> lock(bc->mu);
     bc->planes.clear();
     b200_memset(bc->base, value, bc->size, nullptr);
@@ -594,8 +599,30 @@ bool env_on(const char * name) { const char * e = getenv(name); return !(e && e[
 // tries to run nodes [i, ...) as groups / a chain; returns the index of the first node NOT consumed (== i: nothing done).
 // Decode (n <= 4): groups become single launches, two or more consecutive K-quant groups ONE persistent chain launch. Prefill (n > 4):
 // the nodes that read the same X share the fp16 copy of X and, per weight type, ONE tensor-core GEMM launch (b200_mul_mat_group).
-int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_status & st) {
-    static const bool group_on = env_on("GGML_B200_GROUP"), chain_on = env_on("GGML_B200_CHAIN");
+// byte ranges of two tensors overlap (views included: the range of the bytes the tensor itself spans)
+bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
+    if (!a || !b || !a->data || !b->data) return false;
+    const char * a0 = (const char *) a->data, * b0 = (const char *) b->data;
+    return a0 < b0 + ggml_nbytes(b) && b0 < a0 + ggml_nbytes(a);
+}
+// may node `h` run BEFORE the nodes [from, h_idx) that precede it in the graph? (it does not read what they write, they neither read nor write
+// what it writes: ggml-alloc reuses buffers, so a later node's output may sit on an earlier node's input)
+bool can_hoist(const ggml_cgraph * g, int from, int h_idx) {
+    const ggml_tensor * h = g->nodes[h_idx];
+    for (int s = from; s < h_idx; ++s) {
+        const ggml_tensor * t = g->nodes[s];
+        if (ggml_is_empty(t)) continue;
+        if (ranges_overlap(h, t)) return false;
+        for (int k = 0; k < GGML_MAX_SRC; ++k) {
+            if (t->src[k] && ranges_overlap(h, t->src[k])) return false;
+            if (h->src[k] && (h->src[k] == t || ranges_overlap(h->src[k], t))) return false;
+        }
+    }
+    return true;
+}
+
+int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_status & st, std::vector<char> & done) {
+    static const bool group_on = env_on("GGML_B200_GROUP"), chain_on = env_on("GGML_B200_CHAIN"), hoist_on = env_on("GGML_B200_HOIST");
     st = GGML_STATUS_SUCCESS;
     if (!group_on) return i;
     std::vector<b200_mul_mat_args> args;
@@ -603,7 +630,7 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     int j = i, last = i;
     for (; j < cgraph->n_nodes; ++j) {
         const ggml_tensor * t = cgraph->nodes[j];
-        if (is_noop(t) || skipped(t) || ggml_is_empty(t)) continue;
+        if (done[j] || is_noop(t) || skipped(t) || ggml_is_empty(t)) continue;
         if (!plain_mul_mat(t)) break;
         b200_mul_mat_args a = plain_args(t);
         if (!args.empty() && a.n != args[0].n) break;
@@ -612,6 +639,19 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
         if (same_x) ++sizes.back(); else sizes.push_back(1);
         args.push_back(a);
         last = j + 1;
+    }
+    // wq ... rope ... wv ... wk: the other matmuls of the same X sit a few nodes further down the graph. Pull them into this group when nothing
+    // in between depends on them or touches their output (one launch, one quantisation / fp16 copy of X)
+    if (hoist_on && sizes.size() == 1) {
+        const b200_mul_mat_args head = args[0];
+        for (int h = j; h < cgraph->n_nodes && h < j + 12 && sizes.back() < 4; ++h) {
+            const ggml_tensor * t = cgraph->nodes[h];
+            if (done[h] || !plain_mul_mat(t)) continue;
+            const b200_mul_mat_args a = plain_args(t);
+            if (a.x != head.x || a.n != head.n || a.k != head.k || a.x_row_stride != head.x_row_stride) continue;
+            if (!can_hoist(cgraph, last, h)) continue;
+            args.push_back(a); ++sizes.back(); done[h] = 1;
+        }
     }
     if (args.size() < 2) return i;                       // a single node: the ordinary path
     // workspace for the group launches (the chain does not need one)
@@ -776,15 +816,91 @@ enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgr
     return GGML_STATUS_SUCCESS;
 }
 
+// ---- fusions over the node list (GGML_B200_FUSE=0: off) ----------------------------------------------------------------------------------
+bool norm_weight_ok(const ggml_tensor * w, const ggml_tensor * x) {
+    return w && w->type == GGML_TYPE_F32 && w->nb[0] == sizeof(float) && w->ne[0] == x->ne[0] && ggml_can_repeat(w, x);
+}
+// [ADD ->] RMS_NORM -> MUL(weight) as one kernel; returns the number of nodes consumed (0: no match)
+int try_fuse_norm(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
+    const ggml_tensor * n0 = g->nodes[i];
+    int r = i;                                            // index of the RMS_NORM node
+    const ggml_tensor * add = nullptr;
+    if (n0->op == GGML_OP_ADD) {
+        if (i + 2 >= g->n_nodes || !f32_rows(n0) || !f32_rows(n0->src[0]) || !f32_rows(n0->src[1]) || !ggml_can_repeat(n0->src[1], n0->src[0]) ||
+            n0->src[1]->ne[0] != n0->src[0]->ne[0]) return 0;
+        add = n0; r = i + 1;
+        if (g->nodes[r]->op != GGML_OP_RMS_NORM || g->nodes[r]->src[0] != add || skipped(g->nodes[r])) return 0;
+    }
+    static const enum ggml_op ops[2] = {GGML_OP_RMS_NORM, GGML_OP_MUL};
+    if (!ggml_can_fuse(g, r, ops, 2)) return 0;
+    const ggml_tensor * rms = g->nodes[r], * mul = g->nodes[r + 1];
+    const ggml_tensor * w = mul->src[0] == rms ? mul->src[1] : mul->src[0];
+    if (!f32_rows(rms) || !f32_rows(rms->src[0]) || !f32_rows(mul) || !norm_weight_ok(w, rms)) return 0;
+    float eps; memcpy(&eps, rms->op_params, sizeof(float));
+    const b200_tensor d = bt(mul), tw = bt(w);
+    int rc;
+    if (add) { const b200_tensor ta = bt(add->src[0]), tb = bt(add->src[1]), ts = bt(add); rc = b200_op_add_rms_norm_mul(&ta, &tb, &ts, &tw, &d, eps, bc->stream); }
+    else     { const b200_tensor ta = bt(rms->src[0]); rc = b200_op_add_rms_norm_mul(&ta, nullptr, nullptr, &tw, &d, eps, bc->stream); }
+    if (rc != 0) { GGML_LOG_ERROR("ggml-b200: fused norm (%s) failed: %s\n", mul->name, b200_last_error()); st = GGML_STATUS_FAILED; }
+    return add ? 3 : 2;
+}
+int next_real(const ggml_cgraph * g, int i) {
+    for (++i; i < g->n_nodes; ++i) { const ggml_tensor * t = g->nodes[i]; if (!is_noop(t) && !skipped(t) && !ggml_is_empty(t)) return i; }
+    return -1;
+}
+// MUL_MAT(K, q) -> SOFT_MAX -> MUL_MAT(V^T, P) -> PERMUTE -> CONT for a few query tokens as one kernel; returns the index of the CONT node (-1: no match)
+int try_fuse_attn(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
+    const ggml_tensor * kq = g->nodes[i];
+    if (kq->op != GGML_OP_MUL_MAT || kq->src[0]->type != GGML_TYPE_F16 || kq->src[1]->type != GGML_TYPE_F32) return -1;
+    const int is = next_real(g, i); if (is < 0) return -1;
+    const int iv = next_real(g, is); if (iv < 0) return -1;
+    const int ic = next_real(g, iv); if (ic < 0) return -1;
+    const ggml_tensor * sm = g->nodes[is], * kqv = g->nodes[iv], * cont = g->nodes[ic];
+    if (sm->op != GGML_OP_SOFT_MAX || sm->src[0] != kq || sm->src[2] || kqv->op != GGML_OP_MUL_MAT || kqv->src[1] != sm || kqv->src[0]->type != GGML_TYPE_F16 ||
+        cont->op != GGML_OP_CONT) return -1;
+    const ggml_tensor * perm = cont->src[0];
+    if (!perm || perm->op != GGML_OP_PERMUTE || perm->src[0] != kqv) return -1;
+    if (!ggml_node_has_n_uses(g, i, 1) || !ggml_node_has_n_uses(g, is, 1) || !ggml_node_has_n_uses(g, iv, 1)) return -1;
+    const ggml_tensor * K = kq->src[0], * q = kq->src[1], * V = kqv->src[0], * mask = sm->src[1];
+    const int64_t hd = K->ne[0], n_kv = K->ne[1], n_tok = q->ne[1], n_head = q->ne[2];
+    float scale, max_bias; memcpy(&scale, sm->op_params, sizeof(float)); memcpy(&max_bias, (const float *) sm->op_params + 1, sizeof(float));
+    if (max_bias != 0.0f || n_tok > 16 || n_kv > 11000 || n_kv < 1 || K->ne[3] != 1 || q->ne[3] != 1 || K->nb[0] != 2 || V->nb[0] != 2 || q->nb[0] != 4 ||
+        V->ne[0] != n_kv || V->ne[1] != hd || V->ne[2] != K->ne[2] || n_head % K->ne[2] != 0 || hd % 32 != 0 || K->nb[1] % 16 || K->nb[2] % 16 ||
+        ((uintptr_t) K->data % 16)) return -1;
+    if (mask && !(f_any(mask) && mask->ne[0] >= n_kv && mask->ne[1] >= n_tok)) return -1;
+    // the permuted view must be [head_dim, n_head, n_tokens] of kqv [head_dim, n_tokens, n_head], and CONT its contiguous copy
+    if (perm->ne[0] != hd || perm->ne[1] != n_head || perm->ne[2] != n_tok || perm->nb[1] != kqv->nb[2] || perm->nb[2] != kqv->nb[1] ||
+        cont->type != GGML_TYPE_F32 || !ggml_is_contiguous(cont) || ggml_nelements(cont) != hd * n_head * n_tok) return -1;
+    const b200_tensor tk = bt(K), tq = bt(q), tv = bt(V), td = bt(cont);
+    b200_tensor tm = {}; if (mask) tm = bt(mask);
+    if (b200_op_attn_decode(&tk, &tq, mask ? &tm : nullptr, &tv, &td, scale, bc->stream) != 0) {
+        GGML_LOG_ERROR("ggml-b200: fused attention (%s) failed: %s\n", cont->name, b200_last_error()); st = GGML_STATUS_FAILED;
+    }
+    return ic;
+}
+
 enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
+    static const bool fuse_on = env_on("GGML_B200_FUSE") && glue_on();
+    std::vector<char> done((size_t) cgraph->n_nodes, 0);          // matmuls hoisted into an earlier group
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
-        if (ggml_is_empty(node) || skipped(node)) continue;
+        if (done[i] || ggml_is_empty(node) || skipped(node)) continue;
         enum ggml_status st = GGML_STATUS_SUCCESS;
+        { static const char * pre = getenv("GGML_B200_PRESYNC"); if (pre && !bc->capturing && !strcmp(pre, ggml_op_name(node->op))) b200_stream_synchronize(bc->stream); }
         if (plain_mul_mat(node)) {
-            const int next = compute_decode_run(bc, cgraph, i, st);
+            const int next = compute_decode_run(bc, cgraph, i, st, done);
             if (st != GGML_STATUS_SUCCESS) return st;
             if (next > i) { i = next - 1; continue; }
+        }
+        if (fuse_on && (node->op == GGML_OP_ADD || node->op == GGML_OP_RMS_NORM)) {
+            const int used = try_fuse_norm(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (used > 0) { i += used - 1; continue; }
+        }
+        if (fuse_on && node->op == GGML_OP_MUL_MAT && node->src[0]->type == GGML_TYPE_F16) {
+            const int ic = try_fuse_attn(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (ic > i) { i = ic; continue; }
         }
         switch (node->op) {
             case GGML_OP_NONE:
@@ -798,8 +914,38 @@ enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
             default:                 st = compute_glue(bc, node); break;
         }
         if (st != GGML_STATUS_SUCCESS) return st;
+        // debugging aid: GGML_B200_SYNC=<op name|all> synchronises the stream after every node of that op (never during a capture)
+        static const char * sync_env = getenv("GGML_B200_SYNC");
+        if (sync_env && !bc->capturing && (!strcmp(sync_env, "all") || !strcmp(sync_env, ggml_op_name(node->op)) ||
+                                           (node->op == GGML_OP_MUL_MAT && !strcmp(sync_env, weight_type(node->src[0]->type) ? "MUL_MAT_Q" : "MUL_MAT_F"))))
+            b200_stream_synchronize(bc->stream);
     }
     return GGML_STATUS_SUCCESS;
+}
+
+// set / get in stream order (ggml_backend_i::set_tensor_async / get_tensor_async, ggml-backend-impl.h:92-95): plain tensors of this device's
+// buffers are copied on the backend's stream; a tensor stored in the plane layout takes the synchronous, repack-aware buffer path
+bool plane_tracked(const ggml_tensor * t) {
+    buffer_ctx * bc = owner_ctx(t);
+    if (!bc) return true;                      // not ours: let the buffer decide
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    std::lock_guard<std::mutex> lock(bc->mu);
+    return bc->planes.count(base->data) != 0;
+}
+void backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    if (size == 0) return;
+    const bool whole = offset == 0 && size == ggml_nbytes(tensor);
+    if (plane_tracked(tensor) || (whole && repack_candidate(tensor))) { ggml_backend_tensor_set(tensor, data, offset, size); return; }
+    b200_set_device(bc->device);
+    if (b200_memcpy_h2d((char *) tensor->data + offset, data, size, bc->stream) != 0) GGML_ABORT("ggml-b200: set_tensor_async(%s) failed: %s", tensor->name, b200_last_error());
+}
+void backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    backend_ctx * bc = (backend_ctx *) backend->context;
+    if (size == 0) return;
+    if (plane_tracked(tensor)) { ggml_backend_tensor_get(tensor, data, offset, size); return; }
+    b200_set_device(bc->device);
+    if (b200_memcpy_d2h(data, (const char *) tensor->data + offset, size, bc->stream) != 0) GGML_ABORT("ggml-b200: get_tensor_async(%s) failed: %s", tensor->name, b200_last_error());
 }
 
 void backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
@@ -815,8 +961,8 @@ void backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
 const ggml_backend_i backend_iface = {
     /* .get_name           = */ backend_get_name,
     /* .free               = */ backend_free,
-    /* .set_tensor_async   = */ nullptr,   // set/get go through the buffer (repack-aware, synchronous)
-    /* .get_tensor_async   = */ nullptr,
+    /* .set_tensor_async   = */ backend_set_tensor_async,
+    /* .get_tensor_async   = */ backend_get_tensor_async,
     /* .cpy_tensor_async   = */ nullptr,
     /* .synchronize        = */ backend_synchronize,
     /* .graph_plan_create  = */ nullptr,

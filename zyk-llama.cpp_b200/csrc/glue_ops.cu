@@ -24,6 +24,16 @@ bool contiguous_f(const b200_tensor * t, long long esz) {
 }
 unsigned blocks_for(long long n, int per) { const long long b = (n + per - 1) / per; return (unsigned) (b < 1 ? 1 : b > 0x7fffffffll ? 0x7fffffffll : b); }
 
+// element index -> 4-D coordinates; I = unsigned (32-bit divisions, ~5x cheaper) whenever the tensor has fewer than 2^31 elements
+template <typename I>
+__device__ __forceinline__ void unravel(I i, const long long * ne, I & i0, I & i1, I & i2, I & i3) {
+    const I n0 = (I) ne[0], n1 = (I) ne[1], n2 = (I) ne[2];
+    i0 = i % n0; I r = i / n0; i1 = r % n1; r /= n1; i2 = r % n2; i3 = r / n2;
+}
+#define B200_LAUNCH_IDX(kernel, total, ...) \
+    do { if ((total) < (1ll << 31)) B200_CHECK(b200_launch(kernel<unsigned>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, false, __VA_ARGS__)); \
+         else                       B200_CHECK(b200_launch(kernel<long long>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, false, __VA_ARGS__)); } while (0)
+
 // ---- dequantise ONE element of a canonical ggml row (dequantize_row_*, ggml-quants.c:307-325, 401-415, 1352-1375, 1762-1792, 2530-2551) ----
 __device__ __constant__ signed char kvalues_iq4nl_d[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
 
@@ -76,13 +86,15 @@ __device__ __forceinline__ float deq_one(int type, const uint8_t * row, long lon
 }
 
 // ---- GET_ROWS (ggml_compute_forward_get_rows, ggml-cpu/ops.cpp): dst[:, i10, i11, i12] = row src1[i10, i11, i12] of matrix (i11, i12) of src0 ----
+template <typename I>
 __global__ void __launch_bounds__(256) get_rows_kernel(const T4 a, const T4 ids, const T4w d) {
-    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long e = i % d.ne[0], i10 = (i / d.ne[0]) % d.ne[1], i11 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], i12 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
-        const int r = *reinterpret_cast<const int *>(ids.data + i10 * ids.nb[0] + i11 * ids.nb[1] + i12 * ids.nb[2]);
-        const uint8_t * row = reinterpret_cast<const uint8_t *>(a.data + (long long) r * a.nb[1] + i11 * a.nb[2] + i12 * a.nb[3]);
-        *reinterpret_cast<float *>(d.data + e * d.nb[0] + i10 * d.nb[1] + i11 * d.nb[2] + i12 * d.nb[3]) = deq_one(a.type, row, e);
+    const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I e, i10, i11, i12;
+        unravel<I>(i, d.ne, e, i10, i11, i12);
+        const int r = *reinterpret_cast<const int *>(ids.data + (long long) i10 * ids.nb[0] + (long long) i11 * ids.nb[1] + (long long) i12 * ids.nb[2]);
+        const uint8_t * row = reinterpret_cast<const uint8_t *>(a.data + (long long) r * a.nb[1] + (long long) i11 * a.nb[2] + (long long) i12 * a.nb[3]);
+        *reinterpret_cast<float *>(d.data + (long long) e * d.nb[0] + (long long) i10 * d.nb[1] + (long long) i11 * d.nb[2] + (long long) i12 * d.nb[3]) = deq_one(a.type, row, (long long) e);
     }
 }
 
@@ -105,29 +117,187 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(const T4 a, const T4w d, 
     for (long long i = threadIdx.x; i < a.ne[0]; i += 256) y[i] = x[i] * scale;
 }
 
-// ---- ADD / MUL with ggml broadcasting of src1 (ggml_compute_forward_add / _mul: src1 dims divide src0 dims) ----
-template <int OP>
-__global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, const T4w d) {
-    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long i0 = i % d.ne[0], i1 = (i / d.ne[0]) % d.ne[1], i2 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], i3 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
-        const float x = *reinterpret_cast<const float *>(a.data + i0 * a.nb[0] + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
-        const float y = *reinterpret_cast<const float *>(b.data + (i0 % b.ne[0]) * b.nb[0] + (i1 % b.ne[1]) * b.nb[1] + (i2 % b.ne[2]) * b.nb[2] + (i3 % b.ne[3]) * b.nb[3]);
-        *reinterpret_cast<float *>(d.data + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = OP == 0 ? x + y : x * y;
+// ---- fused [ADD ->] RMS_NORM -> MUL(weight): sum = a + b (stored when `sum` is given), y = sum / sqrt(mean(sum^2) + eps) * w ----
+// (what the llama graph does at every residual: ffn_inp = attn_out + inp; norm = rms_norm(ffn_inp); ffn_norm = norm * ffn_norm.weight;
+//  the reference's CUDA backend fuses the same pattern, ggml-cuda.cu ggml_cuda_can_fuse / rms_norm_mul_f32)
+// one CTA of 1024 threads per row: the row is read once with 128-bit loads (two per thread: rows of up to 8192 elements stay in registers), longer or
+// unaligned rows take the scalar loop. w has ne[0] == row length (checked by the caller), so it is indexed without a modulo.
+__global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, const T4 b, int has_b, const T4w sum, int has_sum, const T4 w, const T4w d, float eps) {
+    const unsigned row = blockIdx.x;
+    const unsigned n1 = (unsigned) a.ne[1], n2 = (unsigned) a.ne[2];
+    const unsigned i1 = row % n1, i2 = (row / n1) % n2, i3 = row / (n1 * n2);
+    const float * x = reinterpret_cast<const float *>(a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+    const float * xb = has_b ? reinterpret_cast<const float *>(b.data + (long long) (i1 % (unsigned) b.ne[1]) * b.nb[1] + (long long) (i2 % (unsigned) b.ne[2]) * b.nb[2] + (long long) (i3 % (unsigned) b.ne[3]) * b.nb[3]) : nullptr;
+    float * so = has_sum ? reinterpret_cast<float *>(sum.data + (long long) i1 * sum.nb[1] + (long long) i2 * sum.nb[2] + (long long) i3 * sum.nb[3]) : nullptr;
+    const float * wr = reinterpret_cast<const float *>(w.data + (long long) (i1 % (unsigned) w.ne[1]) * w.nb[1] + (long long) (i2 % (unsigned) w.ne[2]) * w.nb[2] + (long long) (i3 % (unsigned) w.ne[3]) * w.nb[3]);
+    float * y = reinterpret_cast<float *>(d.data + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]);
+    const int n = (int) a.ne[0];
+    __shared__ float red[32];
+    const bool vec = n <= 8192 && (n & 3) == 0 && ((((uintptr_t) x) | ((uintptr_t) y) | ((uintptr_t) wr) | (xb ? (uintptr_t) xb : 0) | (so ? (uintptr_t) so : 0)) & 15) == 0;
+    float4 v[2];
+    float s = 0.0f;
+    if (vec) {
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            const int i4 = threadIdx.x + t * 1024;
+            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i4 * 4 < n) {
+                e = reinterpret_cast<const float4 *>(x)[i4];
+                if (xb) { const float4 f = reinterpret_cast<const float4 *>(xb)[i4]; e.x += f.x; e.y += f.y; e.z += f.z; e.w += f.w; }
+                if (so) reinterpret_cast<float4 *>(so)[i4] = e;
+            }
+            v[t] = e; s += e.x * e.x + e.y * e.y + e.z * e.z + e.w * e.w;
+        }
+    } else {
+        for (int i = threadIdx.x; i < n; i += 1024) { float e = x[i]; if (xb) e += xb[i]; if (so) so[i] = e; s += e * e; }
+    }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    s = red[threadIdx.x & 31];
+    s = warp_sum(s);
+    const float scale = 1.0f / sqrtf(s / (float) n + eps);
+    if (vec) {
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            const int i4 = threadIdx.x + t * 1024;
+            if (i4 * 4 < n) {
+                const float4 ww = reinterpret_cast<const float4 *>(wr)[i4];
+                reinterpret_cast<float4 *>(y)[i4] = make_float4(v[t].x * scale * ww.x, v[t].y * scale * ww.y, v[t].z * scale * ww.z, v[t].w * scale * ww.w);
+            }
+        }
+    } else {
+        // (so holds the sums when it exists; otherwise recompute: y may alias x only element by element)
+        for (int i = threadIdx.x; i < n; i += 1024) { float e = so ? so[i] : (xb ? x[i] + xb[i] : x[i]); y[i] = e * scale * wr[i]; }
     }
 }
 
+// ---- fused decode attention: softmax(scale * K q + mask) V for a few query tokens, one CTA per (head, token) --------------------------------
+// replaces MUL_MAT(K view f16, Q) -> SOFT_MAX(scale, mask) -> MUL_MAT(V^T view f16, P) -> PERMUTE -> CONT of the llama graph
+// (src/llama-graph.cpp build_attn_mha, the path without flash attention). K: [head_dim, n_kv, n_head_kv] rows contiguous; V^T: [n_kv, head_dim,
+// n_head_kv] rows contiguous; q: [head_dim, n_tokens, n_head]; mask [n_kv, n_tokens(+pad)] f32 / f16 or none; out: [head_dim, n_head, n_tokens] contiguous.
+// Latency is what matters here (32 CTAs, a few KB each): every phase issues all its loads before it uses them.
+//   scores: four lanes per KV row (head_dim / 4 elements each as 128-bit loads), 64 rows per CTA pass;
+//   output: thread (d, part) walks its part of row d of V^T with 128-bit loads, the parts meet in shared memory.
+__global__ void __launch_bounds__(256) attn_decode_kernel(const T4 K, const T4 q, const T4 m, int has_mask, const T4 V, float * __restrict__ out, float scale) {
+    extern __shared__ float sc[];                 // n_kv scores, then head_dim q values, then 256 partial outputs
+    __shared__ float red[8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.x, t = blockIdx.y;
+    const int n_kv = (int) K.ne[1], hd = (int) K.ne[0], n_head = (int) q.ne[2];
+    const int hk = h / (n_head / (int) K.ne[2]);
+    float * qs = sc + n_kv, * part = qs + hd;
+    const float * qv = reinterpret_cast<const float *>(q.data + (long long) t * q.nb[1] + (long long) h * q.nb[2]);
+    for (int e = threadIdx.x; e < hd; e += 256) qs[e] = qv[e];
+    __syncthreads();
+    const char * mp = has_mask ? m.data + (long long) t * m.nb[1] + (long long) (h % (int) m.ne[2]) * m.nb[2] : nullptr;
+    const char * kb = K.data + (long long) hk * K.nb[2];
+    // phase 1: scores. lane quad g = threadIdx.x / 4 owns rows g, g + 64, ...; sub = lane & 3 owns elements [sub * hd / 4, (sub + 1) * hd / 4)
+    const int g = threadIdx.x >> 2, sub = threadIdx.x & 3, per = hd >> 2;      // per is a multiple of 8 (checked by the caller)
+    float mx = -INFINITY;
+    for (int j0 = 0; j0 < n_kv; j0 += 64) {
+        const int j = j0 + g;
+        float a = 0.0f;
+        if (j < n_kv) {
+            const uint4 * kr = reinterpret_cast<const uint4 *>(kb + (long long) j * K.nb[1]) + sub * (per >> 3);
+            for (int c = 0; c < (per >> 3); ++c) {
+                const uint4 kk = kr[c];
+                const float * qq = qs + sub * per + c * 8;
+                const float2 k0 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.x)), k1 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.y));
+                const float2 k2 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.z)), k3 = __half22float2(*reinterpret_cast<const __half2 *>(&kk.w));
+                a += k0.x * qq[0] + k0.y * qq[1] + k1.x * qq[2] + k1.y * qq[3] + k2.x * qq[4] + k2.y * qq[5] + k3.x * qq[6] + k3.y * qq[7];
+            }
+        }
+        a += __shfl_xor_sync(0xffffffffu, a, 1);
+        a += __shfl_xor_sync(0xffffffffu, a, 2);
+        if (j < n_kv) {
+            a *= scale;
+            if (mp) a += m.type == B200_TYPE_F16 ? __half2float(reinterpret_cast<const __half *>(mp)[j]) : reinterpret_cast<const float *>(mp)[j];
+            if (sub == 0) sc[j] = a;
+            mx = fmaxf(mx, a);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+    __syncthreads();
+    // phase 2: exponentials and their sum
+    float s = 0.0f;
+    for (int j = threadIdx.x; j < n_kv; j += 256) { const float e = expf(sc[j] - mx); sc[j] = e; s += e; }
+    s = warp_sum(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i];
+    const float inv = 1.0f / s;
+    // phase 3: out[d] = sum_j p[j] V^T[d][j]; `parts` threads share a row of V^T
+    const int parts = hd <= 256 ? 256 / hd : 1;
+    const int d = threadIdx.x % hd, pt = threadIdx.x / hd;
+    float acc = 0.0f;
+    if (threadIdx.x < hd * parts) {
+        const int chunk = (((n_kv + parts - 1) / parts) + 7) & ~7;
+        const int j_lo = pt * chunk, j_hi = min(n_kv, j_lo + chunk);
+        const __half * vr = reinterpret_cast<const __half *>(V.data + (long long) d * V.nb[1] + (long long) hk * V.nb[2]);
+        int j = j_lo;
+        if ((((uintptr_t) vr) & 15) == 0) {
+            for (; j + 8 <= j_hi; j += 8) {
+                const uint4 vv = *reinterpret_cast<const uint4 *>(vr + j);
+                const float2 v0 = __half22float2(*reinterpret_cast<const __half2 *>(&vv.x)), v1 = __half22float2(*reinterpret_cast<const __half2 *>(&vv.y));
+                const float2 v2 = __half22float2(*reinterpret_cast<const __half2 *>(&vv.z)), v3 = __half22float2(*reinterpret_cast<const __half2 *>(&vv.w));
+                acc += v0.x * sc[j] + v0.y * sc[j + 1] + v1.x * sc[j + 2] + v1.y * sc[j + 3] + v2.x * sc[j + 4] + v2.y * sc[j + 5] + v3.x * sc[j + 6] + v3.y * sc[j + 7];
+            }
+        }
+        for (; j < j_hi; ++j) acc += __half2float(vr[j]) * sc[j];
+    }
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.x < hd) {
+        float r = 0.0f;
+        for (int p = 0; p < parts; ++p) r += part[p * hd + threadIdx.x];
+        out[((long long) t * n_head + h) * hd + threadIdx.x] = r * inv;
+    }
+    // head_dim > 256: the rows past 256 are handled by the same threads in further rounds
+    for (int d2 = threadIdx.x + 256; d2 < hd && parts == 1; d2 += 256) {
+        const __half * vr = reinterpret_cast<const __half *>(V.data + (long long) d2 * V.nb[1] + (long long) hk * V.nb[2]);
+        float r = 0.0f;
+        for (int j = 0; j < n_kv; ++j) r += __half2float(vr[j]) * sc[j];
+        out[((long long) t * n_head + h) * hd + d2] = r * inv;
+    }
+}
+
+// ---- ADD / MUL with ggml broadcasting of src1 (ggml_compute_forward_add / _mul: src1 dims divide src0 dims) ----
+template <int OP, typename I>
+__global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, const T4w d) {
+    const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
+    const I b0 = (I) b.ne[0], b1 = (I) b.ne[1], b2 = (I) b.ne[2], b3 = (I) b.ne[3];
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I i0, i1, i2, i3;
+        unravel<I>(i, d.ne, i0, i1, i2, i3);
+        const float x = *reinterpret_cast<const float *>(a.data + (long long) i0 * a.nb[0] + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+        const I j0 = b0 == (I) d.ne[0] ? i0 : i0 % b0, j1 = b1 == 1 ? 0 : i1 % b1, j2 = b2 == 1 ? 0 : i2 % b2, j3 = b3 == 1 ? 0 : i3 % b3;
+        const float y = *reinterpret_cast<const float *>(b.data + (long long) j0 * b.nb[0] + (long long) j1 * b.nb[1] + (long long) j2 * b.nb[2] + (long long) j3 * b.nb[3]);
+        *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = OP == 0 ? x + y : x * y;
+    }
+}
 // ---- ROPE, modes normal (0) and neox (2), ext_factor == 0 (ggml_compute_forward_rope_flt + ggml_rope_cache_init + rope_yarn, ops.cpp:5524-5790) ----
 struct RopeP { int n_dims, mode; float freq_base, freq_scale, attn_factor; };
+template <typename I>
 __global__ void __launch_bounds__(256) rope_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p) {
-    const long long half = a.ne[0] / 2, total = half * a.ne[1] * a.ne[2] * a.ne[3];
+    const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
+    const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
     const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long ip = i % half, i1 = (i / half) % a.ne[1], i2 = (i / (half * a.ne[1])) % a.ne[2], i3 = i / (half * a.ne[1] * a.ne[2]);
-        const char * src = a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3];
-        char * dst = d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3];
-        if (2 * ip >= p.n_dims) {                // the dimensions past n_dims are copied
-            const long long e = 2 * ip;
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I ip, i1, i2, i3;
+        unravel<I>(i, hne, ip, i1, i2, i3);
+        const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
+        char * dst = d.data + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3];
+        if (2 * (int) ip >= p.n_dims) {                // the dimensions past n_dims are copied
+            const int e = 2 * (int) ip;
             reinterpret_cast<float *>(dst)[e] = reinterpret_cast<const float *>(src)[e];
             reinterpret_cast<float *>(dst)[e + 1] = reinterpret_cast<const float *>(src)[e + 1];
             continue;
@@ -136,7 +306,7 @@ __global__ void __launch_bounds__(256) rope_kernel(const T4 a, const int * __res
         float sn, cs;
         sincosf(theta, &sn, &cs);
         sn *= p.attn_factor; cs *= p.attn_factor;
-        const long long e0 = p.mode == 2 ? ip : 2 * ip, e1 = p.mode == 2 ? ip + p.n_dims / 2 : 2 * ip + 1;
+        const int e0 = p.mode == 2 ? (int) ip : 2 * (int) ip, e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
         const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
         reinterpret_cast<float *>(dst)[e0] = x0 * cs - x1 * sn;
         reinterpret_cast<float *>(dst)[e1] = x0 * sn + x1 * cs;
@@ -151,25 +321,29 @@ __device__ __forceinline__ float load_as(const char * p, int type) {
 }
 
 // ---- SET_ROWS (ggml_compute_forward_set_rows_f32): dst row src1[i01, i02 % ne11, i03 % ne12] of matrix (i02, i03) = src0 row (i01, i02, i03) ----
+template <typename I>
 __global__ void __launch_bounds__(256) set_rows_kernel(const T4 a, const T4 idx, const T4w d) {
-    const long long total = a.ne[0] * a.ne[1] * a.ne[2] * a.ne[3];
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long i0 = i % a.ne[0], i1 = (i / a.ne[0]) % a.ne[1], i2 = (i / (a.ne[0] * a.ne[1])) % a.ne[2], i3 = i / (a.ne[0] * a.ne[1] * a.ne[2]);
-        const char * ip = idx.data + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2];
+    const I total = (I) (a.ne[0] * a.ne[1] * a.ne[2] * a.ne[3]);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I i0, i1, i2, i3;
+        unravel<I>(i, a.ne, i0, i1, i2, i3);
+        const char * ip = idx.data + (long long) i1 * idx.nb[0] + (long long) (i2 % (I) idx.ne[1]) * idx.nb[1] + (long long) (i3 % (I) idx.ne[2]) * idx.nb[2];
         const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
-        const float v = *reinterpret_cast<const float *>(a.data + i0 * a.nb[0] + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
-        store_as(d.data + i0 * d.nb[0] + r * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], d.type, v);
+        const float v = *reinterpret_cast<const float *>(a.data + (long long) i0 * a.nb[0] + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+        store_as(d.data + (long long) i0 * d.nb[0] + r * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3], d.type, v);
     }
 }
 
 // ---- CPY / CONT / DUP between f32 and f16 (ggml_compute_forward_dup): element i of src (row-major over its shape) -> element i of dst ----
+template <typename I>
 __global__ void __launch_bounds__(256) cpy_kernel(const T4 a, const T4w d) {
-    const long long total = d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3];
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long s0 = i % a.ne[0], s1 = (i / a.ne[0]) % a.ne[1], s2 = (i / (a.ne[0] * a.ne[1])) % a.ne[2], s3 = i / (a.ne[0] * a.ne[1] * a.ne[2]);
-        const long long d0 = i % d.ne[0], d1 = (i / d.ne[0]) % d.ne[1], d2 = (i / (d.ne[0] * d.ne[1])) % d.ne[2], d3 = i / (d.ne[0] * d.ne[1] * d.ne[2]);
-        store_as(d.data + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3], d.type,
-                 load_as(a.data + s0 * a.nb[0] + s1 * a.nb[1] + s2 * a.nb[2] + s3 * a.nb[3], a.type));
+    const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I s0, s1, s2, s3, d0, d1, d2, d3;
+        unravel<I>(i, a.ne, s0, s1, s2, s3);
+        unravel<I>(i, d.ne, d0, d1, d2, d3);
+        store_as(d.data + (long long) d0 * d.nb[0] + (long long) d1 * d.nb[1] + (long long) d2 * d.nb[2] + (long long) d3 * d.nb[3], d.type,
+                 load_as(a.data + (long long) s0 * a.nb[0] + (long long) s1 * a.nb[1] + (long long) s2 * a.nb[2] + (long long) s3 * a.nb[3], a.type));
     }
 }
 
@@ -211,19 +385,21 @@ __device__ __forceinline__ float glu_act(int op, float x) {
     if (op == 1) return 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * (1.0f + 0.044715f * x * x)));
     return x / (1.0f + expf(-x));
 }
+template <typename I>
 __global__ void __launch_bounds__(256) glu_kernel(const T4 a, const T4 b, int split, const T4w d, int op, int swapped) {
-    const long long nc = d.ne[0], total = nc * d.ne[1] * d.ne[2] * d.ne[3];
-    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total; i += (long long) gridDim.x * 256) {
-        const long long i0 = i % nc, i1 = (i / nc) % d.ne[1], i2 = (i / (nc * d.ne[1])) % d.ne[2], i3 = i / (nc * d.ne[1] * d.ne[2]);
-        const float * ar = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    const I nc = (I) d.ne[0], total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I i0, i1, i2, i3;
+        unravel<I>(i, d.ne, i0, i1, i2, i3);
+        const float * ar = reinterpret_cast<const float *>(a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
         float x, g;
         if (split) {
-            const float * br = reinterpret_cast<const float *>(b.data + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]);
+            const float * br = reinterpret_cast<const float *>(b.data + (long long) i1 * b.nb[1] + (long long) i2 * b.nb[2] + (long long) i3 * b.nb[3]);
             x = ar[i0]; g = br[i0];
         } else {
             x = ar[swapped ? i0 + nc : i0]; g = ar[swapped ? i0 : i0 + nc];
         }
-        *reinterpret_cast<float *>(d.data + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = glu_act(op, x) * g;
+        *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = glu_act(op, x) * g;
     }
 }
 
@@ -304,7 +480,7 @@ int b200_op_get_rows(const b200_tensor * src0, const b200_tensor * ids, const b2
     B200_REQUIRE(src0->type == B200_TYPE_F32 || src0->type == B200_TYPE_F16 || b200_type_is_weight(src0->type), "b200_op_get_rows: unsupported source type %d", src0->type);
     const long long n = nelem(dst);
     if (n == 0) return 0;
-    B200_CHECK(b200_launch(get_rows_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src0), t4(ids), t4w(dst)));
+    B200_LAUNCH_IDX(get_rows_kernel, n, t4(src0), t4(ids), t4w(dst));
     return 0;
 }
 
@@ -317,6 +493,35 @@ int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps
     return 0;
 }
 
+int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const b200_tensor * sum, const b200_tensor * w, const b200_tensor * dst, float eps, b200_stream_t stream) {
+    B200_REQUIRE(a && w && dst && a->data && w->data && dst->data && (!b || b->data) && (!sum || sum->data), "b200_op_add_rms_norm_mul: null tensor");
+    B200_REQUIRE(a->type == B200_TYPE_F32 && w->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && a->nb[0] == 4 && w->nb[0] == 4 && dst->nb[0] == 4 &&
+                 (!b || (b->type == B200_TYPE_F32 && b->nb[0] == 4 && b->ne[0] == a->ne[0])) && (!sum || (sum->type == B200_TYPE_F32 && sum->nb[0] == 4)),
+                 "b200_op_add_rms_norm_mul: f32 rows with unit stride only");
+    B200_REQUIRE(w->ne[0] > 0 && a->ne[0] % w->ne[0] == 0, "b200_op_add_rms_norm_mul: weight does not broadcast over the rows");
+    const long long rows = a->ne[1] * a->ne[2] * a->ne[3];
+    if (rows == 0 || a->ne[0] == 0) return 0;
+    B200_REQUIRE(w->ne[0] == a->ne[0], "b200_op_add_rms_norm_mul: the weight must have the row length");
+    B200_CHECK(b200_launch(add_rms_norm_mul_kernel, dim3((unsigned) rows), dim3(1024), 0, (cudaStream_t) stream, false, t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
+                           sum ? t4w(sum) : t4w(dst), sum ? 1 : 0, t4(w), t4w(dst), eps));
+    return 0;
+}
+
+int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst, float scale, b200_stream_t stream) {
+    B200_REQUIRE(k && q && v && dst && k->data && q->data && v->data && dst->data && (!mask || mask->data), "b200_op_attn_decode: null tensor");
+    B200_REQUIRE(k->type == B200_TYPE_F16 && v->type == B200_TYPE_F16 && q->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && k->nb[0] == 2 && v->nb[0] == 2 && q->nb[0] == 4,
+                 "b200_op_attn_decode: f16 K / V rows, f32 q");
+    const long long hd = k->ne[0], n_kv = k->ne[1], n_head = q->ne[2], n_tok = q->ne[1];
+    B200_REQUIRE(q->ne[0] == hd && v->ne[0] == n_kv && v->ne[1] == hd && v->ne[2] == k->ne[2] && k->ne[2] > 0 && n_head % k->ne[2] == 0 && k->ne[3] == 1 && q->ne[3] == 1 &&
+                 hd % 32 == 0 && (k->nb[1] % 16) == 0 && (k->nb[2] % 16) == 0 && ((uintptr_t) k->data % 16) == 0 && (v->nb[1] % 2) == 0 && (v->nb[2] % 2) == 0, "b200_op_attn_decode: shapes");
+    B200_REQUIRE(n_kv >= 1 && n_kv <= 11000 && n_tok >= 1 && n_tok <= 65535, "b200_op_attn_decode: n_kv %lld / n_tokens %lld out of range", n_kv, n_tok);
+    B200_REQUIRE(!mask || ((mask->type == B200_TYPE_F32 || mask->type == B200_TYPE_F16) && mask->ne[0] >= n_kv && mask->ne[1] >= n_tok), "b200_op_attn_decode: bad mask");
+    B200_REQUIRE(contiguous_f(dst, 4) && nelem(dst) == hd * n_head * n_tok, "b200_op_attn_decode: dst must be the contiguous [head_dim, n_head, n_tokens] result");
+    B200_CHECK(b200_launch(attn_decode_kernel, dim3((unsigned) n_head, (unsigned) n_tok), dim3(256), (size_t) (n_kv + hd + 256) * sizeof(float), (cudaStream_t) stream, false,
+                           t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
+    return 0;
+}
+
 int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream) {
     B200_REQUIRE(a && b && dst && a->data && b->data && dst->data, "b200_op_binary: null tensor");
     B200_REQUIRE(a->type == B200_TYPE_F32 && b->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32, "b200_op_binary: f32 only");
@@ -324,8 +529,13 @@ int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b
     for (int i = 0; i < 4; ++i) B200_REQUIRE(b->ne[i] > 0 && dst->ne[i] % b->ne[i] == 0 && a->ne[i] == dst->ne[i], "b200_op_binary: src1 does not broadcast over src0");
     const long long n = nelem(dst);
     if (n == 0) return 0;
-    if (op == 0) B200_CHECK(b200_launch(binary_kernel<0>, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), t4(b), t4w(dst)));
-    else         B200_CHECK(b200_launch(binary_kernel<1>, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), t4(b), t4w(dst)));
+    const bool small = n < (1ll << 31);
+    const dim3 grid(blocks_for(n, 256));
+    cudaStream_t st = (cudaStream_t) stream;
+    if (op == 0) { if (small) B200_CHECK(b200_launch(binary_kernel<0, unsigned>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst)));
+                   else       B200_CHECK(b200_launch(binary_kernel<0, long long>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst))); }
+    else         { if (small) B200_CHECK(b200_launch(binary_kernel<1, unsigned>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst)));
+                   else       B200_CHECK(b200_launch(binary_kernel<1, long long>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst))); }
     return 0;
 }
 
@@ -338,8 +548,7 @@ int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_te
     const long long n = nelem(src) / 2;
     if (n == 0) return 0;
     RopeP rp; rp.n_dims = p->n_dims; rp.mode = p->mode; rp.freq_base = p->freq_base; rp.freq_scale = p->freq_scale; rp.attn_factor = p->attn_factor;
-    B200_CHECK(b200_launch(rope_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data,
-                           freq_factors ? (const float *) freq_factors->data : (const float *) nullptr, t4w(dst), rp));
+    B200_LAUNCH_IDX(rope_kernel, n, t4(src), (const int *) pos->data, freq_factors ? (const float *) freq_factors->data : (const float *) nullptr, t4w(dst), rp);
     return 0;
 }
 
@@ -349,7 +558,7 @@ int b200_op_set_rows(const b200_tensor * src, const b200_tensor * idx, const b20
                  "b200_op_set_rows: f32 -> f32 / f16 with i64 / i32 indices only");
     const long long n = nelem(src);
     if (n == 0) return 0;
-    B200_CHECK(b200_launch(set_rows_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4(idx), t4w(dst)));
+    B200_LAUNCH_IDX(set_rows_kernel, n, t4(src), t4(idx), t4w(dst));
     return 0;
 }
 
@@ -363,7 +572,7 @@ int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, b200_stream_t 
         B200_CHECK(cudaMemcpyAsync(dst->data, src->data, (size_t) n * (src->type == B200_TYPE_F32 ? 4 : 2), cudaMemcpyDeviceToDevice, (cudaStream_t) stream));
         return 0;
     }
-    B200_CHECK(b200_launch(cpy_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4w(dst)));
+    B200_LAUNCH_IDX(cpy_kernel, n, t4(src), t4w(dst));
     return 0;
 }
 
@@ -382,10 +591,10 @@ int b200_op_glu(const b200_tensor * a, const b200_tensor * b, const b200_tensor 
     B200_REQUIRE(a && dst && a->data && dst->data, "b200_op_glu: null tensor");
     B200_REQUIRE(a->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && (!b || b->type == B200_TYPE_F32) && a->nb[0] == 4 && (!b || b->nb[0] == 4), "b200_op_glu: f32 rows with unit stride only");
     B200_REQUIRE(glu_op >= 0 && glu_op <= 2, "b200_op_glu: op %d (0 reglu, 1 geglu, 2 swiglu)", glu_op);
-    B200_REQUIRE(b ? (a->ne[0] == dst->ne[0] && b->ne[0] == dst->ne[0]) : a->ne[0] == 2 * dst->ne[0], "b200_op_glu: shapes");
+    B200_REQUIRE(b ? (a->ne[0] == dst->ne[0] && b->ne[0] == dst->ne[0]) : a->ne[0] / 2 == dst->ne[0], "b200_op_glu: shapes");     // (an odd row length drops its last element, as the reference does)
     const long long n = nelem(dst);
     if (n == 0) return 0;
-    B200_CHECK(b200_launch(glu_kernel, dim3(blocks_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, false, t4(a), b ? t4(b) : t4(a), b ? 1 : 0, t4w(dst), glu_op, swapped));
+    B200_LAUNCH_IDX(glu_kernel, n, t4(a), b ? t4(b) : t4(a), b ? 1 : 0, t4w(dst), glu_op, swapped);
     return 0;
 }
 
