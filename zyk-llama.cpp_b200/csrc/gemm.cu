@@ -75,6 +75,7 @@ struct GemmArgs {
     const int * moe_total;      // number of units
     const int * moe_yoff;       // per gathered X row: element offset of its Y row (token * y_token_stride + slot * y_row_stride)
     long long expert_stride;    // bytes between the expert matrices (each one in the plane layout)
+    PeerGather peer;            // row split (world > 1): the epilogue stores every Y value into every rank's arena, the last CTA announces the call
 };
 
 // ---- prologue: X f32 [n][k] (row stride ldx) -> fp16 [n][k] scaled by 2^-e per row, xscale[n] = 2^e ----
@@ -414,6 +415,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
                         const int off = __shfl_sync(0xffffffffu, yo_lane, j);
                         if (row_ok && cc * 32 + j < n_left) yp[off] = val;
                     }
+                } else if (!w.split && a.peer.world > 1) {
+                    // row split: the value goes to the same place of every rank's arena (NVLink peer stores straight from the epilogue: the
+                    // exchange overlaps the MMAs of the next unit instead of following the GEMM as a copy kernel)
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = __uint_as_float(v[j]) * __shfl_sync(0xffffffffu, xs_lane, j);
+                        if (row_ok && cc * 32 + j < n_left) peer_store(a.peer, yp + (int64_t) j * ldy, val);
+                    }
                 } else if (!w.split) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
@@ -439,6 +448,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap & tmap_x, const WMap
     }
     tc_fence_before();
     if (PAIR) cluster_sync_all(); else __syncthreads();   // nobody leaves while the peer may still touch its shared memory / TMEM
+    if (!MOE && a.peer.world > 1 && a.peer.signal && threadIdx.x == 0) peer_signal(a.peer);   // every peer store of this CTA precedes the barrier above
     if (warp == 2) {
         if (PAIR) tmem_dealloc_pair(tmem_d, (uint32_t) (2 * a.acc_cols)); else tmem_dealloc(tmem_d, (uint32_t) (2 * a.acc_cols));
     }
@@ -825,8 +835,9 @@ bool b200_gemm_groupable(const b200_mul_mat_args * args, int count) {
 // the persistent grid (wq/wk/wv and ffn_gate/ffn_up: 7 -> 4 launches per layer, and the 2 x 112 tiles of gate + up fill 74 CTA
 // pairs in 3.03 waves instead of 2 x 2). args[0].flags decides whether X still has to be converted.
 int b200_gemm_launch_group(const b200_mul_mat_args * args, int count, cudaStream_t s) { return b200_gemm_launch_group_ev(args, count, s, nullptr); }
+int b200_gemm_launch_peer(const b200_mul_mat_args * a, cudaStream_t s, const PeerGather * peer) { return b200_gemm_launch_group_ev(a, 1, s, nullptr, peer); }
 
-int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStream_t s, cudaEvent_t after_prologue) {
+int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStream_t s, cudaEvent_t after_prologue, const PeerGather * peer) {
     encode_tiled_fn encode = get_encode_tiled();
     B200_REQUIRE(encode != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
     B200_REQUIRE(b200_gemm_groupable(args, count), "gemm: the %d nodes of the group do not share type / X / workspace", count);
@@ -901,7 +912,8 @@ int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStr
     int64_t full = tiles / workers * workers;
     int64_t rest = tiles - full;
     int ks = 1;
-    while (ks < 16 && rest * ks * 2 <= workers && total_sb / (ks * 2) >= 2) ks *= 2;
+    if (peer && peer->world > 1) { g.peer = *peer; rest = 0; full = tiles; }      // row split: no k-split tiles (they meet through atomics in local memory only)
+    while (rest > 0 && ks < 16 && rest * ks * 2 <= workers && total_sb / (ks * 2) >= 2) ks *= 2;
     if (const char * e = getenv("B200_GEMM_KSPLIT")) { const int v = atoi(e); if (v >= 1 && v <= 16 && total_sb >= v) { ks = v; full = 0; rest = tiles; } }
     if (ks == 1) { full = tiles; rest = 0; }
     g.full_tiles = (int) full; g.ksplit = ks; g.total_units = (int) (full + rest * ks);

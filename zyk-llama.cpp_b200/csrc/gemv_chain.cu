@@ -63,15 +63,17 @@ struct ChainMatD {
 enum { NB_NONE = 0,     // first node: stream order
        NB_FENCED = 1,   // X overlaps something an earlier node wrote: arrival counter with release / acquire fences
        NB_RELAXED = 2,  // X is written by nobody in the chain: the node is merely kept in stream order (counter, no fences)
-       NB_TAGGED = 3 }; // X is exactly the Y of a matrix of the previous node: the values arrive as 64-bit {epoch, f32} words,
+       NB_TAGGED = 3,   // X is exactly the Y of a matrix of the previous node: the values arrive as 64-bit {epoch, f32} words,
                         // each one validates itself, no counter and no fence
+       NB_RELAXED_LOCAL = 4 }; // row split only: as NB_RELAXED, but only THIS rank's CTAs are waited for (no data flows through the boundary and the
+                        // boundary before it was a tagged one, i.e. every rank has already passed the node before the previous one: see chain_plan)
 struct ChainNodeD {
     const float * x; long long ldx;
     int k, act_block, flavour;
     int mode;                             // NB_*
     const unsigned long long * xtag;      // NB_TAGGED: where the previous node publishes this X
     unsigned want;                        // counter value that means "every earlier signalling node is finished everywhere"
-    int signal;                           // what the NEXT node needs from this one: 0 nothing, 1 relaxed arrival, 2 release arrival
+    int signal;                           // what the NEXT node needs from this one: 0 nothing, 1 relaxed arrival, 2 release arrival, 3 relaxed arrival on the rank-local counter
 };
 // one ring stage worth of rows of one matrix, self-contained (the producer thread reads nothing else)
 struct ChainItemD {
@@ -92,6 +94,8 @@ struct ChainArgs {
     unsigned long long * done;      // row split: CTAs of all ranks that have finished the whole chain (never reset)
     unsigned long long * launches;  // launches of this chain so far (local): base of the counter targets and of the tags
     unsigned long long per_launch;  // arrivals one launch adds to `counter` (signalling nodes x CTAs x ranks)
+    unsigned long long * counter_local;   // row split: arrivals of the rank-local barriers (only this rank adds)
+    unsigned long long per_launch_local;
     int world, rank;                // row split over `world` GPUs (1: off): every Y row, tagged word and arrival goes to every rank,
     long long delta[B200_MAX_PEERS];//   local address + delta[g] = the same location of rank g's symmetric arena
     int n_nodes;
@@ -677,12 +681,17 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         if (nd.mode != NB_NONE && nd.mode != NB_TAGGED && tid == 0 && !(a.debug & 1)) {
             // every CTA has finished every earlier node (their arrivals are in). NB_FENCED: X overlaps what they wrote, so the
             // arrivals were releases and this is the acquire; NB_RELAXED: no data flows through this barrier
-            const unsigned long long want = arrivals0 + (unsigned long long) nd.want * (unsigned) a.world;
+            const bool local = nd.mode == NB_RELAXED_LOCAL;
+            const unsigned long long want = local ? launch * a.per_launch_local + (unsigned long long) nd.want : arrivals0 + (unsigned long long) nd.want * (unsigned) a.world;
+            const unsigned long long * cp = local ? a.counter_local : a.counter;
             unsigned long long v, t0 = 0;
             for (unsigned spin = 0;; ++spin) {
-                if (a.world > 1) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
-                else             asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
-                if (v >= want) { if (nd.mode == NB_FENCED) asm volatile("fence.acq_rel.gpu;" ::: "memory"); break; }
+                if (a.world > 1 && !local) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(cp) : "memory");
+                else                       asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(cp) : "memory");
+                if (v >= want) {
+                    if (nd.mode == NB_FENCED) { if (a.world > 1) asm volatile("fence.acq_rel.sys;" ::: "memory"); else asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+                    break;
+                }
                 if ((spin & 4095u) == 4095u) {
                     unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                     if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
@@ -754,7 +763,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
         if (tl && tid == 0) c_rel = clock64();
         cons_bar();                            // every store of this CTA is issued; a release below publishes them (cumulativity)
         if (tid == 0 && nd.signal) {
-            if (a.world > 1) {                  // (row split: relaxed arrivals only, checked at create time)
+            if (nd.signal == 3) asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter_local) : "memory");
+            else if (a.world > 1) {             // row split: the arrival goes to every rank; a fenced boundary releases this CTA's peer stores first
+                if (nd.signal == 2) asm volatile("fence.acq_rel.sys;" ::: "memory");
                 for (int g = 0; g < a.world; ++g)
                     asm volatile("red.relaxed.sys.global.add.u64 [%0], 1;" :: "l"(reinterpret_cast<char *>(a.counter) + a.delta[g]) : "memory");
             } else if (nd.signal == 2) asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter) : "memory");
@@ -1065,12 +1076,10 @@ ChainPlan chain_plan(const b200_mul_mat_args * nodes, const int32_t * group_size
         for (int i = P.first[g - 1]; i < P.first[g] && !no_tags && !all_fenced && !waw_war; ++i)
             if (nodes[i].y - lo_of(i) == a0.x && mf_of(i) == a0.k && (a0.n == 1 || nodes[i].y_row_stride == a0.x_row_stride) &&
                 every_cta_feeds(g - 1, i - P.first[g - 1])) { P.mode[g] = NB_TAGGED; P.feed[g - 1] = i - P.first[g - 1]; }
-        if (split && P.mode[g] == NB_FENCED) {
-            char buf[200];
-            snprintf(buf, sizeof buf, "group %d needs a fenced boundary (it reads or overwrites rows of an earlier group that is not its tagged predecessor): not supported with the row split", g);
-            P.error = buf;
-            return P;
-        }
+        // row split: a stream-order-only boundary need not wait for the other ranks when the boundary before it was a tagged one -- passing that one
+        // already proved that every CTA of every rank has left the node before the previous one, so the ranks stay within one node of each other
+        // and the three tag buffers (node g publishes into buffer g % 3) cannot be overwritten while a slower rank still reads them
+        if (split && P.mode[g] == NB_RELAXED && g >= 2 && P.mode[g - 1] == NB_TAGGED && !getenv("B200_CHAIN_GLOBAL_BARRIERS")) P.mode[g] = NB_RELAXED_LOCAL;
     }
     return P;
 }
@@ -1085,7 +1094,7 @@ int b200_chain_supported(const b200_mul_mat_args * nodes, const int32_t * group_
 
 size_t b200_chain_scratch_bytes(int64_t max_m_full, int ncols) {
     const int64_t tmax = ((max_m_full > 256 ? max_m_full : 256) + 255) & ~(int64_t) 255;
-    return 256 + (size_t) 2 * (size_t) (ncols > 0 ? ncols : 1) * (size_t) tmax * 8;
+    return 256 + (size_t) 3 * (size_t) (ncols > 0 ? ncols : 1) * (size_t) tmax * 8;     // counters + three tag buffers (node g publishes into buffer g % 3)
 }
 
 // host-only view of the plan a chain would get on a device with `sms` SMs (no CUDA call; pointers are only compared):
@@ -1139,24 +1148,25 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     for (int i = 0; i < first[n_groups]; ++i) tmax = mf_of(i) > tmax ? mf_of(i) : tmax;
     tmax = (tmax + 255) & ~(int64_t) 255;
     unsigned long long * d_tags = nullptr;
-    const size_t tag_bytes = (size_t) 2 * ncols * tmax * 8;
+    const size_t tag_bytes = (size_t) 3 * ncols * tmax * 8;
     if (split) {                               // tags and counters live in the symmetric arena: every rank stores into every rank's copy
         if (split->scratch_bytes < 256 + tag_bytes) { b200_set_error("b200_chain_create_split: scratch %zu < %zu bytes", split->scratch_bytes, 256 + tag_bytes); return nullptr; }
         d_tags = (unsigned long long *) ((char *) split->scratch + 256);
     } else if (cudaMalloc((void **) &d_tags, tag_bytes) != cudaSuccess || cudaMemset(d_tags, 0, tag_bytes) != cudaSuccess) {
         cudaGetLastError(); b200_set_error("b200_chain_create: cudaMalloc of %zu bytes failed", tag_bytes); return nullptr;
     }
-    unsigned signalling_total = 0;
+    unsigned signalling_total = 0, signalling_local_total = 0;
     {
-        unsigned signalling = 0;
+        unsigned signalling = 0, signalling_local = 0;      // arrivals so far on the all-ranks counter / on the rank-local counter
         for (int g = 0; g < n_groups; ++g) {
             hn[g].mode = mode[g];
-            hn[g].xtag = mode[g] == NB_TAGGED ? d_tags + (size_t) ((g - 1) & 1) * ncols * tmax : nullptr;
-            hn[g].want = signalling * (unsigned) sms;
-            hn[g].signal = g + 1 < n_groups ? (mode[g + 1] == NB_FENCED ? 2 : mode[g + 1] == NB_RELAXED ? 1 : 0) : 0;
-            if (hn[g].signal) ++signalling;
+            hn[g].xtag = mode[g] == NB_TAGGED ? d_tags + (size_t) ((g - 1) % 3) * ncols * tmax : nullptr;
+            hn[g].want = (mode[g] == NB_RELAXED_LOCAL ? signalling_local : signalling) * (unsigned) sms;
+            const int nm = g + 1 < n_groups ? mode[g + 1] : NB_NONE;
+            hn[g].signal = nm == NB_FENCED ? 2 : nm == NB_RELAXED ? 1 : nm == NB_RELAXED_LOCAL ? 3 : 0;
+            if (hn[g].signal == 3) ++signalling_local; else if (hn[g].signal) ++signalling;
         }
-        signalling_total = signalling;
+        signalling_total = signalling; signalling_local_total = signalling_local;
     }
     std::vector<std::vector<ChainItemD>> per_vc_node((size_t) VC * n_groups);
     std::vector<int> rot(VC, 0);     // gemv_chainx_kernel: tasks dealt to the warps so far, per virtual consumer (restarts with every node)
@@ -1227,7 +1237,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     ChainItemD it = {};
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
-                    it.tag = feed[g] == mi ? d_tags + (size_t) (g & 1) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
+                    it.tag = feed[g] == mi ? d_tags + (size_t) (g % 3) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
                     { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     if (P.xreg) {
                         // `S` carries the rotation: which warp gets the item's first task, so that tasks go round the warps across items
@@ -1298,6 +1308,8 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     c->args.world = world; c->args.rank = split ? split->rank : 0;
     for (int g = 0; g < B200_MAX_PEERS; ++g) c->args.delta[g] = split && g < world ? split->peer_delta[g] : 0;
     c->args.per_launch = (unsigned long long) signalling_total * (unsigned) sms * (unsigned) world;
+    c->args.counter_local = split ? (unsigned long long *) split->scratch + 16 : (unsigned long long *) db + 16;
+    c->args.per_launch_local = (unsigned long long) signalling_local_total * (unsigned) sms;
     c->args.tag_stride = tmax;
     c->args.nodes = (const ChainNodeD *) (db + o_nodes);
     c->args.items = (const ChainItemD *) (db + o_items);

@@ -189,12 +189,17 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) gemv_chainx_kernel(const Cha
         if (tl && tid == 0) tl[n * 8 + 0] = clock64();
         if (nd.mode != NB_NONE && nd.mode != NB_TAGGED && !(a.debug & 1)) {
             if (tid == 0) {
-                const unsigned long long want = arrivals0 + (unsigned long long) nd.want * (unsigned) a.world;
+                const bool local = nd.mode == NB_RELAXED_LOCAL;
+                const unsigned long long want = local ? launch * a.per_launch_local + (unsigned long long) nd.want : arrivals0 + (unsigned long long) nd.want * (unsigned) a.world;
+                const unsigned long long * cp = local ? a.counter_local : a.counter;
                 unsigned long long v, t0 = 0;
                 for (unsigned spin = 0;; ++spin) {
-                    if (a.world > 1) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
-                    else             asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(a.counter) : "memory");
-                    if (v >= want) { if (nd.mode == NB_FENCED) asm volatile("fence.acq_rel.gpu;" ::: "memory"); break; }
+                    if (a.world > 1 && !local) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(cp) : "memory");
+                    else                       asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(cp) : "memory");
+                    if (v >= want) {
+                        if (nd.mode == NB_FENCED) { if (a.world > 1) asm volatile("fence.acq_rel.sys;" ::: "memory"); else asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+                        break;
+                    }
                     if ((spin & 4095u) == 4095u) {
                         unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
                         if (t0 == 0) t0 = t; else if (t - t0 > 4000000000ull) __trap();
@@ -288,7 +293,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) gemv_chainx_kernel(const Cha
             const long long c_rel = tl ? clock64() : 0;
             cons_bar_x();
             if (tid == 0) {
-                if (a.world > 1) {
+                if (nd.signal == 3) asm volatile("red.relaxed.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter_local) : "memory");
+                else if (a.world > 1) {
+                    if (nd.signal == 2) asm volatile("fence.acq_rel.sys;" ::: "memory");
                     for (int g = 0; g < a.world; ++g)
                         asm volatile("red.relaxed.sys.global.add.u64 [%0], 1;" :: "l"(reinterpret_cast<char *>(a.counter) + a.delta[g]) : "memory");
                 } else if (nd.signal == 2) asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(a.counter) : "memory");

@@ -74,8 +74,15 @@ static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerG
     // (2) prefill: tensor-core GEMM on plane layout
     if (a->algo != 1 && fast && b200_gemm_wants(a->type, a->m, a->n, a->k, a->algo == 2)) {
         if (peer && peer->wait) B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, s, false, *peer));
+        if (!peer) return b200_gemm_launch(a, s);
+        // row split. Default: the GEMM keeps its epilogue local (k-split tiles meet through atomics in local memory) and a copy kernel sends the slice to
+        // the peers. B200_GEMM_PEER_EPILOGUE=1: the epilogue itself stores into every rank's arena and the last CTA announces the call -- measured
+        // SLOWER at N = 2 (pp512 37.9 k vs 53 k tokens/s): a rank's slices are 4 - 56 tiles for 74 CTA pairs, and without the k split they leave
+        // most SMs idle; it pays only once the same-X nodes of a rank share one launch
+        static const bool fused_epi = [] { const char * e = getenv("B200_GEMM_PEER_EPILOGUE"); return e && e[0] == '1'; }();
+        if (fused_epi) return b200_gemm_launch_peer(a, s, peer);
         const int rc = b200_gemm_launch(a, s);
-        if (rc || !peer) return rc;
+        if (rc) return rc;
         const int64_t work = (a->m % 4 == 0 ? a->m / 4 : a->m) * a->n;
         const unsigned blocks = (unsigned) (work / 256 + 1 < 148 * 8 ? work / 256 + 1 : 148 * 8);
         B200_CHECK(b200_launch(peer_scatter_kernel, dim3(blocks), dim3(256), 0, s, false, (const float *) a->y, a->y_row_stride, a->m, a->n, *peer));
