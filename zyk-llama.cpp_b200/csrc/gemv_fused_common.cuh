@@ -1,5 +1,5 @@
 // gemv_fused_common.cuh -- scaffolding of the fused decode kernel (gemv_fused.cu; also used by the cp.async-staged variant kept
-// under attic/gemv_staged.cu.txt): launch arguments, the shared-memory view of the quantised activations and the in-kernel
+// under profiles/attic/gemv_staged.cu.txt): launch arguments, the shared-memory view of the quantised activations and the in-kernel
 // activation quantiser.
 #pragma once
 #include "gemv_frag.cuh"
