@@ -41,6 +41,7 @@ enum b200_type {
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
     B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,
     B200_TYPE_Q8_K = 15,
     B200_TYPE_IQ4_XS = 23,

@@ -78,6 +78,7 @@ typedef struct { uint16_t d; uint8_t qs[16]; } blk_q4_0;                        
 typedef struct { uint16_t d; int8_t qs[32]; } blk_q8_0;                               /*  34 B */
 typedef struct { uint16_t d; uint16_t s; int8_t qs[32]; } blk_q8_1;                   /*  36 B */
 typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4_K; /* 144 B */
+typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } blk_q5_K; /* 176 B, ggml-common.h:319-333 */
 typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } blk_q6_K; /* 210 B */
 typedef struct { float d; int8_t qs[256]; int16_t bsums[16]; } blk_q8_K;              /* 292 B */
 typedef struct { uint16_t d; uint16_t scales_h; uint8_t scales_l[4]; uint8_t qs[128]; } blk_iq4_xs; /* 136 B */
@@ -89,7 +90,7 @@ static const int8_t k_iq4nl[16] = { -127, -104, -83, -65, -49, -35, -22, -10, 1,
 int orc_block_elems(int type) {
     switch (type) {
         case ORC_Q4_0: case ORC_Q8_0: case ORC_Q8_1: return QK;
-        case ORC_Q4_K: case ORC_Q6_K: case ORC_Q8_K: case ORC_IQ4_XS: return QKK;
+        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: case ORC_Q8_K: case ORC_IQ4_XS: return QKK;
         case ORC_F32: return 1;
     }
     return 0;
@@ -100,6 +101,7 @@ size_t orc_block_bytes(int type) {
         case ORC_Q8_1: return sizeof(blk_q8_1);   case ORC_Q4_K: return sizeof(blk_q4_K);
         case ORC_Q6_K: return sizeof(blk_q6_K);   case ORC_Q8_K: return sizeof(blk_q8_K);
         case ORC_IQ4_XS: return sizeof(blk_iq4_xs); case ORC_F32: return 4;
+        case ORC_Q5_K: return sizeof(blk_q5_K);
     }
     return 0;
 }
@@ -109,7 +111,7 @@ size_t orc_row_size(int type, int64_t k) { return (size_t)(k / orc_block_elems(t
 int orc_vec_dot_type(int type) {
     switch (type) {
         case ORC_Q4_0: case ORC_Q8_0: return ORC_Q8_0;
-        case ORC_Q4_K: case ORC_Q6_K: case ORC_IQ4_XS: return ORC_Q8_K;
+        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: case ORC_IQ4_XS: return ORC_Q8_K;
     }
     return -1;
 }
@@ -133,6 +135,13 @@ static int iq4xs_ls(const blk_iq4_xs * b, int ib) {
 }
 
 /* signed 6-bit value e (0..255) of a Q6_K super-block (ggml-quants.c:1774-1783) */
+/* 5-bit value l of sub-block sb (32 elements) of a Q5_K super-block: sub-blocks 2j / 2j+1 are the low / high nibbles of
+   qs[32j .. 32j+31]; bit sb of qh[l] is the fifth bit (ggml-quants.c dequantize_row_q5_K, masks u1/u2 shifted by 2 per pair) */
+static int q5k_value(const blk_q5_K * b, int sb, int l) {
+    const uint8_t q = b->qs[32 * (sb >> 1) + l];
+    return ((sb & 1) ? (q >> 4) : (q & 0x0f)) + (((b->qh[l] >> sb) & 1) << 4);
+}
+
 static int q6k_value(const blk_q6_K * b, int e) {
     const int half = e >> 7, r = e & 127, l = r & 31, quarter = r >> 5;
     const uint8_t * ql = b->ql + 64 * half;
@@ -175,6 +184,16 @@ void orc_dequantize_row(int type, const void * src, float * dst, int64_t k) {
                     const int nib = (sb & 1) ? (q[l] >> 4) : (q[l] & 0x0f);
                     dst[i * QKK + sb * 32 + l] = ds * (float) nib - ms;
                 }
+            }
+        } break;
+        case ORC_Q5_K: {   /* ggml-quants.c dequantize_row_q5_K: 4-bit nibble + bit sb of qh[l] as bit 4 */
+            const blk_q5_K * b = (const blk_q5_K *) src + i;
+            const float d = orc_fp16_to_fp32(b->d), dmin = orc_fp16_to_fp32(b->dmin);
+            for (int sb = 0; sb < 8; ++sb) {
+                int sc, mn; q4k_scale_min(b->scales, sb, &sc, &mn);
+                const float ds = d * (float) sc, ms = dmin * (float) mn;
+                for (int l = 0; l < 32; ++l)
+                    dst[i * QKK + sb * 32 + l] = ds * (float) q5k_value(b, sb, l) - ms;
             }
         } break;
         case ORC_Q6_K: {
@@ -426,6 +445,23 @@ float orc_vec_dot(int type, int64_t k, const void * w_row, const void * xq_row) 
         }
         for (int l = 0; l < 8; ++l) sumf += lanes[l];
     } break;
+    case ORC_Q5_K: {   /* ggml-cpu/quants.c ggml_vec_dot_q5_K_q8_K_generic: the Q4_K scheme over 5-bit values */
+        const blk_q5_K * w = (const blk_q5_K *) w_row; const blk_q8_K * x = (const blk_q8_K *) xq_row;
+        float lanes[8] = {0};
+        for (int64_t i = 0; i < nb; ++i) {
+            int32_t lane_acc[8] = {0}; int min_acc = 0;
+            for (int sb = 0; sb < 8; ++sb) {
+                int sc, mn; q4k_scale_min(w[i].scales, sb, &sc, &mn);
+                min_acc += mn * (x[i].bsums[2 * sb] + x[i].bsums[2 * sb + 1]);
+                for (int l = 0; l < 32; ++l)
+                    lane_acc[l & 7] += sc * (q5k_value(&w[i], sb, l) * x[i].qs[32 * sb + l]);
+            }
+            const float d = orc_fp16_to_fp32(w[i].d) * x[i].d;
+            for (int l = 0; l < 8; ++l) lanes[l] += d * (float) lane_acc[l];
+            sumf -= (orc_fp16_to_fp32(w[i].dmin) * x[i].d) * (float) min_acc;
+        }
+        for (int l = 0; l < 8; ++l) sumf += lanes[l];
+    } break;
     case ORC_Q6_K: {
         const blk_q6_K * w = (const blk_q6_K *) w_row; const blk_q8_K * x = (const blk_q8_K *) xq_row;
         float lanes[8] = {0};
@@ -516,6 +552,7 @@ void orc_mul_mat_f64(int type, int64_t m, int64_t n, int64_t k, const void * w, 
 /*   Q4_0  : QS 16 | D 2                                                                        */
 /*   Q8_0  : QS 32 | D 2                                                                        */
 /*   Q4_K  : identity (144 B blocks are already 16 B aligned; header 16 B + 128 B nibbles)       */
+/*   Q5_K  : identity (176 B = header 16 B + 32 B of fifth bits + 128 B nibbles)                 */
 /*   Q6_K  : QL 128 | QH 64 | SC 16 | D 2                                                        */
 /*   IQ4_XS: QS 128 | HDR 8 (d, scales_h, scales_l[4])                                           */
 /* ------------------------------------------------------------------------------------------ */
@@ -526,6 +563,7 @@ static int b200_planes(int type, plane_spec * ps) {
     case ORC_Q4_0:   *ps = (plane_spec){2, {2, 0}, {16, 2}}; return 1;
     case ORC_Q8_0:   *ps = (plane_spec){2, {2, 0}, {32, 2}}; return 1;
     case ORC_Q4_K:   *ps = (plane_spec){1, {0}, {144}}; return 1;
+    case ORC_Q5_K:   *ps = (plane_spec){1, {0}, {176}}; return 1;
     case ORC_Q6_K:   *ps = (plane_spec){4, {0, 128, 192, 208}, {128, 64, 16, 2}}; return 1;
     case ORC_IQ4_XS: *ps = (plane_spec){2, {8, 0}, {128, 8}}; return 1;
     }

@@ -10,7 +10,7 @@ extern "C" {
 
 /* ggml type ids (ggml/include/ggml.h:389-430) */
 enum {
-    ORC_F32 = 0, ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q8_1 = 9, ORC_Q4_K = 12, ORC_Q6_K = 14,
+    ORC_F32 = 0, ORC_Q4_0 = 2, ORC_Q8_0 = 8, ORC_Q8_1 = 9, ORC_Q4_K = 12, ORC_Q5_K = 13, ORC_Q6_K = 14,
     ORC_Q8_K = 15, ORC_IQ4_XS = 23
 };
 

@@ -21,9 +21,9 @@ import numpy as np
 
 HERE = Path(__file__).resolve().parent
 
-F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K, Q8_K, IQ4_XS = 0, 2, 8, 9, 12, 14, 15, 23
-WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS)
-TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q6_K: "q6_K",
+F32, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, IQ4_XS = 0, 2, 8, 9, 12, 13, 14, 15, 23
+WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, IQ4_XS)
+TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K",
               Q8_K: "q8_K", IQ4_XS: "iq4_xs"}
 Q8_REF, Q8_X86 = 0, 1
 
@@ -326,8 +326,8 @@ class Ref:
 # for MUL_MAT, so this covers more of the format than quantising gaussian weights does.
 # ------------------------------------------------------------------------------------------------
 def random_blocks(t: int, m: int, k: int, rng: np.random.Generator, scale: float = 0.02) -> np.ndarray:
-    elems = {Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, IQ4_XS: 256}[t]
-    bsz = {Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, IQ4_XS: 136}[t]
+    elems = {Q4_0: 32, Q8_0: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256, IQ4_XS: 256}[t]
+    bsz = {Q4_0: 18, Q8_0: 34, Q4_K: 144, Q5_K: 176, Q6_K: 210, IQ4_XS: 136}[t]
     nb = m * (k // elems)
     blk = rng.integers(0, 256, size=(nb, bsz), dtype=np.uint8)
 
@@ -341,6 +341,9 @@ def random_blocks(t: int, m: int, k: int, rng: np.random.Generator, scale: float
         put_half(0, mag(127))
     elif t == Q4_K:
         put_half(0, np.abs(mag(15 * 40)))
+        put_half(2, np.abs(mag(40)))
+    elif t == Q5_K:
+        put_half(0, np.abs(mag(31 * 40)))
         put_half(2, np.abs(mag(40)))
     elif t == Q6_K:
         put_half(208, mag(32 * 64))

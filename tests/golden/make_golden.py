@@ -11,7 +11,7 @@ import numpy as np
 
 ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
-from oracle.oracle import Ref, WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q4_0, random_blocks  # noqa: E402
+from oracle.oracle import Ref, WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q5_K, Q4_0, random_blocks  # noqa: E402
 
 
 def main():
@@ -29,7 +29,7 @@ def main():
         r = ref.quantize(q8, x, cpu_variant=False)
         if r is not None:
             out[f"xq_ref_{TYPE_NAMES[q8]}"] = r
-    for t in WEIGHT_TYPES:
+    def per_type(t):
         name = TYPE_NAMES[t]
         wf = (rng.standard_normal((m, k)) * 0.02).astype(np.float32)
         wq = ref.quantize_weights(t, wf)
@@ -50,6 +50,10 @@ def main():
         out[f"id_b1_{name}"] = b1
         out[f"id_y2_{name}"] = ref.mul_mat_id(t, as_, b2, ids)
         out[f"id_y1_{name}"] = ref.mul_mat_id(t, as_, b1, ids)
+
+    first = [t for t in WEIGHT_TYPES if t != Q5_K]      # types added later draw from the generator last: earlier vectors keep their bytes
+    for t in first:
+        per_type(t)
     # the reference CPU's own load-time repacks (CPU_REPACK buffer bytes)
     w4k = random_blocks(Q4_K, 16, 512, rng)
     d = ref.repack_dump(Q4_K, w4k, 16, 512)
@@ -61,6 +65,7 @@ def main():
     if d is not None:
         out["cpu_repack_q4_0_in"] = w40
         out["cpu_repack_q4_0_out"] = d
+    per_type(Q5_K)
     path = Path(__file__).with_name("ref_vectors.npz")
     np.savez_compressed(path, **out)
     print(f"wrote {path} ({path.stat().st_size} bytes, {len(out)} arrays; reference variant {ref.variant})")

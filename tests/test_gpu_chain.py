@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from conftest import nmse
-from oracle.oracle import Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS, TYPE_NAMES, random_blocks
+from oracle.oracle import Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, IQ4_XS, TYPE_NAMES, random_blocks
 
 pytestmark = pytest.mark.gpu
 DECODE_NMSE = 1e-10
@@ -41,6 +41,7 @@ CASES = [
     ("kquants", 2048, [(Q4_K, 1536), (Q4_K, 256), (Q6_K, 256)], 4096, [(Q4_K, 3584), (Q4_K, 3584)], 2048, Q6_K),
     ("q6k_k14336", 4096, [(Q6_K, 14336)], 4096, [(Q6_K, 1024), (Q4_K, 1024)], 2048, Q4_K),
     ("q6k_70b_shapes", 8192, [(Q6_K, 1024), (Q4_K, 27648)], 2048, [(Q6_K, 512)], 256, Q4_K),      # 32 and 112 units per row: one / two rows per tensor copy
+    ("q5k_70b_attn", 8192, [(Q4_K, 2048), (Q4_K, 256), (Q5_K, 256)], 2048, [(Q5_K, 1536), (Q4_K, 512)], 4096, Q5_K),   # 70B recipe: attn_v in Q5_K next to Q4_K
     ("iq4_xs", 1024, [(IQ4_XS, 2048), (IQ4_XS, 512), (Q6_K, 512)], 2048, [(IQ4_XS, 4096)], 1024, IQ4_XS),
     ("q4_0", 2048, [(Q4_0, 2048), (Q4_0, 512), (Q4_0, 512)], 2048, [(Q4_0, 8192), (Q4_0, 8192)], 2048, Q8_0),
     ("q8_0", 1024, [(Q8_0, 1024), (Q8_0, 256)], 512, [(Q8_0, 3072)], 1024, Q4_0),

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from conftest import nmse
-from oracle.oracle import (WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q6_K, Q8_REF, Q8_X86, random_blocks)
+from oracle.oracle import (WEIGHT_TYPES, TYPE_NAMES, Q8_0, Q8_1, Q8_K, Q4_K, Q5_K, Q6_K, Q8_REF, Q8_X86, random_blocks)
 
 pytestmark = pytest.mark.gpu
 ROOT = Path(__file__).resolve().parents[1]
@@ -127,7 +127,7 @@ def test_mul_mat_every_rows_unroll_variant(b200, orc, t, tune):
     assert nmse(got, want) < DECODE_NMSE
 
 
-@pytest.mark.parametrize("t,k", [(2, 32), (2, 96), (8, 32), (8, 160), (12, 256), (14, 256), (23, 256), (2, 8192), (8, 576)])
+@pytest.mark.parametrize("t,k", [(2, 32), (2, 96), (8, 32), (8, 160), (12, 256), (13, 256), (14, 256), (23, 256), (2, 8192), (8, 576)])
 def test_mul_mat_small_and_ragged_k(b200, orc, t, k):
     rng = np.random.default_rng(k + t)
     m = 16
@@ -377,6 +377,11 @@ def test_stream_gemv_vs_oracle(b200, orc, t, n, mk):
     x = _acts(rng, n, k)
     want = orc.mul_mat(t, w, x)
     wp = b200.repack(t, dev(w).reshape(-1), m, k)
+    if t == Q5_K:       # not in the fused kernel (register GEMV only): a forced request is refused, never served by something else
+        with pytest.raises(b200.B200Error):
+            b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=3)
+        assert nmse(b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=1).cpu().numpy(), want) < DECODE_NMSE
+        return
     got = b200.mul_mat(t, wp, dev(x), m, layout=b200.LAYOUT_PLANES, algo=3).cpu().numpy()
     assert nmse(got, want) < DECODE_NMSE
     # the register GEMV runs the same integer arithmetic: the two kernels agree to summation order

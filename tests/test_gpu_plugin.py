@@ -50,8 +50,8 @@ def test_reference_conformance_harness_all_types(op):
     import re
     m = re.search(r"(\d+)/(\d+) tests passed", tail)
     assert m and m.group(1) == m.group(2) and int(m.group(2)) >= 100, tail
-    # every one of the five block formats of the path was actually exercised (not merely declined)
-    for t in ("q4_0", "q8_0", "q4_K", "q6_K", "iq4_xs"):
+    # every one of the six block formats of the path was actually exercised (not merely declined)
+    for t in ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K", "iq4_xs"):
         ok = [ln for ln in r.stdout.splitlines() if f"type_a={t}," in ln and "OK" in ln]
         assert ok, f"no passing {op} case with type_a={t}"
 

@@ -17,7 +17,7 @@ def _call(b, fn, t, layout, w, x, m, y):
     return a, fn(C.byref(a), None)
 
 
-@pytest.mark.parametrize("tname", ["Q4_K", "Q6_K", "Q8_0", "Q4_0", "IQ4_XS"])
+@pytest.mark.parametrize("tname", ["Q4_K", "Q5_K", "Q6_K", "Q8_0", "Q4_0", "IQ4_XS"])
 def test_noalloc_matches_workspace_entry_point_twice_in_a_row(b200, orc, tname):
     import torch
     from oracle.oracle import random_blocks

@@ -20,9 +20,9 @@ from pathlib import Path
 import numpy as np
 
 ROOT = Path(__file__).resolve().parents[1]
-GGML_TYPE_NAMES = {0: "f32", 2: "q4_0", 8: "q8_0", 12: "q4_K", 14: "q6_K", 23: "iq4_xs"}
-F32, Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS = 0, 2, 8, 12, 14, 23
-BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q6_K: (256, 210), IQ4_XS: (256, 136)}
+GGML_TYPE_NAMES = {0: "f32", 2: "q4_0", 8: "q8_0", 12: "q4_K", 13: "q5_K", 14: "q6_K", 23: "iq4_xs"}
+F32, Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, IQ4_XS = 0, 2, 8, 12, 13, 14, 23
+BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), IQ4_XS: (256, 136)}
 ALIGN = 32
 # gguf value types
 T_U32, T_F32, T_STR = 4, 6, 8
@@ -70,6 +70,8 @@ def random_blocks(t: int, rows: int, k: int, rng: np.random.Generator, scale: fl
         blk[:, 0:2] = half(127)
     elif t == Q4_K:
         blk[:, 0:2] = half(15 * 40, True); blk[:, 2:4] = half(40, True)
+    elif t == Q5_K:
+        blk[:, 0:2] = half(31 * 40, True); blk[:, 2:4] = half(40, True)
     elif t == Q6_K:
         blk[:, 208:210] = half(32 * 64)
     elif t == IQ4_XS:

@@ -22,9 +22,9 @@ lib = C.CDLL(str(LIB_PATH))
 
 
 class Types:
-    F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K, Q8_K, IQ4_XS, I32 = 0, 2, 8, 9, 12, 14, 15, 23, 26
-    WEIGHTS = (Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS)
-    NAMES = {0: "f32", 2: "q4_0", 8: "q8_0", 9: "q8_1", 12: "q4_K", 14: "q6_K", 15: "q8_K", 23: "iq4_xs", 26: "i32"}
+    F32, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, IQ4_XS, I32 = 0, 2, 8, 9, 12, 13, 14, 15, 23, 26
+    WEIGHTS = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, IQ4_XS)
+    NAMES = {0: "f32", 2: "q4_0", 8: "q8_0", 9: "q8_1", 12: "q4_K", 13: "q5_K", 14: "q6_K", 15: "q8_K", 23: "iq4_xs", 26: "i32"}
 
 
 LAYOUT_CANONICAL, LAYOUT_PLANES = 0, 1

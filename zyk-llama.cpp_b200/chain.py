@@ -103,7 +103,7 @@ class MatMulChain:
         # "auto": where it is the faster path today (measured on B200: Q4_K / Q6_K models 618 -> 756 tokens/s; the Q8_0, Q4_0 and
         # IQ4_XS fragments of the chain kernel are still the eight-lanes-per-block ones and lose to the per-node kernels)
         if persistent == "auto":
-            persistent = all(o.type in (B.Types.Q4_K, B.Types.Q6_K) for o in ops)
+            persistent = all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K) for o in ops)
         if persistent and world == 1 and all(c[0] is B.lib.b200_mul_mat_group for c in self.calls):
             groups = [list(c[1]) for c in self.calls]
             if B.DecodeChain.supported(groups):

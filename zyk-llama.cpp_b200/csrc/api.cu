@@ -146,13 +146,13 @@ int b200_graph_destroy(b200_graph_t graph) { if (graph) B200_CHECK(cudaGraphExec
 
 // ---- formats (ggml/src/ggml-common.h:170-431) ---------------------------------------------------
 int b200_type_is_weight(int t) {
-    return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS;
+    return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS;
 }
 int b200_block_elems(int t) {
     switch (t) {
         case B200_TYPE_F32: case B200_TYPE_I32: return 1;
         case B200_TYPE_Q4_0: case B200_TYPE_Q8_0: case B200_TYPE_Q8_1: return 32;
-        case B200_TYPE_Q4_K: case B200_TYPE_Q6_K: case B200_TYPE_Q8_K: case B200_TYPE_IQ4_XS: return 256;
+        case B200_TYPE_Q4_K: case B200_TYPE_Q5_K: case B200_TYPE_Q6_K: case B200_TYPE_Q8_K: case B200_TYPE_IQ4_XS: return 256;
     }
     return 0;
 }
@@ -160,7 +160,7 @@ size_t b200_block_bytes(int t) {
     switch (t) {
         case B200_TYPE_F32: case B200_TYPE_I32: return 4;
         case B200_TYPE_Q4_0: return 18;  case B200_TYPE_Q8_0: return 34;  case B200_TYPE_Q8_1: return 36;
-        case B200_TYPE_Q4_K: return 144; case B200_TYPE_Q6_K: return 210; case B200_TYPE_Q8_K: return 292;
+        case B200_TYPE_Q4_K: return 144; case B200_TYPE_Q5_K: return 176; case B200_TYPE_Q6_K: return 210; case B200_TYPE_Q8_K: return 292;
         case B200_TYPE_IQ4_XS: return 136;
     }
     return 0;
@@ -172,7 +172,7 @@ size_t b200_row_size(int t, int64_t k) {
 int b200_act_type(int t) {
     switch (t) {
         case B200_TYPE_Q4_0: case B200_TYPE_Q8_0: return B200_TYPE_Q8_0;
-        case B200_TYPE_Q4_K: case B200_TYPE_Q6_K: case B200_TYPE_IQ4_XS: return B200_TYPE_Q8_K;
+        case B200_TYPE_Q4_K: case B200_TYPE_Q5_K: case B200_TYPE_Q6_K: case B200_TYPE_IQ4_XS: return B200_TYPE_Q8_K;
     }
     return -1;
 }

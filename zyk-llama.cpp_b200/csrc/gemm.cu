@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(256) zero_rows_kernel(float * __restrict__ y, 
 struct RawLoad { int map, smem_off, cstep, coff, bytes; };
 template <int TYPE> struct Raw;
 template <> struct Raw<B200_TYPE_Q4_K>   { static constexpr int BYTES = 18432, N = 1; static constexpr RawLoad L[3] = {{0, 0, 144, 0, 18432}, {}, {}}; };
+template <> struct Raw<B200_TYPE_Q5_K>   { static constexpr int BYTES = 22528, N = 1; static constexpr RawLoad L[3] = {{0, 0, 176, 0, 22528}, {}, {}}; };
 template <> struct Raw<B200_TYPE_Q6_K>   { static constexpr int BYTES = 26624, N = 3; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {1, 16384, 64, 0, 8192}, {2, 24576, 16, 0, 2048}}; };
 template <> struct Raw<B200_TYPE_IQ4_XS> { static constexpr int BYTES = 16384, N = 1; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {}, {}}; };
 template <> struct Raw<B200_TYPE_Q4_0>   { static constexpr int BYTES = 18432, N = 2; static constexpr RawLoad L[3] = {{0, 0, 128, 0, 16384}, {1, 16384, 16, 0, 2048}, {}}; };
@@ -586,6 +587,9 @@ bool make_weight_maps(int type, const GemvW & W, int64_t m, WMaps & w) {
         case B200_TYPE_Q4_K:
             ok = make_plane_map(&w.m[0], W.p0, nb * 144, rows, 144, CU_TENSOR_MAP_SWIZZLE_NONE);
             w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q5_K:
+            ok = make_plane_map(&w.m[0], W.p0, nb * 176, rows, 176, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
         case B200_TYPE_Q6_K:
             ok = make_plane_map(&w.m[0], W.p0, nb * 128, rows, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
                  make_plane_map(&w.m[1], W.p1, nb * 64, rows, 64, CU_TENSOR_MAP_SWIZZLE_64B) &&
@@ -611,6 +615,7 @@ template <int TYPE> constexpr int raw_ring_bytes() { return RAW_STAGES * Raw<TYP
 int raw_ring_bytes_of(int type) {
     switch (type) {
         case B200_TYPE_Q4_K:   return raw_ring_bytes<B200_TYPE_Q4_K>();
+        case B200_TYPE_Q5_K:   return raw_ring_bytes<B200_TYPE_Q5_K>();
         case B200_TYPE_Q6_K:   return raw_ring_bytes<B200_TYPE_Q6_K>();
         case B200_TYPE_Q8_0:   return raw_ring_bytes<B200_TYPE_Q8_0>();
         case B200_TYPE_Q4_0:   return raw_ring_bytes<B200_TYPE_Q4_0>();
@@ -709,6 +714,9 @@ bool make_weight_maps3(int type, const GemvW & W, int64_t m, int64_t e, int64_t 
     switch (type) {
         case B200_TYPE_Q4_K:
             ok = make_plane_map3(&w.m[0], W.p0, nb * 144, rows, E, S, 144, CU_TENSOR_MAP_SWIZZLE_NONE);
+            w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
+        case B200_TYPE_Q5_K:
+            ok = make_plane_map3(&w.m[0], W.p0, nb * 176, rows, E, S, 176, CU_TENSOR_MAP_SWIZZLE_NONE);
             w.m[1] = w.m[0]; w.m[2] = w.m[0]; break;
         case B200_TYPE_Q6_K:
             ok = make_plane_map3(&w.m[0], W.p0, nb * 128, rows, E, S, 128, CU_TENSOR_MAP_SWIZZLE_128B) &&
@@ -813,6 +821,7 @@ int b200_gemm_moe_launch(const b200_mul_mat_id_args * a, cudaStream_t s) {
     dim3 grid(h.pair ? 2 * nw : nw);
     switch (a->type) {
         case B200_TYPE_Q4_K:   return launch_gemm_moe<B200_TYPE_Q4_K>(tm, wm, g, grid, smem, s, h.pair);
+        case B200_TYPE_Q5_K:   return launch_gemm_moe<B200_TYPE_Q5_K>(tm, wm, g, grid, smem, s, h.pair);
         case B200_TYPE_Q6_K:   return launch_gemm_moe<B200_TYPE_Q6_K>(tm, wm, g, grid, smem, s, h.pair);
         case B200_TYPE_Q8_0:   return launch_gemm_moe<B200_TYPE_Q8_0>(tm, wm, g, grid, smem, s, h.pair);
         case B200_TYPE_Q4_0:   return launch_gemm_moe<B200_TYPE_Q4_0>(tm, wm, g, grid, smem, s, h.pair);
@@ -952,6 +961,7 @@ int b200_gemm_launch_group_ev(const b200_mul_mat_args * args, int count, cudaStr
     dim3 grid(pair ? 2 * nw : nw);
     switch (a->type) {
         case B200_TYPE_Q4_K:   return launch_gemm<B200_TYPE_Q4_K>(tm, wm, g, grid, smem, s, pair);
+        case B200_TYPE_Q5_K:   return launch_gemm<B200_TYPE_Q5_K>(tm, wm, g, grid, smem, s, pair);
         case B200_TYPE_Q6_K:   return launch_gemm<B200_TYPE_Q6_K>(tm, wm, g, grid, smem, s, pair);
         case B200_TYPE_Q8_0:   return launch_gemm<B200_TYPE_Q8_0>(tm, wm, g, grid, smem, s, pair);
         case B200_TYPE_Q4_0:   return launch_gemm<B200_TYPE_Q4_0>(tm, wm, g, grid, smem, s, pair);

@@ -89,6 +89,49 @@ template <> struct Deq<B200_TYPE_Q4_K> {
     }
 };
 
+// ---- Q5_K (canonical 176 B blocks: hdr 16 | qh 32 | qs 128; dequantize_row_q5_K, ggml-quants.c) ----------
+template <> struct Deq<B200_TYPE_Q5_K> {
+    uint4 hdr, h0, h1, q0, q1;
+    __device__ __forceinline__ void load(const GemvW & W, int64_t row, int kb) {
+        const uint8_t * b = W.p0 + (row * W.nb + (kb >> 2)) * 176;
+        hdr = ld_cached16(b); h0 = ld_cached16(b + 16); h1 = ld_cached16(b + 32);
+        q0 = ld_stream16(b + 48 + 32 * (kb & 3));
+        q1 = ld_stream16(b + 64 + 32 * (kb & 3));
+    }
+    // raw: [128][176] no swizzle (44-word rows: 8 consecutive rows x 16 B cover all 32 banks once)
+    __device__ __forceinline__ void load_smem(uint32_t raw, int r, int j, uint2) {
+        const uint32_t b = raw + (uint32_t) (r * 176);
+        hdr = raw_lds16(b); h0 = raw_lds16(b + 16); h1 = raw_lds16(b + 32);
+        q0 = raw_lds16(b + 48 + 32 * j); q1 = raw_lds16(b + 64 + 32 * j);
+    }
+    static __device__ __forceinline__ uint2 aux_load(const GemvW &, int64_t, int) { return make_uint2(0u, 0u); }
+    __device__ __forceinline__ void store(uint32_t row_addr, int r, int kb) const {
+        const int j0 = 2 * (kb & 3);
+        int sc0, sc1, m0, m1;
+        if (j0 < 4) {
+            sc0 = byte_of(hdr, 4 + j0) & 63;      m0 = byte_of(hdr, 8 + j0) & 63;
+            sc1 = byte_of(hdr, 5 + j0) & 63;      m1 = byte_of(hdr, 9 + j0) & 63;
+        } else {
+            const uint32_t a0 = byte_of(hdr, 8 + j0), a1 = byte_of(hdr, 9 + j0);
+            sc0 = (a0 & 0xf) | ((byte_of(hdr, j0) >> 6) << 4);      m0 = (a0 >> 4) | ((byte_of(hdr, 4 + j0) >> 6) << 4);
+            sc1 = (a1 & 0xf) | ((byte_of(hdr, 1 + j0) >> 6) << 4);  m1 = (a1 >> 4) | ((byte_of(hdr, 5 + j0) >> 6) << 4);
+        }
+        const float2 dm = __half22float2(u32_as_h2(hdr.x));
+        const __half2 s0 = __float2half2_rn(dm.x * (float) sc0), s1 = __float2half2_rn(dm.x * (float) sc1);
+        const __half2 c0 = __float2half2_rn(-dm.y * (float) m0), c1 = __float2half2_rn(-dm.y * (float) m1);
+        const __half2 bias = __float2half2_rn(1024.0f);
+        const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint32_t hb[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t l0 = ((hb[2 * c] >> j0) & 0x01010101u) << 4, l1 = ((hb[2 * c + 1] >> j0) & 0x01010101u) << 4;
+            const uint32_t u0 = ((hb[2 * c] >> (j0 + 1)) & 0x01010101u) << 4, u1 = ((hb[2 * c + 1] >> (j0 + 1)) & 0x01010101u) << 4;
+            emit8(row_addr, r, c,     (w[2 * c] & 0x0f0f0f0fu) | l0,        (w[2 * c + 1] & 0x0f0f0f0fu) | l1,        bias, s0, c0);
+            emit8(row_addr, r, c + 4, ((w[2 * c] >> 4) & 0x0f0f0f0fu) | u0, ((w[2 * c + 1] >> 4) & 0x0f0f0f0fu) | u1, bias, s1, c1);
+        }
+    }
+};
+
 // ---- Q6_K (planes: QL 128 | QH 64 | SC 16 | D 2) -------------------------------------------------------
 template <> struct Deq<B200_TYPE_Q6_K> {
     uint4 ql[4], qh[2], sc; uint16_t d;

@@ -158,6 +158,7 @@ int b200_gemv_launch(int type, const GemvArgs & a, int ncols, int64_t pairs, int
     gemv_pick(type, a.m, a.k, tune, &R, &U);
     switch (type) {
         case B200_TYPE_Q4_K:   return dispatch_gemv<B200_TYPE_Q4_K>(a, ncols, pairs, R, U, s);
+        case B200_TYPE_Q5_K:   return dispatch_gemv<B200_TYPE_Q5_K>(a, ncols, pairs, R, U, s);
         case B200_TYPE_Q6_K:   return dispatch_gemv<B200_TYPE_Q6_K>(a, ncols, pairs, R, U, s);
         case B200_TYPE_IQ4_XS: return dispatch_gemv<B200_TYPE_IQ4_XS>(a, ncols, pairs, R, U, s);
         case B200_TYPE_Q4_0:   return dispatch_gemv<B200_TYPE_Q4_0>(a, ncols, pairs, R, U, s);

@@ -113,6 +113,7 @@ struct ChainArgs {
 __host__ __device__ inline int plane_bytes(int type, int p) {
     switch (type) {
         case B200_TYPE_Q4_K:   return p == 0 ? 144 : 0;
+        case B200_TYPE_Q5_K:   return p == 0 ? 176 : 0;
         case B200_TYPE_Q6_K:   return p == 0 ? 128 : p == 1 ? 64 : p == 2 ? 16 : p == 3 ? 2 : 0;
         case B200_TYPE_IQ4_XS: return p == 0 ? 128 : p == 1 ? 8 : 0;
         case B200_TYPE_Q4_0:   return p == 0 ? 128 : p == 1 ? 16 : 0;
@@ -350,6 +351,53 @@ __device__ __forceinline__ void unit_q4k(uint32_t wb, uint32_t xb, int x_col_str
     }
 }
 
+// ---- Q5_K: one 256-block per lane; the Q4_K scheme over 5-bit values (fifth bit: bit j of qh[l] for sub-block j) ----------
+// block bytes (ggml-common.h:319-333): d, dmin, scales[12], qh[32], qs[128]; arithmetic of ggml_vec_dot_q5_K_q8_K
+template <int NCOLS>
+__device__ __forceinline__ void unit_q5k(uint32_t wb, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint4 hdr = lds16(wb), h0 = lds16(wb + 16), h1 = lds16(wb + 32);
+    const uint32_t sc03 = hdr.y & 0x3f3f3f3fu, mn03 = hdr.z & 0x3f3f3f3fu;
+    const uint32_t sc47 = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+    const uint32_t mn47 = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+    const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
+    int isum[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) isum[c] = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 qa = lds16(wb + 48 + 32 * j), qb = lds16(wb + 64 + 32 * j);
+        const uint4 fa = and4(shr4(h0, 2 * j), 0x03030303u), fb = and4(shr4(h1, 2 * j), 0x03030303u);   // bit 0: sub-block 2j, bit 1: 2j + 1
+        const uint4 la = make_uint4((qa.x & 0x0f0f0f0fu) | ((fa.x & 0x01010101u) << 4), (qa.y & 0x0f0f0f0fu) | ((fa.y & 0x01010101u) << 4),
+                                    (qa.z & 0x0f0f0f0fu) | ((fa.z & 0x01010101u) << 4), (qa.w & 0x0f0f0f0fu) | ((fa.w & 0x01010101u) << 4));
+        const uint4 lb = make_uint4((qb.x & 0x0f0f0f0fu) | ((fb.x & 0x01010101u) << 4), (qb.y & 0x0f0f0f0fu) | ((fb.y & 0x01010101u) << 4),
+                                    (qb.z & 0x0f0f0f0fu) | ((fb.z & 0x01010101u) << 4), (qb.w & 0x0f0f0f0fu) | ((fb.w & 0x01010101u) << 4));
+        const uint4 ha = make_uint4(((qa.x >> 4) & 0x0f0f0f0fu) | ((fa.x & 0x02020202u) << 3), ((qa.y >> 4) & 0x0f0f0f0fu) | ((fa.y & 0x02020202u) << 3),
+                                    ((qa.z >> 4) & 0x0f0f0f0fu) | ((fa.z & 0x02020202u) << 3), ((qa.w >> 4) & 0x0f0f0f0fu) | ((fa.w & 0x02020202u) << 3));
+        const uint4 hb = make_uint4(((qb.x >> 4) & 0x0f0f0f0fu) | ((fb.x & 0x02020202u) << 3), ((qb.y >> 4) & 0x0f0f0f0fu) | ((fb.y & 0x02020202u) << 3),
+                                    ((qb.z >> 4) & 0x0f0f0f0fu) | ((fb.z & 0x02020202u) << 3), ((qb.w >> 4) & 0x0f0f0f0fu) | ((fb.w & 0x02020202u) << 3));
+        const uint32_t scw = j < 2 ? sc03 : sc47;
+        const int s0 = (int) ((scw >> (16 * (j & 1))) & 0xffu), s1 = (int) ((scw >> (16 * (j & 1) + 8)) & 0xffu);
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+            const uint4 x0 = lds16(xc + xpos(4 * j) * 16), x1 = lds16(xc + xpos(4 * j + 1) * 16);
+            const uint4 x2 = lds16(xc + xpos(4 * j + 2) * 16), x3 = lds16(xc + xpos(4 * j + 3) * 16);
+            isum[c] += s0 * (dot16(la, x0) + dot16(lb, x1)) + s1 * (dot16(ha, x2) + dot16(hb, x3));
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+        const uint4 bs = lds16(xc + XU_BS32);
+        int msum = __dp2a_lo((int) bs.x, (int) mn03, 0);
+        msum = __dp2a_hi((int) bs.y, (int) mn03, msum);
+        msum = __dp2a_lo((int) bs.z, (int) mn47, msum);
+        msum = __dp2a_hi((int) bs.w, (int) mn47, msum);
+        const float dx = ldsf(xc + XU_D);
+        acc[c] += dx * (dm.x * (float) isum[c] - dm.y * (float) msum);
+    }
+}
+
 // ---- Q6_K: eight lanes per 256-block, planes QL 128 | QH 64 | SC 16 | D 2 ---------------------------------------------
 // arithmetic of ggml_vec_dot_q6_K_q8_K (ggml-cpu/quants.c:705-760); lane g owns elements e0 + [0,16) and e0 + 64 + [0,16),
 // e0 = 128 (g >> 2) + 32 ((g >> 1) & 1) + 16 (g & 1) (dequantize_row_q6_K, ggml-quants.c:1762-1792)
@@ -521,12 +569,14 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
     }
 }
 
-template <bool Q6, int NCOLS>
+constexpr int LU_Q4K = 0, LU_Q6K = 1, LU_Q5K = 2;       // block-per-lane formats
+template <int Q6, int NCOLS>
 __device__ __forceinline__ void lane_unit(uint32_t stage, int nunits, int u, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
-    if constexpr (Q6) unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
-    else              unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
+    if constexpr (Q6 == LU_Q6K)      unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
+    else if constexpr (Q6 == LU_Q5K) unit_q5k<NCOLS>(stage + (uint32_t) u * 176, xb, x_col_stride, acc);
+    else                             unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
 }
-template <int NCOLS, bool Q6 = false>
+template <int NCOLS, int Q6 = LU_Q4K>
 __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride,
                                          const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane,
                                          int rp, int sub, int b) {
@@ -732,7 +782,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
             } else if (type == B200_TYPE_Q4_K) {
                 item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
             } else if (type == CH_T_Q6K_SW) {
-                item_q4k<NCOLS, true>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+                item_q4k<NCOLS, LU_Q6K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+            } else if (type == B200_TYPE_Q5_K) {
+                item_q4k<NCOLS, LU_Q5K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q6_K) {
                 item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
             } else if (type == B200_TYPE_IQ4_XS) {
@@ -818,7 +870,7 @@ struct Chain {
 int cx_nw() { static const int v = [] { const char * e = getenv("B200_CHAIN_NW"); const int n = e ? atoi(e) : 8; return n == 12 ? 12 : 8; }(); return v; }
 #define CX_NW cx_nw()
 
-bool chain_type_ok(int t) { return t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0; }
+bool chain_type_ok(int t) { return t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K || t == B200_TYPE_IQ4_XS || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0; }
 int gcd_i(int a, int b) { while (b) { int t = a % b; a = b; b = t; } return a; }
 // rows of one item must keep every plane piece a multiple of 16 bytes, in size and in source address
 int row_granule(int type, int upr) {
@@ -909,7 +961,7 @@ const char * chain_check(const b200_mul_mat_args * nodes, const int32_t * group_
             if (a.m < (split ? 0 : 1) || a.m > (1 << 30)) return "m out of range";      // a rank's slice of a small matrix may be empty
             if (a.x != a0.x || a.k != a0.k || a.x_row_stride != a0.x_row_stride || a.flavour != a0.flavour) return "nodes of a group must read the same X";
             if (b200_act_type(a.type) != b200_act_type(a0.type)) return "nodes of a group need the same activation format";
-            if (a.layout != B200_LAYOUT_PLANES && a.type != B200_TYPE_Q4_K) return "plane layout required";
+            if (a.layout != B200_LAYOUT_PLANES && a.type != B200_TYPE_Q4_K && a.type != B200_TYPE_Q5_K) return "plane layout required";
             if (a.w_row_stride != 0 && a.w_row_stride != (int64_t) b200_row_size(a.type, a.k)) return "packed rows required";
             if ((((uintptr_t) a.w) & 15) != 0) return "weights must be 16 B aligned";
             if (a.m % row_granule(a.type, (int) (a.k >> 8)) != 0) return "row count incompatible with 16-byte plane pieces";
@@ -1238,7 +1290,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
                     it.tag = feed[g] == mi ? d_tags + (size_t) (g % 3) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
-                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     if (P.xreg) {
                         // `S` carries the rotation: which warp gets the item's first task, so that tasks go round the warps across items
                         if (it.segs == 1) { const int rp = 32 / upr; it.S = rot[vc] % CX_NW; rot[vc] = (rot[vc] + (it.nrows + rp - 1) / rp) % CX_NW; }

@@ -12,7 +12,7 @@
 
 // the weight matrix as the kernels see it
 struct GemvW {
-    const uint8_t * p0;   // Q4_0/Q8_0/IQ4_XS: QS plane | Q6_K: QL plane | Q4_K: blocks
+    const uint8_t * p0;   // Q4_0/Q8_0/IQ4_XS: QS plane | Q6_K: QL plane | Q4_K, Q5_K: blocks
     const uint8_t * p1;   // Q4_0/Q8_0: D plane | Q6_K: QH plane | IQ4_XS: HDR plane
     const uint8_t * p2;   // Q6_K: SC plane
     const uint8_t * p3;   // Q6_K: D plane
@@ -49,6 +49,7 @@ template <int TYPE> struct Fmt;
 
 // element offsets (inside the lane's 256- or 32-element block) of run0 / run1
 template <> struct Fmt<B200_TYPE_Q4_K>   { static constexpr int BLK = 256; __device__ static int off0(int g) { return 64 * (g >> 1) + 16 * (g & 1); } static constexpr int RUN1 = 32; };
+template <> struct Fmt<B200_TYPE_Q5_K>   { static constexpr int BLK = 256; __device__ static int off0(int g) { return 64 * (g >> 1) + 16 * (g & 1); } static constexpr int RUN1 = 32; };
 template <> struct Fmt<B200_TYPE_Q6_K>   { static constexpr int BLK = 256; __device__ static int off0(int g) { return 128 * (g >> 2) + 32 * ((g >> 1) & 1) + 16 * (g & 1); } static constexpr int RUN1 = 64; };
 template <> struct Fmt<B200_TYPE_IQ4_XS> { static constexpr int BLK = 256; __device__ static int off0(int g) { return 32 * g; } static constexpr int RUN1 = 16; };
 template <> struct Fmt<B200_TYPE_Q4_0>   { static constexpr int BLK = 32;  __device__ static int off0(int) { return 0; } static constexpr int RUN1 = 16; };
@@ -115,6 +116,39 @@ template <> struct WFrag<B200_TYPE_Q4_K> {
             dhi = dp4a_us(hi.z, x[c].x1.z, dhi);
             dhi = dp4a_us(hi.w, x[c].x1.w, dhi);
             const int isum = sc0 * dot16(lo, x[c].x0) + sc1 * (dhi >> 4);
+            const int msum = m0 * x[c].bs0 + m1 * x[c].bs1;
+            acc[c] += x[c].dx * (dm.x * (float) isum - dm.y * (float) msum);
+        }
+    }
+};
+
+// ---- Q5_K: canonical 176 B blocks {d, dmin, scales[12], qh[32], qs[128]} (ggml-common.h:319-333) ----
+// Same sub-block geometry as Q4_K; bit j of qh[l] is the fifth bit of element l of sub-block j
+// (ggml-cpu/quants.c ggml_vec_dot_q5_K_q8_K_generic builds the same 0..31 values before the int8 products).
+template <> struct WFrag<B200_TYPE_Q5_K> {
+    uint4 hdr, h, q;
+    __device__ __forceinline__ void load(const GemvW & W, int64_t row, int64_t blk, int g) {
+        const uint8_t * b = W.p0 + (row * W.nb + blk) * 176;
+        hdr = ld_stream16(b);
+        h = ld_stream16(b + 16 + 16 * (g & 1));
+        q = ld_stream16(b + 48 + 16 * g);
+    }
+    template <int NCOLS>
+    __device__ __forceinline__ void dot(const XFrag (&x)[NCOLS], float (&acc)[NCOLS], int g) const {
+        const int sh = (g & 2) << 3;
+        const uint32_t y16 = (hdr.y >> sh) & 0xffffu, z16 = (hdr.z >> sh) & 0xffffu, w16 = (hdr.w >> sh) & 0xffffu;
+        const bool upper = g >= 4;
+        const uint32_t sc = upper ? ((w16 & 0x0f0fu) | ((y16 >> 2) & 0x3030u)) : (y16 & 0x3f3fu);
+        const uint32_t mn = upper ? (((w16 >> 4) & 0x0f0fu) | ((z16 >> 2) & 0x3030u)) : (z16 & 0x3f3fu);
+        const int sc0 = (int) (sc & 0xffu), sc1 = (int) (sc >> 8), m0 = (int) (mn & 0xffu), m1 = (int) (mn >> 8);
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&hdr.x));
+        const int j0 = g & 6;                                          // sub-block of the low nibbles; the high nibbles are j0 + 1
+        const uint4 b0 = and4(shr4(h, j0), 0x01010101u), b1 = and4(shr4(h, j0 + 1), 0x01010101u);
+        const uint4 lo = make_uint4((q.x & 0x0f0f0f0fu) | (b0.x << 4), (q.y & 0x0f0f0f0fu) | (b0.y << 4), (q.z & 0x0f0f0f0fu) | (b0.z << 4), (q.w & 0x0f0f0f0fu) | (b0.w << 4));
+        const uint4 hi = make_uint4(((q.x >> 4) & 0x0f0f0f0fu) | (b1.x << 4), ((q.y >> 4) & 0x0f0f0f0fu) | (b1.y << 4), ((q.z >> 4) & 0x0f0f0f0fu) | (b1.z << 4), ((q.w >> 4) & 0x0f0f0f0fu) | (b1.w << 4));
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const int isum = sc0 * dot16(lo, x[c].x0) + sc1 * dot16(hi, x[c].x1);
             const int msum = m0 * x[c].bs0 + m1 * x[c].bs1;
             acc[c] += x[c].dx * (dm.x * (float) isum - dm.y * (float) msum);
         }

@@ -158,6 +158,7 @@ bool b200_gemv_stream_wants(const GemvGroup & g, bool force) {
     const int act = b200_act_type(g.type[0]);
     for (int i = 0; i < g.count; ++i) {
         if (b200_act_type(g.type[i]) != act || g.m[i] <= 0) return false;
+        if (g.type[i] == B200_TYPE_Q5_K) return false;   // register GEMV only: keeps the fused kernel's code size where it was
         if ((((uintptr_t) g.w[i]) & 15) != 0) return false;
     }
     const int B = act == B200_TYPE_Q8_K ? 256 : 32;

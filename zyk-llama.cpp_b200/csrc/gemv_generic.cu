@@ -37,6 +37,20 @@ __device__ float group_dot(const uint8_t * __restrict__ wrow, int64_t sb, const 
         int s = 0;
         for (int l = 0; l < 32; ++l) { const int v = ld_u8(q + l); s += ((j & 1) ? (v >> 4) : (v & 15)) * x[l]; }
         return dx * (ld_f16(b) * (float) (scale * s) - ld_f16(b + 2) * (float) (mn * bsum));
+    } else if (TYPE == B200_TYPE_Q5_K) {
+        const uint8_t * b = wrow + (sb >> 3) * 176;
+        const int j = (int) (sb & 7);
+        const uint8_t * sc = b + 4;
+        int scale, mn;
+        if (j < 4) { scale = ld_u8(sc + j) & 63; mn = ld_u8(sc + j + 4) & 63; }
+        else { scale = (ld_u8(sc + j + 4) & 15) | ((ld_u8(sc + j - 4) >> 6) << 4); mn = (ld_u8(sc + j + 4) >> 4) | ((ld_u8(sc + j) >> 6) << 4); }
+        const uint8_t * q = b + 48 + 32 * (j >> 1);
+        int s = 0;
+        for (int l = 0; l < 32; ++l) {
+            const int v = ld_u8(q + l);
+            s += (((j & 1) ? (v >> 4) : (v & 15)) | (((ld_u8(b + 16 + l) >> j) & 1) << 4)) * x[l];
+        }
+        return dx * (ld_f16(b) * (float) (scale * s) - ld_f16(b + 2) * (float) (mn * bsum));
     } else if (TYPE == B200_TYPE_Q6_K) {
         const uint8_t * b = wrow + (sb >> 3) * 210;
         const int q32 = (int) (sb & 7);            // which 32-element quarter of the 256 block
@@ -99,7 +113,7 @@ int b200_gemv_generic_launch(int type, const GemvGenericArgs & a, int64_t pairs,
     dim3 grid((unsigned) ((a.m + 3) / 4), (unsigned) pairs);
 #define B200_GEN(T) case T: B200_CHECK(b200_launch(gemv_generic_kernel<T>, grid, dim3(128), 0, s, a.pdl != 0, a)); return 0
     switch (type) {
-        B200_GEN(B200_TYPE_Q4_0); B200_GEN(B200_TYPE_Q8_0); B200_GEN(B200_TYPE_Q4_K); B200_GEN(B200_TYPE_Q6_K); B200_GEN(B200_TYPE_IQ4_XS);
+        B200_GEN(B200_TYPE_Q4_0); B200_GEN(B200_TYPE_Q8_0); B200_GEN(B200_TYPE_Q4_K); B200_GEN(B200_TYPE_Q5_K); B200_GEN(B200_TYPE_Q6_K); B200_GEN(B200_TYPE_IQ4_XS);
     }
 #undef B200_GEN
     b200_set_error("gemv_generic: unsupported weight type %d", type);

@@ -661,7 +661,7 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     for (auto & a : args) { a.workspace = bc->workspace; a.workspace_size = bc->workspace_size; }
 
     bool kquant = true;
-    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q6_K);
+    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q5_K || a.type == B200_TYPE_Q6_K);
     if (chain_on && kquant && args[0].n <= 4 && sizes.size() >= 2 && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
         b200_chain_t chain = nullptr;
         for (auto & c : bc->chains)

@@ -62,6 +62,18 @@ __device__ __forceinline__ float deq_one(int type, const uint8_t * row, long lon
             const uint8_t qb = b[16 + 32 * g + l];
             return d * (float) s * (float) (hi ? (qb >> 4) : (qb & 0x0f)) - dmin * (float) m;
         }
+        case B200_TYPE_Q5_K: {
+            const uint8_t * b = row + (e >> 8) * 176; const int r = (int) (e & 255);
+            const int g = r >> 6, hi = (r >> 5) & 1, l = r & 31, is = 2 * g + hi;
+            const uint8_t * sc = b + 4;
+            int s, m;
+            if (is < 4) { s = sc[is] & 63; m = sc[is + 4] & 63; }
+            else { s = (sc[is + 4] & 0x0f) | ((sc[is - 4] >> 6) << 4); m = (sc[is + 4] >> 4) | ((sc[is] >> 6) << 4); }
+            const float d = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b)), dmin = half_bits_to_float(*reinterpret_cast<const uint16_t *>(b + 2));
+            const uint8_t qb = b[48 + 32 * g + l];
+            const int v = (hi ? (qb >> 4) : (qb & 0x0f)) | (((b[16 + l] >> is) & 1) << 4);
+            return d * (float) s * (float) v - dmin * (float) m;
+        }
         case B200_TYPE_Q6_K: {
             const uint8_t * b = row + (e >> 8) * 210; const int r = (int) (e & 255);
             const int n = r >> 7, rr = r & 127, quarter = rr >> 5, l = rr & 31;

@@ -10,7 +10,7 @@ static bool planes_fast_path(int type, int layout, int64_t m, int64_t k, const v
     const bool packed = w_row_stride == 0 || w_row_stride == (int64_t) b200_row_size(type, k);
     if (!packed || (k % 256) != 0 || (((uintptr_t) w) & 15) != 0) return false;
     if (layout == B200_LAYOUT_PLANES) return true;
-    return type == B200_TYPE_Q4_K;   // canonical Q4_K is its own plane layout
+    return type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K;   // canonical Q4_K / Q5_K are their own plane layout
     (void) m;
 }
 

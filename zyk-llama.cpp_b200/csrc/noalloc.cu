@@ -71,7 +71,7 @@ int b200_mul_mat_noalloc(const b200_mul_mat_args * a, b200_stream_t stream) {
     const bool pdl = (a->flags & B200_MM_PDL) != 0;
     const bool packed = a->w_row_stride == 0 || a->w_row_stride == (int64_t) b200_row_size(a->type, a->k);
     const bool fast = packed && (a->k % 256) == 0 && (((uintptr_t) a->w) & 15) == 0 &&
-                      (a->layout == B200_LAYOUT_PLANES || a->type == B200_TYPE_Q4_K);
+                      (a->layout == B200_LAYOUT_PLANES || a->type == B200_TYPE_Q4_K || a->type == B200_TYPE_Q5_K);
     B200_REQUIRE(fast || a->layout == B200_LAYOUT_CANONICAL, "b200_mul_mat_noalloc: plane layout with unsupported stride/alignment");
 
     const XqPlanes pl = xq_planes_carve(scratch, act, a->n, a->k);

@@ -25,6 +25,7 @@ static inline bool plane_spec(int type, PlaneSpec * ps) {
         case B200_TYPE_Q4_0:   { const int o[] = {2, 0},             l[] = {16, 2};           set(18, 2, o, l);  return true; }
         case B200_TYPE_Q8_0:   { const int o[] = {2, 0},             l[] = {32, 2};           set(34, 2, o, l);  return true; }
         case B200_TYPE_Q4_K:   { const int o[] = {0},                l[] = {144};             set(144, 1, o, l); return true; }
+        case B200_TYPE_Q5_K:   { const int o[] = {0},                l[] = {176};             set(176, 1, o, l); return true; }
         case B200_TYPE_Q6_K:   { const int o[] = {0, 128, 192, 208}, l[] = {128, 64, 16, 2};  set(210, 4, o, l); return true; }
         case B200_TYPE_IQ4_XS: { const int o[] = {8, 0},             l[] = {128, 8};          set(136, 2, o, l); return true; }
     }

@@ -12,8 +12,8 @@ from dataclasses import dataclass
 
 import torch
 
-F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K, Q8_K, IQ4_XS = 0, 2, 8, 9, 12, 14, 15, 23
-BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q6_K: (256, 210), IQ4_XS: (256, 136)}
+F32, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, IQ4_XS = 0, 2, 8, 9, 12, 13, 14, 15, 23
+BLOCK = {Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), IQ4_XS: (256, 136)}
 
 
 def row_bytes(t: int, k: int) -> int:
@@ -61,6 +61,8 @@ def llama_dense(n_layer: int, n_embd: int, n_ff: int, n_head: int, n_kv: int, n_
         tv = Q6_K if more else base
         td = Q6_K if more else base
         tk = base
+        if n_layer == 80 and tv == Q4_K:            # llama-quant.cpp:305-310: the 70B model (8 heads share attn_v) takes Q5_K where Q4_K was due
+            tv = Q5_K
         if n_expert == 8 and ftype == "q4_k_m":     # llama-quant.cpp:311-322: 8-expert models keep attn_k/attn_v in Q8_0
             tv = tk = Q8_0
         p = f"blk.{i}."
@@ -146,6 +148,9 @@ def random_weight(t: int, m: int, k: int, device, gen: torch.Generator, scale: f
             blk[:, 0:2] = half_field(nb, 127)
         elif t == Q4_K:
             blk[:, 0:2] = half_field(nb, 15 * 40, True)
+            blk[:, 2:4] = half_field(nb, 40, True)
+        elif t == Q5_K:
+            blk[:, 0:2] = half_field(nb, 31 * 40, True)
             blk[:, 2:4] = half_field(nb, 40, True)
         elif t == Q6_K:
             blk[:, 208:210] = half_field(nb, 32 * 64)
