@@ -90,6 +90,11 @@ B200_API int  b200_memcpy_d2h(void * host_dst, const void * src, size_t bytes, b
 B200_API int  b200_memcpy_d2d(void * dst, const void * src, size_t bytes, b200_stream_t stream);
 B200_API int  b200_memcpy_peer(void * dst, int dst_device, const void * src, int src_device, size_t bytes, b200_stream_t stream);
 B200_API int  b200_memset(void * dst, int value, size_t bytes, b200_stream_t stream);
+/* strided copy between any two devices of this process / the host, unified addressing (ggml_cuda_Memcpy2DPeerAsync, ggml-cuda.cu:1403-1436) */
+B200_API int  b200_memcpy2d(void * dst, size_t dpitch, const void * src, size_t spitch, size_t width, size_t height, b200_stream_t stream);
+/* kernels of `device` may load / store the memory of `peer` afterwards (ggml_cuda_set_peer_access, ggml-cuda.cu:1438-1480); -1 when the
+   two devices have no peer path */
+B200_API int  b200_enable_peer_access(int device, int peer);
 /* device_i::event_new/free/synchronize, backend_i::event_record/event_wait (ggml-backend-impl.h:112-116,178-181) */
 B200_API b200_event_t b200_event_create(int device);
 B200_API int  b200_event_destroy(b200_event_t ev);

@@ -38,6 +38,12 @@ static Run open_model(const char * path, int ngl, int n_ctx) {
     llama_model_params mp = llama_model_default_params();
     mp.n_gpu_layers = ngl;
     mp.use_mmap = false;
+    // LLAMA_LOGITS_SPLIT=row: weights through the backend's "ggml_backend_split_buffer_type" proc (llama-bench -sm row); =none: one device
+    if (const char * sm = getenv("LLAMA_LOGITS_SPLIT")) {
+        if (!strcmp(sm, "row")) mp.split_mode = LLAMA_SPLIT_MODE_ROW;
+        else if (!strcmp(sm, "none")) mp.split_mode = LLAMA_SPLIT_MODE_NONE;
+        else mp.split_mode = LLAMA_SPLIT_MODE_LAYER;
+    }
     Run r = {};
     r.model = llama_model_load_from_file(path, mp);
     if (!r.model) { fprintf(stderr, "cannot load %s (ngl %d)\n", path, ngl); exit(2); }

@@ -82,6 +82,23 @@ def test_whole_llama_graph_logits_match_reference_cpu_backend(tiny_gguf, mode, n
     assert r.returncode == 0 and "LLAMA_LOGITS_CHECK OK" in r.stdout, r.stdout[-3000:]
 
 
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("graphs", ["1", "0"], ids=["cuda-graphs", "eager"])
+def test_row_split_buffer_type_logits_match_reference_cpu_backend(tiny_gguf, graphs):
+    """`-sm row` through the reference's loader: llama-model.cpp:388-410 asks the registry for "ggml_backend_split_buffer_type" and puts the
+    MUL_MAT weights there. One GPU: every row stays on the main device, the split buffer's init_tensor / set_tensor / compute path is
+    still the one that runs. Two or more GPUs (gpurun --gpus N): rows are spread, Y arrives by peer stores. Same logits bar as above."""
+    env = _need("llama_logits_check")
+    env.update({"LLAMA_LOGITS_SPLIT": "row", "GGML_B200_GRAPHS": graphs})
+    r = subprocess.run([str(VAR / "llama_logits_check"), str(tiny_gguf), "40", "6"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0 and "LLAMA_LOGITS_CHECK OK" in r.stdout, r.stdout[-3000:]
+    assert "_Split" in r.stdout, "the loader did not place any tensor in the split buffer type:\n" + r.stdout[-3000:]
+
+
 GLUE_OPS = ["GET_ROWS", "RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "ROPE", "SET_ROWS", "CPY", "CONT", "DUP", "SOFT_MAX", "SWIGLU", "GEGLU", "REGLU"]
 
 

@@ -103,6 +103,24 @@ int b200_memcpy_peer(void * dst, int dst_device, const void * src, int src_devic
     if (n) B200_CHECK(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, n, (cudaStream_t) s));
     return 0;
 }
+int b200_memcpy2d(void * dst, size_t dpitch, const void * src, size_t spitch, size_t width, size_t height, b200_stream_t s) {
+    if (width && height) B200_CHECK(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyDefault, (cudaStream_t) s));
+    return 0;
+}
+int b200_enable_peer_access(int device, int peer) {
+    if (device == peer) return 0;
+    int can = 0;
+    B200_CHECK(cudaDeviceCanAccessPeer(&can, device, peer));
+    if (!can) { b200_set_error("device %d cannot access the memory of device %d", device, peer); return -1; }
+    int cur = 0;
+    B200_CHECK(cudaGetDevice(&cur));
+    B200_CHECK(cudaSetDevice(device));
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) (void) cudaGetLastError();
+    else if (e != cudaSuccess) { cudaSetDevice(cur); b200_set_error("cudaDeviceEnablePeerAccess(%d -> %d): %s", device, peer, cudaGetErrorString(e)); return -1; }
+    B200_CHECK(cudaSetDevice(cur));
+    return 0;
+}
 int b200_memset(void * dst, int value, size_t n, b200_stream_t s) {
     if (n) B200_CHECK(cudaMemsetAsync(dst, value, n, (cudaStream_t) s));
     return 0;

@@ -31,6 +31,17 @@ void b200_count_launch(void);
     } while (0)
 
 // every kernel launch of this library goes through here (launch counter + PDL attribute)
+// "first launch of this kernel on the CURRENT device": function attributes (dynamic shared memory size) are per device, and one process may
+// drive several GPUs (the plugin's row-split buffer type). `mask` is a function-local static of the caller.
+static inline bool b200_first_on_device(unsigned & mask) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned bit = 1u << (dev & 31);
+    if (mask & bit) return false;
+    mask |= bit;
+    return true;
+}
+
 template <typename... KArgs, typename... Args>
 static inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                       cudaStream_t stream, bool pdl, Args... args) {

@@ -626,11 +626,10 @@ int raw_ring_bytes_of(int type) {
 
 template <int TYPE>
 int launch_gemm(const CUtensorMap & tm, const WMapSet & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
-    static bool configured = false;
-    if (!configured) {
+    static unsigned configured = 0;
+    if (b200_first_on_device(configured)) {
         B200_CHECK(cudaFuncSetAttribute(gemm_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         B200_CHECK(cudaFuncSetAttribute(gemm_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
-        configured = true;
     }
     if (pair) B200_CHECK(b200_launch(gemm_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, g.pdl != 0, tm, w, g));
     else      B200_CHECK(b200_launch(gemm_kernel<TYPE>, grid, dim3(THREADS), smem, s, g.pdl != 0, tm, w, g));
@@ -689,11 +688,10 @@ MoeCarve moe_carve(void * ws, int64_t k, int64_t n_as, const MoeShape & h) {
 }
 template <int TYPE>
 int launch_gemm_moe(const CUtensorMap & tm, const WMapSet & w, const GemmArgs & g, dim3 grid, size_t smem, cudaStream_t s, bool pair) {
-    static bool configured = false;
-    if (!configured) {
+    static unsigned configured = 0;
+    if (b200_first_on_device(configured)) {
         B200_CHECK(cudaFuncSetAttribute(gemm_moe_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
         B200_CHECK(cudaFuncSetAttribute(gemm_moe_pair_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SMEM_BUDGET + 1024)));
-        configured = true;
     }
     if (pair) B200_CHECK(b200_launch(gemm_moe_pair_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));
     else      B200_CHECK(b200_launch(gemm_moe_kernel<TYPE>, grid, dim3(THREADS), smem, s, false, tm, w, g));

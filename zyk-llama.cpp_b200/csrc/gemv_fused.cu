@@ -137,11 +137,10 @@ __global__ void __launch_bounds__(FTHREADS, 2) gemv_fused_kernel(const FusedArgs
 
 template <int NCOLS>
 int launch_fused(const FusedArgs & a, int grid, size_t smem, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
+    static unsigned configured = 0;
+    if (b200_first_on_device(configured)) {
         B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS, KV_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         B200_CHECK(cudaFuncSetAttribute(gemv_fused_kernel<NCOLS, KV_PEER>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        configured = true;
     }
     if (a.peer.world > 1) B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS, KV_PEER>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));
     else                  B200_CHECK(b200_launch(gemv_fused_kernel<NCOLS, KV_PLAIN>, dim3((unsigned) grid), dim3(FTHREADS), smem, s, a.pdl != 0, a));

@@ -4,8 +4,11 @@
 //
 // What the device claims (supports_op): the layout no-ops (NONE / VIEW / RESHAPE / PERMUTE /
 // TRANSPOSE) and GGML_OP_MUL_MAT / GGML_OP_MUL_MAT_ID with Q4_0 / Q8_0 / Q4_K / Q6_K / IQ4_XS
-// weights, f32 activations and f32 results. Everything else stays with the caller's other
-// backends (ggml_backend_sched splits on supports_op, ggml-backend.cpp:787-842).
+// weights (also Q5_K), f32 activations and f32 results, plus the glue ops of a llama-arch graph (csrc/glue_ops.cu). Everything else
+// stays with the caller's other backends (ggml_backend_sched splits on supports_op, ggml-backend.cpp:787-842).
+//
+// Several GPUs in one process: every B200 is a device of the registry; proc "ggml_backend_split_buffer_type" hands out the row-split
+// weight buffer type behind `-sm row` (see the split_* functions).
 //
 // Load-time repack: a whole-tensor set_tensor of a contiguous, non-view weight tensor with
 // ne0 % 256 == 0 is stored in the B200 plane layout (b200_repack); get_tensor hands canonical
@@ -86,7 +89,48 @@ struct backend_ctx {
     std::vector<cached_graph> graphs;
     uint64_t graph_stamp = 0;
     bool capturing = false;        // a stream capture is open: nothing may allocate or synchronise
+    // row-split weights (ggml_backend_split_buffer_type): one helper stream, workspace and copy of X per OTHER device that holds a slice
+    struct aux_device {
+        int           device = -1;
+        b200_stream_t stream = nullptr;
+        b200_event_t  done = nullptr;
+        void *        workspace = nullptr; size_t workspace_size = 0;
+        void *        x = nullptr;         size_t x_size = 0;
+    };
+    std::vector<aux_device> aux;
+    b200_event_t fork = nullptr;   // recorded on `stream` when X is ready, awaited by the helper streams
 };
+
+// ---- row-split weight tensors (one slice of rows per device of this process) -----------------------------------------------------------
+struct split_slice { void * data = nullptr; int64_t lo = 0, hi = 0; bool planes = false; };
+struct split_tensor {
+    int type = 0; int64_t m = 0, k = 0;
+    int n_dev = 0;
+    split_slice s[B200_MAX_DEVICES];     // by position in the registry's device list
+};
+struct split_buft_ctx {
+    int main = 0, n_dev = 0;
+    int cuda_index[B200_MAX_DEVICES];
+    float cum[B200_MAX_DEVICES + 1];     // cumulative row fractions: device i owns [cum[i], cum[i + 1]) of the rows
+    std::string name;
+    ggml_backend_buffer_type buft{};
+};
+struct split_buffer_ctx {
+    split_buft_ctx * bt = nullptr;
+    std::vector<split_tensor *> tensors;
+    void * staging[B200_MAX_DEVICES] = {};
+    size_t staging_size[B200_MAX_DEVICES] = {};
+};
+const char * split_buft_get_name(ggml_backend_buffer_type_t buft);
+// the slices of a MUL_MAT weight that lives in a split buffer, else nullptr
+const split_tensor * split_of(const ggml_tensor * w) {
+    if (!w || !w->buffer || w->buffer->buft->iface.get_name != split_buft_get_name) return nullptr;
+    return (const split_tensor *) w->extra;
+}
+bool in_split_buffer(const ggml_tensor * t) {
+    const ggml_tensor * b = t && t->view_src ? t->view_src : t;
+    return b && b->buffer && b->buffer->buft->iface.get_name == split_buft_get_name;
+}
 
 bool repack_enabled() {
     static const bool on = [] { const char * e = getenv("GGML_B200_REPACK"); return !(e && e[0] == '0'); }();
@@ -363,6 +407,163 @@ const ggml_backend_buffer_type_i host_buft_iface = {
 };
 
 // ---------------------------------------------------------------------------------------------------
+// row-split buffer type: proc "ggml_backend_split_buffer_type" (ggml-backend.h:199-200; caller src/llama-model.cpp:388-410, `-sm row`).
+// The reference's counterpart is ggml_backend_cuda_split_buffer_type (ggml-cuda.cu:811-1107). A weight matrix placed here is cut into
+// one run of rows per device of this process (tensor_split fractions, boundaries on multiples of 128 rows); every slice is an ordinary
+// plane-layout matrix on its device. The buffer itself owns no storage (its base is a dummy address, like the reference's): slices are
+// allocated per tensor in init_tensor. Only whole-tensor set / get are legal, as in the reference.
+// ---------------------------------------------------------------------------------------------------
+const char * split_buft_get_name(ggml_backend_buffer_type_t buft) { return ((split_buft_ctx *) buft->context)->name.c_str(); }
+
+void split_rows(const split_buft_ctx * bt, int64_t m, int64_t * lo, int64_t * hi) {
+    for (int i = 0; i < bt->n_dev; ++i) {
+        int64_t a = i == 0 ? 0 : (int64_t) ((double) m * bt->cum[i]) / 128 * 128;
+        int64_t b = i == bt->n_dev - 1 ? m : (int64_t) ((double) m * bt->cum[i + 1]) / 128 * 128;
+        if (a > m) a = m;
+        if (b > m) b = m;
+        if (b < a) b = a;
+        lo[i] = a; hi[i] = b;
+    }
+}
+
+void split_buffer_free(ggml_backend_buffer_t buffer) {
+    split_buffer_ctx * sc = (split_buffer_ctx *) buffer->context;
+    for (split_tensor * t : sc->tensors) {
+        for (int i = 0; i < t->n_dev; ++i) if (t->s[i].data) { b200_device_synchronize(sc->bt->cuda_index[i]); b200_free(sc->bt->cuda_index[i], t->s[i].data); }
+        delete t;
+    }
+    for (int i = 0; i < sc->bt->n_dev; ++i) if (sc->staging[i]) b200_free(sc->bt->cuda_index[i], sc->staging[i]);
+    delete sc;
+}
+void * split_buffer_get_base(ggml_backend_buffer_t) { return (void *) 0x1000; }   // never dereferenced: the data live in the slices
+
+enum ggml_status split_buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor) {
+    split_buffer_ctx * sc = (split_buffer_ctx *) buffer->context;
+    GGML_ASSERT(tensor->view_src == nullptr && "ggml-b200: views of row-split tensors are not supported");
+    GGML_ASSERT(weight_type(tensor->type) && ggml_is_contiguous(tensor) && tensor->ne[2] == 1 && tensor->ne[3] == 1 &&
+                "ggml-b200: the split buffer type holds 2-D quantised MUL_MAT weights only");
+    split_tensor * t = new split_tensor;
+    t->type = (int) tensor->type; t->m = tensor->ne[1]; t->k = tensor->ne[0]; t->n_dev = sc->bt->n_dev;
+    int64_t lo[B200_MAX_DEVICES], hi[B200_MAX_DEVICES];
+    split_rows(sc->bt, t->m, lo, hi);
+    const size_t row = b200_row_size(t->type, t->k);
+    for (int i = 0; i < t->n_dev; ++i) {
+        t->s[i].lo = lo[i]; t->s[i].hi = hi[i];
+        if (hi[i] == lo[i]) continue;
+        t->s[i].data = b200_malloc(sc->bt->cuda_index[i], (size_t) (hi[i] - lo[i]) * row + 512);
+        if (!t->s[i].data) {
+            GGML_LOG_ERROR("ggml-b200: allocating a %.1f MiB slice of %s on device %d failed: %s\n", (hi[i] - lo[i]) * row / 1048576.0, tensor->name,
+                           sc->bt->cuda_index[i], b200_last_error());
+            for (int j = 0; j < i; ++j) if (t->s[j].data) b200_free(sc->bt->cuda_index[j], t->s[j].data);
+            delete t;
+            return GGML_STATUS_ALLOC_FAILED;
+        }
+    }
+    sc->tensors.push_back(t);
+    tensor->extra = t;
+    return GGML_STATUS_SUCCESS;
+}
+
+void * split_stage(split_buffer_ctx * sc, int i, size_t n) {
+    if (n > sc->staging_size[i]) {
+        const int dev = sc->bt->cuda_index[i];
+        if (sc->staging[i]) { b200_device_synchronize(dev); b200_free(dev, sc->staging[i]); }
+        sc->staging[i] = b200_malloc(dev, n);
+        sc->staging_size[i] = sc->staging[i] ? n : 0;
+    }
+    return sc->staging[i];
+}
+
+void split_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    split_buffer_ctx * sc = (split_buffer_ctx *) buffer->context;
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "ggml-b200: row-split tensors are written whole (ggml-cuda.cu:1019-1021 has the same rule)");
+    split_tensor * t = (split_tensor *) tensor->extra;
+    const size_t row = b200_row_size(t->type, t->k);
+    for (int i = 0; i < t->n_dev; ++i) {
+        split_slice & s = t->s[i];
+        const int64_t rows = s.hi - s.lo;
+        if (rows == 0) continue;
+        const int dev = sc->bt->cuda_index[i];
+        b200_set_device(dev);
+        b200_device_synchronize(dev);                      // kernels of an earlier graph may still read the slice
+        const size_t bytes = (size_t) rows * row;
+        const char * src = (const char *) data + (size_t) s.lo * row;
+        const bool repack = repack_enabled() && t->k % 256 == 0 && b200_repack_supported(t->type, rows, t->k);
+        void * tmp = repack ? split_stage(sc, i, bytes) : nullptr;
+        int rc;
+        if (tmp) {
+            rc = b200_memcpy_h2d(tmp, src, bytes, nullptr);
+            if (rc == 0) rc = b200_repack(t->type, rows, t->k, tmp, s.data, nullptr);
+            s.planes = rc == 0;
+        } else {
+            rc = b200_memcpy_h2d(s.data, src, bytes, nullptr);
+            s.planes = false;
+        }
+        if (rc != 0 || b200_stream_synchronize(nullptr) != 0) GGML_ABORT("ggml-b200: set_tensor(%s) on the split buffer failed: %s", tensor->name, b200_last_error());
+    }
+}
+
+void split_buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    split_buffer_ctx * sc = (split_buffer_ctx *) buffer->context;
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "ggml-b200: row-split tensors are read whole");
+    const split_tensor * t = (const split_tensor *) tensor->extra;
+    const size_t row = b200_row_size(t->type, t->k);
+    for (int i = 0; i < t->n_dev; ++i) {
+        const split_slice & s = t->s[i];
+        const int64_t rows = s.hi - s.lo;
+        if (rows == 0) continue;
+        const int dev = sc->bt->cuda_index[i];
+        b200_set_device(dev);
+        b200_device_synchronize(dev);
+        const size_t bytes = (size_t) rows * row;
+        const void * src = s.data;
+        if (s.planes) {                                   // canonical ggml bytes go back out
+            void * tmp = split_stage(sc, i, bytes);
+            GGML_ASSERT(tmp && "ggml-b200: out of device memory in get_tensor");
+            if (b200_unrepack(t->type, rows, t->k, s.data, tmp, nullptr) != 0) GGML_ABORT("ggml-b200: unrepack failed: %s", b200_last_error());
+            src = tmp;
+        }
+        if (b200_memcpy_d2h((char *) data + (size_t) s.lo * row, src, bytes, nullptr) != 0 || b200_stream_synchronize(nullptr) != 0)
+            GGML_ABORT("ggml-b200: get_tensor(%s) on the split buffer failed: %s", tensor->name, b200_last_error());
+    }
+}
+
+void split_buffer_clear(ggml_backend_buffer_t, uint8_t) {}      // nothing is allocated before init_tensor
+
+const ggml_backend_buffer_i split_buffer_iface = {
+    /* .free_buffer   = */ split_buffer_free,
+    /* .get_base      = */ split_buffer_get_base,
+    /* .init_tensor   = */ split_buffer_init_tensor,
+    /* .memset_tensor = */ nullptr,
+    /* .set_tensor    = */ split_buffer_set_tensor,
+    /* .get_tensor    = */ split_buffer_get_tensor,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ split_buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+ggml_backend_buffer_t split_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    split_buffer_ctx * sc = new split_buffer_ctx;
+    sc->bt = (split_buft_ctx *) buft->context;
+    return ggml_backend_buffer_init(buft, split_buffer_iface, sc, size);
+}
+size_t split_buft_get_alignment(ggml_backend_buffer_type_t) { return B200_ALIGNMENT; }
+size_t split_buft_get_alloc_size(ggml_backend_buffer_type_t buft, const ggml_tensor * tensor) {
+    const split_buft_ctx * bt = (const split_buft_ctx *) buft->context;
+    return ggml_nbytes(tensor) + (size_t) bt->n_dev * 512;          // what init_tensor allocates over all devices
+}
+bool split_buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i split_buft_iface = {
+    /* .get_name       = */ split_buft_get_name,
+    /* .alloc_buffer   = */ split_buft_alloc_buffer,
+    /* .get_alignment  = */ split_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ split_buft_get_alloc_size,
+    /* .is_host        = */ split_buft_is_host,
+};
+
+// ---------------------------------------------------------------------------------------------------
 // op support
 // ---------------------------------------------------------------------------------------------------
 bool mul_mat_operands_ok(const ggml_tensor * w, const ggml_tensor * x, const ggml_tensor * y) {
@@ -422,6 +623,12 @@ bool glue_supports(const ggml_tensor * op) {
 }
 
 bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    // a row-split tensor can only be src0 of a plain 2-D MUL_MAT (the reference has the same restriction: ggml-cuda.cu:4530-4545, :2274)
+    for (int j = 0; j < GGML_MAX_SRC; ++j) {
+        if (!op->src[j] || !in_split_buffer(op->src[j])) continue;
+        const ggml_tensor * w = op->src[0], * x = op->src[1];
+        if (op->op != GGML_OP_MUL_MAT || j != 0 || w->view_src || !x || x->ne[2] != 1 || x->ne[3] != 1 || w->ne[2] != 1 || w->ne[3] != 1) return false;
+    }
     switch (op->op) {
         case GGML_OP_NONE:
         case GGML_OP_VIEW:
@@ -463,6 +670,16 @@ void backend_free(ggml_backend_t backend) {
     b200_set_device(bc->device);
     if (bc->stream) { b200_stream_synchronize(bc->stream); b200_stream_destroy(bc->stream); }
     if (bc->workspace) b200_free(bc->device, bc->workspace);
+    for (auto & a : bc->aux) {
+        b200_set_device(a.device);
+        b200_stream_synchronize(a.stream);
+        if (a.workspace) b200_free(a.device, a.workspace);
+        if (a.x) b200_free(a.device, a.x);
+        b200_event_destroy(a.done);
+        b200_stream_destroy(a.stream);
+    }
+    if (bc->fork) b200_event_destroy(bc->fork);
+    b200_set_device(bc->device);
     for (auto & c : bc->chains) b200_chain_destroy(c.chain);
     for (auto & g : bc->graphs) if (g.exec) b200_graph_destroy(g.exec);
     delete bc;
@@ -489,7 +706,99 @@ bool backend_reserve(backend_ctx * bc, size_t need) {
     return bc->workspace != nullptr;
 }
 
+// ---- MUL_MAT whose weight rows are spread over the devices of this process --------------------------------------------------------------
+// Every device multiplies its rows by the same X and writes its part of Y straight into dst on the backend's device (peer stores over
+// NVLink; the reference gathers with ggml_cuda_Memcpy2DPeerAsync instead, ggml-cuda.cu:1725-1744). X reaches the other devices with one
+// strided peer copy per node. Fork / join are events, so the whole thing is capturable into the backend's CUDA graph.
+backend_ctx::aux_device * aux_for(backend_ctx * bc, int device) {
+    for (auto & a : bc->aux) if (a.device == device) return &a;
+    if (bc->capturing) return nullptr;
+    if (b200_enable_peer_access(device, bc->device) != 0 || b200_enable_peer_access(bc->device, device) != 0) return nullptr;
+    backend_ctx::aux_device a;
+    a.device = device;
+    a.stream = b200_stream_create(device);
+    a.done = b200_event_create(device);
+    if (!a.stream || !a.done) return nullptr;
+    bc->aux.push_back(a);
+    return &bc->aux.back();
+}
+bool aux_reserve(backend_ctx * bc, backend_ctx::aux_device * a, void ** buf, size_t * have, size_t need) {
+    if (need <= *have) return true;
+    if (bc->capturing) return false;
+    b200_stream_synchronize(a->stream);
+    if (*buf) b200_free(a->device, *buf);
+    for (auto & g : bc->graphs) if (g.exec) b200_graph_destroy(g.exec);   // captured launches carry the old pointers
+    bc->graphs.clear();
+    need = (need + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+    *buf = b200_malloc(a->device, need);
+    *have = *buf ? need : 0;
+    return *buf != nullptr;
+}
+
+enum ggml_status compute_mul_mat_split(backend_ctx * bc, const ggml_tensor * dst, const split_tensor * st) {
+    const ggml_tensor * w = dst->src[0], * x = dst->src[1];
+    const split_buft_ctx * bt = (const split_buft_ctx *) w->buffer->buft->context;
+    const int64_t k = st->k, n = x->ne[1];
+    const size_t need = b200_mul_mat_workspace(st->type, n, k);
+    if (!backend_reserve(bc, need)) return GGML_STATUS_ALLOC_FAILED;
+    if (!bc->fork) {
+        if (bc->capturing) return GGML_STATUS_FAILED;
+        bc->fork = b200_event_create(bc->device);
+        if (!bc->fork) return GGML_STATUS_FAILED;
+    }
+    enum ggml_status result = GGML_STATUS_SUCCESS;
+    std::vector<backend_ctx::aux_device *> used;
+    bool forked = false;
+    auto fill = [&](b200_mul_mat_args & a, const split_slice & s) {
+        a.type = st->type; a.layout = s.planes ? B200_LAYOUT_PLANES : B200_LAYOUT_CANONICAL;
+        a.m = s.hi - s.lo; a.n = n; a.k = k;
+        a.w = s.data; a.w_row_stride = 0;
+        a.y = (float *) dst->data + s.lo; a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
+        a.flavour = B200_Q8_X86;
+    };
+    for (int i = 0; i < st->n_dev && result == GGML_STATUS_SUCCESS; ++i) {
+        const split_slice & s = st->s[i];
+        const int dev = bt->cuda_index[i];
+        if (s.hi == s.lo || dev == bc->device) continue;
+        backend_ctx::aux_device * ax = aux_for(bc, dev);
+        if (!ax) { GGML_LOG_ERROR("ggml-b200: no peer path between devices %d and %d: %s\n", bc->device, dev, b200_last_error()); result = GGML_STATUS_FAILED; break; }
+        if (!aux_reserve(bc, ax, &ax->workspace, &ax->workspace_size, need) || !aux_reserve(bc, ax, &ax->x, &ax->x_size, (size_t) n * k * sizeof(float))) {
+            result = GGML_STATUS_ALLOC_FAILED; break;
+        }
+        if (!forked) { b200_event_record(bc->fork, bc->stream); forked = true; }
+        b200_set_device(dev);
+        b200_stream_wait_event(ax->stream, bc->fork);
+        b200_mul_mat_args a = {};
+        fill(a, s);
+        a.x = (const float *) ax->x; a.x_row_stride = k;
+        a.workspace = ax->workspace; a.workspace_size = ax->workspace_size;
+        if (b200_memcpy2d(ax->x, (size_t) k * sizeof(float), x->data, x->nb[1], (size_t) k * sizeof(float), (size_t) n, ax->stream) != 0 ||
+            b200_mul_mat(&a, ax->stream) != 0) {
+            GGML_LOG_ERROR("ggml-b200: MUL_MAT %s, rows [%lld, %lld) on device %d failed: %s\n", dst->name, (long long) s.lo, (long long) s.hi, dev, b200_last_error());
+            result = GGML_STATUS_FAILED;
+        }
+        b200_event_record(ax->done, ax->stream);
+        used.push_back(ax);
+    }
+    b200_set_device(bc->device);
+    for (int i = 0; i < st->n_dev && result == GGML_STATUS_SUCCESS; ++i) {
+        const split_slice & s = st->s[i];
+        if (s.hi == s.lo || bt->cuda_index[i] != bc->device) continue;
+        b200_mul_mat_args a = {};
+        fill(a, s);
+        a.x = (const float *) x->data; a.x_row_stride = (int64_t) (x->nb[1] / sizeof(float));
+        a.workspace = bc->workspace; a.workspace_size = bc->workspace_size;
+        if (b200_mul_mat(&a, bc->stream) != 0) {
+            GGML_LOG_ERROR("ggml-b200: MUL_MAT %s, local rows failed: %s\n", dst->name, b200_last_error());
+            result = GGML_STATUS_FAILED;
+        }
+    }
+    for (auto * ax : used) b200_stream_wait_event(bc->stream, ax->done);      // join (also on failure: an open capture must see every fork rejoin)
+    return result;
+}
+
 enum ggml_status compute_mul_mat(backend_ctx * bc, const ggml_tensor * dst) {
+    if (const split_tensor * st = split_of(dst->src[0])) return compute_mul_mat_split(bc, dst, st);
     const ggml_tensor * w = dst->src[0], * x = dst->src[1];
     const int64_t k = w->ne[0], m = w->ne[1], n = x->ne[1];
     const int layout = weight_layout(w);
@@ -570,7 +879,7 @@ bool skipped(const ggml_tensor * t) { return (t->flags & GGML_TENSOR_FLAG_COMPUT
 bool plain_mul_mat(const ggml_tensor * t) {
     if (t->op != GGML_OP_MUL_MAT || skipped(t)) return false;
     const ggml_tensor * w = t->src[0], * x = t->src[1];
-    if (!weight_type(w->type)) return false;
+    if (!weight_type(w->type) || in_split_buffer(w)) return false;
     return x->ne[2] == 1 && x->ne[3] == 1 && w->ne[2] == 1 && w->ne[3] == 1 && x->nb[0] == sizeof(float) && t->nb[0] == sizeof(float);
 }
 b200_mul_mat_args plain_args(const ggml_tensor * dst) {
@@ -1034,6 +1343,7 @@ ggml_backend_buffer_type_t device_get_host_buffer_type(ggml_backend_dev_t dev) {
 bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
     // our own device memory on this device, or any host-visible buffer type is NOT enough: the kernels
     // dereference device pointers, so only buffers of this very device qualify
+    if (buft->iface.get_name == split_buft_get_name) return buft->device == dev;       // the split type made for this device as main device
     return buft->iface.get_name == buft_get_name && buft->device == dev;
 }
 
@@ -1092,8 +1402,39 @@ ggml_backend_feature * reg_get_features(ggml_backend_reg_t) {
     return features;
 }
 
+// proc "ggml_backend_split_buffer_type" (ggml-backend.h:199-200): main_device indexes this registry's device list, tensor_split holds one
+// weight per device (all zero: equal shares). One buffer type object per distinct (main_device, split), kept for the life of the process.
+ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tensor_split) {
+    static std::mutex mu;
+    static std::vector<split_buft_ctx *> made;
+    ggml_backend_reg_t reg = ggml_backend_init();
+    reg_ctx * rc = (reg_ctx *) reg->context;
+    const int n = (int) rc->devices.size();
+    if (n < 1 || main_device < 0 || main_device >= n) return nullptr;
+    float share[B200_MAX_DEVICES];
+    float sum = 0.0f;
+    for (int i = 0; i < n; ++i) { share[i] = tensor_split ? tensor_split[i] : 0.0f; if (share[i] < 0.0f) share[i] = 0.0f; sum += share[i]; }
+    if (sum <= 0.0f) { for (int i = 0; i < n; ++i) share[i] = 1.0f; sum = (float) n; }
+    float cum[B200_MAX_DEVICES + 1];
+    cum[0] = 0.0f;
+    for (int i = 0; i < n; ++i) cum[i + 1] = cum[i] + share[i] / sum;
+    cum[n] = 1.0f;
+    std::lock_guard<std::mutex> lock(mu);
+    for (split_buft_ctx * c : made)
+        if (c->main == main_device && c->n_dev == n && memcmp(c->cum, cum, sizeof(float) * (size_t) (n + 1)) == 0) return &c->buft;
+    split_buft_ctx * c = new split_buft_ctx;
+    c->main = main_device; c->n_dev = n;
+    for (int i = 0; i < n; ++i) c->cuda_index[i] = rc->ctxs[i]->index;
+    memcpy(c->cum, cum, sizeof(float) * (size_t) (n + 1));
+    c->name = rc->ctxs[main_device]->name + "_Split";
+    c->buft = ggml_backend_buffer_type{ /* .iface = */ split_buft_iface, /* .device = */ &rc->devices[main_device], /* .context = */ c };
+    made.push_back(c);
+    return &c->buft;
+}
+
 void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) reg_get_features;
+    if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;
     return nullptr;
 }
 
