@@ -382,6 +382,20 @@ def main():
             chain_pp.close()
             del chain_pp
             torch.cuda.empty_cache()
+            if world > 1 and W.tg_bytes(ops) < 60e9:
+                # prefill of INDEPENDENT ubatches shards by tokens, not by rows: every rank holds the whole model (it fits) and runs its own
+                # ubatch with no exchange at all; the row-split figure above is what ONE ubatch gets from N GPUs
+                try:
+                    own = MatMulChain(ops, args.pp, device=local, persistent=False)
+                    ms_own, _ = time_chain(own, pp_steps, 3)
+                    res["token_parallel"] = {"value": world * args.pp / (ms_own * 1e-3), "unit": "tokens/s", "ms_per_ubatch": ms_own,
+                                             "ubatches_in_flight": world, "sharding": "one ubatch per rank, weights replicated, no collective",
+                                             "scaling": "weak"}
+                    own.close()
+                    del own
+                    torch.cuda.empty_cache()
+                except Exception as e:  # noqa: BLE001
+                    res["token_parallel"] = {"error": str(e)[:200]}
             return res
         except RuntimeError:
             raise

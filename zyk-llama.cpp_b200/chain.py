@@ -100,10 +100,10 @@ class MatMulChain:
         self.calls = self._build_calls()
         # decode on one GPU: the whole pass as ONE persistent launch (b200_chain_*), when every node is eligible
         self.decode_chain = None
-        # "auto": where it is the faster path today (measured on B200: Q4_K / Q6_K models 618 -> 756 tokens/s; the Q8_0, Q4_0 and
-        # IQ4_XS fragments of the chain kernel are still the eight-lanes-per-block ones and lose to the per-node kernels)
+        # "auto": where it is the faster path today (measured on B200: Q4_K / Q6_K models 618 -> 794 tokens/s; 1B Q4_0 2584 -> 2620 with the
+        # unit-per-lane Q4_0 path; IQ4_XS 464 chain vs 476 per node and Q8_0 440 vs 577 stay on the per-node kernels)
         if persistent == "auto":
-            persistent = all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K) for o in ops)
+            persistent = all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K, B.Types.Q4_0) for o in ops)
         if persistent and world == 1 and all(c[0] is B.lib.b200_mul_mat_group for c in self.calls):
             groups = [list(c[1]) for c in self.calls]
             if B.DecodeChain.supported(groups):

@@ -107,6 +107,7 @@ struct ChainArgs {
     int inflight;             // copies per group that may be in flight (issued, not landed): bounds the queueing delay the stream adds to the node barrier
     int debug;                // B200_CHAIN_DEBUG (timing experiments, results wrong): 1 no node wait, 2 no dot products, 4 no X quantiser, 8 no row sums
     int ns;                   // gemv_chainx_kernel: ring stages per CTA
+    int lanes8;               // B200_CHAIN_LANES8=1: IQ4_XS / Q4_0 items on the older eight-lanes-per-block fragments (comparison runs)
 };
 
 // bytes per 256-element unit in plane p of the plane layout (repack.cu); 0 terminates
@@ -135,6 +136,7 @@ __device__ __forceinline__ int ldss1(uint32_t a) { int r; asm volatile("ld.share
 __device__ __forceinline__ float ldsf(uint32_t a) { float r; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(a)); return r; }
 __device__ __forceinline__ void sts8(uint32_t a, uint32_t x, uint32_t y) { asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(a), "r"(x), "r"(y) : "memory"); }
 __device__ __forceinline__ void sts2(uint32_t a, uint16_t x) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(a), "h"(x) : "memory"); }
+__device__ __forceinline__ void sts4(uint32_t a, uint32_t x) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(x) : "memory"); }
 __device__ __forceinline__ void stsf(uint32_t a, float x) { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(x) : "memory"); }
 
 // X changes while the kernel runs (it is the Y of an earlier node): read it at L2, never through the non-coherent path
@@ -491,7 +493,69 @@ __device__ __forceinline__ void unit_q6k(uint32_t stage, int nunits, int u, uint
     }
 }
 
-// ---- IQ4_XS / Q4_0 / Q8_0: eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ------------
+// ---- IQ4_XS / Q4_0, one 256-element unit per lane ----------------------------------------------------------------------------
+// The QS plane is 128 B per unit, so 32 lanes reading the same 16-byte chunk of 32 consecutive units would all hit the same four banks.
+// Lane b therefore walks its eight 32-element sub-blocks in the order t ^ rho(b), rho(b) = (b & 7) ^ ((b >> 1) & 2): within every group
+// of eight lanes the weight chunks AND the two activation chunks (placed by xpos, unit stride 336 B) fall into eight different 16-byte
+// bank groups (exhaustive search over the permutations of 0..7; an additive rotation cannot satisfy both). Stage layout = the item's
+// planes back to back, as the bulk copies land them.
+__device__ __forceinline__ int lane_rho(int b) { return (b & 7) ^ ((b >> 1) & 2); }
+__device__ __forceinline__ int xpos_rt(int ch) { return ch < 8 ? ch : 8 + ((ch + 4) & 7); }
+// arithmetic of ggml_vec_dot_iq4_xs_q8_K (ggml-cpu/quants.c:1137-1181): per sub-block ls * sum(kvalues[nib] * q8), one d * d_x per super-block
+template <int NCOLS>
+__device__ __forceinline__ void unit_iq4xs(uint32_t stage, int nunits, int u, int b, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint2 hdr = lds8(stage + (uint32_t) (nunits * 128 + u * 8));          // d, scales_h | scales_l[4]
+    const uint32_t sh = hdr.x >> 16;
+    const uint32_t qs = stage + (uint32_t) (u * 128);
+    const int rho = lane_rho(b);
+    int isum[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) isum[c] = 0;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        const int ib = t ^ rho;
+        const uint4 q = lds16(qs + (uint32_t) (ib << 4));
+        const int ls = (int) (((hdr.y >> (4 * ib)) & 0xfu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;
+        const uint32_t p0 = (uint32_t) xpos_rt(2 * ib) << 4, p1 = (uint32_t) xpos_rt(2 * ib + 1) << 4;
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+            const uint4 x0 = lds16(xc + p0), x1 = lds16(xc + p1);
+            int d = iq4_word_dot(q.x, x0.x, x1.x, 0);
+            d = iq4_word_dot(q.y, x0.y, x1.y, d);
+            d = iq4_word_dot(q.z, x0.z, x1.z, d);
+            d = iq4_word_dot(q.w, x0.w, x1.w, d);
+            isum[c] += ls * d;
+        }
+    }
+    const float dw = half_bits_to_float((uint16_t) (hdr.x & 0xffffu));
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) acc[c] += (ldsf(xb + (uint32_t) (c * x_col_stride) + XU_D) * dw) * (float) isum[c];
+}
+// arithmetic of ggml_vec_dot_q4_0_q8_0 (ggml-cpu/quants.c:115-150): per 32-block (sum(nib * q8) - 8 * sum(q8)) * d_w * d_x
+template <int NCOLS>
+__device__ __forceinline__ void unit_q40(uint32_t stage, int nunits, int u, int b, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint32_t qs = stage + (uint32_t) (u * 128), dp = stage + (uint32_t) (nunits * 128 + u * 16);
+    const int rho = lane_rho(b);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        const int ib = t ^ rho;
+        const uint4 q = lds16(qs + (uint32_t) (ib << 4));
+        const float dw = half_bits_to_float(lds2(dp + (uint32_t) (ib << 1)));
+        const uint4 lo = and4(q, 0x0f0f0f0fu), hi = and4(shr4(q, 4), 0x0f0f0f0fu);
+        const uint32_t p0 = (uint32_t) xpos_rt(2 * ib) << 4, p1 = (uint32_t) xpos_rt(2 * ib + 1) << 4;
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+            const uint4 x0 = lds16(xc + p0), x1 = lds16(xc + p1);
+            const int bs = (int) (int16_t) lds2(xc + XU_BS32 + (uint32_t) (ib << 1));
+            const int isum = dot16(lo, x0) + dot16(hi, x1) - 8 * bs;
+            acc[c] += (ldsf(xc + XU_D + (uint32_t) (ib << 2)) * dw) * (float) isum;
+        }
+    }
+}
+
+// ---- Q8_0 (and shapes the paths above do not take): eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ----
 template <int TYPE> __device__ __forceinline__ void wfrag_lds(WFrag<TYPE> & f, uint32_t stage, int nunits, int u, int g);
 template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_IQ4_XS>(WFrag<B200_TYPE_IQ4_XS> & f, uint32_t stage, int nunits, int u, int g) {
     f.q = lds16(stage + (uint32_t) (u * 128 + 16 * g));
@@ -543,11 +607,11 @@ inline ItemPlan plan_item(bool lane_per_unit, int nrows, int upr) {       // hos
 
 template <int TYPE, int NCOLS>
 __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride, int act_block,
-                                            const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane) {
+                                            const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int first, int lane) {
     const int nunits = nrows * upr;
     const int j = lane >> 3, g = lane & 7;
-    int row = 0, seg = gwarp;
-    for (int t = gwarp; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
+    int row = 0, seg = first;
+    for (int t = first; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
         while (seg >= pl.segs) { seg -= pl.segs; ++row; }
         const int u_end = min(upr, (seg + 1) * pl.S);
         float acc[NCOLS];
@@ -569,25 +633,27 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
     }
 }
 
-constexpr int LU_Q4K = 0, LU_Q6K = 1, LU_Q5K = 2;       // block-per-lane formats
+constexpr int LU_Q4K = 0, LU_Q6K = 1, LU_Q5K = 2, LU_IQ4XS = 3, LU_Q40 = 4;       // block-per-lane formats
 template <int Q6, int NCOLS>
-__device__ __forceinline__ void lane_unit(uint32_t stage, int nunits, int u, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
-    if constexpr (Q6 == LU_Q6K)      unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
-    else if constexpr (Q6 == LU_Q5K) unit_q5k<NCOLS>(stage + (uint32_t) u * 176, xb, x_col_stride, acc);
-    else                             unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
+__device__ __forceinline__ void lane_unit(uint32_t stage, int nunits, int u, int b, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    if constexpr (Q6 == LU_Q6K)        unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
+    else if constexpr (Q6 == LU_Q5K)   unit_q5k<NCOLS>(stage + (uint32_t) u * 176, xb, x_col_stride, acc);
+    else if constexpr (Q6 == LU_IQ4XS) unit_iq4xs<NCOLS>(stage, nunits, u, b, xb, x_col_stride, acc);
+    else if constexpr (Q6 == LU_Q40)   unit_q40<NCOLS>(stage, nunits, u, b, xb, x_col_stride, acc);
+    else                               unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
 }
 template <int NCOLS, int Q6 = LU_Q4K>
 __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uint32_t xs, int x_col_stride,
-                                         const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int gwarp, int lane,
+                                         const ItemPlan pl, uint32_t part, int part_stride, const YOut & out, int first, int lane,
                                          int rp, int sub, int b) {
     if (upr <= 32) {                                           // rp rows side by side in one warp: lane = (sub, b)
-        for (int t = gwarp; t * rp < nrows; t += CH_GWARPS) {
+        for (int t = first; t * rp < nrows; t += CH_GWARPS) {
             const int row = t * rp + sub;
             const bool live = sub < rp && row < nrows;
             float acc[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-            if (live) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+            if (live) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) {
                 float v = acc[c];
@@ -599,14 +665,14 @@ __device__ __forceinline__ void item_q4k(uint32_t stage, int nrows, int upr, uin
             }
         }
     } else {
-        int row = 0, seg = gwarp;
-        for (int t = gwarp; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
+        int row = 0, seg = first;
+        for (int t = first; t < nrows * pl.segs; t += CH_GWARPS, seg += CH_GWARPS) {
             while (seg >= pl.segs) { seg -= pl.segs; ++row; }
             const int b = seg * 32 + lane;
             float acc[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
-            if (b < upr) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
+            if (b < upr) lane_unit<Q6, NCOLS>(stage, nrows * upr, row * upr + b, b, xs + (uint32_t) (b * XU_BYTES), x_col_stride, acc);
 #pragma unroll
             for (int c = 0; c < NCOLS; ++c) {
                 const float v = warp_sum(acc[c]);
@@ -778,21 +844,24 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
             ItemPlan pl; pl.segs = (int) d1.z; pl.S = (int) d1.w;
 
             // phase A: every warp reduces its tasks (rows, or runs of units of a row)
+            const int first = gwarp;
             if (a.debug & 2) {
             } else if (type == B200_TYPE_Q4_K) {
-                item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+                item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else if (type == CH_T_Q6K_SW) {
-                item_q4k<NCOLS, LU_Q6K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+                item_q4k<NCOLS, LU_Q6K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q5_K) {
-                item_q4k<NCOLS, LU_Q5K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, gwarp, lane, q4_rp, q4_sub, q4_b);
+                item_q4k<NCOLS, LU_Q5K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q6_K) {
-                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
+                item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
             } else if (type == B200_TYPE_IQ4_XS) {
-                item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
+                if (a.lanes8) item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+                else          item_q4k<NCOLS, LU_IQ4XS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else if (type == B200_TYPE_Q4_0) {
-                item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
+                if (a.lanes8) item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+                else          item_q4k<NCOLS, LU_Q40>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else {
-                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, gwarp, lane);
+                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_bar(grp, st));     // this warp is done with the stage (and its descriptor)
@@ -1171,6 +1240,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     const char * why = chain_check(nodes, group_sizes, n_groups, split != nullptr);
     if (why) { b200_set_error("b200_chain_create: %s", why); return nullptr; }
     const int world = split ? split->world : 1;
+    const bool lanes8 = getenv("B200_CHAIN_LANES8") != nullptr;
     if (split && (world < 2 || world > B200_MAX_PEERS || split->rank < 0 || split->rank >= world || !split->scratch || !split->row_lo || !split->m_full ||
                   split->peer_delta[split->rank] != 0 || (((uintptr_t) split->scratch) & 255) != 0)) {
         b200_set_error("b200_chain_create_split: bad descriptor (world %d rank %d)", world, split->rank); return nullptr;
@@ -1290,7 +1360,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
                     it.tag = feed[g] == mi ? d_tags + (size_t) (g % 3) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
-                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || map0 >= 0, it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || map0 >= 0 || (!lanes8 && (type == B200_TYPE_IQ4_XS || type == B200_TYPE_Q4_0)), it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     if (P.xreg) {
                         // `S` carries the rotation: which warp gets the item's first task, so that tasks go round the warps across items
                         if (it.segs == 1) { const int rp = 32 / upr; it.S = rot[vc] % CX_NW; rot[vc] = (rot[vc] + (it.nrows + rp - 1) / rp) % CX_NW; }
@@ -1373,6 +1443,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     c->args.inflight = getenv("B200_CHAIN_INFLIGHT") ? atoi(getenv("B200_CHAIN_INFLIGHT")) : CH_NS;
     if (c->args.inflight < 1) c->args.inflight = 1;
     c->args.debug = getenv("B200_CHAIN_DEBUG") ? atoi(getenv("B200_CHAIN_DEBUG")) : 0;
+    c->args.lanes8 = lanes8 ? 1 : 0;
     c->args.n_nodes = n_groups; c->args.stage_bytes = stage; c->args.max_units = max_units; c->args.x_bytes = x_bytes; c->args.ns = P.ns;
     c->smem = P.smem;
     c->cooperative = coop != 0 && !getenv("B200_CHAIN_NO_COOP");

@@ -187,7 +187,7 @@ template <> struct WFrag<B200_TYPE_Q6_K> {
 
 // ---- IQ4_XS planes: QS 128 | HDR 8 {d, scales_h, scales_l[4]} (ggml-common.h:425-431) -----------
 // kvalues_iq4nl (ggml-common.h:1088) as four byte-permute registers
-__device__ __forceinline__ uint32_t iq4nl_lut4(uint32_t nib) {
+__device__ __forceinline__ uint32_t iq4nl_lut4(uint32_t nib) {     // four indices, one per byte (used by the GEMM dequantiser)
     const uint32_t sel = nib & 0x07070707u;
     const uint32_t s = sel | (sel >> 4);
     const uint32_t s16 = (s & 0xffu) | ((s >> 8) & 0xff00u);
@@ -195,6 +195,20 @@ __device__ __forceinline__ uint32_t iq4nl_lut4(uint32_t nib) {
     const uint32_t hi = __byte_perm(0x26190D01u, 0x71594535u, s16);
     const uint32_t mask = ((nib >> 3) & 0x01010101u) * 0xffu;
     return (hi & mask) | (lo & ~mask);
+}
+// four PACKED indices (bits 0..15 of h, the other bits are ignored) -> four table bytes. The nibbles of a weight word already are the
+// selector format of PRMT: bits 0..2 pick inside a table half, bit 3 picks the half with a third PRMT -- 6 instructions per 4 values.
+__device__ __forceinline__ uint32_t iq4nl_lut_packed(uint32_t h) {
+    const uint32_t s = h & 0x7777u;
+    const uint32_t lo = __byte_perm(0xBFAD9881u, 0xF6EADDCFu, s);
+    const uint32_t hi = __byte_perm(0x26190D01u, 0x71594535u, s);
+    return __byte_perm(lo, hi, ((h >> 1) & 0x4444u) | 0x3210u);
+}
+// the looked-up bytes of a weight word come out as (lo0, hi0, lo1, hi1) / (lo2, hi2, lo3, hi3): the ACTIVATIONS are interleaved to match
+// (once per lane step, shared by all rows) instead of de-interleaving every weight word
+__device__ __forceinline__ int iq4_word_dot(uint32_t q, uint32_t x0, uint32_t x1, int acc) {
+    acc = __dp4a((int) iq4nl_lut_packed(q), (int) __byte_perm(x0, x1, 0x5140u), acc);
+    return __dp4a((int) iq4nl_lut_packed(q >> 16), (int) __byte_perm(x0, x1, 0x7362u), acc);
 }
 template <> struct WFrag<B200_TYPE_IQ4_XS> {
     uint4 q; uint2 hdr;
@@ -207,11 +221,14 @@ template <> struct WFrag<B200_TYPE_IQ4_XS> {
     __device__ __forceinline__ void dot(const XFrag (&x)[NCOLS], float (&acc)[NCOLS], int g) const {
         const int ls = (int) (((hdr.y >> (4 * g)) & 0xfu) | ((((hdr.x >> 16) >> (2 * g)) & 3u) << 4)) - 32;
         const float dl = half_bits_to_float((uint16_t) (hdr.x & 0xffffu)) * (float) ls;
-        const uint4 lo = make_uint4(iq4nl_lut4(q.x & 0x0f0f0f0fu), iq4nl_lut4(q.y & 0x0f0f0f0fu), iq4nl_lut4(q.z & 0x0f0f0f0fu), iq4nl_lut4(q.w & 0x0f0f0f0fu));
-        const uint4 hi = make_uint4(iq4nl_lut4((q.x >> 4) & 0x0f0f0f0fu), iq4nl_lut4((q.y >> 4) & 0x0f0f0f0fu), iq4nl_lut4((q.z >> 4) & 0x0f0f0f0fu), iq4nl_lut4((q.w >> 4) & 0x0f0f0f0fu));
 #pragma unroll
-        for (int c = 0; c < NCOLS; ++c)
-            acc[c] += (x[c].dx * dl) * (float) (dot16(lo, x[c].x0) + dot16(hi, x[c].x1));
+        for (int c = 0; c < NCOLS; ++c) {
+            int s = iq4_word_dot(q.x, x[c].x0.x, x[c].x1.x, 0);
+            s = iq4_word_dot(q.y, x[c].x0.y, x[c].x1.y, s);
+            s = iq4_word_dot(q.z, x[c].x0.z, x[c].x1.z, s);
+            s = iq4_word_dot(q.w, x[c].x0.w, x[c].x1.w, s);
+            acc[c] += (x[c].dx * dl) * (float) s;
+        }
     }
 };
 
