@@ -7,6 +7,7 @@
 // exactly the variants implemented here (supports_op) and the reference's test-backend-ops compares them with its CPU backend.
 // All kernels are HBM / L2 bound elementwise or row kernels: one thread per element or one CTA per row, no tensor cores (the
 // attention matmuls of a 512-token ubatch are the exception that would merit them).
+#include <stdlib.h>
 #include "common.cuh"
 
 #include <math.h>
@@ -391,6 +392,40 @@ __global__ void __launch_bounds__(256) soft_max_kernel(const T4 a, const T4 m, i
     for (long long i = threadIdx.x; i < n; i += 256) y[i] *= inv;
 }
 
+// rows of up to 1024 elements (attention scores over the KV cache): one WARP per row, the row lives in registers between the passes
+__global__ void __launch_bounds__(128) soft_max_warp_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale, long long rows) {
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long) blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
+    const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    float * y = reinterpret_cast<float *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const char * mp = has_mask ? m.data + i1 * m.nb[1] + (i2 % m.ne[2]) * m.nb[2] + (i3 % m.ne[3]) * m.nb[3] : nullptr;
+    const int n = (int) a.ne[0];
+    float v[32];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const int i = lane + 32 * j;
+        v[j] = -INFINITY;
+        if (i < n) {
+            float t = x[i] * scale;
+            if (mp) t += m.type == B200_TYPE_F16 ? __half2float(reinterpret_cast<const __half *>(mp)[i]) : reinterpret_cast<const float *>(mp)[i];
+            v[j] = t;
+        }
+        mx = fmaxf(mx, v[j]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) { if (lane + 32 * j < n) { v[j] = expf(v[j] - mx); s += v[j]; } }
+    s = warp_sum(s);
+    const float inv = 1.0f / s;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) { const int i = lane + 32 * j; if (i < n) y[i] = v[j] * inv; }
+}
+
 // ---- GLU: reglu 0, geglu 1, swiglu 2 (enum ggml_glu_op, ggml.h; ggml_compute_forward_glu, ops.cpp): dst = act(x) * g ----
 __device__ __forceinline__ float glu_act(int op, float x) {
     if (op == 0) return x > 0.0f ? x : 0.0f;
@@ -412,6 +447,19 @@ __global__ void __launch_bounds__(256) glu_kernel(const T4 a, const T4 b, int sp
             x = ar[swapped ? i0 + nc : i0]; g = ar[swapped ? i0 : i0 + nc];
         }
         *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = glu_act(op, x) * g;
+    }
+}
+
+// 2-D, split operands, rows of a multiple of four floats, everything 16-byte aligned (the SwiGLU of a prefill ubatch): float4 per thread
+__global__ void __launch_bounds__(256) glu_vec4_kernel(const T4 a, const T4 b, const T4w d, int op, int swapped, long long total4) {
+    const long long q = d.ne[0] >> 2;
+    for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long) gridDim.x * 256) {
+        const long long row = i / q, c = (i - row * q) * 16;
+        float4 x = *reinterpret_cast<const float4 *>(a.data + row * a.nb[1] + c), g = *reinterpret_cast<const float4 *>(b.data + row * b.nb[1] + c);
+        if (swapped) { const float4 t = x; x = g; g = t; }
+        float4 r;
+        r.x = glu_act(op, x.x) * g.x; r.y = glu_act(op, x.y) * g.y; r.z = glu_act(op, x.z) * g.z; r.w = glu_act(op, x.w) * g.w;
+        *reinterpret_cast<float4 *>(d.data + row * d.nb[1] + c) = r;
     }
 }
 
@@ -480,6 +528,86 @@ __global__ void __launch_bounds__(256) mm_tile_kernel(const T4 a, const T4 b, co
             const long long m = m0 + tx * 4 + i, n = n0 + ty * 4 + j;
             if (m < M && n < N) *reinterpret_cast<float *>(d.data + m * d.nb[0] + n * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = acc[j][i];
         }
+}
+
+// f16 rows x many f32 rows on the tensor cores (the K^T Q and V P products of prefill attention: K = 128 / n_kv, 512 query tokens, 32 heads):
+// 64 x 64 output tile per CTA of four warps, k in steps of 32; the activations are rounded to f16 on their way into shared memory (what the
+// reference CPU does for an F16 src0: vec_dot_type F16, ggml-cpu.c:217-235) and products accumulate in f32 (mma.sync.m16n8k16; these
+// are small batched matmuls between the quantised GEMMs, the warp-level MMA is enough to take them off the critical path).
+// Needs K % 32 == 0 and 16-byte aligned rows of both operands (host check); everything else stays on mm_tile_kernel.
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__global__ void __launch_bounds__(128) mm_mma_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    constexpr int BK = 32, LD = BK + 8;                       // row stride 40 halves = 20 words: the fragment loads below are conflict-free
+    __shared__ __align__(16) __half As[64][LD], Bs[64][LD];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const long long m0 = (long long) blockIdx.x * 64, n0 = (long long) blockIdx.y * 64;
+    const long long i2 = blockIdx.z % d.ne[2], i3 = blockIdx.z / d.ne[2];
+    const char * ab = a.data + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3];
+    const char * bb = b.data + i2 * b.nb[2] + i3 * b.nb[3];
+    const long long K = a.ne[0], M = a.ne[1], N = b.ne[1];
+    // loads: thread -> row tid / 2, 16 consecutive k of the 32 (tid & 1)
+    const int lr = tid >> 1, lk = (tid & 1) * 16;
+    const bool a_ok = m0 + lr < M, b_ok = n0 + lr < N;
+    const char * ap = ab + (a_ok ? m0 + lr : 0) * a.nb[1] + lk * 2;
+    const char * bp = bb + (b_ok ? n0 + lr : 0) * b.nb[1] + lk * 4;
+    uint4 ra[2]; float4 rb[4];
+    auto fetch = [&](long long k0) {
+        if (a_ok) { ra[0] = *reinterpret_cast<const uint4 *>(ap + k0 * 2); ra[1] = *reinterpret_cast<const uint4 *>(ap + k0 * 2 + 16); }
+        else { ra[0] = make_uint4(0, 0, 0, 0); ra[1] = ra[0]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) rb[i] = b_ok ? *reinterpret_cast<const float4 *>(bp + k0 * 4 + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    auto stash = [&]() {
+        *reinterpret_cast<uint4 *>(&As[lr][lk]) = ra[0];
+        *reinterpret_cast<uint4 *>(&As[lr][lk + 8]) = ra[1];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __half2 h0 = __floats2half2_rn(rb[i].x, rb[i].y), h1 = __floats2half2_rn(rb[i].z, rb[i].w);
+            *reinterpret_cast<uint2 *>(&Bs[lr][lk + 4 * i]) = make_uint2(*reinterpret_cast<const uint32_t *>(&h0), *reinterpret_cast<const uint32_t *>(&h1));
+        }
+    };
+    // warp tile: 32 (m) x 32 (n) = 2 x 4 MMAs per k16
+    const int wm = (warp & 1) * 32, wn = (warp >> 1) * 32;
+    float acc[2][4][4] = {};
+    fetch(0);
+    for (long long k0 = 0; k0 < K; k0 += BK) {
+        __syncthreads();                                        // the previous step's fragment loads are done
+        stash();
+        __syncthreads();
+        if (k0 + BK < K) fetch(k0 + BK);                        // in flight during the MMAs
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 16) {
+            uint32_t fa[2][4], fb[4][2];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const __half * r0 = &As[wm + 16 * i + g][kk + 2 * t], * r1 = &As[wm + 16 * i + g + 8][kk + 2 * t];
+                fa[i][0] = *reinterpret_cast<const uint32_t *>(r0);     fa[i][1] = *reinterpret_cast<const uint32_t *>(r1);
+                fa[i][2] = *reinterpret_cast<const uint32_t *>(r0 + 8); fa[i][3] = *reinterpret_cast<const uint32_t *>(r1 + 8);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const __half * r = &Bs[wn + 8 * j + g][kk + 2 * t];
+                fb[j][0] = *reinterpret_cast<const uint32_t *>(r); fb[j][1] = *reinterpret_cast<const uint32_t *>(r + 8);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma16816(acc[i][j], fa[i], fb[j]);
+        }
+    }
+    char * db = d.data + i2 * d.nb[2] + i3 * d.nb[3];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const long long m = m0 + wm + 16 * i + g + 8 * (e >> 1), n = n0 + wn + 8 * j + 2 * t + (e & 1);
+                if (m < M && n < N) *reinterpret_cast<float *>(db + m * 4 + n * d.nb[1]) = acc[i][j][e];
+            }
 }
 
 } // namespace
@@ -595,6 +723,10 @@ int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b2
     const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
     if (rows == 0 || src->ne[0] == 0) return 0;
     T4 m = mask ? t4(mask) : t4(src);
+    if (src->ne[0] <= 1024 && rows >= 512) {        // enough rows to fill the machine with one warp each
+        B200_CHECK(b200_launch(soft_max_warp_kernel, dim3(blocks_for(rows, 4)), dim3(128), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale, rows));
+        return 0;
+    }
     B200_CHECK(b200_launch(soft_max_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale));
     return 0;
 }
@@ -606,6 +738,14 @@ int b200_op_glu(const b200_tensor * a, const b200_tensor * b, const b200_tensor 
     B200_REQUIRE(b ? (a->ne[0] == dst->ne[0] && b->ne[0] == dst->ne[0]) : a->ne[0] / 2 == dst->ne[0], "b200_op_glu: shapes");     // (an odd row length drops its last element, as the reference does)
     const long long n = nelem(dst);
     if (n == 0) return 0;
+    auto al16 = [](const b200_tensor * t) { return ((uintptr_t) t->data % 16) == 0 && t->nb[1] % 16 == 0; };
+    if (b && dst->ne[2] == 1 && dst->ne[3] == 1 && dst->ne[0] % 4 == 0 && dst->nb[0] == 4 && al16(a) && al16(b) && al16(dst) && n >= (1 << 16)) {
+        const long long total4 = n / 4;
+        const long long blocks = (total4 + 255) / 256;
+        B200_CHECK(b200_launch(glu_vec4_kernel, dim3((unsigned) (blocks > 148 * 16 ? 148 * 16 : blocks)), dim3(256), 0, (cudaStream_t) stream, false,
+                               t4(a), t4(b), t4w(dst), glu_op, swapped, total4));
+        return 0;
+    }
     B200_LAUNCH_IDX(glu_kernel, n, t4(a), b ? t4(b) : t4(a), b ? 1 : 0, t4w(dst), glu_op, swapped);
     return 0;
 }
@@ -630,6 +770,12 @@ int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_t
         return 0;
     }
     dim3 grid(blocks_for(a->ne[1], 64), blocks_for(n, 64), (unsigned) batch);
+    static const bool mma_on = [] { const char * e = getenv("B200_ATTN_MMA"); return !(e && e[0] == '0'); }();
+    auto aligned16 = [](const b200_tensor * t) { return ((uintptr_t) t->data % 16) == 0 && t->nb[1] % 16 == 0 && t->nb[2] % 16 == 0 && t->nb[3] % 16 == 0; };
+    if (ah && mma_on && a->ne[0] % 32 == 0 && aligned16(a) && aligned16(b)) {
+        B200_CHECK(b200_launch(mm_mma_kernel, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
+        return 0;
+    }
     if (ah) B200_CHECK(b200_launch(mm_tile_kernel<true>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
     else    B200_CHECK(b200_launch(mm_tile_kernel<false>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
     return 0;
