@@ -162,6 +162,12 @@ enum {
 B200_API size_t b200_mul_mat_workspace(int type, int64_t n, int64_t k);
 /* replaces ggml_compute_forward_mul_mat (ggml-cpu.c:1227-1427) for a 2-D slice */
 B200_API int    b200_mul_mat(const b200_mul_mat_args * args, b200_stream_t stream);
+/* MUL_MAT whose activations are still to be gated: Y = W * (act(x) * x2), act = reglu / geglu / swiglu (enum ggml_glu_op 0 / 1 / 2;
+   swapped: act(x2) * x). The GLU node in front of ffn_down (ggml_compute_forward_glu, ggml-cpu/ops.cpp) disappears into the activation
+   quantiser; the reference CUDA backend fuses the same pair from the other side (mul_mat_vec_q<..., has_fusion>, mmvq.cu:173-218).
+   args->x is x, n <= 8. */
+B200_API int    b200_mul_mat_glu(const b200_mul_mat_args * args, const float * x2, int64_t x2_row_stride, int32_t glu_op, int32_t swapped,
+                                 b200_stream_t stream);
 /* `count` MUL_MAT nodes that read the same X (wq/wk/wv, ffn_gate/ffn_up: same x, n, k, strides): issued as ONE
  * streaming launch when n <= 4 and every matrix is in the plane layout, else as `count` b200_mul_mat calls.
  * Counterpart of the reference's fused gate/up GEMV (ggml_cuda_should_fuse_mul_mat_vec_q, ggml-cuda.cu:2144-2180). */
@@ -299,6 +305,12 @@ B200_API int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, cons
                           const b200_rope_params * params, b200_stream_t stream);
 /* ggml_compute_forward_set_rows: dst row idx[i] (i64 / i32) = src row i; src f32, dst f32 / f16 (KV cache writes) */
 B200_API int b200_op_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, b200_stream_t stream);
+/* ROPE whose result also goes, converted, into the rows of a cache tensor: the ROPE(k) -> SET_ROWS(k cache) pair of build_attn
+   (src/llama-graph.cpp; reference kernels ggml-cuda/rope.cu + set-rows.cu, two launches there), plus optionally an independent second
+   SET_ROWS (v cache) in the same launch. sr_src is the SET_ROWS source: a contiguous reshape of dst (same data pointer). */
+B200_API int b200_op_rope_set_rows(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
+                                   const b200_rope_params * params, const b200_tensor * sr_src, const b200_tensor * sr_idx, const b200_tensor * sr_dst,
+                                   const b200_tensor * v_src, const b200_tensor * v_idx, const b200_tensor * v_dst, b200_stream_t stream);
 /* ggml_compute_forward_dup (CPY / CONT / DUP) between f32 and f16, any strides */
 B200_API int b200_op_cpy(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
 /* ggml_compute_forward_soft_max_f32 (ops.cpp:5160-5280): softmax(src * scale + mask) per row; mask f32 / f16 or NULL; max_bias == 0, no sinks */

@@ -1,0 +1,122 @@
+"""The fused glue entry points of the C ABI against their unfused counterparts (same kernels' arithmetic: bit-identical) and the oracle:
+b200_op_rope_set_rows (ROPE -> SET_ROWS [-> SET_ROWS] of build_attn in one launch) and b200_mul_mat_glu (GLU folded into the activation
+quantiser of the following MUL_MAT). Through the plugin both are covered by the whole-graph logits test in test_gpu_plugin.py."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import nmse
+from oracle.oracle import Q4_K, Q6_K, Q8_0, random_blocks
+
+pytestmark = pytest.mark.gpu
+
+F32, F16, I32, I64 = 0, 1, 26, 27
+
+
+class Tensor(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("pad", C.c_int32), ("ne", C.c_int64 * 4), ("nb", C.c_int64 * 4)]
+
+
+class RopeParams(C.Structure):
+    _fields_ = [("n_dims", C.c_int32), ("mode", C.c_int32), ("freq_base", C.c_float), ("freq_scale", C.c_float), ("ext_factor", C.c_float), ("attn_factor", C.c_float)]
+
+
+def _t(x, gtype, ne=None):
+    """ggml view of a contiguous torch tensor: ne is the ggml shape (fastest dimension first); default: the reversed torch shape"""
+    es = x.element_size()
+    ne = list(ne if ne is not None else reversed(x.shape))
+    ne += [1] * (4 - len(ne))
+    nb = [es]
+    for d in ne[:3]:
+        nb.append(nb[-1] * d)
+    return Tensor(x.data_ptr(), gtype, 0, (C.c_int64 * 4)(*ne), (C.c_int64 * 4)(*nb))
+
+
+def _ok(b, rc):
+    assert rc == 0, b.lib.b200_last_error().decode()
+
+
+@pytest.mark.parametrize("mode", [0, 2])
+@pytest.mark.parametrize("n_tok", [1, 7, 40])
+@pytest.mark.parametrize("with_v", [False, True])
+def test_rope_set_rows_equals_the_separate_ops(b200, mode, n_tok, with_v):
+    import torch
+    b = b200
+    for f in ("b200_op_rope", "b200_op_set_rows", "b200_op_rope_set_rows"):
+        getattr(b.lib, f).restype = C.c_int
+    torch.manual_seed(n_tok * 3 + mode)
+    hd, nh, n_ctx = 128, 8, 96
+    dev = "cuda"
+    k = torch.randn((n_tok, nh, hd), device=dev)
+    v = torch.randn((n_tok, nh * hd), device=dev)
+    pos = torch.arange(17, 17 + n_tok, dtype=torch.int32, device=dev)
+    ff = (torch.rand(hd // 2, device=dev) + 0.5).contiguous()
+    idx = torch.randperm(n_ctx, device=dev)[:n_tok].to(torch.int64).contiguous()
+    vidx = torch.randperm(n_ctx, device=dev)[:n_tok].to(torch.int32).contiguous()
+    rp = RopeParams(hd, mode, 500000.0, 1.0, 0.0, 1.0)
+
+    def run(fused):
+        out = torch.zeros_like(k)
+        kc = torch.zeros((n_ctx, nh * hd), dtype=torch.float16, device=dev)
+        vc = torch.zeros((n_ctx, nh * hd), dtype=torch.float32, device=dev)
+        ts, tp, tf, td = _t(k, F32), _t(pos, I32), _t(ff, F32), _t(out, F32)
+        sr_src = _t(out, F32, ne=[nh * hd, n_tok])            # the 2-D reshape the graph hands to SET_ROWS
+        ti, tc = _t(idx, I64), _t(kc, F16)
+        tv, tvi, tvc = _t(v, F32), _t(vidx, I32), _t(vc, F32)
+        if fused:
+            _ok(b, b.lib.b200_op_rope_set_rows(C.byref(ts), C.byref(tp), C.byref(tf), C.byref(td), C.byref(rp), C.byref(sr_src), C.byref(ti), C.byref(tc),
+                                               C.byref(tv) if with_v else None, C.byref(tvi) if with_v else None, C.byref(tvc) if with_v else None, None))
+        else:
+            _ok(b, b.lib.b200_op_rope(C.byref(ts), C.byref(tp), C.byref(tf), C.byref(td), C.byref(rp), None))
+            _ok(b, b.lib.b200_op_set_rows(C.byref(sr_src), C.byref(ti), C.byref(tc), None))
+            if with_v:
+                _ok(b, b.lib.b200_op_set_rows(C.byref(tv), C.byref(tvi), C.byref(tvc), None))
+        torch.cuda.synchronize()
+        return out, kc, vc
+
+    a, c = run(True), run(False)
+    for x, y in zip(a, c):
+        assert torch.equal(x, y)
+    out, kc, vc = a
+    assert float(out.abs().sum()) > 0 and float(kc.float().abs().sum()) > 0
+    # the cache rows named by idx hold the rope result rounded to f16, every other row is untouched
+    assert torch.equal(kc[idx.long()], out.reshape(n_tok, nh * hd).to(torch.float16))
+    assert int((kc.float().abs().sum(dim=1) > 0).sum()) == n_tok
+    if with_v:
+        assert torch.equal(vc[vidx.long()], v)
+    else:
+        assert float(vc.abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("t", [Q4_K, Q6_K, Q8_0])
+@pytest.mark.parametrize("n", [1, 3, 8])
+@pytest.mark.parametrize("op", [0, 1, 2])
+def test_mul_mat_glu_equals_glu_then_mul_mat(b200, orc, t, n, op):
+    import torch
+    b = b200
+    b.lib.b200_mul_mat_glu.restype = C.c_int
+    b.lib.b200_op_glu.restype = C.c_int
+    rng = np.random.default_rng(t * 100 + n * 10 + op)
+    m, k = 320, 3584
+    w = torch.from_numpy(random_blocks(t, m, k, rng)).cuda().reshape(-1)
+    wp = b.repack(t, w, m, k)
+    g = torch.from_numpy((rng.standard_normal((n, k)) * 2).astype(np.float32)).cuda()
+    u = torch.from_numpy(rng.standard_normal((n, k)).astype(np.float32)).cuda()
+    # unfused: the GLU kernel, then the quantiser + register GEMV
+    x = torch.empty_like(g)
+    tg, tu, tx = _t(g, F32), _t(u, F32), _t(x, F32)
+    _ok(b, b.lib.b200_op_glu(C.byref(tg), C.byref(tu), C.byref(tx), op, 0, None))
+    want = b.mul_mat(t, wp, x, m, layout=b.LAYOUT_PLANES, algo=1)
+    # fused
+    y = torch.full((n, m), float("nan"), device="cuda")
+    ws = torch.empty(b.mul_mat_workspace(t, n, k) + 256, dtype=torch.uint8, device="cuda")
+    wsp = (ws.data_ptr() + 255) & ~255
+    a = b.MulMatArgs(t, b.LAYOUT_PLANES, m, n, k, wp.data_ptr(), 0, g.data_ptr(), g.stride(0), y.data_ptr(), y.stride(0),
+                     wsp, ws.numel() - (wsp - ws.data_ptr()), b.Q8_X86, 0, 0, 0)
+    _ok(b, b.lib.b200_mul_mat_glu(C.byref(a), C.c_void_p(u.data_ptr()), C.c_int64(u.stride(0)), op, 0, None))
+    torch.cuda.synchronize()
+    assert torch.equal(y, want), f"max |diff| {(y - want).abs().max().item():.3e}"
+    # and against the oracle on the gated activations the device produced
+    ref = orc.mul_mat(t, w.cpu().numpy().reshape(m, -1), x.cpu().numpy())
+    assert nmse(y.cpu().numpy(), ref) < 1e-10

@@ -101,9 +101,17 @@ __device__ __forceinline__ void quant_chunk256(const float (&v)[8], int lane, in
 
 // One warp quantises one chunk of 256 consecutive elements of one row; lane l owns elements
 // [8l, 8l+8). CANON selects canonical ggml block bytes (y) or the plane layout (pl).
+// An activation source that is still to be gated: X = act(x) * x2 (GGML_OP_GLU with split operands; op 0 reglu, 1 geglu, 2 swiglu as in
+// ggml_compute_forward_glu), so the GLU node in front of ffn_down needs no launch and no round trip of its own. op < 0: plain X.
+struct ActGlu { const float * x2; int64_t ldx2; int op; int swapped; };
+__device__ __forceinline__ float act_glu_fn(int op, float x) {
+    if (op == 0) return x > 0.0f ? x : 0.0f;
+    if (op == 1) return 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * (1.0f + 0.044715f * x * x)));
+    return x / (1.0f + expf(-x));
+}
 template <int QT, int FLAVOUR, bool CANON>
 __global__ void __launch_bounds__(128) act_quant_kernel(const float * __restrict__ x, int64_t ldx, int64_t nrows, int64_t k,
-                                                        uint8_t * __restrict__ y, XqPlanes pl, bool pdl) {
+                                                        uint8_t * __restrict__ y, XqPlanes pl, bool pdl, ActGlu glu) {
     const int lane = threadIdx.x & 31;
     const int64_t chunk = (int64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t nchunks = (k + 255) >> 8;
@@ -127,6 +135,11 @@ __global__ void __launch_bounds__(128) act_quant_kernel(const float * __restrict
         } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
+        }
+        if (glu.op >= 0 && live) {
+            const float * ur = glu.x2 + row * glu.ldx2 + e0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float u = ur[j]; v[j] = glu.swapped ? act_glu_fn(glu.op, u) * v[j] : act_glu_fn(glu.op, v[j]) * u; }
         }
 
         int q[8];
@@ -174,4 +187,4 @@ __global__ void __launch_bounds__(128) act_quant_kernel(const float * __restrict
 // host launchers (quantize.cu)
 int b200_act_quant_canonical(int q8_type, int flavour, const float * x, int64_t ldx, void * y, int64_t nrows, int64_t k, cudaStream_t s);
 int b200_act_quant_planes(int act_type, int flavour, const float * x, int64_t ldx, const XqPlanes & pl, int64_t nrows, int64_t k,
-                          cudaStream_t s, bool pdl);
+                          cudaStream_t s, bool pdl, const ActGlu * glu = nullptr);

@@ -1013,6 +1013,14 @@ void ensure_canonical(const ggml_tensor * t) {
     std::lock_guard<std::mutex> lock(bc->mu);
     planes_demote_locked(bc, base->data);
 }
+b200_rope_params rope_params_of(const ggml_tensor * node) {
+    const int32_t * p = (const int32_t *) node->op_params;
+    b200_rope_params rp = {};
+    rp.n_dims = p[1]; rp.mode = p[2];
+    memcpy(&rp.freq_base, p + 5, sizeof(float)); memcpy(&rp.freq_scale, p + 6, sizeof(float));
+    memcpy(&rp.ext_factor, p + 7, sizeof(float)); memcpy(&rp.attn_factor, p + 8, sizeof(float));
+    return rp;
+}
 enum ggml_status compute_glue(backend_ctx * bc, const ggml_tensor * node) {
     const ggml_tensor * a = node->src[0], * b = node->src[1];
     const b200_tensor d = bt(node);
@@ -1023,11 +1031,7 @@ enum ggml_status compute_glue(backend_ctx * bc, const ggml_tensor * node) {
         case GGML_OP_ADD:
         case GGML_OP_MUL: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_binary(node->op == GGML_OP_ADD ? 0 : 1, &ta, &tb, &d, bc->stream); } break;
         case GGML_OP_ROPE: {
-            const int32_t * p = (const int32_t *) node->op_params;
-            b200_rope_params rp = {};
-            rp.n_dims = p[1]; rp.mode = p[2];
-            memcpy(&rp.freq_base, p + 5, sizeof(float)); memcpy(&rp.freq_scale, p + 6, sizeof(float));
-            memcpy(&rp.ext_factor, p + 7, sizeof(float)); memcpy(&rp.attn_factor, p + 8, sizeof(float));
+            const b200_rope_params rp = rope_params_of(node);
             const b200_tensor ta = bt(a), tb = bt(b);
             b200_tensor tf = {}; if (node->src[2]) tf = bt(node->src[2]);
             rc = b200_op_rope(&ta, &tb, node->src[2] ? &tf : nullptr, &d, &rp, bc->stream);
@@ -1188,6 +1192,61 @@ int try_fuse_attn(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & s
     return ic;
 }
 
+// ROPE(k) -> SET_ROWS(k cache) [-> SET_ROWS(v cache)] as one launch (b200_op_rope_set_rows); returns the index of the last node consumed (-1: no match)
+int try_fuse_kv(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
+    const ggml_tensor * R = g->nodes[i];
+    const int is1 = next_real(g, i);
+    if (is1 < 0) return -1;
+    const ggml_tensor * S1 = g->nodes[is1];
+    if (S1->op != GGML_OP_SET_ROWS || !glue_supports(R) || !glue_supports(S1)) return -1;
+    const ggml_tensor * v = S1->src[0];
+    if (!v || v->data != R->data || v->type != GGML_TYPE_F32 || !ggml_is_contiguous(v) || !ggml_is_contiguous(R) || ggml_nelements(v) != ggml_nelements(R) || R->view_src) return -1;
+    const ggml_tensor * root = v;
+    while (root->view_src) root = root->view_src;
+    if (root != R || ranges_overlap(S1, R) || ranges_overlap(S1, R->src[0])) return -1;
+    int last = is1;
+    const ggml_tensor * S2 = nullptr;
+    const int is2 = next_real(g, is1);
+    if (is2 >= 0 && g->nodes[is2]->op == GGML_OP_SET_ROWS && glue_supports(g->nodes[is2])) {
+        const ggml_tensor * c = g->nodes[is2];
+        // independent of the pair: it neither reads what they write nor writes what they read or write
+        if (!ranges_overlap(c->src[0], R) && !ranges_overlap(c->src[0], S1) && !ranges_overlap(c, S1) && !ranges_overlap(c, R) && !ranges_overlap(c, R->src[0]) &&
+            !ranges_overlap(c->src[1], R) && !ranges_overlap(c, S1->src[1])) { S2 = c; last = is2; }
+    }
+    const b200_rope_params rp = rope_params_of(R);
+    const b200_tensor ta = bt(R->src[0]), tp = bt(R->src[1]), td = bt(R), tv = bt(v), ti = bt(S1->src[1]), tc = bt(S1);
+    b200_tensor tf = {}; if (R->src[2]) tf = bt(R->src[2]);
+    b200_tensor v2 = {}, i2 = {}, c2 = {};
+    if (S2) { v2 = bt(S2->src[0]); i2 = bt(S2->src[1]); c2 = bt(S2); }
+    if (b200_op_rope_set_rows(&ta, &tp, R->src[2] ? &tf : nullptr, &td, &rp, &tv, &ti, &tc, S2 ? &v2 : nullptr, S2 ? &i2 : nullptr, S2 ? &c2 : nullptr, bc->stream) != 0) {
+        GGML_LOG_ERROR("ggml-b200: fused rope + set_rows (%s) failed: %s\n", R->name, b200_last_error()); st = GGML_STATUS_FAILED;
+    }
+    return last;
+}
+
+// GLU(gate, up) -> MUL_MAT(w, .) at decode: the gate goes into the activation quantiser of the matmul (b200_mul_mat_glu); returns the index of the
+// MUL_MAT node (-1: no match)
+int try_fuse_glu(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
+    const ggml_tensor * G = g->nodes[i];
+    if (!G->src[1] || !glue_supports(G) || !ggml_node_has_n_uses(g, i, 1)) return -1;
+    const int im = next_real(g, i);
+    if (im < 0) return -1;
+    const ggml_tensor * M = g->nodes[im];
+    if (!plain_mul_mat(M) || M->src[1] != G || M->src[1]->ne[1] > 8) return -1;
+    const ggml_tensor * a = G->src[0], * b = G->src[1];
+    if (a->ne[2] != 1 || a->ne[3] != 1 || !ggml_are_same_shape(a, b) || a->ne[0] != G->ne[0] || a->nb[0] != sizeof(float) || b->nb[0] != sizeof(float) ||
+        a->nb[1] % sizeof(float) || b->nb[1] % sizeof(float)) return -1;
+    b200_mul_mat_args args = plain_args(M);
+    args.x = (const float *) a->data; args.x_row_stride = (int64_t) (a->nb[1] / sizeof(float));
+    const size_t need = b200_mul_mat_workspace(args.type, args.n, args.k);
+    if (!backend_reserve(bc, need)) { st = GGML_STATUS_ALLOC_FAILED; return im; }
+    args.workspace = bc->workspace; args.workspace_size = bc->workspace_size;
+    if (b200_mul_mat_glu(&args, (const float *) b->data, (int64_t) (b->nb[1] / sizeof(float)), ggml_get_op_params_i32(G, 0), ggml_get_op_params_i32(G, 1), bc->stream) != 0) {
+        GGML_LOG_ERROR("ggml-b200: fused glu + MUL_MAT (%s) failed: %s\n", M->name, b200_last_error()); st = GGML_STATUS_FAILED;
+    }
+    return im;
+}
+
 enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
     static const bool fuse_on = env_on("GGML_B200_FUSE") && glue_on();
     std::vector<char> done((size_t) cgraph->n_nodes, 0);          // matmuls hoisted into an earlier group
@@ -1205,6 +1264,16 @@ enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
             const int used = try_fuse_norm(bc, cgraph, i, st);
             if (st != GGML_STATUS_SUCCESS) return st;
             if (used > 0) { i += used - 1; continue; }
+        }
+        if (fuse_on && node->op == GGML_OP_GLU) {
+            const int im = try_fuse_glu(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (im > i) { i = im; continue; }
+        }
+        if (fuse_on && node->op == GGML_OP_ROPE) {
+            const int last = try_fuse_kv(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (last > i) { i = last; continue; }
         }
         if (fuse_on && node->op == GGML_OP_MUL_MAT && node->src[0]->type == GGML_TYPE_F16) {
             const int ic = try_fuse_attn(bc, cgraph, i, st);

@@ -347,6 +347,61 @@ __global__ void __launch_bounds__(256) set_rows_kernel(const T4 a, const T4 idx,
     }
 }
 
+// ---- decode / prefill KV-cache prologue in ONE launch: ROPE(k) whose result goes to its own tensor AND, converted, into the K cache rows
+// (the SET_ROWS that follows it in build_attn, src/llama-graph.cpp), plus optionally the independent SET_ROWS of V in the tail blocks.
+// `sa` = shape of the SET_ROWS source (a reshaped, contiguous view of the ROPE result: element L of one is element L of the other).
+template <typename I>
+__global__ void __launch_bounds__(256) rope_set_rows_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p,
+                                                           const T4 sa, const T4 idx, const T4w cache, unsigned kblocks,
+                                                           const T4 va, const T4 vidx, const T4w vcache) {
+    if (blockIdx.x >= kblocks) {                              // SET_ROWS of V: the body of set_rows_kernel on the tail blocks
+        const I total = (I) (va.ne[0] * va.ne[1] * va.ne[2] * va.ne[3]);
+        for (I i = (I) (blockIdx.x - kblocks) * 256 + threadIdx.x; i < total; i += (I) (gridDim.x - kblocks) * 256) {
+            I i0, i1, i2, i3;
+            unravel<I>(i, va.ne, i0, i1, i2, i3);
+            const char * ip = vidx.data + (long long) i1 * vidx.nb[0] + (long long) (i2 % (I) vidx.ne[1]) * vidx.nb[1] + (long long) (i3 % (I) vidx.ne[2]) * vidx.nb[2];
+            const long long r = vidx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
+            const float v = *reinterpret_cast<const float *>(va.data + (long long) i0 * va.nb[0] + (long long) i1 * va.nb[1] + (long long) i2 * va.nb[2] + (long long) i3 * va.nb[3]);
+            store_as(vcache.data + (long long) i0 * vcache.nb[0] + r * vcache.nb[1] + (long long) i2 * vcache.nb[2] + (long long) i3 * vcache.nb[3], vcache.type, v);
+        }
+        return;
+    }
+    const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
+    const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
+    const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) kblocks * 256) {
+        I ip, i1, i2, i3;
+        unravel<I>(i, hne, ip, i1, i2, i3);
+        const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
+        int e0, e1; float y0, y1;
+        if (2 * (int) ip >= p.n_dims) {
+            e0 = 2 * (int) ip; e1 = e0 + 1;
+            y0 = reinterpret_cast<const float *>(src)[e0]; y1 = reinterpret_cast<const float *>(src)[e1];
+        } else {
+            const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
+            float sn, cs;
+            sincosf(theta, &sn, &cs);
+            sn *= p.attn_factor; cs *= p.attn_factor;
+            e0 = p.mode == 2 ? (int) ip : 2 * (int) ip; e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
+            const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
+            y0 = x0 * cs - x1 * sn; y1 = x0 * sn + x1 * cs;
+        }
+        // d is contiguous (host check): linear element index of (e, i1, i2, i3)
+        const I base = (I) (((long long) i3 * d.ne[2] + i2) * d.ne[1] + i1) * (I) d.ne[0];
+        float * dp = reinterpret_cast<float *>(d.data) + base;
+        dp[e0] = y0; dp[e1] = y1;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const I L = base + (I) (h ? e1 : e0);
+            I j0, j1, j2, j3;
+            unravel<I>(L, sa.ne, j0, j1, j2, j3);
+            const char * xp = idx.data + (long long) j1 * idx.nb[0] + (long long) (j2 % (I) idx.ne[1]) * idx.nb[1] + (long long) (j3 % (I) idx.ne[2]) * idx.nb[2];
+            const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(xp) : *reinterpret_cast<const long long *>(xp);
+            store_as(cache.data + (long long) j0 * cache.nb[0] + r * cache.nb[1] + (long long) j2 * cache.nb[2] + (long long) j3 * cache.nb[3], cache.type, h ? y1 : y0);
+        }
+    }
+}
+
 // ---- CPY / CONT / DUP between f32 and f16 (ggml_compute_forward_dup): element i of src (row-major over its shape) -> element i of dst ----
 template <typename I>
 __global__ void __launch_bounds__(256) cpy_kernel(const T4 a, const T4w d) {
@@ -392,38 +447,46 @@ __global__ void __launch_bounds__(256) soft_max_kernel(const T4 a, const T4 m, i
     for (long long i = threadIdx.x; i < n; i += 256) y[i] *= inv;
 }
 
-// rows of up to 1024 elements (attention scores over the KV cache): one WARP per row, the row lives in registers between the passes
-__global__ void __launch_bounds__(128) soft_max_warp_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale, long long rows) {
+// rows of up to 1024 elements (attention scores over the KV cache): one WARP per row, the row lives in registers between the passes.
+// NJ = elements per lane (8 / 16 / 32 for rows of up to 256 / 512 / 1024); 32-bit index arithmetic (the host checks the row count)
+template <int NJ>
+__global__ void __launch_bounds__(128) soft_max_warp_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale, unsigned rows) {
     const int lane = threadIdx.x & 31;
-    const long long row = (long long) blockIdx.x * 4 + (threadIdx.x >> 5);
+    const unsigned row = blockIdx.x * 4u + (threadIdx.x >> 5);
     if (row >= rows) return;
-    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
-    const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
-    float * y = reinterpret_cast<float *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
-    const char * mp = has_mask ? m.data + i1 * m.nb[1] + (i2 % m.ne[2]) * m.nb[2] + (i3 % m.ne[3]) * m.nb[3] : nullptr;
+    const unsigned ne1 = (unsigned) a.ne[1], ne2 = (unsigned) a.ne[2];
+    const unsigned i1 = row % ne1, r12 = row / ne1, i2 = r12 % ne2, i3 = r12 / ne2;
+    const float * x = reinterpret_cast<const float *>(a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+    float * y = reinterpret_cast<float *>(d.data + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]);
+    const char * mp = has_mask ? m.data + (long long) i1 * m.nb[1] + (long long) (i2 % (unsigned) m.ne[2]) * m.nb[2] + (long long) (i3 % (unsigned) m.ne[3]) * m.nb[3] : nullptr;
     const int n = (int) a.ne[0];
-    float v[32];
+    const bool mh = m.type == B200_TYPE_F16;
+    float v[NJ];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) { const int i = lane + 32 * j; v[j] = i < n ? x[i] : -INFINITY; }
+    if (mp) {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+            const int i = lane + 32 * j;
+            const float mk = i < n ? (mh ? __half2float(reinterpret_cast<const __half *>(mp)[i]) : reinterpret_cast<const float *>(mp)[i]) : 0.0f;
+            v[j] = v[j] * scale + mk;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) v[j] *= scale;
+    }
     float mx = -INFINITY;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        const int i = lane + 32 * j;
-        v[j] = -INFINITY;
-        if (i < n) {
-            float t = x[i] * scale;
-            if (mp) t += m.type == B200_TYPE_F16 ? __half2float(reinterpret_cast<const __half *>(mp)[i]) : reinterpret_cast<const float *>(mp)[i];
-            v[j] = t;
-        }
-        mx = fmaxf(mx, v[j]);
-    }
+    for (int j = 0; j < NJ; ++j) mx = fmaxf(mx, v[j]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     float s = 0.0f;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) { if (lane + 32 * j < n) { v[j] = expf(v[j] - mx); s += v[j]; } }
+    for (int j = 0; j < NJ; ++j) { v[j] = lane + 32 * j < n ? expf(v[j] - mx) : 0.0f; s += v[j]; }
     s = warp_sum(s);
     const float inv = 1.0f / s;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) { const int i = lane + 32 * j; if (i < n) y[i] = v[j] * inv; }
+    for (int j = 0; j < NJ; ++j) { const int i = lane + 32 * j; if (i < n) y[i] = v[j] * inv; }
 }
 
 // ---- GLU: reglu 0, geglu 1, swiglu 2 (enum ggml_glu_op, ggml.h; ggml_compute_forward_glu, ops.cpp): dst = act(x) * g ----
@@ -692,6 +755,36 @@ int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_te
     return 0;
 }
 
+int b200_op_rope_set_rows(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst, const b200_rope_params * p,
+                          const b200_tensor * sr_src, const b200_tensor * sr_idx, const b200_tensor * sr_dst,
+                          const b200_tensor * v_src, const b200_tensor * v_idx, const b200_tensor * v_dst, b200_stream_t stream) {
+    B200_REQUIRE(src && pos && dst && p && sr_src && sr_idx && sr_dst && src->data && pos->data && dst->data && sr_idx->data && sr_dst->data, "b200_op_rope_set_rows: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && pos->type == B200_TYPE_I32 && src->nb[0] == 4, "b200_op_rope_set_rows: f32 rows, i32 positions");
+    B200_REQUIRE((p->mode == 0 || p->mode == 2) && p->ext_factor == 0.0f && p->n_dims > 0 && p->n_dims % 2 == 0 && p->n_dims <= src->ne[0] && src->ne[0] % 2 == 0,
+                 "b200_op_rope_set_rows: mode %d / ext_factor %g / n_dims %d not supported", p->mode, (double) p->ext_factor, p->n_dims);
+    B200_REQUIRE(pos->ne[0] >= src->ne[2], "b200_op_rope_set_rows: %lld positions for %lld tokens", (long long) pos->ne[0], (long long) src->ne[2]);
+    B200_REQUIRE(contiguous_f(dst, 4) && sr_src->data == dst->data && sr_src->type == B200_TYPE_F32 && contiguous_f(sr_src, 4) && nelem(sr_src) == nelem(dst),
+                 "b200_op_rope_set_rows: the SET_ROWS source must be a contiguous reshape of the ROPE result");
+    B200_REQUIRE((sr_dst->type == B200_TYPE_F32 || sr_dst->type == B200_TYPE_F16) && (sr_idx->type == B200_TYPE_I64 || sr_idx->type == B200_TYPE_I32), "b200_op_rope_set_rows: cache f32 / f16, indices i64 / i32");
+    if (v_src) {
+        B200_REQUIRE(v_idx && v_dst && v_src->data && v_idx->data && v_dst->data && v_src->type == B200_TYPE_F32 && (v_dst->type == B200_TYPE_F32 || v_dst->type == B200_TYPE_F16) &&
+                     (v_idx->type == B200_TYPE_I64 || v_idx->type == B200_TYPE_I32), "b200_op_rope_set_rows: bad second SET_ROWS");
+    }
+    const long long n = nelem(src) / 2, nv = v_src ? nelem(v_src) : 0;
+    if (n == 0) return v_src ? b200_op_set_rows(v_src, v_idx, v_dst, stream) : 0;
+    RopeP rp; rp.n_dims = p->n_dims; rp.mode = p->mode; rp.freq_base = p->freq_base; rp.freq_scale = p->freq_scale; rp.attn_factor = p->attn_factor;
+    const unsigned kb = blocks_for(n, 256), vb = nv ? blocks_for(nv, 256) : 0;
+    const float * ffp = freq_factors ? (const float *) freq_factors->data : (const float *) nullptr;
+    const T4 tv = v_src ? t4(v_src) : t4(src), tvi = v_src ? t4(v_idx) : t4(sr_idx); const T4w tvc = v_src ? t4w(v_dst) : t4w(sr_dst);
+    if (nelem(dst) < (1ll << 31) && nv < (1ll << 31))
+        B200_CHECK(b200_launch(rope_set_rows_kernel<unsigned>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
+                               t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
+    else
+        B200_CHECK(b200_launch(rope_set_rows_kernel<long long>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
+                               t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
+    return 0;
+}
+
 int b200_op_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, b200_stream_t stream) {
     B200_REQUIRE(src && idx && dst && src->data && idx->data && dst->data, "b200_op_set_rows: null tensor");
     B200_REQUIRE(src->type == B200_TYPE_F32 && (dst->type == B200_TYPE_F32 || dst->type == B200_TYPE_F16) && (idx->type == B200_TYPE_I64 || idx->type == B200_TYPE_I32),
@@ -723,8 +816,12 @@ int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b2
     const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
     if (rows == 0 || src->ne[0] == 0) return 0;
     T4 m = mask ? t4(mask) : t4(src);
-    if (src->ne[0] <= 1024 && rows >= 512) {        // enough rows to fill the machine with one warp each
-        B200_CHECK(b200_launch(soft_max_warp_kernel, dim3(blocks_for(rows, 4)), dim3(128), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale, rows));
+    if (src->ne[0] <= 1024 && rows >= 512 && rows < (1ll << 31)) {        // enough rows to fill the machine with one warp each
+        const dim3 grid(blocks_for(rows, 4));
+        const T4 ts = t4(src); const T4w td = t4w(dst);
+        if (src->ne[0] <= 256)      B200_CHECK(b200_launch(soft_max_warp_kernel<8>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
+        else if (src->ne[0] <= 512) B200_CHECK(b200_launch(soft_max_warp_kernel<16>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
+        else                        B200_CHECK(b200_launch(soft_max_warp_kernel<32>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
         return 0;
     }
     B200_CHECK(b200_launch(soft_max_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale));

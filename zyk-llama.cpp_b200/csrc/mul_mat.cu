@@ -54,7 +54,7 @@ static __global__ void __launch_bounds__(256) peer_scatter_kernel(const float * 
 
 // `peer` (may be null): fused row-split exchange for this node; peer->wait / peer->signal say whether this node's first
 // kernel waits for the earlier calls and whether its last kernel announces the end of the call
-static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerGather * peer) {
+static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerGather * peer, const ActGlu * glu = nullptr) {
     B200_REQUIRE(a && a->w && a->x && a->y, "b200_mul_mat: null pointer");
     B200_REQUIRE(b200_type_is_weight(a->type), "b200_mul_mat: unsupported weight type %d", a->type);
     const int be = b200_block_elems(a->type);
@@ -72,7 +72,7 @@ static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerG
     const bool fast = planes_fast_path(a->type, a->layout, a->m, a->k, a->w, a->w_row_stride);
 
     // (2) prefill: tensor-core GEMM on plane layout
-    if (a->algo != 1 && fast && b200_gemm_wants(a->type, a->m, a->n, a->k, a->algo == 2)) {
+    if (!glu && a->algo != 1 && fast && b200_gemm_wants(a->type, a->m, a->n, a->k, a->algo == 2)) {
         if (peer && peer->wait) B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, s, false, *peer));
         if (!peer) return b200_gemm_launch(a, s);
         // row split. Default: the GEMM keeps its epilogue local (k-split tiles meet through atomics in local memory) and a copy kernel sends the slice to
@@ -95,7 +95,7 @@ static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerG
     const XqPlanes pl = xq_planes_carve(a->workspace, act, a->n, a->k);
 
     // (1) decode, streaming kernel: one launch, activation quantiser fused (quantised X also left in the workspace)
-    if (fast && a->n <= 4 && a->algo != 1 && !(a->flags & B200_MM_X_PREQUANTISED)) {
+    if (!glu && fast && a->n <= 4 && a->algo != 1 && !(a->flags & B200_MM_X_PREQUANTISED)) {
         GemvGroup g = {};
         g.count = 1; g.type[0] = a->type; g.w[0] = a->w; g.m[0] = a->m; g.y[0] = a->y;
         g.ldy[0] = a->y_row_stride;
@@ -110,7 +110,7 @@ static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerG
     // (3) + (1): quantise activations into the workspace planes, then register GEMV in column groups of <= 8
     if (peer && peer->wait) B200_CHECK(b200_launch(peer_wait_kernel, dim3(1), dim3(32), 0, s, false, *peer));
     if (!(a->flags & B200_MM_X_PREQUANTISED)) {
-        int rc = b200_act_quant_planes(act, a->flavour, a->x, a->x_row_stride, pl, a->n, a->k, s, pdl);
+        int rc = b200_act_quant_planes(act, a->flavour, a->x, a->x_row_stride, pl, a->n, a->k, s, pdl, glu);
         if (rc) return rc;
     }
     B200_REQUIRE(!peer || fast, "b200_mul_mat_gather: the row-split exchange needs the plane layout (type %d m=%lld k=%lld)", a->type,
@@ -146,6 +146,15 @@ static int mul_mat_impl(const b200_mul_mat_args * a, cudaStream_t s, const PeerG
 }
 
 int b200_mul_mat(const b200_mul_mat_args * a, b200_stream_t stream) { return mul_mat_impl(a, (cudaStream_t) stream, nullptr); }
+
+// Y = W * glu(x, x2): the activation quantiser gates on the fly (act_quant_kernel), then the register GEMV. Decode shapes only (n <= 8).
+int b200_mul_mat_glu(const b200_mul_mat_args * a, const float * x2, int64_t x2_row_stride, int32_t glu_op, int32_t swapped, b200_stream_t stream) {
+    B200_REQUIRE(a && x2, "b200_mul_mat_glu: null pointer");
+    B200_REQUIRE(glu_op >= 0 && glu_op <= 2, "b200_mul_mat_glu: op %d (0 reglu, 1 geglu, 2 swiglu)", glu_op);
+    B200_REQUIRE(a->n >= 1 && a->n <= 8 && !(a->flags & B200_MM_X_PREQUANTISED) && a->algo != 2 && a->algo != 3, "b200_mul_mat_glu: decode shapes (n <= 8) on the quantiser + GEMV path only");
+    const ActGlu g = {x2, x2_row_stride, (int) glu_op, (int) swapped};
+    return mul_mat_impl(a, (cudaStream_t) stream, nullptr, &g);
+}
 
 // do `count` nodes that read the same X all take the GEMM, or all take the quantiser + register GEMV with the same activation
 // format? Then the first call converts X into the common workspace and the others reuse it (B200_MM_X_PREQUANTISED).
