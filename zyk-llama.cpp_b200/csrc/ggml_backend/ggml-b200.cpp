@@ -132,6 +132,10 @@ bool in_split_buffer(const ggml_tensor * t) {
     return b && b->buffer && b->buffer->buft->iface.get_name == split_buft_get_name;
 }
 
+// GGML_B200_PDL=0: launch the matmul kernels without programmatic dependent launch (their weight prefetch then starts only when the
+// previous kernel of the stream has drained)
+int32_t mm_flags() { static const int32_t f = [] { const char * e = getenv("GGML_B200_PDL"); return (e && e[0] == '0') ? 0 : (int32_t) B200_MM_PDL; }(); return f; }
+
 bool repack_enabled() {
     static const bool on = [] { const char * e = getenv("GGML_B200_REPACK"); return !(e && e[0] == '0'); }();
     return on;
@@ -754,7 +758,7 @@ enum ggml_status compute_mul_mat_split(backend_ctx * bc, const ggml_tensor * dst
         a.m = s.hi - s.lo; a.n = n; a.k = k;
         a.w = s.data; a.w_row_stride = 0;
         a.y = (float *) dst->data + s.lo; a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
-        a.flavour = B200_Q8_X86;
+        a.flavour = B200_Q8_X86; a.flags = mm_flags();
     };
     for (int i = 0; i < st->n_dev && result == GGML_STATUS_SUCCESS; ++i) {
         const split_slice & s = st->s[i];
@@ -820,7 +824,7 @@ enum ggml_status compute_mul_mat(backend_ctx * bc, const ggml_tensor * dst) {
             a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
             a.workspace = bc->workspace;
             a.workspace_size = bc->workspace_size;
-            a.flavour = B200_Q8_X86;
+            a.flavour = B200_Q8_X86; a.flags = mm_flags();
             if (b200_mul_mat(&a, bc->stream) != 0) {
                 GGML_LOG_ERROR("ggml-b200: MUL_MAT %s failed: %s\n", dst->name, b200_last_error());
                 return GGML_STATUS_FAILED;
@@ -855,7 +859,7 @@ enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
         a.y = (float *) ((char *) dst->data + t0 * dst->nb[2]);
         a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float)); a.y_token_stride = (int64_t) (dst->nb[2] / sizeof(float));
         a.workspace = bc->workspace; a.workspace_size = bc->workspace_size;
-        a.flavour = B200_Q8_X86;
+        a.flavour = B200_Q8_X86; a.flags = mm_flags();
         if (b200_mul_mat_id(&a, bc->stream) != 0) {
             GGML_LOG_ERROR("ggml-b200: MUL_MAT_ID %s failed: %s\n", dst->name, b200_last_error());
             return GGML_STATUS_FAILED;
@@ -890,7 +894,7 @@ b200_mul_mat_args plain_args(const ggml_tensor * dst) {
     a.w = w->data; a.w_row_stride = a.layout == B200_LAYOUT_PLANES ? 0 : (int64_t) w->nb[1];
     a.x = (const float *) x->data; a.x_row_stride = (int64_t) (x->nb[1] / sizeof(float));
     a.y = (float *) dst->data; a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float));
-    a.flavour = B200_Q8_X86;
+    a.flavour = B200_Q8_X86; a.flags = mm_flags();
     return a;
 }
 // two argument lists describe the same chain (field by field: the structs carry padding)

@@ -23,6 +23,8 @@ long long nelem(const b200_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] *
 bool contiguous_f(const b200_tensor * t, long long esz) {
     return t->nb[0] == esz && t->nb[1] == t->nb[0] * t->ne[0] && t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
 }
+// B200_GLUE_PDL=0: launch the glue kernels without the programmatic-dependent-launch attribute
+bool glue_pdl() { static const bool on = [] { const char * e = getenv("B200_GLUE_PDL"); return !(e && e[0] == '0'); }(); return on; }
 unsigned blocks_for(long long n, int per) { const long long b = (n + per - 1) / per; return (unsigned) (b < 1 ? 1 : b > 0x7fffffffll ? 0x7fffffffll : b); }
 
 // element index -> 4-D coordinates; I = unsigned (32-bit divisions, ~5x cheaper) whenever the tensor has fewer than 2^31 elements
@@ -32,8 +34,8 @@ __device__ __forceinline__ void unravel(I i, const long long * ne, I & i0, I & i
     i0 = i % n0; I r = i / n0; i1 = r % n1; r /= n1; i2 = r % n2; i3 = r / n2;
 }
 #define B200_LAUNCH_IDX(kernel, total, ...) \
-    do { if ((total) < (1ll << 31)) B200_CHECK(b200_launch(kernel<unsigned>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, false, __VA_ARGS__)); \
-         else                       B200_CHECK(b200_launch(kernel<long long>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, false, __VA_ARGS__)); } while (0)
+    do { if ((total) < (1ll << 31)) B200_CHECK(b200_launch(kernel<unsigned>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), __VA_ARGS__)); \
+         else                       B200_CHECK(b200_launch(kernel<long long>, dim3(blocks_for(total, 256)), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), __VA_ARGS__)); } while (0)
 
 // ---- dequantise ONE element of a canonical ggml row (dequantize_row_*, ggml-quants.c:307-325, 401-415, 1352-1375, 1762-1792, 2530-2551) ----
 __device__ __constant__ signed char kvalues_iq4nl_d[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
@@ -101,6 +103,7 @@ __device__ __forceinline__ float deq_one(int type, const uint8_t * row, long lon
 // ---- GET_ROWS (ggml_compute_forward_get_rows, ggml-cpu/ops.cpp): dst[:, i10, i11, i12] = row src1[i10, i11, i12] of matrix (i11, i12) of src0 ----
 template <typename I>
 __global__ void __launch_bounds__(256) get_rows_kernel(const T4 a, const T4 ids, const T4w d) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
     for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
         I e, i10, i11, i12;
@@ -113,6 +116,7 @@ __global__ void __launch_bounds__(256) get_rows_kernel(const T4 a, const T4 ids,
 
 // ---- RMS_NORM (ggml_compute_forward_rms_norm_f32): y = x / sqrt(mean(x^2) + eps), one CTA per row ----
 __global__ void __launch_bounds__(256) rms_norm_kernel(const T4 a, const T4w d, float eps) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const long long row = blockIdx.x;
     const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
     const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
@@ -136,6 +140,7 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(const T4 a, const T4w d, 
 // one CTA of 1024 threads per row: the row is read once with 128-bit loads (two per thread: rows of up to 8192 elements stay in registers), longer or
 // unaligned rows take the scalar loop. w has ne[0] == row length (checked by the caller), so it is indexed without a modulo.
 __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, const T4 b, int has_b, const T4w sum, int has_sum, const T4 w, const T4w d, float eps) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const unsigned row = blockIdx.x;
     const unsigned n1 = (unsigned) a.ne[1], n2 = (unsigned) a.ne[2];
     const unsigned i1 = row % n1, i2 = (row / n1) % n2, i3 = row / (n1 * n2);
@@ -193,6 +198,7 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, cons
 //   scores: four lanes per KV row (head_dim / 4 elements each as 128-bit loads), 64 rows per CTA pass;
 //   output: thread (d, part) walks its part of row d of V^T with 128-bit loads, the parts meet in shared memory.
 __global__ void __launch_bounds__(256) attn_decode_kernel(const T4 K, const T4 q, const T4 m, int has_mask, const T4 V, float * __restrict__ out, float scale) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     extern __shared__ float sc[];                 // n_kv scores, then head_dim q values, then 256 partial outputs
     __shared__ float red[8];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -286,6 +292,7 @@ __global__ void __launch_bounds__(256) attn_decode_kernel(const T4 K, const T4 q
 // ---- ADD / MUL with ggml broadcasting of src1 (ggml_compute_forward_add / _mul: src1 dims divide src0 dims) ----
 template <int OP, typename I>
 __global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, const T4w d) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
     const I b0 = (I) b.ne[0], b1 = (I) b.ne[1], b2 = (I) b.ne[2], b3 = (I) b.ne[3];
     for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
@@ -301,6 +308,7 @@ __global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, con
 struct RopeP { int n_dims, mode; float freq_base, freq_scale, attn_factor; };
 template <typename I>
 __global__ void __launch_bounds__(256) rope_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
     const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
     const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
@@ -336,6 +344,7 @@ __device__ __forceinline__ float load_as(const char * p, int type) {
 // ---- SET_ROWS (ggml_compute_forward_set_rows_f32): dst row src1[i01, i02 % ne11, i03 % ne12] of matrix (i02, i03) = src0 row (i01, i02, i03) ----
 template <typename I>
 __global__ void __launch_bounds__(256) set_rows_kernel(const T4 a, const T4 idx, const T4w d) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const I total = (I) (a.ne[0] * a.ne[1] * a.ne[2] * a.ne[3]);
     for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
         I i0, i1, i2, i3;
@@ -354,6 +363,7 @@ template <typename I>
 __global__ void __launch_bounds__(256) rope_set_rows_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p,
                                                            const T4 sa, const T4 idx, const T4w cache, unsigned kblocks,
                                                            const T4 va, const T4 vidx, const T4w vcache) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     if (blockIdx.x >= kblocks) {                              // SET_ROWS of V: the body of set_rows_kernel on the tail blocks
         const I total = (I) (va.ne[0] * va.ne[1] * va.ne[2] * va.ne[3]);
         for (I i = (I) (blockIdx.x - kblocks) * 256 + threadIdx.x; i < total; i += (I) (gridDim.x - kblocks) * 256) {
@@ -405,6 +415,7 @@ __global__ void __launch_bounds__(256) rope_set_rows_kernel(const T4 a, const in
 // ---- CPY / CONT / DUP between f32 and f16 (ggml_compute_forward_dup): element i of src (row-major over its shape) -> element i of dst ----
 template <typename I>
 __global__ void __launch_bounds__(256) cpy_kernel(const T4 a, const T4w d) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
     for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
         I s0, s1, s2, s3, d0, d1, d2, d3;
@@ -417,6 +428,7 @@ __global__ void __launch_bounds__(256) cpy_kernel(const T4 a, const T4w d) {
 
 // ---- SOFT_MAX with scale and an optional f32 / f16 mask, max_bias == 0, no sinks (ggml_compute_forward_soft_max_f32, ops.cpp:5160-5280) ----
 __global__ void __launch_bounds__(256) soft_max_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const long long row = blockIdx.x;
     const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
     const float * x = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
@@ -451,6 +463,7 @@ __global__ void __launch_bounds__(256) soft_max_kernel(const T4 a, const T4 m, i
 // NJ = elements per lane (8 / 16 / 32 for rows of up to 256 / 512 / 1024); 32-bit index arithmetic (the host checks the row count)
 template <int NJ>
 __global__ void __launch_bounds__(128) soft_max_warp_kernel(const T4 a, const T4 m, int has_mask, const T4w d, float scale, unsigned rows) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const int lane = threadIdx.x & 31;
     const unsigned row = blockIdx.x * 4u + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -497,6 +510,7 @@ __device__ __forceinline__ float glu_act(int op, float x) {
 }
 template <typename I>
 __global__ void __launch_bounds__(256) glu_kernel(const T4 a, const T4 b, int split, const T4w d, int op, int swapped) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const I nc = (I) d.ne[0], total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
     for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
         I i0, i1, i2, i3;
@@ -515,6 +529,7 @@ __global__ void __launch_bounds__(256) glu_kernel(const T4 a, const T4 b, int sp
 
 // 2-D, split operands, rows of a multiple of four floats, everything 16-byte aligned (the SwiGLU of a prefill ubatch): float4 per thread
 __global__ void __launch_bounds__(256) glu_vec4_kernel(const T4 a, const T4 b, const T4w d, int op, int swapped, long long total4) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const long long q = d.ne[0] >> 2;
     for (long long i = (long long) blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long) gridDim.x * 256) {
         const long long row = i / q, c = (i - row * q) * 16;
@@ -530,6 +545,7 @@ __global__ void __launch_bounds__(256) glu_vec4_kernel(const T4 a, const T4 b, c
 // few activation rows: one warp per (src0 row, batch), every lane strides over k, all n columns at once (n <= 8)
 template <int NCOLS, bool AH>
 __global__ void __launch_bounds__(128) mm_rows_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const int lane = threadIdx.x & 31;
     const long long row = (long long) blockIdx.x * 4 + (threadIdx.x >> 5);
     if (row >= a.ne[1]) return;
@@ -553,6 +569,7 @@ __global__ void __launch_bounds__(128) mm_rows_kernel(const T4 a, const T4 b, co
 // many activation rows: 64 x 64 output tile per CTA of 256 threads (4 x 4 per thread), k in steps of 16 through shared memory
 template <bool AH>
 __global__ void __launch_bounds__(256) mm_tile_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     __shared__ float As[16][64 + 4], Bs[16][64 + 4];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const long long m0 = (long long) blockIdx.x * 64, n0 = (long long) blockIdx.y * 64;
@@ -603,6 +620,7 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 __global__ void __launch_bounds__(128) mm_mma_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     constexpr int BK = 32, LD = BK + 8;                       // row stride 40 halves = 20 words: the fragment loads below are conflict-free
     __shared__ __align__(16) __half As[64][LD], Bs[64][LD];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
@@ -692,7 +710,7 @@ int b200_op_rms_norm(const b200_tensor * src, const b200_tensor * dst, float eps
     B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && src->nb[0] == 4 && dst->nb[0] == 4, "b200_op_rms_norm: f32 rows with unit stride only");
     const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
     if (rows == 0 || src->ne[0] == 0) return 0;
-    B200_CHECK(b200_launch(rms_norm_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), t4w(dst), eps));
+    B200_CHECK(b200_launch(rms_norm_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), t4w(dst), eps));
     return 0;
 }
 
@@ -705,7 +723,7 @@ int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const
     const long long rows = a->ne[1] * a->ne[2] * a->ne[3];
     if (rows == 0 || a->ne[0] == 0) return 0;
     B200_REQUIRE(w->ne[0] == a->ne[0], "b200_op_add_rms_norm_mul: the weight must have the row length");
-    B200_CHECK(b200_launch(add_rms_norm_mul_kernel, dim3((unsigned) rows), dim3(1024), 0, (cudaStream_t) stream, false, t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
+    B200_CHECK(b200_launch(add_rms_norm_mul_kernel, dim3((unsigned) rows), dim3(1024), 0, (cudaStream_t) stream, glue_pdl(), t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
                            sum ? t4w(sum) : t4w(dst), sum ? 1 : 0, t4(w), t4w(dst), eps));
     return 0;
 }
@@ -720,7 +738,7 @@ int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200
     B200_REQUIRE(n_kv >= 1 && n_kv <= 11000 && n_tok >= 1 && n_tok <= 65535, "b200_op_attn_decode: n_kv %lld / n_tokens %lld out of range", n_kv, n_tok);
     B200_REQUIRE(!mask || ((mask->type == B200_TYPE_F32 || mask->type == B200_TYPE_F16) && mask->ne[0] >= n_kv && mask->ne[1] >= n_tok), "b200_op_attn_decode: bad mask");
     B200_REQUIRE(contiguous_f(dst, 4) && nelem(dst) == hd * n_head * n_tok, "b200_op_attn_decode: dst must be the contiguous [head_dim, n_head, n_tokens] result");
-    B200_CHECK(b200_launch(attn_decode_kernel, dim3((unsigned) n_head, (unsigned) n_tok), dim3(256), (size_t) (n_kv + hd + 256) * sizeof(float), (cudaStream_t) stream, false,
+    B200_CHECK(b200_launch(attn_decode_kernel, dim3((unsigned) n_head, (unsigned) n_tok), dim3(256), (size_t) (n_kv + hd + 256) * sizeof(float), (cudaStream_t) stream, glue_pdl(),
                            t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
     return 0;
 }
@@ -735,10 +753,10 @@ int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b
     const bool small = n < (1ll << 31);
     const dim3 grid(blocks_for(n, 256));
     cudaStream_t st = (cudaStream_t) stream;
-    if (op == 0) { if (small) B200_CHECK(b200_launch(binary_kernel<0, unsigned>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst)));
-                   else       B200_CHECK(b200_launch(binary_kernel<0, long long>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst))); }
-    else         { if (small) B200_CHECK(b200_launch(binary_kernel<1, unsigned>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst)));
-                   else       B200_CHECK(b200_launch(binary_kernel<1, long long>, grid, dim3(256), 0, st, false, t4(a), t4(b), t4w(dst))); }
+    if (op == 0) { if (small) B200_CHECK(b200_launch(binary_kernel<0, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
+                   else       B200_CHECK(b200_launch(binary_kernel<0, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
+    else         { if (small) B200_CHECK(b200_launch(binary_kernel<1, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
+                   else       B200_CHECK(b200_launch(binary_kernel<1, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
     return 0;
 }
 
@@ -777,10 +795,10 @@ int b200_op_rope_set_rows(const b200_tensor * src, const b200_tensor * pos, cons
     const float * ffp = freq_factors ? (const float *) freq_factors->data : (const float *) nullptr;
     const T4 tv = v_src ? t4(v_src) : t4(src), tvi = v_src ? t4(v_idx) : t4(sr_idx); const T4w tvc = v_src ? t4w(v_dst) : t4w(sr_dst);
     if (nelem(dst) < (1ll << 31) && nv < (1ll << 31))
-        B200_CHECK(b200_launch(rope_set_rows_kernel<unsigned>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
+        B200_CHECK(b200_launch(rope_set_rows_kernel<unsigned>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
                                t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
     else
-        B200_CHECK(b200_launch(rope_set_rows_kernel<long long>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, false, t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
+        B200_CHECK(b200_launch(rope_set_rows_kernel<long long>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
                                t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
     return 0;
 }
@@ -819,12 +837,12 @@ int b200_op_soft_max(const b200_tensor * src, const b200_tensor * mask, const b2
     if (src->ne[0] <= 1024 && rows >= 512 && rows < (1ll << 31)) {        // enough rows to fill the machine with one warp each
         const dim3 grid(blocks_for(rows, 4));
         const T4 ts = t4(src); const T4w td = t4w(dst);
-        if (src->ne[0] <= 256)      B200_CHECK(b200_launch(soft_max_warp_kernel<8>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
-        else if (src->ne[0] <= 512) B200_CHECK(b200_launch(soft_max_warp_kernel<16>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
-        else                        B200_CHECK(b200_launch(soft_max_warp_kernel<32>, grid, dim3(128), 0, (cudaStream_t) stream, false, ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
+        if (src->ne[0] <= 256)      B200_CHECK(b200_launch(soft_max_warp_kernel<8>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
+        else if (src->ne[0] <= 512) B200_CHECK(b200_launch(soft_max_warp_kernel<16>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
+        else                        B200_CHECK(b200_launch(soft_max_warp_kernel<32>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), ts, m, mask ? 1 : 0, td, scale, (unsigned) rows));
         return 0;
     }
-    B200_CHECK(b200_launch(soft_max_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, false, t4(src), m, mask ? 1 : 0, t4w(dst), scale));
+    B200_CHECK(b200_launch(soft_max_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), m, mask ? 1 : 0, t4w(dst), scale));
     return 0;
 }
 
@@ -839,7 +857,7 @@ int b200_op_glu(const b200_tensor * a, const b200_tensor * b, const b200_tensor 
     if (b && dst->ne[2] == 1 && dst->ne[3] == 1 && dst->ne[0] % 4 == 0 && dst->nb[0] == 4 && al16(a) && al16(b) && al16(dst) && n >= (1 << 16)) {
         const long long total4 = n / 4;
         const long long blocks = (total4 + 255) / 256;
-        B200_CHECK(b200_launch(glu_vec4_kernel, dim3((unsigned) (blocks > 148 * 16 ? 148 * 16 : blocks)), dim3(256), 0, (cudaStream_t) stream, false,
+        B200_CHECK(b200_launch(glu_vec4_kernel, dim3((unsigned) (blocks > 148 * 16 ? 148 * 16 : blocks)), dim3(256), 0, (cudaStream_t) stream, glue_pdl(),
                                t4(a), t4(b), t4w(dst), glu_op, swapped, total4));
         return 0;
     }
@@ -860,8 +878,8 @@ int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_t
     const bool ah = a->type == B200_TYPE_F16;
     if (n <= 8) {
         dim3 grid(blocks_for(a->ne[1], 4), (unsigned) batch);
-#define B200_MMR(nc) case nc: if (ah) B200_CHECK(b200_launch(mm_rows_kernel<nc, true>, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3)); \
-                              else    B200_CHECK(b200_launch(mm_rows_kernel<nc, false>, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3)); break
+#define B200_MMR(nc) case nc: if (ah) B200_CHECK(b200_launch(mm_rows_kernel<nc, true>, grid, dim3(128), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3)); \
+                              else    B200_CHECK(b200_launch(mm_rows_kernel<nc, false>, grid, dim3(128), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3)); break
         switch ((int) n) { B200_MMR(1); B200_MMR(2); B200_MMR(3); B200_MMR(4); B200_MMR(5); B200_MMR(6); B200_MMR(7); B200_MMR(8); }
 #undef B200_MMR
         return 0;
@@ -870,11 +888,11 @@ int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_t
     static const bool mma_on = [] { const char * e = getenv("B200_ATTN_MMA"); return !(e && e[0] == '0'); }();
     auto aligned16 = [](const b200_tensor * t) { return ((uintptr_t) t->data % 16) == 0 && t->nb[1] % 16 == 0 && t->nb[2] % 16 == 0 && t->nb[3] % 16 == 0; };
     if (ah && mma_on && a->ne[0] % 32 == 0 && aligned16(a) && aligned16(b)) {
-        B200_CHECK(b200_launch(mm_mma_kernel, grid, dim3(128), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
+        B200_CHECK(b200_launch(mm_mma_kernel, grid, dim3(128), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3));
         return 0;
     }
-    if (ah) B200_CHECK(b200_launch(mm_tile_kernel<true>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
-    else    B200_CHECK(b200_launch(mm_tile_kernel<false>, grid, dim3(256), 0, s, false, t4(a), t4(b), t4w(dst), r2, r3));
+    if (ah) B200_CHECK(b200_launch(mm_tile_kernel<true>, grid, dim3(256), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3));
+    else    B200_CHECK(b200_launch(mm_tile_kernel<false>, grid, dim3(256), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3));
     return 0;
 }
 
