@@ -689,7 +689,11 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void cons_bar() { asm volatile("bar.sync 3, %0;" :: "n"(CH_CONSUMERS) : "memory"); }
 
-template <int NCOLS>
+// KS = which item kinds are compiled in: 0 Q4_K / Q6_K one block per lane (what the 8B Q4_K_M file needs), 1 + Q5_K (70B) and Q6_K rows that are not a
+// multiple of 8 units, 2 + Q4_0 / Q8_0 / IQ4_XS. Code a chain never runs still costs it: with every item kind in one kernel the 8B token runs at 770
+// tokens/s, 785 with Q4_K / Q5_K / Q6_K, 813 with KS = 0. (The effect is ptxas scheduling, not size as such: compiling the row-split and timeline branches
+// out as well gave 760.)
+template <int NCOLS, int KS>
 __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -850,10 +854,11 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 item_q4k<NCOLS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else if (type == CH_T_Q6K_SW) {
                 item_q4k<NCOLS, LU_Q6K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
-            } else if (type == B200_TYPE_Q5_K) {
+            } else if (KS >= 1 && type == B200_TYPE_Q5_K) {
                 item_q4k<NCOLS, LU_Q5K>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
-            } else if (type == B200_TYPE_Q6_K) {
+            } else if (KS >= 1 && type == B200_TYPE_Q6_K) {
                 item_lanes8<B200_TYPE_Q6_K, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+            } else if (KS < 2) {
             } else if (type == B200_TYPE_IQ4_XS) {
                 if (a.lanes8) item_lanes8<B200_TYPE_IQ4_XS, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
                 else          item_q4k<NCOLS, LU_IQ4XS>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
@@ -933,6 +938,7 @@ struct Chain {
     size_t smem = 0;
     bool cooperative = true;
     bool xreg = false;            // gemv_chainx_kernel (activations in registers) instead of gemv_chain_kernel
+    int kset = 0;                 // item kinds the chain needs: gemv_chain_kernel<NCOLS, kset>
 };
 
 // consumer warps of gemv_chainx_kernel (8 or 12; B200_CHAIN_NW)
@@ -954,14 +960,14 @@ int row_granule(int type, int upr) {
     return g;
 }
 
-template <int NCOLS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s) {
+template <int NCOLS, int KS> cudaError_t chain_launch_t(const Chain & c, cudaStream_t s) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) c.sms); cfg.blockDim = dim3(CH_THREADS); cfg.dynamicSmemBytes = c.smem; cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative; attr[0].val.cooperative = 1;
     cfg.attrs = attr; cfg.numAttrs = c.cooperative ? 1 : 0;
     b200_count_launch();
-    return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS>, c.args);
+    return cudaLaunchKernelEx(&cfg, gemv_chain_kernel<NCOLS, KS>, c.args);
 }
 cudaError_t chainx_launch(const Chain & c, cudaStream_t s) {
     cudaLaunchConfig_t cfg = {};
@@ -1241,6 +1247,13 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     if (why) { b200_set_error("b200_chain_create: %s", why); return nullptr; }
     const int world = split ? split->world : 1;
     const bool lanes8 = getenv("B200_CHAIN_LANES8") != nullptr;
+    int kset = 0;
+    { int total = 0; for (int g = 0; g < n_groups; ++g) total += group_sizes[g];
+      for (int i = 0; i < total; ++i) {
+          const int t = nodes[i].type;
+          const int need = (t == B200_TYPE_Q4_K || (t == B200_TYPE_Q6_K && q6_swizzled_shape(nodes[i]))) ? 0 : (t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K) ? 1 : 2;
+          kset = need > kset ? need : kset;
+      } }
     if (split && (world < 2 || world > B200_MAX_PEERS || split->rank < 0 || split->rank >= world || !split->scratch || !split->row_lo || !split->m_full ||
                   split->peer_delta[split->rank] != 0 || (((uintptr_t) split->scratch) & 255) != 0)) {
         b200_set_error("b200_chain_create_split: bad descriptor (world %d rank %d)", world, split->rank); return nullptr;
@@ -1328,6 +1341,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     return nullptr;
                 }
             }
+            if (a.type == B200_TYPE_Q6_K && map0 < 0 && kset < 1) kset = 1;      // this matrix takes the eight-lanes-per-block Q6_K items
             mat_R.push_back(R);
             mat_map.push_back(map0);
         }
@@ -1422,6 +1436,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     c->d_tags = split ? nullptr : d_tags;
     c->device = device; c->sms = sms; c->ncols = ncols; c->n_nodes = n_groups; c->d_blob = d;
     c->xreg = P.xreg;
+    c->kset = kset;
     uint8_t * db = (uint8_t *) d;
     // single GPU: counters in the chain's own blob; row split: in the symmetric arena (peers add to them)
     c->args.counter = split ? (unsigned long long *) split->scratch : (unsigned long long *) db;
@@ -1451,10 +1466,18 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     if (c->xreg) e = CX_NW == 12 ? cudaFuncSetAttribute(gemv_chainx_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                  : cudaFuncSetAttribute(gemv_chainx_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem);
     else switch (ncols) {
-        case 1: e = cudaFuncSetAttribute(gemv_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        case 2: e = cudaFuncSetAttribute(gemv_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        case 3: e = cudaFuncSetAttribute(gemv_chain_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        default: e = cudaFuncSetAttribute(gemv_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        case 1: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
+                                  : cudaFuncSetAttribute(gemv_chain_kernel<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        case 2: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
+                                  : cudaFuncSetAttribute(gemv_chain_kernel<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        case 3: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
+                                  : cudaFuncSetAttribute(gemv_chain_kernel<3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
+        default: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
+                                  : cudaFuncSetAttribute(gemv_chain_kernel<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
     }
     if (e != cudaSuccess) {
         b200_set_error("b200_chain_create: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -1470,10 +1493,10 @@ int b200_chain_launch(b200_chain_t chain, b200_stream_t stream) {
     cudaError_t e;
     if (c->xreg) e = chainx_launch(*c, s);
     else switch (c->ncols) {
-        case 1: e = chain_launch_t<1>(*c, s); break;
-        case 2: e = chain_launch_t<2>(*c, s); break;
-        case 3: e = chain_launch_t<3>(*c, s); break;
-        default: e = chain_launch_t<4>(*c, s); break;
+        case 1: e = c->kset == 2 ? chain_launch_t<1, 2>(*c, s) : c->kset == 1 ? chain_launch_t<1, 1>(*c, s) : chain_launch_t<1, 0>(*c, s); break;
+        case 2: e = c->kset == 2 ? chain_launch_t<2, 2>(*c, s) : c->kset == 1 ? chain_launch_t<2, 1>(*c, s) : chain_launch_t<2, 0>(*c, s); break;
+        case 3: e = c->kset == 2 ? chain_launch_t<3, 2>(*c, s) : c->kset == 1 ? chain_launch_t<3, 1>(*c, s) : chain_launch_t<3, 0>(*c, s); break;
+        default: e = c->kset == 2 ? chain_launch_t<4, 2>(*c, s) : c->kset == 1 ? chain_launch_t<4, 1>(*c, s) : chain_launch_t<4, 0>(*c, s); break;
     }
     B200_CHECK(e);
     return 0;
