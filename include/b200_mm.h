@@ -297,8 +297,14 @@ B200_API int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor *
  * k: f16 [head_dim, n_kv, n_head_kv]; v: f16 [n_kv, head_dim, n_head_kv] (transposed V cache); q: f32 [head_dim, n_tokens, n_head]; n_kv <= 12000 */
 B200_API int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst,
                                  float scale, b200_stream_t stream);
-/* ggml_compute_forward_add / _mul, f32, src1 broadcast over src0 (ggml_can_repeat); op: 0 = add, 1 = mul */
+/* ggml_compute_forward_add / _mul / _div, f32, src1 broadcast over src0 (ggml_can_repeat); op: 0 = add, 1 = mul, 2 = div */
 B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream);
+/* the router of a mixture-of-experts layer (build_moe_ffn, src/llama-graph.cpp:1000-1150): ggml_compute_forward_scale (op 0: x * p0 + p1) and
+   _clamp (op 1: to [p0, p1]); _sum_rows (f32 [k, ...] -> [1, ...]); _argsort_f32 (i32 indices that sort each row; order 0 ascending, 1
+   descending as enum ggml_sort_order; rows of up to 1024 elements) -- ggml-cpu/ops.cpp */
+B200_API int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, float p0, float p1, b200_stream_t stream);
+B200_API int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
+B200_API int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, b200_stream_t stream);
 /* ggml_compute_forward_rope_flt (ops.cpp:5655-5790) for mode 0 (normal) and 2 (neox), ext_factor == 0; pos i32 [n_tokens], freq_factors f32 [n_dims / 2] or NULL */
 typedef struct b200_rope_params { int32_t n_dims, mode; float freq_base, freq_scale, ext_factor, attn_factor; } b200_rope_params;
 B200_API int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,

@@ -99,7 +99,27 @@ def test_row_split_buffer_type_logits_match_reference_cpu_backend(tiny_gguf, gra
     assert "_Split" in r.stdout, "the loader did not place any tensor in the split buffer type:\n" + r.stdout[-3000:]
 
 
-GLUE_OPS = ["GET_ROWS", "RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "ROPE", "SET_ROWS", "CPY", "CONT", "DUP", "SOFT_MAX", "SWIGLU", "GEGLU", "REGLU"]
+@pytest.fixture(scope="module")
+def tiny_moe_gguf(tmp_path_factory):
+    """2 layers of Mixtral-8x7B shapes (8 experts, 2 used; Q4_K_M recipe: Q8_0 attn_k / attn_v, Q6_K on the use_more_bits layers), random-init"""
+    import sys
+    path = tmp_path_factory.mktemp("gguf") / "tiny-mixtral.gguf"
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "mixtral-8x7b-q4_k_m", "--layers", "2", "--out", str(path)],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:]
+    return path
+
+
+def test_whole_mixtral_graph_logits_match_reference_cpu_backend(tiny_moe_gguf):
+    """build_moe_ffn on the device: router matmul (f32), SOFT_MAX, ARGSORT + view (top-k), GET_ROWS of the probabilities, SUM_ROWS / CLAMP / DIV,
+    MUL_MAT_ID x 3, SWIGLU, MUL by the weights, the ADDs over the used experts -- logits of llama_decode against the reference CPU backend"""
+    env = _need("llama_logits_check")
+    r = subprocess.run([str(VAR / "llama_logits_check"), str(tiny_moe_gguf), "40", "6"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0 and "LLAMA_LOGITS_CHECK OK" in r.stdout, r.stdout[-3000:]
+
+
+GLUE_OPS = ["GET_ROWS", "RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "DIV", "SCALE", "CLAMP", "SUM_ROWS", "ARGSORT", "ROPE", "SET_ROWS", "CPY", "CONT", "DUP", "SOFT_MAX",
+            "SWIGLU", "GEGLU", "REGLU"]
 
 
 @pytest.mark.parametrize("op", GLUE_OPS)

@@ -593,7 +593,15 @@ bool glue_supports(const ggml_tensor * op) {
             return f32_rows(a) && f32_rows(op);
         case GGML_OP_ADD:
         case GGML_OP_MUL:
+        case GGML_OP_DIV:
             return a && b && a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ggml_can_repeat(b, a);
+        case GGML_OP_SCALE:
+        case GGML_OP_CLAMP:
+            return a && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ggml_are_same_shape(a, op);
+        case GGML_OP_SUM_ROWS:
+            return a && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32;
+        case GGML_OP_ARGSORT:
+            return a && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_I32 && a->ne[0] <= 1024 && op->nb[0] == sizeof(int32_t);
         case GGML_OP_ROPE: {
             if (!f32_rows(a) || !f32_rows(op) || !b || b->type != GGML_TYPE_I32) return false;
             const int32_t * p = (const int32_t *) op->op_params;
@@ -1033,7 +1041,15 @@ enum ggml_status compute_glue(backend_ctx * bc, const ggml_tensor * node) {
         case GGML_OP_GET_ROWS: { ensure_canonical(a); const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_get_rows(&ta, &tb, &d, bc->stream); } break;
         case GGML_OP_RMS_NORM: { float eps; memcpy(&eps, node->op_params, sizeof(float)); const b200_tensor ta = bt(a); rc = b200_op_rms_norm(&ta, &d, eps, bc->stream); } break;
         case GGML_OP_ADD:
-        case GGML_OP_MUL: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_binary(node->op == GGML_OP_ADD ? 0 : 1, &ta, &tb, &d, bc->stream); } break;
+        case GGML_OP_MUL:
+        case GGML_OP_DIV: { const b200_tensor ta = bt(a), tb = bt(b); rc = b200_op_binary(node->op == GGML_OP_ADD ? 0 : node->op == GGML_OP_MUL ? 1 : 2, &ta, &tb, &d, bc->stream); } break;
+        case GGML_OP_SCALE:
+        case GGML_OP_CLAMP: {
+            float p0, p1; memcpy(&p0, node->op_params, sizeof(float)); memcpy(&p1, (const float *) node->op_params + 1, sizeof(float));
+            const b200_tensor ta = bt(a); rc = b200_op_unary(node->op == GGML_OP_SCALE ? 0 : 1, &ta, &d, p0, p1, bc->stream);
+        } break;
+        case GGML_OP_SUM_ROWS: { const b200_tensor ta = bt(a); rc = b200_op_sum_rows(&ta, &d, bc->stream); } break;
+        case GGML_OP_ARGSORT: { const b200_tensor ta = bt(a); rc = b200_op_argsort(&ta, &d, ggml_get_op_params_i32(node, 0), bc->stream); } break;
         case GGML_OP_ROPE: {
             const b200_rope_params rp = rope_params_of(node);
             const b200_tensor ta = bt(a), tb = bt(b);

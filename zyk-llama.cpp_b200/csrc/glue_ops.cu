@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(256) attn_decode_kernel(const T4 K, const T4 q
     }
 }
 
-// ---- ADD / MUL with ggml broadcasting of src1 (ggml_compute_forward_add / _mul: src1 dims divide src0 dims) ----
+// ---- ADD / MUL / DIV with ggml broadcasting of src1 (ggml_compute_forward_add / _mul / _div: src1 dims divide src0 dims) ----
 template <int OP, typename I>
 __global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, const T4w d) {
     pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
@@ -301,9 +301,72 @@ __global__ void __launch_bounds__(256) binary_kernel(const T4 a, const T4 b, con
         const float x = *reinterpret_cast<const float *>(a.data + (long long) i0 * a.nb[0] + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
         const I j0 = b0 == (I) d.ne[0] ? i0 : i0 % b0, j1 = b1 == 1 ? 0 : i1 % b1, j2 = b2 == 1 ? 0 : i2 % b2, j3 = b3 == 1 ? 0 : i3 % b3;
         const float y = *reinterpret_cast<const float *>(b.data + (long long) j0 * b.nb[0] + (long long) j1 * b.nb[1] + (long long) j2 * b.nb[2] + (long long) j3 * b.nb[3]);
-        *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = OP == 0 ? x + y : x * y;
+        *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = OP == 0 ? x + y : OP == 1 ? x * y : x / y;
     }
 }
+// ---- the router of a mixture-of-experts layer (build_moe_ffn, src/llama-graph.cpp): SCALE, CLAMP, SUM_ROWS, ARGSORT --------------------------
+// x * scale + bias (ggml_compute_forward_scale) and min(max(x, lo), hi) (ggml_compute_forward_clamp), f32, any strides
+template <int OP, typename I>
+__global__ void __launch_bounds__(256) unary_kernel(const T4 a, const T4w d, float p0, float p1) {
+    pdl_launch_dependents(); pdl_wait();
+    const I total = (I) (d.ne[0] * d.ne[1] * d.ne[2] * d.ne[3]);
+    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+        I i0, i1, i2, i3;
+        unravel<I>(i, d.ne, i0, i1, i2, i3);
+        const float x = *reinterpret_cast<const float *>(a.data + (long long) i0 * a.nb[0] + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+        const float y = OP == 0 ? x * p0 + p1 : fminf(fmaxf(x, p0), p1);
+        *reinterpret_cast<float *>(d.data + (long long) i0 * d.nb[0] + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]) = y;
+    }
+}
+// ggml_compute_forward_sum_rows: dst[0, i1, i2, i3] = sum over i0; one warp per row
+__global__ void __launch_bounds__(128) sum_rows_kernel(const T4 a, const T4w d, long long rows) {
+    pdl_launch_dependents(); pdl_wait();
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long) blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
+    const char * x = a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3];
+    float s = 0.0f;
+    for (long long i = lane; i < a.ne[0]; i += 32) s += *reinterpret_cast<const float *>(x + i * a.nb[0]);
+    s = warp_sum(s);
+    if (lane == 0) *reinterpret_cast<float *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = s;
+}
+// ggml_compute_forward_argsort_f32: dst row = the indices that sort the src row (order 0 ascending, 1 descending). One CTA per row, bitonic
+// network over the next power of two in shared memory (rows of up to 1024 elements: expert scores); padding sorts last in either order.
+__global__ void __launch_bounds__(256) argsort_kernel(const T4 a, const T4w d, int order, int npad) {
+    pdl_launch_dependents(); pdl_wait();
+    __shared__ float key[1024];
+    __shared__ int idx[1024];
+    const long long row = blockIdx.x;
+    const long long i1 = row % a.ne[1], i2 = (row / a.ne[1]) % a.ne[2], i3 = row / (a.ne[1] * a.ne[2]);
+    const char * x = a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3];
+    const int n = (int) a.ne[0];
+    for (int i = threadIdx.x; i < npad; i += 256) { idx[i] = i; key[i] = i < n ? *reinterpret_cast<const float *>(x + (long long) i * a.nb[0]) : 0.0f; }
+    __syncthreads();
+    // "p before q" in the requested order; a padded slot (index >= n) goes after every real one
+    auto before = [&](int p, int q) {
+        const int ip = idx[p], iq = idx[q];
+        if (ip >= n) return false;
+        if (iq >= n) return true;
+        return order == 0 ? key[p] < key[q] : key[p] > key[q];
+    };
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < npad; i += 256) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const bool up = (i & k) == 0;
+                    const bool swap = up ? before(l, i) : before(i, l);
+                    if (swap) { const float tk = key[i]; key[i] = key[l]; key[l] = tk; const int ti = idx[i]; idx[i] = idx[l]; idx[l] = ti; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    int * out = reinterpret_cast<int *>(d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    for (int i = threadIdx.x; i < n; i += 256) out[i] = idx[i];
+}
+
 // ---- ROPE, modes normal (0) and neox (2), ext_factor == 0 (ggml_compute_forward_rope_flt + ggml_rope_cache_init + rope_yarn, ops.cpp:5524-5790) ----
 struct RopeP { int n_dims, mode; float freq_base, freq_scale, attn_factor; };
 template <typename I>
@@ -746,7 +809,7 @@ int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200
 int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream) {
     B200_REQUIRE(a && b && dst && a->data && b->data && dst->data, "b200_op_binary: null tensor");
     B200_REQUIRE(a->type == B200_TYPE_F32 && b->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32, "b200_op_binary: f32 only");
-    B200_REQUIRE(op == 0 || op == 1, "b200_op_binary: op %d (0 add, 1 mul)", op);
+    B200_REQUIRE(op >= 0 && op <= 2, "b200_op_binary: op %d (0 add, 1 mul, 2 div)", op);
     for (int i = 0; i < 4; ++i) B200_REQUIRE(b->ne[i] > 0 && dst->ne[i] % b->ne[i] == 0 && a->ne[i] == dst->ne[i], "b200_op_binary: src1 does not broadcast over src0");
     const long long n = nelem(dst);
     if (n == 0) return 0;
@@ -755,8 +818,52 @@ int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b
     cudaStream_t st = (cudaStream_t) stream;
     if (op == 0) { if (small) B200_CHECK(b200_launch(binary_kernel<0, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
                    else       B200_CHECK(b200_launch(binary_kernel<0, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
-    else         { if (small) B200_CHECK(b200_launch(binary_kernel<1, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
-                   else       B200_CHECK(b200_launch(binary_kernel<1, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
+    else if (op == 1) { if (small) B200_CHECK(b200_launch(binary_kernel<1, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
+                        else       B200_CHECK(b200_launch(binary_kernel<1, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
+    else              { if (small) B200_CHECK(b200_launch(binary_kernel<2, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst)));
+                        else       B200_CHECK(b200_launch(binary_kernel<2, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(a), t4(b), t4w(dst))); }
+    return 0;
+}
+
+int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, float p0, float p1, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_unary: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32, "b200_op_unary: f32 only");
+    B200_REQUIRE(op == 0 || op == 1, "b200_op_unary: op %d (0 scale: x * p0 + p1, 1 clamp to [p0, p1])", op);
+    for (int i = 0; i < 4; ++i) B200_REQUIRE(src->ne[i] == dst->ne[i], "b200_op_unary: shapes differ");
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    const bool small = n < (1ll << 31);
+    const dim3 grid(blocks_for(n, 256));
+    cudaStream_t st = (cudaStream_t) stream;
+    if (op == 0) { if (small) B200_CHECK(b200_launch(unary_kernel<0, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(src), t4w(dst), p0, p1));
+                   else       B200_CHECK(b200_launch(unary_kernel<0, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(src), t4w(dst), p0, p1)); }
+    else         { if (small) B200_CHECK(b200_launch(unary_kernel<1, unsigned>, grid, dim3(256), 0, st, glue_pdl(), t4(src), t4w(dst), p0, p1));
+                   else       B200_CHECK(b200_launch(unary_kernel<1, long long>, grid, dim3(256), 0, st, glue_pdl(), t4(src), t4w(dst), p0, p1)); }
+    return 0;
+}
+
+int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_sum_rows: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && dst->ne[0] == 1 && dst->ne[1] == src->ne[1] && dst->ne[2] == src->ne[2] && dst->ne[3] == src->ne[3],
+                 "b200_op_sum_rows: f32 [k, ...] -> f32 [1, ...]");
+    const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
+    if (rows == 0) return 0;
+    B200_CHECK(b200_launch(sum_rows_kernel, dim3(blocks_for(rows, 4)), dim3(128), 0, (cudaStream_t) stream, glue_pdl(), t4(src), t4w(dst), rows));
+    return 0;
+}
+
+int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, b200_stream_t stream) {
+    B200_REQUIRE(src && dst && src->data && dst->data, "b200_op_argsort: null tensor");
+    B200_REQUIRE(src->type == B200_TYPE_F32 && dst->type == B200_TYPE_I32 && dst->nb[0] == 4, "b200_op_argsort: f32 -> i32 indices");
+    B200_REQUIRE(order == 0 || order == 1, "b200_op_argsort: order %d (0 ascending, 1 descending)", order);
+    B200_REQUIRE(src->ne[0] >= 1 && src->ne[0] <= 1024, "b200_op_argsort: rows of 1..1024 elements (got %lld)", (long long) src->ne[0]);
+    for (int i = 0; i < 4; ++i) B200_REQUIRE(src->ne[i] == dst->ne[i], "b200_op_argsort: shapes differ");
+    const long long rows = src->ne[1] * src->ne[2] * src->ne[3];
+    if (rows == 0) return 0;
+    B200_REQUIRE(rows < (1ll << 31), "b200_op_argsort: too many rows");
+    int npad = 1;
+    while (npad < src->ne[0]) npad <<= 1;
+    B200_CHECK(b200_launch(argsort_kernel, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), t4w(dst), order, npad));
     return 0;
 }
 
