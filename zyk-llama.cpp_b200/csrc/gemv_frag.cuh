@@ -196,19 +196,21 @@ __device__ __forceinline__ uint32_t iq4nl_lut4(uint32_t nib) {     // four indic
     const uint32_t mask = ((nib >> 3) & 0x01010101u) * 0xffu;
     return (hi & mask) | (lo & ~mask);
 }
-// four PACKED indices (bits 0..15 of h, the other bits are ignored) -> four table bytes. The nibbles of a weight word already are the
-// selector format of PRMT: bits 0..2 pick inside a table half, bit 3 picks the half with a third PRMT -- 6 instructions per 4 values.
-__device__ __forceinline__ uint32_t iq4nl_lut_packed(uint32_t h) {
-    const uint32_t s = h & 0x7777u;
+// four PACKED indices (bits 0..15 of the selector words) -> four table bytes. The nibbles of a weight word already are the selector format
+// of PRMT: bits 0..2 pick inside a table half (s), bit 3 picks the half with a third PRMT (sel = 0x3210 | 4 * bit 3 per nibble).
+__device__ __forceinline__ uint32_t iq4nl_lut_sel(uint32_t s, uint32_t sel) {
     const uint32_t lo = __byte_perm(0xBFAD9881u, 0xF6EADDCFu, s);
     const uint32_t hi = __byte_perm(0x26190D01u, 0x71594535u, s);
-    return __byte_perm(lo, hi, ((h >> 1) & 0x4444u) | 0x3210u);
+    return __byte_perm(lo, hi, sel);
 }
+__device__ __forceinline__ uint32_t iq4nl_lut_packed(uint32_t h) { return iq4nl_lut_sel(h & 0x7777u, ((h >> 1) & 0x4444u) | 0x3210u); }
 // the looked-up bytes of a weight word come out as (lo0, hi0, lo1, hi1) / (lo2, hi2, lo3, hi3): the ACTIVATIONS are interleaved to match
-// (once per lane step, shared by all rows) instead of de-interleaving every weight word
+// (once per lane step, shared by all rows) instead of de-interleaving every weight word. Both selector words are built for the whole 32-bit
+// word at once (PRMT reads only the low 16 bits): 5 logic / shift instructions + 6 PRMT + 2 dp4a per 8 weights.
 __device__ __forceinline__ int iq4_word_dot(uint32_t q, uint32_t x0, uint32_t x1, int acc) {
-    acc = __dp4a((int) iq4nl_lut_packed(q), (int) __byte_perm(x0, x1, 0x5140u), acc);
-    return __dp4a((int) iq4nl_lut_packed(q >> 16), (int) __byte_perm(x0, x1, 0x7362u), acc);
+    const uint32_t s = q & 0x77777777u, sel = ((q >> 1) & 0x44444444u) | 0x32103210u;
+    acc = __dp4a((int) iq4nl_lut_sel(s, sel), (int) __byte_perm(x0, x1, 0x5140u), acc);
+    return __dp4a((int) iq4nl_lut_sel(s >> 16, sel >> 16), (int) __byte_perm(x0, x1, 0x7362u), acc);
 }
 template <> struct WFrag<B200_TYPE_IQ4_XS> {
     uint4 q; uint2 hdr;
