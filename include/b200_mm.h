@@ -297,6 +297,11 @@ B200_API int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor *
  * k: f16 [head_dim, n_kv, n_head_kv]; v: f16 [n_kv, head_dim, n_head_kv] (transposed V cache); q: f32 [head_dim, n_tokens, n_head]; n_kv <= 12000 */
 B200_API int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst,
                                  float scale, b200_stream_t stream);
+/* the same run of nodes for a prefill ubatch (any number of query tokens): one pass over the KV cache with an online softmax, both products on
+   the tensor cores, the score matrix never written; head_dim 64 or 128, n_kv a multiple of 64, 16-byte aligned rows. The reference reaches
+   this only through FLASH_ATTN_EXT (ggml-cuda/fattn*.cu); here the plain MUL_MAT / SOFT_MAX / MUL_MAT graph gets it */
+B200_API int b200_op_attn_prefill(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst,
+                                  float scale, b200_stream_t stream);
 /* ggml_compute_forward_add / _mul / _div, f32, src1 broadcast over src0 (ggml_can_repeat); op: 0 = add, 1 = mul, 2 = div */
 B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, b200_stream_t stream);
 /* the router of a mixture-of-experts layer (build_moe_ffn, src/llama-graph.cpp:1000-1150): ggml_compute_forward_scale (op 0: x * p0 + p1) and

@@ -120,3 +120,45 @@ def test_mul_mat_glu_equals_glu_then_mul_mat(b200, orc, t, n, op):
     # and against the oracle on the gated activations the device produced
     ref = orc.mul_mat(t, w.cpu().numpy().reshape(m, -1), x.cpu().numpy())
     assert nmse(y.cpu().numpy(), ref) < 1e-10
+
+
+@pytest.mark.parametrize("hd", [64, 128])
+@pytest.mark.parametrize("n_tok,n_kv", [(40, 256), (512, 512), (130, 320)])
+@pytest.mark.parametrize("masked", [True, False])
+def test_attn_prefill_matches_fp32_attention(b200, hd, n_tok, n_kv, masked):
+    """b200_op_attn_prefill (online softmax, mma.sync) against plain fp32 attention on the same f16-rounded K / V / q: the tolerance is the f16
+    rounding of the probabilities (the reference CPU rounds them the same way before its V product). Causal mask with -inf, GQA 4:1, a token count
+    that is not a multiple of the 64-row tile."""
+    import torch
+    b = b200
+    b.lib.b200_op_attn_prefill.restype = C.c_int
+    torch.manual_seed(hd + n_tok)
+    dev = "cuda"
+    n_head, n_hkv = 8, 2
+    K = (torch.randn((n_hkv, n_kv, hd), device=dev) * 0.5).to(torch.float16)
+    VT = torch.randn((n_hkv, hd, n_kv), device=dev).to(torch.float16)
+    q = torch.randn((n_head, n_tok, hd), device=dev)
+    scale = 1.0 / hd ** 0.5
+    pad = (n_tok + 63) // 64 * 64
+    mask = torch.zeros((pad, n_kv), device=dev)
+    if masked:
+        past = n_kv - n_tok                          # token i sees the first past + i + 1 cache rows
+        col = torch.arange(n_kv, device=dev)[None, :]
+        row = torch.arange(pad, device=dev)[:, None]
+        mask = torch.where(col <= past + row, 0.0, float("-inf"))
+    mask16 = mask.to(torch.float16).contiguous()
+    out = torch.full((n_tok, n_head, hd), float("nan"), device=dev)
+    tk, tq, tv = _t(K, F16), _t(q, F32), _t(VT, F16)
+    tm, td = _t(mask16, F16), _t(out, F32)
+    _ok(b, b.lib.b200_op_attn_prefill(C.byref(tk), C.byref(tq), C.byref(tm) if masked else None, C.byref(tv), C.byref(td), C.c_float(scale), None))
+    torch.cuda.synchronize()
+    qh = q.to(torch.float16).float()
+    want = torch.empty_like(out)
+    for h in range(n_head):
+        kh = h // (n_head // n_hkv)
+        s = qh[h] @ K[kh].float().T * scale + mask[:n_tok]
+        p = torch.softmax(s, dim=-1)
+        want[:, h, :] = p @ VT[kh].float().T
+    assert torch.isfinite(out).all()
+    err = float(((out - want) ** 2).sum() / (want ** 2).sum())
+    assert err < 1e-5, f"nmse {err:.3e}"

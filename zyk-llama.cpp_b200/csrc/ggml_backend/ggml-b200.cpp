@@ -1197,7 +1197,13 @@ int try_fuse_attn(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & s
     const ggml_tensor * K = kq->src[0], * q = kq->src[1], * V = kqv->src[0], * mask = sm->src[1];
     const int64_t hd = K->ne[0], n_kv = K->ne[1], n_tok = q->ne[1], n_head = q->ne[2];
     float scale, max_bias; memcpy(&scale, sm->op_params, sizeof(float)); memcpy(&max_bias, (const float *) sm->op_params + 1, sizeof(float));
-    if (max_bias != 0.0f || n_tok > 16 || n_kv > 11000 || n_kv < 1 || K->ne[3] != 1 || q->ne[3] != 1 || K->nb[0] != 2 || V->nb[0] != 2 || q->nb[0] != 4 ||
+    static const bool prefill_on = env_on("GGML_B200_FUSE_PREFILL_ATTN");
+    const bool decode = n_tok <= 16 && n_kv <= 11000;
+    auto al16 = [](const ggml_tensor * t) { return ((uintptr_t) t->data % 16) == 0 && t->nb[1] % 16 == 0 && t->nb[2] % 16 == 0; };
+    // more query tokens: the tensor-core kernel (b200_op_attn_prefill) with its own shape rules
+    const bool prefill = !decode && prefill_on && (hd == 64 || hd == 128) && n_kv >= 64 && n_kv % 64 == 0 && n_head <= 65535 && V->ne[3] == 1 && al16(K) && al16(V) && al16(q) &&
+                         (!mask || (mask->ne[2] == 1 && mask->ne[3] == 1 && ((uintptr_t) mask->data % 8) == 0 && mask->nb[1] % 8 == 0));
+    if (max_bias != 0.0f || (!decode && !prefill) || n_kv < 1 || K->ne[3] != 1 || q->ne[3] != 1 || K->nb[0] != 2 || V->nb[0] != 2 || q->nb[0] != 4 ||
         V->ne[0] != n_kv || V->ne[1] != hd || V->ne[2] != K->ne[2] || n_head % K->ne[2] != 0 || hd % 32 != 0 || K->nb[1] % 16 || K->nb[2] % 16 ||
         ((uintptr_t) K->data % 16)) return -1;
     if (mask && !(f_any(mask) && mask->ne[0] >= n_kv && mask->ne[1] >= n_tok)) return -1;
@@ -1206,7 +1212,9 @@ int try_fuse_attn(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & s
         cont->type != GGML_TYPE_F32 || !ggml_is_contiguous(cont) || ggml_nelements(cont) != hd * n_head * n_tok) return -1;
     const b200_tensor tk = bt(K), tq = bt(q), tv = bt(V), td = bt(cont);
     b200_tensor tm = {}; if (mask) tm = bt(mask);
-    if (b200_op_attn_decode(&tk, &tq, mask ? &tm : nullptr, &tv, &td, scale, bc->stream) != 0) {
+    const int rc = decode ? b200_op_attn_decode(&tk, &tq, mask ? &tm : nullptr, &tv, &td, scale, bc->stream)
+                          : b200_op_attn_prefill(&tk, &tq, mask ? &tm : nullptr, &tv, &td, scale, bc->stream);
+    if (rc != 0) {
         GGML_LOG_ERROR("ggml-b200: fused attention (%s) failed: %s\n", cont->name, b200_last_error()); st = GGML_STATUS_FAILED;
     }
     return ic;

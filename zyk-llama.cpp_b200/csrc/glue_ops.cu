@@ -754,6 +754,149 @@ __global__ void __launch_bounds__(128) mm_mma_kernel(const T4 a, const T4 b, con
             }
 }
 
+// ---- prefill attention for the MUL_MAT(K, q) -> SOFT_MAX -> MUL_MAT(V^T, p) -> PERMUTE -> CONT run of build_attn (no FLASH_ATTN_EXT in the graph):
+// one pass over the KV cache with an online softmax, both products on the tensor cores (mma.sync.m16n8k16, f16 operands, f32 accumulation;
+// q and the probabilities are rounded to f16 exactly where the reference CPU rounds them: src1 of an F16 matmul). The score matrix never
+// reaches memory. CTA = 64 query tokens of one head (four warps x 16 rows), KV tiles of 64; a tile whose mask is -inf for all 64 x 64
+// entries (the upper triangle of a causal ubatch) is skipped before its K / V are loaded. HD = head dimension (64 or 128).
+template <int HD>
+__global__ void __launch_bounds__(128) attn_prefill_kernel(const T4 k, const T4 q, const T4 m, int has_mask, const T4 v, float * __restrict__ dst, float scale) {
+    pdl_launch_dependents(); pdl_wait();
+    constexpr int LDK = HD + 8, LDV = 64 + 8;                  // row strides in halves: conflict-free fragment loads (see mm_mma_kernel)
+    __shared__ __align__(16) __half Ks[64][LDK];               // K tile [kv][d]; first used to stage the q tile [token][d]
+    __shared__ __align__(16) __half Vs[HD][LDV];               // V^T tile [d][kv]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int n_kv = (int) k.ne[1], n_tok = (int) q.ne[1], n_head = (int) q.ne[2];
+    const int head = blockIdx.y, kvh = head / (n_head / (int) k.ne[2]);
+    const int tok0 = blockIdx.x * 64;
+    const char * kb = k.data + (long long) kvh * k.nb[2];
+    const char * vb = v.data + (long long) kvh * v.nb[2];
+    const char * qb = q.data + (long long) head * q.nb[2];
+
+    // q tile -> f16 fragments (A operand of the score product), kept in registers for the whole pass
+    for (int i = tid; i < 64 * (HD / 4); i += 128) {
+        const int r = i / (HD / 4), c = (i - r * (HD / 4)) * 4;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tok0 + r < n_tok) x = *reinterpret_cast<const float4 *>(qb + (long long) (tok0 + r) * q.nb[1] + c * 4);
+        const __half2 h0 = __floats2half2_rn(x.x, x.y), h1 = __floats2half2_rn(x.z, x.w);
+        *reinterpret_cast<uint2 *>(&Ks[r][c]) = make_uint2(*reinterpret_cast<const uint32_t *>(&h0), *reinterpret_cast<const uint32_t *>(&h1));
+    }
+    __syncthreads();
+    uint32_t qf[HD / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) {
+        const __half * r0 = &Ks[warp * 16 + g][ks * 16 + 2 * t], * r1 = &Ks[warp * 16 + g + 8][ks * 16 + 2 * t];
+        qf[ks][0] = *reinterpret_cast<const uint32_t *>(r0);     qf[ks][1] = *reinterpret_cast<const uint32_t *>(r1);
+        qf[ks][2] = *reinterpret_cast<const uint32_t *>(r0 + 8); qf[ks][3] = *reinterpret_cast<const uint32_t *>(r1 + 8);
+    }
+    float o[HD / 8][4];
+#pragma unroll
+    for (int j = 0; j < HD / 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
+    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+    const int tokr[2] = {tok0 + warp * 16 + g, tok0 + warp * 16 + g + 8};
+    const bool mh = m.type == B200_TYPE_F16;
+
+    for (int kv0 = 0; kv0 < n_kv; kv0 += 64) {
+        // mask values of this thread's 2 x 16 score entries (columns 8 j + 2 t + {0, 1})
+        float mk[2][16];
+        int finite = 0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const bool live = tokr[h] < n_tok;
+            const char * mp = has_mask && live ? m.data + (long long) tokr[h] * m.nb[1] : nullptr;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float a = 0.f, b = 0.f;
+                if (mp) {
+                    const int c = kv0 + 8 * j + 2 * t;
+                    if (mh) { const __half2 hv = *reinterpret_cast<const __half2 *>(mp + c * 2); a = __low2float(hv); b = __high2float(hv); }
+                    else    { const float2 fv = *reinterpret_cast<const float2 *>(mp + c * 4); a = fv.x; b = fv.y; }
+                }
+                mk[h][2 * j] = a; mk[h][2 * j + 1] = b;
+                finite |= (live && (a > -INFINITY || b > -INFINITY)) ? 1 : 0;
+            }
+        }
+        __syncthreads();                                        // the previous tile's fragment loads are done (and the q staging, first time round)
+        if (!__syncthreads_or(finite)) continue;                // nothing of this tile is visible to any of the 64 tokens
+        for (int i = tid; i < 64 * (HD / 8); i += 128) {        // K tile: 64 rows x HD halves
+            const int r = i / (HD / 8), c = (i - r * (HD / 8)) * 8;
+            *reinterpret_cast<uint4 *>(&Ks[r][c]) = *reinterpret_cast<const uint4 *>(kb + (long long) (kv0 + r) * k.nb[1] + c * 2);
+        }
+        for (int i = tid; i < HD * 8; i += 128) {               // V^T tile: HD rows x 64 halves
+            const int r = i >> 3, c = (i & 7) * 8;
+            *reinterpret_cast<uint4 *>(&Vs[r][c]) = *reinterpret_cast<const uint4 *>(vb + (long long) r * v.nb[1] + (long long) (kv0 + c) * 2);
+        }
+        __syncthreads();
+        // scores: 16 rows x 64 kv per warp
+        float sc[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { sc[j][0] = 0.f; sc[j][1] = 0.f; sc[j][2] = 0.f; sc[j][3] = 0.f; }
+#pragma unroll
+        for (int ks = 0; ks < HD / 16; ++ks)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const __half * r = &Ks[8 * j + g][ks * 16 + 2 * t];
+                const uint32_t fb[2] = {*reinterpret_cast<const uint32_t *>(r), *reinterpret_cast<const uint32_t *>(r + 8)};
+                mma16816(sc[j], qf[ks], fb);
+            }
+        // online softmax over the tile (rows g and g + 8 of the warp; a row lives in the four lanes of a quad)
+        uint32_t pf[4][4];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float mx = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                sc[j][2 * h] = sc[j][2 * h] * scale + mk[h][2 * j];
+                sc[j][2 * h + 1] = sc[j][2 * h + 1] * scale + mk[h][2 * j + 1];
+                mx = fmaxf(mx, fmaxf(sc[j][2 * h], sc[j][2 * h + 1]));
+            }
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            const float mnew = fmaxf(mrow[h], mx);
+            const float base = mnew == -INFINITY ? 0.f : mnew;          // a row that has seen nothing but -inf so far: keep everything at zero
+            const float corr = expf(mrow[h] - base);                   // mrow = -inf -> 0
+            float sum = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float p0 = expf(sc[j][2 * h] - base), p1 = expf(sc[j][2 * h + 1] - base);
+                sc[j][2 * h] = p0; sc[j][2 * h + 1] = p1;
+                sum += p0 + p1;
+            }
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            lrow[h] = lrow[h] * corr + sum;
+            mrow[h] = mnew;
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) { o[j][2 * h] *= corr; o[j][2 * h + 1] *= corr; }
+        }
+        // probabilities as the A operand of the second product: two adjacent 8-column score tiles are one 16-wide k step
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+            const __half2 a0 = __floats2half2_rn(sc[2 * ks][0], sc[2 * ks][1]), a1 = __floats2half2_rn(sc[2 * ks][2], sc[2 * ks][3]);
+            const __half2 a2 = __floats2half2_rn(sc[2 * ks + 1][0], sc[2 * ks + 1][1]), a3 = __floats2half2_rn(sc[2 * ks + 1][2], sc[2 * ks + 1][3]);
+            pf[ks][0] = *reinterpret_cast<const uint32_t *>(&a0); pf[ks][1] = *reinterpret_cast<const uint32_t *>(&a1);
+            pf[ks][2] = *reinterpret_cast<const uint32_t *>(&a2); pf[ks][3] = *reinterpret_cast<const uint32_t *>(&a3);
+        }
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) {
+                const __half * r = &Vs[8 * j + g][ks * 16 + 2 * t];
+                const uint32_t fb[2] = {*reinterpret_cast<const uint32_t *>(r), *reinterpret_cast<const uint32_t *>(r + 8)};
+                mma16816(o[j], pf[ks], fb);
+            }
+    }
+    // dst [head_dim, n_head, n_tokens] contiguous
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (tokr[h] >= n_tok) continue;
+        const float inv = 1.0f / lrow[h];
+        float * dp = dst + ((long long) tokr[h] * n_head + head) * HD;
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) *reinterpret_cast<float2 *>(dp + 8 * j + 2 * t) = make_float2(o[j][2 * h] * inv, o[j][2 * h + 1] * inv);
+    }
+}
+
 } // namespace
 
 extern "C" {
@@ -803,6 +946,24 @@ int b200_op_attn_decode(const b200_tensor * k, const b200_tensor * q, const b200
     B200_REQUIRE(contiguous_f(dst, 4) && nelem(dst) == hd * n_head * n_tok, "b200_op_attn_decode: dst must be the contiguous [head_dim, n_head, n_tokens] result");
     B200_CHECK(b200_launch(attn_decode_kernel, dim3((unsigned) n_head, (unsigned) n_tok), dim3(256), (size_t) (n_kv + hd + 256) * sizeof(float), (cudaStream_t) stream, glue_pdl(),
                            t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
+    return 0;
+}
+
+int b200_op_attn_prefill(const b200_tensor * k, const b200_tensor * q, const b200_tensor * mask, const b200_tensor * v, const b200_tensor * dst, float scale, b200_stream_t stream) {
+    B200_REQUIRE(k && q && v && dst && k->data && q->data && v->data && dst->data && (!mask || mask->data), "b200_op_attn_prefill: null tensor");
+    B200_REQUIRE(k->type == B200_TYPE_F16 && v->type == B200_TYPE_F16 && q->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && k->nb[0] == 2 && v->nb[0] == 2 && q->nb[0] == 4,
+                 "b200_op_attn_prefill: f16 K / V rows, f32 q");
+    const long long hd = k->ne[0], n_kv = k->ne[1], n_head = q->ne[2], n_tok = q->ne[1];
+    auto al16 = [](const b200_tensor * t) { return ((uintptr_t) t->data % 16) == 0 && t->nb[1] % 16 == 0 && t->nb[2] % 16 == 0; };
+    B200_REQUIRE((hd == 64 || hd == 128) && q->ne[0] == hd && v->ne[0] == n_kv && v->ne[1] == hd && v->ne[2] == k->ne[2] && k->ne[2] > 0 && n_head % k->ne[2] == 0 &&
+                 k->ne[3] == 1 && q->ne[3] == 1 && v->ne[3] == 1 && n_kv >= 64 && n_kv % 64 == 0 && al16(k) && al16(v) && al16(q), "b200_op_attn_prefill: shapes / alignment");
+    B200_REQUIRE(n_tok >= 1 && n_head >= 1 && n_head <= 65535, "b200_op_attn_prefill: n_tokens %lld / n_head %lld out of range", n_tok, n_head);
+    B200_REQUIRE(!mask || ((mask->type == B200_TYPE_F32 || mask->type == B200_TYPE_F16) && mask->ne[0] >= n_kv && mask->ne[1] >= n_tok && mask->ne[2] == 1 && mask->ne[3] == 1 &&
+                           mask->nb[0] == (mask->type == B200_TYPE_F16 ? 2 : 4) && ((uintptr_t) mask->data % 8) == 0 && mask->nb[1] % 8 == 0), "b200_op_attn_prefill: bad mask");
+    B200_REQUIRE(contiguous_f(dst, 4) && nelem(dst) == hd * n_head * n_tok && ((uintptr_t) dst->data % 8) == 0, "b200_op_attn_prefill: dst must be the contiguous [head_dim, n_head, n_tokens] result");
+    const dim3 grid(blocks_for(n_tok, 64), (unsigned) n_head);
+    if (hd == 128) B200_CHECK(b200_launch(attn_prefill_kernel<128>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
+    else           B200_CHECK(b200_launch(attn_prefill_kernel<64>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
     return 0;
 }
 
