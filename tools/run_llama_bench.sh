@@ -25,9 +25,9 @@ echo "== 1. reference CPU backend, Llama-3.2-1B Q4_0, $T threads"
 env -u GGML_BACKEND_PATH "$BIN" -m "$TMP/llama-3.2-1b-q4_0.gguf" -p 512 -n 128 -r 2 -t "$T" -ngl 0 2>&1 | tee "$OUT/cpu_1b_q4_0.txt" | tail -6
 fi
 echo "== 2. this plugin as the GPU device, Llama-3-8B Q4_K_M (MUL_MAT on the B200, the rest on the CPU backend, KV cache on the host)"
-GGML_BACKEND_PATH="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so" timeout 900 "$BIN" -m "$TMP/llama-3-8b-q4_k_m.gguf" -p 512 -n 128 -r 3 -t "$T" -ngl 99 2>&1 | tee "$OUT/b200_8b_q4_k_m.txt" | tail -6
+GGML_BACKEND_PATH="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so" timeout 900 "$BIN" -m "$TMP/llama-3-8b-q4_k_m.gguf" -p 512 -n 128 -r 5 -t "$T" -ngl 99 2>&1 | tee "$OUT/b200_8b_q4_k_m.txt" | tail -6
 echo "== 2b. this plugin, Llama-3.2-1B Q4_0"
-GGML_BACKEND_PATH="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so" timeout 900 "$BIN" -m "$TMP/llama-3.2-1b-q4_0.gguf" -p 512 -n 128 -r 3 -ngl 99 2>&1 | tee "$OUT/b200_1b_q4_0.txt" | tail -4
+GGML_BACKEND_PATH="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so" timeout 900 "$BIN" -m "$TMP/llama-3.2-1b-q4_0.gguf" -p 512 -n 128 -r 5 -ngl 99 2>&1 | tee "$OUT/b200_1b_q4_0.txt" | tail -4
 if [ -z "${ONLY_PLUGIN:-}" ] && [ -f "$ROOT/oracle/_ref/cuda/libggml-cuda.so" ]; then
     echo "== 3. the reference's CUDA backend, Llama-3-8B Q4_K_M"
     GGML_BACKEND_PATH="$ROOT/oracle/_ref/cuda/libggml-cuda.so" timeout 900 "$BIN" -m "$TMP/llama-3-8b-q4_k_m.gguf" -p 512 -n 128 -r 3 -ngl 99 2>&1 | tee "$OUT/cuda_8b_q4_k_m.txt" | tail -6

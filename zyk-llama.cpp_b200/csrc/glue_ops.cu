@@ -137,9 +137,10 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(const T4 a, const T4w d, 
 // ---- fused [ADD ->] RMS_NORM -> MUL(weight): sum = a + b (stored when `sum` is given), y = sum / sqrt(mean(sum^2) + eps) * w ----
 // (what the llama graph does at every residual: ffn_inp = attn_out + inp; norm = rms_norm(ffn_inp); ffn_norm = norm * ffn_norm.weight;
 //  the reference's CUDA backend fuses the same pattern, ggml-cuda.cu ggml_cuda_can_fuse / rms_norm_mul_f32)
-// one CTA of 1024 threads per row: the row is read once with 128-bit loads (two per thread: rows of up to 8192 elements stay in registers), longer or
+// one CTA per row, 1024 threads for a few rows (decode) and 256 for many (a prefill ubatch: more rows in flight per SM, eight loads per thread): the row is read once with 128-bit loads (two per thread: rows of up to 8192 elements stay in registers), longer or
 // unaligned rows take the scalar loop. w has ne[0] == row length (checked by the caller), so it is indexed without a modulo.
-__global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, const T4 b, int has_b, const T4w sum, int has_sum, const T4 w, const T4w d, float eps) {
+template <int NT>
+__global__ void __launch_bounds__(NT) add_rms_norm_mul_kernel(const T4 a, const T4 b, int has_b, const T4w sum, int has_sum, const T4 w, const T4w d, float eps) {
     pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
     const unsigned row = blockIdx.x;
     const unsigned n1 = (unsigned) a.ne[1], n2 = (unsigned) a.ne[2];
@@ -152,12 +153,13 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, cons
     const int n = (int) a.ne[0];
     __shared__ float red[32];
     const bool vec = n <= 8192 && (n & 3) == 0 && ((((uintptr_t) x) | ((uintptr_t) y) | ((uintptr_t) wr) | (xb ? (uintptr_t) xb : 0) | (so ? (uintptr_t) so : 0)) & 15) == 0;
-    float4 v[2];
+    constexpr int NV = 8192 / (4 * NT);                   // 128-bit pieces per thread: 2 (1024 threads) or 8 (256 threads)
+    float4 v[NV];
     float s = 0.0f;
     if (vec) {
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            const int i4 = threadIdx.x + t * 1024;
+        for (int t = 0; t < NV; ++t) {
+            const int i4 = threadIdx.x + t * NT;
             float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
             if (i4 * 4 < n) {
                 e = reinterpret_cast<const float4 *>(x)[i4];
@@ -167,18 +169,18 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, cons
             v[t] = e; s += e.x * e.x + e.y * e.y + e.z * e.z + e.w * e.w;
         }
     } else {
-        for (int i = threadIdx.x; i < n; i += 1024) { float e = x[i]; if (xb) e += xb[i]; if (so) so[i] = e; s += e * e; }
+        for (int i = threadIdx.x; i < n; i += NT) { float e = x[i]; if (xb) e += xb[i]; if (so) so[i] = e; s += e * e; }
     }
     s = warp_sum(s);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
     __syncthreads();
-    s = red[threadIdx.x & 31];
+    s = (threadIdx.x & 31) < NT / 32 ? red[threadIdx.x & 31] : 0.0f;
     s = warp_sum(s);
     const float scale = 1.0f / sqrtf(s / (float) n + eps);
     if (vec) {
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            const int i4 = threadIdx.x + t * 1024;
+        for (int t = 0; t < NV; ++t) {
+            const int i4 = threadIdx.x + t * NT;
             if (i4 * 4 < n) {
                 const float4 ww = reinterpret_cast<const float4 *>(wr)[i4];
                 reinterpret_cast<float4 *>(y)[i4] = make_float4(v[t].x * scale * ww.x, v[t].y * scale * ww.y, v[t].z * scale * ww.z, v[t].w * scale * ww.w);
@@ -186,7 +188,7 @@ __global__ void __launch_bounds__(1024) add_rms_norm_mul_kernel(const T4 a, cons
         }
     } else {
         // (so holds the sums when it exists; otherwise recompute: y may alias x only element by element)
-        for (int i = threadIdx.x; i < n; i += 1024) { float e = so ? so[i] : (xb ? x[i] + xb[i] : x[i]); y[i] = e * scale * wr[i]; }
+        for (int i = threadIdx.x; i < n; i += NT) { float e = so ? so[i] : (xb ? x[i] + xb[i] : x[i]); y[i] = e * scale * wr[i]; }
     }
 }
 
@@ -369,31 +371,62 @@ __global__ void __launch_bounds__(256) argsort_kernel(const T4 a, const T4w d, i
 
 // ---- ROPE, modes normal (0) and neox (2), ext_factor == 0 (ggml_compute_forward_rope_flt + ggml_rope_cache_init + rope_yarn, ops.cpp:5524-5790) ----
 struct RopeP { int n_dims, mode; float freq_base, freq_scale, attn_factor; };
-template <typename I>
+// one thread = one rotation pair position (ip, token) for a chunk of `hc` heads: the angle (powf, sincosf) is computed once per chunk. hc = 8 for a
+// prefill ubatch (the angle arithmetic dominated: 11 -> 5 us per 512 x 32 x 128 tensor), 1 for a few tokens (decode wants the threads, not the reuse)
+inline int rope_hc(const b200_tensor * src) { return src->ne[2] * src->ne[3] >= 32 ? 8 : 1; }      // template instantiations: 1 and 8
+__device__ __forceinline__ void rope_angle(const RopeP & p, float theta_scale, int pos, int ip, const float * ff, float & sn, float & cs) {
+    const float theta = (float) pos * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
+    sincosf(theta, &sn, &cs);
+    sn *= p.attn_factor; cs *= p.attn_factor;
+}
+template <typename I, int ROPE_HC>
 __global__ void __launch_bounds__(256) rope_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p) {
     pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
-    const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
-    const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
-    const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
-    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
-        I ip, i1, i2, i3;
-        unravel<I>(i, hne, ip, i1, i2, i3);
-        const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
-        char * dst = d.data + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3];
-        if (2 * (int) ip >= p.n_dims) {                // the dimensions past n_dims are copied
-            const int e = 2 * (int) ip;
-            reinterpret_cast<float *>(dst)[e] = reinterpret_cast<const float *>(src)[e];
-            reinterpret_cast<float *>(dst)[e + 1] = reinterpret_cast<const float *>(src)[e + 1];
-            continue;
+    if constexpr (ROPE_HC == 1) {      // one thread per pair and head (decode: the kernel is all latency, keep it short)
+        const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
+        const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
+        const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+        for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+            I ip, i1, i2, i3;
+            unravel<I>(i, hne, ip, i1, i2, i3);
+            const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
+            char * dst = d.data + (long long) i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3];
+            if (2 * (int) ip >= p.n_dims) {                // the dimensions past n_dims are copied
+                const int e = 2 * (int) ip;
+                reinterpret_cast<float *>(dst)[e] = reinterpret_cast<const float *>(src)[e];
+                reinterpret_cast<float *>(dst)[e + 1] = reinterpret_cast<const float *>(src)[e + 1];
+                continue;
+            }
+            const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
+            float sn, cs;
+            sincosf(theta, &sn, &cs);
+            sn *= p.attn_factor; cs *= p.attn_factor;
+            const int e0 = p.mode == 2 ? (int) ip : 2 * (int) ip, e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
+            const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
+            reinterpret_cast<float *>(dst)[e0] = x0 * cs - x1 * sn;
+            reinterpret_cast<float *>(dst)[e1] = x0 * sn + x1 * cs;
         }
-        const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
-        float sn, cs;
-        sincosf(theta, &sn, &cs);
-        sn *= p.attn_factor; cs *= p.attn_factor;
-        const int e0 = p.mode == 2 ? (int) ip : 2 * (int) ip, e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
-        const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
-        reinterpret_cast<float *>(dst)[e0] = x0 * cs - x1 * sn;
-        reinterpret_cast<float *>(dst)[e1] = x0 * sn + x1 * cs;
+    } else {
+        const long long hch = (a.ne[1] + ROPE_HC - 1) / ROPE_HC;
+        const long long hne[4] = {a.ne[0] / 2, hch, a.ne[2], a.ne[3]};
+        const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
+        const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+        for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) gridDim.x * 256) {
+            I ip, ic, i2, i3;
+            unravel<I>(i, hne, ip, ic, i2, i3);
+            const bool rot = 2 * (int) ip < p.n_dims;           // the dimensions past n_dims are copied
+            float sn = 0.0f, cs = 1.0f;
+            if (rot) rope_angle(p, theta_scale, pos[i2], (int) ip, ff, sn, cs);
+            const int e0 = rot && p.mode == 2 ? (int) ip : 2 * (int) ip, e1 = rot && p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
+            const long long h1 = (long long) ic * ROPE_HC + ROPE_HC < a.ne[1] ? (long long) ic * ROPE_HC + ROPE_HC : a.ne[1];
+            for (long long i1 = (long long) ic * ROPE_HC; i1 < h1; ++i1) {
+                const float * src = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+                float * dst = reinterpret_cast<float *>(d.data + i1 * d.nb[1] + (long long) i2 * d.nb[2] + (long long) i3 * d.nb[3]);
+                const float x0 = src[e0], x1 = src[e1];
+                dst[e0] = rot ? x0 * cs - x1 * sn : x0;
+                dst[e1] = rot ? x0 * sn + x1 * cs : x1;
+            }
+        }
     }
 }
 
@@ -422,55 +455,101 @@ __global__ void __launch_bounds__(256) set_rows_kernel(const T4 a, const T4 idx,
 // ---- decode / prefill KV-cache prologue in ONE launch: ROPE(k) whose result goes to its own tensor AND, converted, into the K cache rows
 // (the SET_ROWS that follows it in build_attn, src/llama-graph.cpp), plus optionally the independent SET_ROWS of V in the tail blocks.
 // `sa` = shape of the SET_ROWS source (a reshaped, contiguous view of the ROPE result: element L of one is element L of the other).
-template <typename I>
+template <typename I, int ROPE_HC>
 __global__ void __launch_bounds__(256) rope_set_rows_kernel(const T4 a, const int * __restrict__ pos, const float * __restrict__ ff, const T4w d, const RopeP p,
                                                            const T4 sa, const T4 idx, const T4w cache, unsigned kblocks,
                                                            const T4 va, const T4 vidx, const T4w vcache) {
     pdl_launch_dependents(); pdl_wait();      // programmatic dependent launch (no-ops without the launch attribute)
-    if (blockIdx.x >= kblocks) {                              // SET_ROWS of V: the body of set_rows_kernel on the tail blocks
-        const I total = (I) (va.ne[0] * va.ne[1] * va.ne[2] * va.ne[3]);
-        for (I i = (I) (blockIdx.x - kblocks) * 256 + threadIdx.x; i < total; i += (I) (gridDim.x - kblocks) * 256) {
-            I i0, i1, i2, i3;
-            unravel<I>(i, va.ne, i0, i1, i2, i3);
-            const char * ip = vidx.data + (long long) i1 * vidx.nb[0] + (long long) (i2 % (I) vidx.ne[1]) * vidx.nb[1] + (long long) (i3 % (I) vidx.ne[2]) * vidx.nb[2];
-            const long long r = vidx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
-            const float v = *reinterpret_cast<const float *>(va.data + (long long) i0 * va.nb[0] + (long long) i1 * va.nb[1] + (long long) i2 * va.nb[2] + (long long) i3 * va.nb[3]);
-            store_as(vcache.data + (long long) i0 * vcache.nb[0] + r * vcache.nb[1] + (long long) i2 * vcache.nb[2] + (long long) i3 * vcache.nb[3], vcache.type, v);
+    if constexpr (ROPE_HC == 1) {      // one thread per pair and head (decode: the kernel is all latency, keep it short)
+        if (blockIdx.x >= kblocks) {                              // SET_ROWS of V: the body of set_rows_kernel on the tail blocks
+            const I total = (I) (va.ne[0] * va.ne[1] * va.ne[2] * va.ne[3]);
+            for (I i = (I) (blockIdx.x - kblocks) * 256 + threadIdx.x; i < total; i += (I) (gridDim.x - kblocks) * 256) {
+                I i0, i1, i2, i3;
+                unravel<I>(i, va.ne, i0, i1, i2, i3);
+                const char * ip = vidx.data + (long long) i1 * vidx.nb[0] + (long long) (i2 % (I) vidx.ne[1]) * vidx.nb[1] + (long long) (i3 % (I) vidx.ne[2]) * vidx.nb[2];
+                const long long r = vidx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
+                const float v = *reinterpret_cast<const float *>(va.data + (long long) i0 * va.nb[0] + (long long) i1 * va.nb[1] + (long long) i2 * va.nb[2] + (long long) i3 * va.nb[3]);
+                store_as(vcache.data + (long long) i0 * vcache.nb[0] + r * vcache.nb[1] + (long long) i2 * vcache.nb[2] + (long long) i3 * vcache.nb[3], vcache.type, v);
+            }
+            return;
         }
-        return;
-    }
-    const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
-    const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
-    const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
-    for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) kblocks * 256) {
-        I ip, i1, i2, i3;
-        unravel<I>(i, hne, ip, i1, i2, i3);
-        const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
-        int e0, e1; float y0, y1;
-        if (2 * (int) ip >= p.n_dims) {
-            e0 = 2 * (int) ip; e1 = e0 + 1;
-            y0 = reinterpret_cast<const float *>(src)[e0]; y1 = reinterpret_cast<const float *>(src)[e1];
-        } else {
-            const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
-            float sn, cs;
-            sincosf(theta, &sn, &cs);
-            sn *= p.attn_factor; cs *= p.attn_factor;
-            e0 = p.mode == 2 ? (int) ip : 2 * (int) ip; e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
-            const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
-            y0 = x0 * cs - x1 * sn; y1 = x0 * sn + x1 * cs;
+        const long long hne[4] = {a.ne[0] / 2, a.ne[1], a.ne[2], a.ne[3]};
+        const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
+        const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+        for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) kblocks * 256) {
+            I ip, i1, i2, i3;
+            unravel<I>(i, hne, ip, i1, i2, i3);
+            const char * src = a.data + (long long) i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3];
+            int e0, e1; float y0, y1;
+            if (2 * (int) ip >= p.n_dims) {
+                e0 = 2 * (int) ip; e1 = e0 + 1;
+                y0 = reinterpret_cast<const float *>(src)[e0]; y1 = reinterpret_cast<const float *>(src)[e1];
+            } else {
+                const float theta = (float) pos[i2] * powf(theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f) * p.freq_scale;
+                float sn, cs;
+                sincosf(theta, &sn, &cs);
+                sn *= p.attn_factor; cs *= p.attn_factor;
+                e0 = p.mode == 2 ? (int) ip : 2 * (int) ip; e1 = p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
+                const float x0 = reinterpret_cast<const float *>(src)[e0], x1 = reinterpret_cast<const float *>(src)[e1];
+                y0 = x0 * cs - x1 * sn; y1 = x0 * sn + x1 * cs;
+            }
+            // d is contiguous (host check): linear element index of (e, i1, i2, i3)
+            const I base = (I) (((long long) i3 * d.ne[2] + i2) * d.ne[1] + i1) * (I) d.ne[0];
+            float * dp = reinterpret_cast<float *>(d.data) + base;
+            dp[e0] = y0; dp[e1] = y1;
+    #pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const I L = base + (I) (h ? e1 : e0);
+                I j0, j1, j2, j3;
+                unravel<I>(L, sa.ne, j0, j1, j2, j3);
+                const char * xp = idx.data + (long long) j1 * idx.nb[0] + (long long) (j2 % (I) idx.ne[1]) * idx.nb[1] + (long long) (j3 % (I) idx.ne[2]) * idx.nb[2];
+                const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(xp) : *reinterpret_cast<const long long *>(xp);
+                store_as(cache.data + (long long) j0 * cache.nb[0] + r * cache.nb[1] + (long long) j2 * cache.nb[2] + (long long) j3 * cache.nb[3], cache.type, h ? y1 : y0);
+            }
         }
-        // d is contiguous (host check): linear element index of (e, i1, i2, i3)
-        const I base = (I) (((long long) i3 * d.ne[2] + i2) * d.ne[1] + i1) * (I) d.ne[0];
-        float * dp = reinterpret_cast<float *>(d.data) + base;
-        dp[e0] = y0; dp[e1] = y1;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const I L = base + (I) (h ? e1 : e0);
-            I j0, j1, j2, j3;
-            unravel<I>(L, sa.ne, j0, j1, j2, j3);
-            const char * xp = idx.data + (long long) j1 * idx.nb[0] + (long long) (j2 % (I) idx.ne[1]) * idx.nb[1] + (long long) (j3 % (I) idx.ne[2]) * idx.nb[2];
-            const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(xp) : *reinterpret_cast<const long long *>(xp);
-            store_as(cache.data + (long long) j0 * cache.nb[0] + r * cache.nb[1] + (long long) j2 * cache.nb[2] + (long long) j3 * cache.nb[3], cache.type, h ? y1 : y0);
+    } else {
+        if (blockIdx.x >= kblocks) {                              // SET_ROWS of V: the body of set_rows_kernel on the tail blocks
+            const I total = (I) (va.ne[0] * va.ne[1] * va.ne[2] * va.ne[3]);
+            for (I i = (I) (blockIdx.x - kblocks) * 256 + threadIdx.x; i < total; i += (I) (gridDim.x - kblocks) * 256) {
+                I i0, i1, i2, i3;
+                unravel<I>(i, va.ne, i0, i1, i2, i3);
+                const char * ip = vidx.data + (long long) i1 * vidx.nb[0] + (long long) (i2 % (I) vidx.ne[1]) * vidx.nb[1] + (long long) (i3 % (I) vidx.ne[2]) * vidx.nb[2];
+                const long long r = vidx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(ip) : *reinterpret_cast<const long long *>(ip);
+                const float v = *reinterpret_cast<const float *>(va.data + (long long) i0 * va.nb[0] + (long long) i1 * va.nb[1] + (long long) i2 * va.nb[2] + (long long) i3 * va.nb[3]);
+                store_as(vcache.data + (long long) i0 * vcache.nb[0] + r * vcache.nb[1] + (long long) i2 * vcache.nb[2] + (long long) i3 * vcache.nb[3], vcache.type, v);
+            }
+            return;
+        }
+        const long long hch = (a.ne[1] + ROPE_HC - 1) / ROPE_HC;
+        const long long hne[4] = {a.ne[0] / 2, hch, a.ne[2], a.ne[3]};
+        const I total = (I) (hne[0] * hne[1] * hne[2] * hne[3]);
+        const float theta_scale = powf(p.freq_base, -2.0f / (float) p.n_dims);
+        for (I i = (I) blockIdx.x * 256 + threadIdx.x; i < total; i += (I) kblocks * 256) {
+            I ip, ic, i2, i3;
+            unravel<I>(i, hne, ip, ic, i2, i3);
+            const bool rot = 2 * (int) ip < p.n_dims;
+            float sn = 0.0f, cs = 1.0f;
+            if (rot) rope_angle(p, theta_scale, pos[i2], (int) ip, ff, sn, cs);
+            const int e0 = rot && p.mode == 2 ? (int) ip : 2 * (int) ip, e1 = rot && p.mode == 2 ? (int) ip + p.n_dims / 2 : 2 * (int) ip + 1;
+            const long long h1 = (long long) ic * ROPE_HC + ROPE_HC < a.ne[1] ? (long long) ic * ROPE_HC + ROPE_HC : a.ne[1];
+            for (long long i1 = (long long) ic * ROPE_HC; i1 < h1; ++i1) {
+                const float * src = reinterpret_cast<const float *>(a.data + i1 * a.nb[1] + (long long) i2 * a.nb[2] + (long long) i3 * a.nb[3]);
+                const float x0 = src[e0], x1 = src[e1];
+                const float y0 = rot ? x0 * cs - x1 * sn : x0, y1 = rot ? x0 * sn + x1 * cs : x1;
+                // d is contiguous (host check): linear element index of (e, i1, i2, i3)
+                const I base = (I) ((((long long) i3 * d.ne[2] + i2) * d.ne[1] + i1) * d.ne[0]);
+                float * dp = reinterpret_cast<float *>(d.data) + base;
+                dp[e0] = y0; dp[e1] = y1;
+    #pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const I L = base + (I) (h ? e1 : e0);
+                    I j0, j1, j2, j3;
+                    unravel<I>(L, sa.ne, j0, j1, j2, j3);
+                    const char * xp = idx.data + (long long) j1 * idx.nb[0] + (long long) (j2 % (I) idx.ne[1]) * idx.nb[1] + (long long) (j3 % (I) idx.ne[2]) * idx.nb[2];
+                    const long long r = idx.type == B200_TYPE_I32 ? (long long) *reinterpret_cast<const int *>(xp) : *reinterpret_cast<const long long *>(xp);
+                    store_as(cache.data + (long long) j0 * cache.nb[0] + r * cache.nb[1] + (long long) j2 * cache.nb[2] + (long long) j3 * cache.nb[3], cache.type, h ? y1 : y0);
+                }
+            }
         }
     }
 }
@@ -929,8 +1008,12 @@ int b200_op_add_rms_norm_mul(const b200_tensor * a, const b200_tensor * b, const
     const long long rows = a->ne[1] * a->ne[2] * a->ne[3];
     if (rows == 0 || a->ne[0] == 0) return 0;
     B200_REQUIRE(w->ne[0] == a->ne[0], "b200_op_add_rms_norm_mul: the weight must have the row length");
-    B200_CHECK(b200_launch(add_rms_norm_mul_kernel, dim3((unsigned) rows), dim3(1024), 0, (cudaStream_t) stream, glue_pdl(), t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
-                           sum ? t4w(sum) : t4w(dst), sum ? 1 : 0, t4(w), t4w(dst), eps));
+    if (rows >= 128)
+        B200_CHECK(b200_launch(add_rms_norm_mul_kernel<256>, dim3((unsigned) rows), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
+                               sum ? t4w(sum) : t4w(dst), sum ? 1 : 0, t4(w), t4w(dst), eps));
+    else
+        B200_CHECK(b200_launch(add_rms_norm_mul_kernel<1024>, dim3((unsigned) rows), dim3(1024), 0, (cudaStream_t) stream, glue_pdl(), t4(a), b ? t4(b) : t4(a), b ? 1 : 0,
+                               sum ? t4w(sum) : t4w(dst), sum ? 1 : 0, t4(w), t4w(dst), eps));
     return 0;
 }
 
@@ -1034,10 +1117,20 @@ int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_te
     B200_REQUIRE((p->mode == 0 || p->mode == 2) && p->ext_factor == 0.0f && p->n_dims > 0 && p->n_dims % 2 == 0 && p->n_dims <= src->ne[0] && src->ne[0] % 2 == 0,
                  "b200_op_rope: mode %d / ext_factor %g / n_dims %d not supported", p->mode, (double) p->ext_factor, p->n_dims);
     B200_REQUIRE(pos->ne[0] >= src->ne[2], "b200_op_rope: %lld positions for %lld tokens", (long long) pos->ne[0], (long long) src->ne[2]);
-    const long long n = nelem(src) / 2;
-    if (n == 0) return 0;
+    if (nelem(src) == 0) return 0;
+    const int ROPE_HC = rope_hc(src);
+    const long long n = (src->ne[0] / 2) * ((src->ne[1] + ROPE_HC - 1) / ROPE_HC) * src->ne[2] * src->ne[3];      // one thread per (pair, chunk of heads, token)
     RopeP rp; rp.n_dims = p->n_dims; rp.mode = p->mode; rp.freq_base = p->freq_base; rp.freq_scale = p->freq_scale; rp.attn_factor = p->attn_factor;
-    B200_LAUNCH_IDX(rope_kernel, n, t4(src), (const int *) pos->data, freq_factors ? (const float *) freq_factors->data : (const float *) nullptr, t4w(dst), rp);
+    const float * ffp = freq_factors ? (const float *) freq_factors->data : (const float *) nullptr;
+    const dim3 grid(blocks_for(n, 256));
+    cudaStream_t st = (cudaStream_t) stream;
+    if (nelem(src) < (1ll << 31)) {
+        if (ROPE_HC == 1) B200_CHECK(b200_launch(rope_kernel<unsigned, 1>, grid, dim3(256), 0, st, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp));
+        else              B200_CHECK(b200_launch(rope_kernel<unsigned, 8>, grid, dim3(256), 0, st, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp));
+    } else {
+        if (ROPE_HC == 1) B200_CHECK(b200_launch(rope_kernel<long long, 1>, grid, dim3(256), 0, st, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp));
+        else              B200_CHECK(b200_launch(rope_kernel<long long, 8>, grid, dim3(256), 0, st, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp));
+    }
     return 0;
 }
 
@@ -1056,18 +1149,19 @@ int b200_op_rope_set_rows(const b200_tensor * src, const b200_tensor * pos, cons
         B200_REQUIRE(v_idx && v_dst && v_src->data && v_idx->data && v_dst->data && v_src->type == B200_TYPE_F32 && (v_dst->type == B200_TYPE_F32 || v_dst->type == B200_TYPE_F16) &&
                      (v_idx->type == B200_TYPE_I64 || v_idx->type == B200_TYPE_I32), "b200_op_rope_set_rows: bad second SET_ROWS");
     }
-    const long long n = nelem(src) / 2, nv = v_src ? nelem(v_src) : 0;
-    if (n == 0) return v_src ? b200_op_set_rows(v_src, v_idx, v_dst, stream) : 0;
+    const long long nv = v_src ? nelem(v_src) : 0;
+    if (nelem(src) == 0) return v_src ? b200_op_set_rows(v_src, v_idx, v_dst, stream) : 0;
+    const int ROPE_HC = rope_hc(src);
+    const long long n = (src->ne[0] / 2) * ((src->ne[1] + ROPE_HC - 1) / ROPE_HC) * src->ne[2] * src->ne[3];
     RopeP rp; rp.n_dims = p->n_dims; rp.mode = p->mode; rp.freq_base = p->freq_base; rp.freq_scale = p->freq_scale; rp.attn_factor = p->attn_factor;
     const unsigned kb = blocks_for(n, 256), vb = nv ? blocks_for(nv, 256) : 0;
     const float * ffp = freq_factors ? (const float *) freq_factors->data : (const float *) nullptr;
     const T4 tv = v_src ? t4(v_src) : t4(src), tvi = v_src ? t4(v_idx) : t4(sr_idx); const T4w tvc = v_src ? t4w(v_dst) : t4w(sr_dst);
-    if (nelem(dst) < (1ll << 31) && nv < (1ll << 31))
-        B200_CHECK(b200_launch(rope_set_rows_kernel<unsigned>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
-                               t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
-    else
-        B200_CHECK(b200_launch(rope_set_rows_kernel<long long>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), (const int *) pos->data, ffp, t4w(dst), rp,
-                               t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc));
+#define B200_RSR(I, HC) B200_CHECK(b200_launch(rope_set_rows_kernel<I, HC>, dim3(kb + vb), dim3(256), 0, (cudaStream_t) stream, glue_pdl(), t4(src), (const int *) pos->data, ffp, \
+                                               t4w(dst), rp, t4(sr_src), t4(sr_idx), t4w(sr_dst), kb, tv, tvi, tvc))
+    if (nelem(dst) < (1ll << 31) && nv < (1ll << 31)) { if (ROPE_HC == 1) B200_RSR(unsigned, 1); else B200_RSR(unsigned, 8); }
+    else                                              { if (ROPE_HC == 1) B200_RSR(long long, 1); else B200_RSR(long long, 8); }
+#undef B200_RSR
     return 0;
 }
 
