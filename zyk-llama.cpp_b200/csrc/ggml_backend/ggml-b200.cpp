@@ -71,6 +71,10 @@ struct buffer_ctx {
         }
         return staging;
     }
+    // the scratch of a big tensor (431 MB for an 8B output matrix, ~1 GB at 70B) is not kept for the life of the buffer
+    void trim() {
+        if (staging && staging_size > (size_t(32) << 20)) { b200_device_synchronize(device); b200_free(device, staging); staging = nullptr; staging_size = 0; }
+    }
 };
 
 struct backend_ctx {
@@ -192,6 +196,9 @@ void planes_demote_locked(buffer_ctx * bc, const void * data) {
     b200_memcpy_d2d((void *) data, tmp, e.nbytes, nullptr);
     b200_stream_synchronize(nullptr);
     bc->planes.erase(it);
+    bc->trim();
+    static bool told = false;
+    if (!told) { told = true; GGML_LOG_INFO("ggml-b200: a repacked weight tensor (%lld x %lld, type %d) went back to the GGUF byte layout (partial write, memset or a differently shaped view); its matmuls take the canonical-layout kernels from now on\n", (long long) e.m, (long long) e.k, e.type); }
 }
 
 // the buffer context that owns a tensor allocated in one of OUR device buffers, else nullptr
@@ -257,6 +264,7 @@ void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const
             int rc = b200_memcpy_h2d(tmp, data, size, nullptr);
             if (rc == 0 && planes_store(bc, tensor, tmp)) {
                 b200_stream_synchronize(nullptr);
+                bc->trim();
                 return;
             }
         }
@@ -285,6 +293,7 @@ void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor,
     }
     if (b200_memcpy_d2h(data, src, size, nullptr) != 0 || b200_stream_synchronize(nullptr) != 0)
         GGML_ABORT("ggml-b200: get_tensor(%s) failed: %s", tensor->name, b200_last_error());
+    bc->trim();
 }
 
 void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
