@@ -256,7 +256,34 @@ __global__ void __launch_bounds__(256) attn_decode_kernel(const T4 K, const T4 q
 #pragma unroll
     for (int i = 0; i < 8; ++i) s += red[i];
     const float inv = 1.0f / s;
-    // phase 3: out[d] = sum_j p[j] V^T[d][j]; `parts` threads share a row of V^T
+    // phase 3: out[d] = sum_j p[j] V^T[d][j]. Aligned rows of a multiple of 8 entries: a warp takes four rows of V^T at a time and its lanes walk
+    // them in consecutive 16-byte pieces (coalesced: one 512-byte run per row and step), four independent loads in flight per lane
+    const char * vbase = V.data + (long long) hk * V.nb[2];
+    if ((n_kv & 7) == 0 && (hd & 3) == 0 && (((uintptr_t) vbase | (uintptr_t) V.nb[1]) & 15) == 0) {
+        __syncthreads();                                    // every sc[j] holds its exponential
+        for (int d0 = warp * 4; d0 < hd; d0 += 32) {
+            float acc4[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int j = lane * 8; j < n_kv; j += 256) {
+                const float4 p0 = *reinterpret_cast<const float4 *>(sc + j), p1 = *reinterpret_cast<const float4 *>(sc + j + 4);
+                uint4 vv[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) vv[r] = *reinterpret_cast<const uint4 *>(vbase + (long long) (d0 + r) * V.nb[1] + j * 2);
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const float2 v0 = __half22float2(*reinterpret_cast<const __half2 *>(&vv[r].x)), v1 = __half22float2(*reinterpret_cast<const __half2 *>(&vv[r].y));
+                    const float2 v2 = __half22float2(*reinterpret_cast<const __half2 *>(&vv[r].z)), v3 = __half22float2(*reinterpret_cast<const __half2 *>(&vv[r].w));
+                    acc4[r] += v0.x * p0.x + v0.y * p0.y + v1.x * p0.z + v1.y * p0.w + v2.x * p1.x + v2.y * p1.y + v3.x * p1.z + v3.y * p1.w;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const float v = warp_sum(acc4[r]);
+                if (lane == 0) out[((long long) t * n_head + h) * hd + d0 + r] = v * inv;
+            }
+        }
+        return;
+    }
+    // any other shape: `parts` threads share a row of V^T
     const int parts = hd <= 256 ? 256 / hd : 1;
     const int d = threadIdx.x % hd, pt = threadIdx.x / hd;
     float acc = 0.0f;
