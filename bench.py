@@ -179,6 +179,42 @@ def plugin_e2e(steps: int, warmup: int, pp: int, pp_steps: int):
         return {"error": str(e)[:300]}
 
 
+def llama_bench_leg(model: str, reps: int = 3):
+    """The reference's own llama-bench binary (compiled from /root/reference into oracle/_ref, unmodified) on a random-init GGUF of the headline
+    model (tools/make_gguf.py), with this repository's plugin as its GPU device: the WHOLE llama graph (matmuls, norms, rope, KV cache, attention)
+    on the B200, pp512 and tg128 as llama-bench defines them. The file lives in a temporary directory for the duration of the call."""
+    import tempfile
+    try:
+        from oracle.oracle import ref_dir
+        d = ref_dir()
+        exe = d / "llama-bench" if d else None
+        plugin = ROOT / "zyk-llama.cpp_b200" / "lib" / "libggml-b200.so"
+        if exe is None or not exe.exists() or not plugin.exists():
+            return {"unavailable": "oracle/_ref/*/llama-bench or libggml-b200.so not built for this host"}
+        with tempfile.TemporaryDirectory() as tmp:
+            gguf = Path(tmp) / "m.gguf"
+            r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", model, "--out", str(gguf)],
+                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+            if r.returncode != 0:
+                return {"error": "make_gguf: " + r.stdout[-300:]}
+            env = dict(os.environ, GGML_BACKEND_PATH=str(plugin))
+            r = subprocess.run([str(exe), "-m", str(gguf), "-p", "512", "-n", "128", "-r", str(reps), "-ngl", "99", "-o", "json"],
+                               env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+        if r.returncode != 0:
+            return {"error": (r.stderr or r.stdout)[-300:]}
+        start = r.stdout.find("[")
+        rows = json.loads(r.stdout[start:])
+        out = {"through": "reference llama-bench (oracle/_ref, unmodified) -> reference loader, scheduler and llama_decode -> this plugin (GGML_BACKEND_PATH), -ngl 99",
+               "model": model, "data": "random-init GGUF (tools/make_gguf.py)", "repetitions": reps}
+        for row in rows:
+            key = "pp%d" % row["n_prompt"] if row.get("n_prompt") else "tg%d" % row["n_gen"]
+            out[key] = {"value": row["avg_ts"], "stddev": row["stddev_ts"], "unit": "tokens/s"}
+            out.setdefault("backend", row.get("backends"))
+        return out
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:300]}
+
+
 def workload_string(model: str, n_nodes: int) -> str:
     """the same string in both arms' config.workload"""
     return f"{model} tg (N=1): every quantised MUL_MAT of one token ({n_nodes} nodes)"
@@ -227,6 +263,7 @@ def main():
     ap.add_argument("--pp", type=int, default=512, help="prefill ubatch (0 = skip the pp leg)")
     ap.add_argument("--pp-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-llama-bench", action="store_true", help="skip the llama_bench key (the reference's llama-bench binary on the plugin, N = 1 only)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="row split (N > 1): Y slices stored into every rank's arena by the kernels, or one NCCL all-gather per node")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -499,6 +536,11 @@ def main():
     if world == 1 and args.model == "llama-3-8b-q4_k_m":
         e2e_plugin = plugin_e2e(args.steps, warmup, args.pp, max(3, args.pp_steps // 2))
 
+    # ---- the whole llama graph: the reference's llama-bench binary with the plugin as its GPU device (N = 1; the real-model counterpart of `value`) ----
+    llama_bench = None
+    if world == 1 and not args.no_llama_bench and args.model in ("llama-3-8b-q4_k_m",):
+        llama_bench = llama_bench_leg(args.model)
+
     # DRAM traffic of the dominant kernel from the ncu capture committed under profiles/ -- only when it is a capture of the kernel that ran
     traffic, traffic_src = None, None
     tf = ROOT / "profiles" / "traffic.json"
@@ -532,6 +574,7 @@ def main():
         "e2e": {"value": e2e_tg, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "through": "C ABI (ctypes -> libb200mm.so): pinned host x in, logits out, host sync per token"},
         "e2e_plugin": e2e_plugin,
+        "llama_bench": llama_bench,
         "gpu_launches": hx["launches"],
         "roofline": roof,
         "tg_per_group": tg_per_group,
