@@ -983,7 +983,11 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
             args.push_back(a); ++sizes.back(); done[h] = 1;
         }
     }
-    if (args.size() < 2) return i;                       // a single node: the ordinary path
+    // a single group also takes the chain kernel (one persistent launch for one group: its block-per-lane items out of a shared-memory ring beat
+    // the per-node GEMV in a real graph: llama-bench 8B tg128 353 -> 386); GGML_B200_CHAIN_SINGLE=0: only runs of two or more groups
+    static const bool chain_single = env_on("GGML_B200_CHAIN_SINGLE");
+    static const bool chain_q40 = [] { const char * e = getenv("GGML_B200_CHAIN_Q4_0"); return e && e[0] == '1'; }();
+    if (args.size() < 2 && !(chain_single && args[0].n <= 4)) return i;                       // a single node: the ordinary path
     // workspace for the group launches (the chain does not need one)
     size_t need = 0;
     for (const auto & a : args) { const size_t w = b200_mul_mat_workspace(a.type, a.n, a.k); need = w > need ? w : need; }
@@ -991,15 +995,15 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     for (auto & a : args) { a.workspace = bc->workspace; a.workspace_size = bc->workspace_size; }
 
     bool kquant = true;
-    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q5_K || a.type == B200_TYPE_Q6_K);
-    if (chain_on && kquant && args[0].n <= 4 && sizes.size() >= 2 && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
+    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q5_K || a.type == B200_TYPE_Q6_K || (chain_q40 && a.type == B200_TYPE_Q4_0));
+    if (chain_on && kquant && args[0].n <= 4 && (sizes.size() >= 2 || chain_single) && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
         b200_chain_t chain = nullptr;
         for (auto & c : bc->chains)
             if (c.sizes == sizes && same_args(c.args, args)) { chain = c.chain; break; }
         if (!chain) {
             chain = b200_chain_create(bc->device, args.data(), sizes.data(), (int) sizes.size());
             if (chain) {
-                if (bc->chains.size() >= 16) { b200_stream_synchronize(bc->stream); b200_chain_destroy(bc->chains.front().chain); bc->chains.erase(bc->chains.begin()); }
+                if (bc->chains.size() >= (chain_single ? 1024u : 16u)) { b200_stream_synchronize(bc->stream); b200_chain_destroy(bc->chains.front().chain); bc->chains.erase(bc->chains.begin()); }
                 bc->chains.push_back({args, sizes, chain});
             }
         }
@@ -1265,7 +1269,8 @@ int try_fuse_kv(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st)
 // MUL_MAT node (-1: no match)
 int try_fuse_glu(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
     const ggml_tensor * G = g->nodes[i];
-    if (!G->src[1] || !glue_supports(G) || !ggml_node_has_n_uses(g, i, 1)) return -1;
+    static const bool glu_on = env_on("GGML_B200_FUSE_GLU");
+    if (!glu_on || !G->src[1] || !glue_supports(G) || !ggml_node_has_n_uses(g, i, 1)) return -1;
     const int im = next_real(g, i);
     if (im < 0) return -1;
     const ggml_tensor * M = g->nodes[im];
