@@ -100,6 +100,31 @@ def test_row_split_buffer_type_logits_match_reference_cpu_backend(tiny_gguf, gra
 
 
 @pytest.fixture(scope="module")
+def tiny_kquant_gguf(tmp_path_factory):
+    """3 layers of Llama-3-8B shapes in the Q4_K_M recipe (Q4_K + Q6_K on the use_more_bits layers, Q6_K output), random-init"""
+    import sys
+    path = tmp_path_factory.mktemp("gguf") / "tiny-8b-q4_k_m.gguf"
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "llama-3-8b-q4_k_m", "--layers", "3", "--out", str(path)],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:]
+    return path
+
+
+KQ_MODES = [({}, "default"), ({"GGML_B200_CHAIN_SINGLE": "0"}, "per-node-gemv"), ({"GGML_B200_FUSE": "0"}, "no-fusion"), ({"GGML_B200_PDL": "0", "B200_GLUE_PDL": "0"}, "no-pdl")]
+
+
+@pytest.mark.parametrize("mode,name", KQ_MODES, ids=[m[1] for m in KQ_MODES])
+def test_whole_kquant_graph_logits_match_reference_cpu_backend(tiny_kquant_gguf, mode, name):
+    """The K-quant decode path of the plugin in a real graph: every MUL_MAT group is one chain-kernel launch (a chain of a single group), GLU goes
+    into the quantiser of ffn_down, rope + KV-cache writes are one launch, prefill attention is the fused tensor-core kernel -- logits of
+    llama_decode (40-token prompt + 6 decoded tokens) against the reference CPU backend, and the same with each of those switched off."""
+    env = _need("llama_logits_check")
+    env.update(mode)
+    r = subprocess.run([str(VAR / "llama_logits_check"), str(tiny_kquant_gguf), "40", "6"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
+    assert r.returncode == 0 and "LLAMA_LOGITS_CHECK OK" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.fixture(scope="module")
 def tiny_moe_gguf(tmp_path_factory):
     """2 layers of Mixtral-8x7B shapes (8 experts, 2 used; Q4_K_M recipe: Q8_0 attn_k / attn_v, Q6_K on the use_more_bits layers), random-init"""
     import sys
