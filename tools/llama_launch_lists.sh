@@ -7,7 +7,7 @@ OUT="${1:-$ROOT/gpurun_out/llama_launches}"
 mkdir -p "$OUT"
 BIN="$ROOT/oracle/_ref/avx512vnni/llama-bench"
 TMP="${TMPDIR:-/tmp}"
-python "$ROOT/tools/make_gguf.py" --model llama-3-8b-q4_k_m --layers 4 --out "$TMP/cut.gguf" > /dev/null 2>&1 || exit 5
+python "$ROOT/tools/make_gguf.py" --model "${MODEL:-llama-3-8b-q4_k_m}" --layers "${LAYERS:-4}" --out "$TMP/cut.gguf" > /dev/null 2>&1 || exit 5
 export GGML_BACKEND_PATH="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so"
 # plain runs first (the profiled command must have exited 0 without ncu)
 "$BIN" -m "$TMP/cut.gguf" -p 512 -n 0 -r 1 -ngl 99 > "$OUT/plain_pp.txt" 2>&1 || { tail -5 "$OUT/plain_pp.txt"; exit 6; }

@@ -851,7 +851,7 @@ enum ggml_status compute_mul_mat(backend_ctx * bc, const ggml_tensor * dst) {
     return GGML_STATUS_SUCCESS;
 }
 
-enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
+enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst, bool x_prequantised = false) {
     const ggml_tensor * as = dst->src[0], * b = dst->src[1], * ids = dst->src[2];
     const int64_t k = as->ne[0], m = as->ne[1], n_as = as->ne[2];
     const int64_t n_used = ids->ne[0], n_tokens = ids->ne[1], nb1 = b->ne[1];
@@ -876,7 +876,7 @@ enum ggml_status compute_mul_mat_id(backend_ctx * bc, const ggml_tensor * dst) {
         a.y = (float *) ((char *) dst->data + t0 * dst->nb[2]);
         a.y_row_stride = (int64_t) (dst->nb[1] / sizeof(float)); a.y_token_stride = (int64_t) (dst->nb[2] / sizeof(float));
         a.workspace = bc->workspace; a.workspace_size = bc->workspace_size;
-        a.flavour = B200_Q8_X86; a.flags = mm_flags();
+        a.flavour = B200_Q8_X86; a.flags = mm_flags() | (x_prequantised && n_tokens <= chunk ? (int32_t) B200_MM_X_PREQUANTISED : 0);
         if (b200_mul_mat_id(&a, bc->stream) != 0) {
             GGML_LOG_ERROR("ggml-b200: MUL_MAT_ID %s failed: %s\n", dst->name, b200_last_error());
             return GGML_STATUS_FAILED;
@@ -1293,10 +1293,12 @@ int try_fuse_glu(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st
 enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
     static const bool fuse_on = env_on("GGML_B200_FUSE") && glue_on();
     std::vector<char> done((size_t) cgraph->n_nodes, 0);          // matmuls hoisted into an earlier group
+    const ggml_tensor * last_id = nullptr, * keep_id = nullptr;
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
         if (done[i] || ggml_is_empty(node) || skipped(node)) continue;
         enum ggml_status st = GGML_STATUS_SUCCESS;
+        if (!is_noop(node)) { last_id = keep_id; keep_id = nullptr; }       // last_id: the MUL_MAT_ID that ran immediately before this node, if any
         { static const char * pre = getenv("GGML_B200_PRESYNC"); if (pre && !bc->capturing && !strcmp(pre, ggml_op_name(node->op))) b200_stream_synchronize(bc->stream); }
         if (plain_mul_mat(node)) {
             const int next = compute_decode_run(bc, cgraph, i, st, done);
@@ -1331,7 +1333,15 @@ enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
             case GGML_OP_TRANSPOSE:
                 break;
             case GGML_OP_MUL_MAT:    st = weight_type(node->src[0]->type) ? compute_mul_mat(bc, node) : compute_glue(bc, node); break;
-            case GGML_OP_MUL_MAT_ID: st = compute_mul_mat_id(bc, node); break;
+            case GGML_OP_MUL_MAT_ID: {
+                // ffn_gate_exps after ffn_up_exps (or the other way round): same activations, same shapes, nothing in between -> quantised once
+                const ggml_tensor * p = last_id;
+                const bool same = p && p->src[1] == node->src[1] && p->src[2] == node->src[2] && p->src[0]->ne[0] == node->src[0]->ne[0] && p->src[0]->ne[1] == node->src[0]->ne[1] &&
+                                  p->src[0]->ne[2] == node->src[0]->ne[2] && b200_act_type((int) p->src[0]->type) == b200_act_type((int) node->src[0]->type) &&
+                                  node->src[2]->ne[0] * node->src[2]->ne[1] <= 8;       // (decode: the per-pair GEMV path on both calls)
+                st = compute_mul_mat_id(bc, node, same);
+                keep_id = node;
+            } break;
             default:                 st = compute_glue(bc, node); break;
         }
         if (st != GGML_STATUS_SUCCESS) return st;

@@ -735,6 +735,34 @@ __global__ void __launch_bounds__(128) mm_rows_kernel(const T4 a, const T4 b, co
         if (lane == 0) *reinterpret_cast<float *>(d.data + row * d.nb[0] + c * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = v;
     }
 }
+// few src0 rows with a long k (the router of a mixture-of-experts layer: 4096 -> 8): one CTA of 256 threads per row instead of one warp
+template <int NCOLS, bool AH>
+__global__ void __launch_bounds__(256) mm_rowblock_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
+    pdl_launch_dependents(); pdl_wait();
+    __shared__ float red[NCOLS][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long row = blockIdx.x;
+    const long long i2 = blockIdx.y % d.ne[2], i3 = blockIdx.y / d.ne[2];
+    const char * ar = a.data + row * a.nb[1] + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3];
+    const char * bb = b.data + i2 * b.nb[2] + i3 * b.nb[3];
+    float acc[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) acc[c] = 0.0f;
+    for (long long k = threadIdx.x; k < a.ne[0]; k += 256) {
+        const float w = AH ? __half2float(reinterpret_cast<const __half *>(ar)[k]) : reinterpret_cast<const float *>(ar)[k];
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) acc[c] += w * reinterpret_cast<const float *>(bb + c * b.nb[1])[k];
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) { const float v = warp_sum(acc[c]); if (lane == 0) red[c][warp] = v; }
+    __syncthreads();
+    if (threadIdx.x < NCOLS) {
+        float v = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += red[threadIdx.x][w];
+        *reinterpret_cast<float *>(d.data + row * d.nb[0] + threadIdx.x * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = v;
+    }
+}
 // many activation rows: 64 x 64 output tile per CTA of 256 threads (4 x 4 per thread), k in steps of 16 through shared memory
 template <bool AH>
 __global__ void __launch_bounds__(256) mm_tile_kernel(const T4 a, const T4 b, const T4w d, long long r2, long long r3) {
@@ -1265,6 +1293,14 @@ int b200_op_mul_mat_f(const b200_tensor * a, const b200_tensor * b, const b200_t
     B200_REQUIRE(batch <= 65535, "b200_op_mul_mat_f: %lld batches exceed one launch", batch);
     cudaStream_t s = (cudaStream_t) stream;
     const bool ah = a->type == B200_TYPE_F16;
+    if (n <= 8 && a->ne[1] <= 64 && a->ne[0] >= 1024) {
+        dim3 grid((unsigned) a->ne[1], (unsigned) batch);
+#define B200_MMB(nc) case nc: if (ah) B200_CHECK(b200_launch(mm_rowblock_kernel<nc, true>, grid, dim3(256), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3)); \
+                              else    B200_CHECK(b200_launch(mm_rowblock_kernel<nc, false>, grid, dim3(256), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3)); break
+        switch ((int) n) { B200_MMB(1); B200_MMB(2); B200_MMB(3); B200_MMB(4); B200_MMB(5); B200_MMB(6); B200_MMB(7); B200_MMB(8); }
+#undef B200_MMB
+        return 0;
+    }
     if (n <= 8) {
         dim3 grid(blocks_for(a->ne[1], 4), (unsigned) batch);
 #define B200_MMR(nc) case nc: if (ah) B200_CHECK(b200_launch(mm_rows_kernel<nc, true>, grid, dim3(128), 0, s, glue_pdl(), t4(a), t4(b), t4w(dst), r2, r3)); \

@@ -415,8 +415,10 @@ int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
     }
     const XqPlanes pl = xq_planes_carve(a->workspace, act, rows, a->k);
 
-    // quantise every b row once: token-major, nb1 rows per token (b strides may be arbitrary)
-    if (a->b_token_stride == a->nb1 * a->b_row_stride) {
+    // quantise every b row once: token-major, nb1 rows per token (b strides may be arbitrary). B200_MM_X_PREQUANTISED: the previous call left exactly
+    // these rows in the workspace (ffn_gate_exps / ffn_up_exps read the same activations)
+    if (a->flags & B200_MM_X_PREQUANTISED) {
+    } else if (a->b_token_stride == a->nb1 * a->b_row_stride) {
         int rc = b200_act_quant_planes(act, a->flavour, a->b, a->b_row_stride, pl, rows, a->k, s, pdl);
         if (rc) return rc;
     } else {
