@@ -307,6 +307,11 @@ B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b
 /* the router of a mixture-of-experts layer (build_moe_ffn, src/llama-graph.cpp:1000-1150): ggml_compute_forward_scale (op 0: x * p0 + p1) and
    _clamp (op 1: to [p0, p1]); _sum_rows (f32 [k, ...] -> [1, ...]); _argsort_f32 (i32 indices that sort each row; order 0 ascending, 1
    descending as enum ggml_sort_order; rows of up to 1024 elements) -- ggml-cpu/ops.cpp */
+/* the six router nodes of build_moe_ffn in one launch (softmax gating, weights renormalised over the used experts: Mixtral): probs = softmax(logits),
+   order = argsort(probs, descending), picked = probs at the first n_used indices, sum = clamp(sum(picked), lo, hi), weights = picked / sum.
+   logits [n_expert <= 32, n_tokens]; every output is the contiguous tensor of its node; probs, picked and sum may be NULL (not needed by anyone else). */
+B200_API int b200_op_moe_route(const b200_tensor * logits, const b200_tensor * probs, const b200_tensor * order, const b200_tensor * picked, const b200_tensor * sum,
+                               const b200_tensor * weights, int n_used, float clamp_lo, float clamp_hi, b200_stream_t stream);
 B200_API int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, float p0, float p1, b200_stream_t stream);
 B200_API int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
 B200_API int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, b200_stream_t stream);

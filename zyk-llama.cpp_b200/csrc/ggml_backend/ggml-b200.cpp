@@ -24,6 +24,7 @@
 #include "b200_mm.h"
 #include "ggml_b200.h"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -1290,6 +1291,57 @@ int try_fuse_glu(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st
     return im;
 }
 
+// SOFT_MAX -> ARGSORT(desc) -> GET_ROWS(probs, first n_used of the order) -> SUM_ROWS -> CLAMP -> DIV: the router of build_moe_ffn (src/llama-graph.cpp:1040-1140,
+// softmax gating with renormalised weights) as one launch; returns the index of the DIV node (-1: no match)
+const ggml_tensor * view_root(const ggml_tensor * t) { while (t && t->view_src) t = t->view_src; return t; }
+#define MR_FAIL(n) do { static const bool dbg = getenv("GGML_B200_DEBUG_FUSE") != nullptr; if (dbg) fprintf(stderr, "ggml-b200: moe router not fused at node %d: check %d\n", i, n); } while (0)
+int try_fuse_moe_route(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st) {
+    const ggml_tensor * sm = g->nodes[i];
+    if (sm->src[1] || sm->src[2] || !sm->src[0] || sm->src[0]->type != GGML_TYPE_F32 || sm->ne[0] > 32 || sm->ne[2] != 1 || sm->ne[3] != 1) { MR_FAIL(1); return -1; }
+    float scale, max_bias; memcpy(&scale, sm->op_params, sizeof(float)); memcpy(&max_bias, (const float *) sm->op_params + 1, sizeof(float));
+    if (scale != 1.0f || max_bias != 0.0f) { MR_FAIL(2); return -1; }
+    const int ia = next_real(g, i);  if (ia < 0) { MR_FAIL(3); return -1; }
+    const int ig = next_real(g, ia); if (ig < 0) { MR_FAIL(4); return -1; }
+    const int is = next_real(g, ig); if (is < 0) { MR_FAIL(5); return -1; }
+    const int ic = next_real(g, is); if (ic < 0) { MR_FAIL(6); return -1; }
+    const int id = next_real(g, ic); if (id < 0) { MR_FAIL(7); return -1; }
+    const ggml_tensor * as = g->nodes[ia], * gr = g->nodes[ig], * su = g->nodes[is], * cl = g->nodes[ic], * dv = g->nodes[id];
+    if (as->op != GGML_OP_ARGSORT || as->src[0] != sm || ggml_get_op_params_i32(as, 0) != (int32_t) GGML_SORT_ORDER_DESC) { MR_FAIL(8); return -1; }
+    if (gr->op != GGML_OP_GET_ROWS || view_root(gr->src[0]) != sm || gr->src[0]->data != sm->data || view_root(gr->src[1]) != as || gr->src[1]->data != as->data) { MR_FAIL(9); return -1; }
+    const int64_t n_expert = sm->ne[0], n_tok = sm->ne[1], n_used = gr->src[1]->ne[0];
+    if (gr->src[0]->ne[0] != 1 || gr->src[0]->ne[1] != n_expert || gr->src[0]->ne[2] != n_tok || gr->src[1]->ne[1] != n_tok || gr->src[1]->nb[1] != as->nb[1] || n_used > n_expert ||
+        gr->ne[0] != 1 || gr->ne[1] != n_used || gr->ne[2] != n_tok) { MR_FAIL(10); return -1; }
+    if (su->op != GGML_OP_SUM_ROWS || view_root(su->src[0]) != gr || su->src[0]->data != gr->data || su->src[0]->ne[0] != n_used || su->src[0]->ne[1] != n_tok) { MR_FAIL(11); return -1; }
+    if (cl->op != GGML_OP_CLAMP || view_root(cl->src[0]) != su || cl->src[0]->data != su->data || cl->data != su->data) { MR_FAIL(12); return -1; }       // (ggml_clamp works in place)
+    if (dv->op != GGML_OP_DIV || view_root(dv->src[0]) != gr || dv->src[0]->data != gr->data || view_root(dv->src[1]) != su || dv->src[1]->data != su->data ||
+        dv->ne[0] != n_used || dv->ne[1] != n_tok) { MR_FAIL(13); return -1; }
+    { const ggml_tensor * cs[6] = {sm, sm->src[0], as, gr, su, dv}; for (const ggml_tensor * t : cs) if (!ggml_is_contiguous(t)) { MR_FAIL(14); return -1; } }
+    if (as->type != GGML_TYPE_I32 || gr->type != GGML_TYPE_F32 || su->type != GGML_TYPE_F32 || dv->type != GGML_TYPE_F32 || sm->type != GGML_TYPE_F32) { MR_FAIL(15); return -1; }
+    { const int qs[6] = {i, ia, ig, is, ic, id}; for (int q : qs) if (skipped(g->nodes[q])) { MR_FAIL(16); return -1; } }
+    // probabilities, picked values and their sum are dead after these six nodes unless something further down reads them: ggml-alloc then hands their memory
+    // to each other and to later tensors, so they are only written when they have readers (the order and the weights always are)
+    bool need_p = false, need_g = false, need_s = false;
+    for (int q = id + 1; q < g->n_nodes; ++q)
+        for (int k = 0; k < GGML_MAX_SRC; ++k) {
+            const ggml_tensor * r = view_root(g->nodes[q]->src[k]);
+            need_p = need_p || (r && r == sm); need_g = need_g || (r && r == gr); need_s = need_s || (r && r == su);
+        }
+    const ggml_tensor * outs[5] = {need_p ? sm : nullptr, as, need_g ? gr : nullptr, need_s ? su : nullptr, dv};
+    for (int a = 0; a < 5; ++a) for (int b = a + 1; b < 5; ++b)
+        if (outs[a] && outs[b] && !(a == 2 && b == 4) && ranges_overlap(outs[a], outs[b])) { MR_FAIL(17); return -1; }
+    // a warp reads its token's logits before it writes anything, but with several tokens another warp may already be writing: then no output may sit on the
+    // logits (ggml-alloc reuses the memory of the dead logits / probabilities for the later tensors), except the probabilities of an in-place softmax
+    if (n_tok > 1)
+        for (int a = 0; a < 5; ++a)
+            if (outs[a] && !(a == 0 && sm->data == sm->src[0]->data) && ranges_overlap(sm->src[0], outs[a])) { MR_FAIL(18); return -1; }
+    float lo, hi; memcpy(&lo, cl->op_params, sizeof(float)); memcpy(&hi, (const float *) cl->op_params + 1, sizeof(float));
+    const b200_tensor tl = bt(sm->src[0]), tp = bt(sm), to = bt(as), tg = bt(gr), ts = bt(su), tw = bt(dv);
+    if (b200_op_moe_route(&tl, need_p ? &tp : nullptr, &to, need_g ? &tg : nullptr, need_s ? &ts : nullptr, &tw, (int) n_used, lo, hi, bc->stream) != 0) {
+        GGML_LOG_ERROR("ggml-b200: fused MoE router (%s) failed: %s\n", dv->name, b200_last_error()); st = GGML_STATUS_FAILED;
+    }
+    return id;
+}
+
 enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
     static const bool fuse_on = env_on("GGML_B200_FUSE") && glue_on();
     std::vector<char> done((size_t) cgraph->n_nodes, 0);          // matmuls hoisted into an earlier group
@@ -1309,6 +1361,11 @@ enum ggml_status graph_issue(backend_ctx * bc, ggml_cgraph * cgraph) {
             const int used = try_fuse_norm(bc, cgraph, i, st);
             if (st != GGML_STATUS_SUCCESS) return st;
             if (used > 0) { i += used - 1; continue; }
+        }
+        if (fuse_on && node->op == GGML_OP_SOFT_MAX && !node->src[1]) {
+            const int id = try_fuse_moe_route(bc, cgraph, i, st);
+            if (st != GGML_STATUS_SUCCESS) return st;
+            if (id > i) { i = id; continue; }
         }
         if (fuse_on && node->op == GGML_OP_GLU) {
             const int im = try_fuse_glu(bc, cgraph, i, st);

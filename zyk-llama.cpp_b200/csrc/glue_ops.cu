@@ -1031,6 +1031,34 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const T4 k, const T4 
     }
 }
 
+// ---- the router of build_moe_ffn as ONE launch (softmax gating, weights renormalised over the used experts): SOFT_MAX -> ARGSORT (descending) ->
+// GET_ROWS of the probabilities at the first n_used indices -> SUM_ROWS -> CLAMP -> DIV. One warp per token, lane e = expert e (n_expert <= 32);
+// every intermediate tensor of the six nodes is written, so the rest of the graph reads them as if the nodes had run one by one.
+__global__ void __launch_bounds__(128) moe_route_kernel(const float * __restrict__ logits, float * __restrict__ probs, int * __restrict__ order, float * __restrict__ picked,
+                                                        float * __restrict__ sum, float * __restrict__ weights, int n_expert, int n_used, int n_tok, float lo, float hi) {
+    pdl_launch_dependents(); pdl_wait();
+    const int lane = threadIdx.x & 31;
+    const int t = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (t >= n_tok) return;
+    const bool live = lane < n_expert;
+    const float x = live ? logits[(long long) t * n_expert + lane] : -INFINITY;
+    float mx = x;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const float e = live ? expf(x - mx) : 0.0f;
+    const float p = e * (1.0f / warp_sum(e));
+    if (live && probs) probs[(long long) t * n_expert + lane] = p;
+    int rank = 0;                                            // position of this expert in descending order (ties: lower index first)
+    for (int j = 0; j < n_expert; ++j) { const float pj = __shfl_sync(0xffffffffu, p, j); rank += (pj > p || (pj == p && j < lane)) ? 1 : 0; }
+    if (live) order[(long long) t * n_expert + rank] = lane;
+    const bool used = live && rank < n_used;
+    if (used && picked) picked[(long long) t * n_used + rank] = p;
+    float s = warp_sum(used ? p : 0.0f);
+    s = fminf(fmaxf(s, lo), hi);
+    if (lane == 0 && sum) sum[t] = s;
+    if (used) weights[(long long) t * n_used + rank] = p / s;
+}
+
 } // namespace
 
 extern "C" {
@@ -1102,6 +1130,23 @@ int b200_op_attn_prefill(const b200_tensor * k, const b200_tensor * q, const b20
     const dim3 grid(blocks_for(n_tok, 64), (unsigned) n_head);
     if (hd == 128) B200_CHECK(b200_launch(attn_prefill_kernel<128>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
     else           B200_CHECK(b200_launch(attn_prefill_kernel<64>, grid, dim3(128), 0, (cudaStream_t) stream, glue_pdl(), t4(k), t4(q), mask ? t4(mask) : t4(q), mask ? 1 : 0, t4(v), (float *) dst->data, scale));
+    return 0;
+}
+
+int b200_op_moe_route(const b200_tensor * logits, const b200_tensor * probs, const b200_tensor * order, const b200_tensor * picked, const b200_tensor * sum,
+                      const b200_tensor * weights, int n_used, float clamp_lo, float clamp_hi, b200_stream_t stream) {
+    B200_REQUIRE(logits && order && weights && logits->data && order->data && weights->data && (!probs || probs->data) && (!picked || picked->data) && (!sum || sum->data), "b200_op_moe_route: null tensor");
+    const long long n_expert = logits->ne[0], n_tok = logits->ne[1];
+    B200_REQUIRE(logits->type == B200_TYPE_F32 && (!probs || probs->type == B200_TYPE_F32) && order->type == B200_TYPE_I32 && (!picked || picked->type == B200_TYPE_F32) &&
+                 (!sum || sum->type == B200_TYPE_F32) && weights->type == B200_TYPE_F32, "b200_op_moe_route: f32 tensors, i32 order");
+    B200_REQUIRE(n_expert >= 1 && n_expert <= 32 && n_used >= 1 && n_used <= n_expert && n_tok >= 1 && n_tok < (1ll << 30) && logits->ne[2] == 1 && logits->ne[3] == 1,
+                 "b200_op_moe_route: %lld experts / %d used / %lld tokens", n_expert, n_used, n_tok);
+    B200_REQUIRE(contiguous_f(logits, 4) && (!probs || (contiguous_f(probs, 4) && nelem(probs) == n_expert * n_tok)) && contiguous_f(order, 4) &&
+                 (!picked || (contiguous_f(picked, 4) && nelem(picked) == n_used * n_tok)) && (!sum || (contiguous_f(sum, 4) && nelem(sum) == n_tok)) && contiguous_f(weights, 4) &&
+                 nelem(order) == n_expert * n_tok && nelem(weights) == n_used * n_tok,
+                 "b200_op_moe_route: contiguous tensors of the shapes of the six nodes");
+    B200_CHECK(b200_launch(moe_route_kernel, dim3(blocks_for(n_tok, 4)), dim3(128), 0, (cudaStream_t) stream, glue_pdl(), (const float *) logits->data, probs ? (float *) probs->data : nullptr,
+                           (int *) order->data, picked ? (float *) picked->data : nullptr, sum ? (float *) sum->data : nullptr, (float *) weights->data, (int) n_expert, n_used, (int) n_tok, clamp_lo, clamp_hi));
     return 0;
 }
 
