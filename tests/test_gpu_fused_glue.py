@@ -162,3 +162,37 @@ def test_attn_prefill_matches_fp32_attention(b200, hd, n_tok, n_kv, masked):
     assert torch.isfinite(out).all()
     err = float(((out - want) ** 2).sum() / (want ** 2).sum())
     assert err < 1e-5, f"nmse {err:.3e}"
+
+
+@pytest.mark.parametrize("n_expert,n_used,n_tok", [(8, 2, 1), (8, 2, 33), (32, 4, 7), (5, 5, 3)])
+@pytest.mark.parametrize("optional", [True, False])
+def test_moe_route_matches_the_six_ops(b200, n_expert, n_used, n_tok, optional):
+    """b200_op_moe_route against torch for the node sequence of build_moe_ffn: softmax, descending argsort, the probabilities of the first n_used
+    experts, their clamped sum and the renormalised weights; with and without the optional (dead) intermediates."""
+    import torch
+    b = b200
+    b.lib.b200_op_moe_route.restype = C.c_int
+    torch.manual_seed(n_expert * 100 + n_tok)
+    dev = "cuda"
+    logits = torch.randn((n_tok, n_expert), device=dev) * 2
+    probs = torch.full((n_tok, n_expert), float("nan"), device=dev)
+    order = torch.full((n_tok, n_expert), -1, dtype=torch.int32, device=dev)
+    picked = torch.full((n_tok, n_used), float("nan"), device=dev)
+    ssum = torch.full((n_tok,), float("nan"), device=dev)
+    weights = torch.full((n_tok, n_used), float("nan"), device=dev)
+    tl, tp, to = _t(logits, F32), _t(probs, F32), _t(order, I32)
+    tg, ts, tw = _t(picked, F32, ne=[1, n_used, n_tok]), _t(ssum, F32, ne=[1, n_tok]), _t(weights, F32)
+    lo, hi = 6.103515625e-5, float("inf")
+    _ok(b, b.lib.b200_op_moe_route(C.byref(tl), C.byref(tp) if optional else None, C.byref(to), C.byref(tg) if optional else None, C.byref(ts) if optional else None,
+                                   C.byref(tw), n_used, C.c_float(lo), C.c_float(hi), None))
+    torch.cuda.synchronize()
+    p = torch.softmax(logits, dim=-1)
+    idx = torch.argsort(p, dim=-1, descending=True, stable=True)
+    top = torch.gather(p, 1, idx[:, :n_used])
+    s = top.sum(dim=-1).clamp(lo, hi)
+    assert torch.equal(order.long(), idx)
+    assert torch.allclose(weights, top / s[:, None], rtol=1e-5, atol=1e-7)
+    if optional:
+        assert torch.allclose(probs, p, rtol=1e-5, atol=1e-7) and torch.allclose(picked, top, rtol=1e-5, atol=1e-7) and torch.allclose(ssum, s, rtol=1e-5)
+    else:
+        assert torch.isnan(probs).all() and torch.isnan(picked).all() and torch.isnan(ssum).all()
