@@ -179,7 +179,7 @@ def plugin_e2e(steps: int, warmup: int, pp: int, pp_steps: int):
         return {"error": str(e)[:300]}
 
 
-def llama_bench_leg(model: str, reps: int = 3):
+def llama_bench_leg(model: str, reps: int = 5):
     """The reference's own llama-bench binary (compiled from /root/reference into oracle/_ref, unmodified) on a random-init GGUF of the headline
     model (tools/make_gguf.py), with this repository's plugin as its GPU device: the WHOLE llama graph (matmuls, norms, rope, KV cache, attention)
     on the B200, pp512 and tg128 as llama-bench defines them. The file lives in a temporary directory for the duration of the call."""
