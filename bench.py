@@ -383,6 +383,7 @@ def main():
         achieved = bytes_tok / world / (ms_step * 1e-3) / 1e9
         out.update({"tg": {"value": 1e3 / ms_step, "unit": "tokens/s", "ms_per_step": ms_step, "steps": steps,
                            "decode_kernel": ("persistent chain: one launch per token, %d dependent MUL_MAT groups" % info["n_groups"]) if persistent
+                                            else "gemv_chain_kernel, one launch per MUL_MAT group (chains of a single group; CUDA graph replay)" if getattr(chain, "group_chains", None) is not None
                                             else "one launch per MUL_MAT group (CUDA graph replay)" if chain.graph is not None else "one launch per MUL_MAT group (eager)"},
                     "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                                  "frac_of_8tbs": achieved / 8000.0, "algorithmic_bytes": bytes_tok / world, "peak_source": peak_src}})
@@ -479,10 +480,22 @@ def main():
         ms2, _ = time_chain(ch2, args.steps, warmup)
         ach2 = bytes_tok / (ms2 * 1e-3) / 1e9
         tg_per_group = {"value": 1e3 / ms2, "unit": "tokens/s", "ms_per_step": ms2, "decode_kernel": "one launch per MUL_MAT group (gemv_fused_kernel / act_quant + gemv_kernel), CUDA graph replay",
-                        "roofline_frac": ach2 / peaks["hbm_gbs"], "note": "what graph_compute reaches on a real llama.cpp graph (groups separated by non-MUL_MAT ops)"}
+                        "roofline_frac": ach2 / peaks["hbm_gbs"], "note": "the per-node GEMV kernels, one launch per group of nodes that share X"}
         ch2.close()
         del ch2
         torch.cuda.empty_cache()
+        # what the plugin does on a real llama.cpp graph since round 2: every group is its own ONE-group chain-kernel launch
+        try:
+            ch3 = MatMulChain(ops, 1, device=local, persistent="groups")
+            ms3, _ = time_chain(ch3, args.steps, warmup)
+            tg_per_group["group_chains"] = {"value": 1e3 / ms3, "unit": "tokens/s", "ms_per_step": ms3, "roofline_frac": bytes_tok / (ms3 * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                                            "decode_kernel": "gemv_chain_kernel, one launch per MUL_MAT group (a chain of a single group), CUDA graph replay",
+                                            "note": "what graph_compute reaches on a real llama.cpp graph (groups separated by non-MUL_MAT ops)"}
+            ch3.close()
+            del ch3
+            torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001
+            tg_per_group["group_chains"] = {"error": str(e)[:200]}
 
     # ---- pp: N = 512 ubatch through the same nodes -----------------------------------------------------------
     pp = bench_pp(ops, args.model, args.pp_steps) if args.pp > 0 else None

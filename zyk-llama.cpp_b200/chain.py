@@ -100,11 +100,23 @@ class MatMulChain:
         self.calls = self._build_calls()
         # decode on one GPU: the whole pass as ONE persistent launch (b200_chain_*), when every node is eligible
         self.decode_chain = None
+        self.group_chains = None      # persistent == "groups": one single-group chain per call (what the plugin does on a real llama.cpp graph)
         # "auto": where it is the faster path today (measured on B200: Q4_K / Q6_K models 618 -> 794 tokens/s; 1B Q4_0 2584 -> 2620 with the
         # unit-per-lane Q4_0 path; IQ4_XS 464 chain vs 476 per node and Q8_0 440 vs 577 stay on the per-node kernels)
         if persistent == "auto":
             persistent = all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K, B.Types.Q4_0) for o in ops)
-        if persistent and world == 1 and all(c[0] is B.lib.b200_mul_mat_group for c in self.calls):
+            # (IQ4_XS files: per node 486, one-group chains 452, whole-token chain 464 tokens/s on this MUL_MAT-only pass; in a real graph the plugin's one-group
+            # chains for the k = 4096 groups win: llama-bench tg128 298 -> 310)
+        if persistent == "groups" and world == 1:
+            # every group that the chain kernel takes becomes its own one-group chain launch; the others keep their per-node launch
+            self.group_chains = []
+            for c in self.calls:
+                ch = None
+                if c[0] is B.lib.b200_mul_mat_group and n <= 4 and B.DecodeChain.supported([list(c[1])]) and \
+                        all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K, B.Types.IQ4_XS) for o in c[2]):
+                    ch = B.DecodeChain(device, [list(c[1])])
+                self.group_chains.append(ch)
+        elif persistent and world == 1 and all(c[0] is B.lib.b200_mul_mat_group for c in self.calls):
             groups = [list(c[1]) for c in self.calls]
             if B.DecodeChain.supported(groups):
                 self.decode_chain = B.DecodeChain(device, groups)
@@ -179,6 +191,9 @@ class MatMulChain:
         if self.fused_exchange:
             B._check(B.lib.b200_row_gather_step(self.arena.step_ptr, h))
         for i, (fn, a, ops, ys, _ws) in enumerate(self.calls):
+            if self.group_chains is not None and self.group_chains[i] is not None:
+                self.group_chains[i].launch(self.stream)
+                continue
             if self.fused_exchange and i in self.mid_waits:
                 B._check(B.lib.b200_row_gather_wait(C.byref(self.mid_waits[i]), h))
             if fn is B.lib.b200_mul_mat_gather:
@@ -225,6 +240,13 @@ class MatMulChain:
             self.arena.close()
             dist.barrier(group=self.rowsplit.group)
             self.arena = None
+        if self.group_chains is not None:
+            self.stream.synchronize()
+            self.graph = None
+            for ch in self.group_chains:
+                if ch is not None:
+                    ch.close()
+            self.group_chains = None
 
     def weight_bytes_resident(self) -> int:
         return sum(w.numel() for w in self.weights)
