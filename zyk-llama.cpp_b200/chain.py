@@ -102,7 +102,7 @@ class MatMulChain:
         self.decode_chain = None
         self.group_chains = None      # persistent == "groups": one single-group chain per call (what the plugin does on a real llama.cpp graph)
         # "auto": where it is the faster path today (measured on B200: Q4_K / Q6_K models 618 -> 794 tokens/s; 1B Q4_0 2584 -> 2620 with the
-        # unit-per-lane Q4_0 path; IQ4_XS 464 chain vs 476 per node and Q8_0 440 vs 577 stay on the per-node kernels)
+        # unit-per-lane Q4_0 path; IQ4_XS 464 chain vs 476 per node and Q8_0 550 (412 before its unit-per-lane path) vs 583 stay on the per-node kernels)
         if persistent == "auto":
             persistent = all(o.type in (B.Types.Q4_K, B.Types.Q5_K, B.Types.Q6_K, B.Types.Q4_0) for o in ops)
             # (IQ4_XS files: per node 486, one-group chains 452, whole-token chain 464 tokens/s on this MUL_MAT-only pass; in a real graph the plugin's one-group

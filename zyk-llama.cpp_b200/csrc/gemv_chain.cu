@@ -555,7 +555,30 @@ __device__ __forceinline__ void unit_q40(uint32_t stage, int nunits, int u, int 
     }
 }
 
-// ---- Q8_0 (and shapes the paths above do not take): eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ----
+// ---- Q8_0, one 256-element unit per lane: QS 256 B | D 16 B per unit. Lane b takes its sixteen 16-byte chunks in the order t ^ rho8(b): the weight chunks of
+// eight neighbouring lanes always fall into eight different bank groups, the activation chunks collide two ways in half of the steps (no order does
+// better with the xpos placement: exhaustive search). Chunks 2 i and 2 i + 1 are one 32-block: ggml_vec_dot_q8_0_q8_0 (ggml-cpu/quants.c:305-335).
+__device__ __forceinline__ int lane_rho8(int b) { return (int) ((0x54672318u >> (4 * (b & 7))) & 0xfu); }
+template <int NCOLS>
+__device__ __forceinline__ void unit_q80(uint32_t stage, int nunits, int u, int b, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
+    const uint32_t qs = stage + (uint32_t) (u * 256), dp = stage + (uint32_t) (nunits * 256 + u * 16);
+    const int rho = lane_rho8(b);
+#pragma unroll
+    for (int tp = 0; tp < 8; ++tp) {
+        const int j0 = (2 * tp) ^ rho, j1 = j0 ^ 1, blk = j0 >> 1;
+        const uint4 w0 = lds16(qs + (uint32_t) (j0 << 4)), w1 = lds16(qs + (uint32_t) (j1 << 4));
+        const float dw = half_bits_to_float(lds2(dp + (uint32_t) (blk << 1)));
+        const uint32_t p0 = (uint32_t) xpos_rt(j0) << 4, p1 = (uint32_t) xpos_rt(j1) << 4;
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            const uint32_t xc = xb + (uint32_t) (c * x_col_stride);
+            const uint4 x0 = lds16(xc + p0), x1 = lds16(xc + p1);
+            acc[c] += (ldsf(xc + XU_D + (uint32_t) (blk << 2)) * dw) * (float) (dot16(w0, x0) + dot16(w1, x1));
+        }
+    }
+}
+
+// ---- shapes the paths above do not take: eight lanes per 256 elements, fragments of gemv_frag.cuh filled from shared memory ----
 template <int TYPE> __device__ __forceinline__ void wfrag_lds(WFrag<TYPE> & f, uint32_t stage, int nunits, int u, int g);
 template <> __device__ __forceinline__ void wfrag_lds<B200_TYPE_IQ4_XS>(WFrag<B200_TYPE_IQ4_XS> & f, uint32_t stage, int nunits, int u, int g) {
     f.q = lds16(stage + (uint32_t) (u * 128 + 16 * g));
@@ -633,13 +656,14 @@ __device__ __forceinline__ void item_lanes8(uint32_t stage, int nrows, int upr, 
     }
 }
 
-constexpr int LU_Q4K = 0, LU_Q6K = 1, LU_Q5K = 2, LU_IQ4XS = 3, LU_Q40 = 4;       // block-per-lane formats
+constexpr int LU_Q4K = 0, LU_Q6K = 1, LU_Q5K = 2, LU_IQ4XS = 3, LU_Q40 = 4, LU_Q80 = 5;       // block-per-lane formats
 template <int Q6, int NCOLS>
 __device__ __forceinline__ void lane_unit(uint32_t stage, int nunits, int u, int b, uint32_t xb, int x_col_stride, float (&acc)[NCOLS]) {
     if constexpr (Q6 == LU_Q6K)        unit_q6k<NCOLS>(stage, nunits, u, xb, x_col_stride, acc);
     else if constexpr (Q6 == LU_Q5K)   unit_q5k<NCOLS>(stage + (uint32_t) u * 176, xb, x_col_stride, acc);
     else if constexpr (Q6 == LU_IQ4XS) unit_iq4xs<NCOLS>(stage, nunits, u, b, xb, x_col_stride, acc);
     else if constexpr (Q6 == LU_Q40)   unit_q40<NCOLS>(stage, nunits, u, b, xb, x_col_stride, acc);
+    else if constexpr (Q6 == LU_Q80)   unit_q80<NCOLS>(stage, nunits, u, b, xb, x_col_stride, acc);
     else                               unit_q4k<NCOLS>(stage + (uint32_t) u * 144, xb, x_col_stride, acc);
 }
 template <int NCOLS, int Q6 = LU_Q4K>
@@ -866,7 +890,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 if (a.lanes8) item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
                 else          item_q4k<NCOLS, LU_Q40>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else {
-                item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+                if (a.lanes8) item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+                else          item_q4k<NCOLS, LU_Q80>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_bar(grp, st));     // this warp is done with the stage (and its descriptor)
@@ -1374,7 +1399,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
                     it.nrows = (int) (r1 - r < per ? r1 - r : per); it.type = type;
                     it.y = M.y + r; it.ldy = M.ldy;
                     it.tag = feed[g] == mi ? d_tags + (size_t) (g % 3) * ncols * tmax + lo_of(idx + mi) + r : nullptr;
-                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || map0 >= 0 || (!lanes8 && (type == B200_TYPE_IQ4_XS || type == B200_TYPE_Q4_0)), it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
+                    { const ItemPlan pl = plan_item(type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || map0 >= 0 || (!lanes8 && (type == B200_TYPE_IQ4_XS || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0)), it.nrows, upr); it.segs = pl.segs; it.S = pl.S; }
                     if (P.xreg) {
                         // `S` carries the rotation: which warp gets the item's first task, so that tasks go round the warps across items
                         if (it.segs == 1) { const int rp = 32 / upr; it.S = rot[vc] % CX_NW; rot[vc] = (rot[vc] + (it.nrows + rp - 1) / rp) % CX_NW; }

@@ -988,6 +988,7 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     // the per-node GEMV in a real graph: llama-bench 8B tg128 353 -> 386); GGML_B200_CHAIN_SINGLE=0: only runs of two or more groups
     static const bool chain_single = env_on("GGML_B200_CHAIN_SINGLE");
     static const bool chain_q40 = [] { const char * e = getenv("GGML_B200_CHAIN_Q4_0"); return e && e[0] == '1'; }();
+    static const bool chain_q80 = [] { const char * e = getenv("GGML_B200_CHAIN_Q8_0"); return e && e[0] == '1'; }();
     static const bool chain_iq4 = env_on("GGML_B200_CHAIN_IQ4_XS");      // IQ4_XS groups too (llama-bench 8B IQ4_XS tg128 298 -> 310); Q4_0 / Q8_0 stay per node (1B Q4_0: 1059 vs 988)
     if (args.size() < 2 && !(chain_single && args[0].n <= 4)) return i;                       // a single node: the ordinary path
     // workspace for the group launches (the chain does not need one)
@@ -997,7 +998,7 @@ int compute_decode_run(backend_ctx * bc, ggml_cgraph * cgraph, int i, enum ggml_
     for (auto & a : args) { a.workspace = bc->workspace; a.workspace_size = bc->workspace_size; }
 
     bool kquant = true;
-    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q5_K || a.type == B200_TYPE_Q6_K || (chain_q40 && a.type == B200_TYPE_Q4_0) || (chain_iq4 && a.type == B200_TYPE_IQ4_XS));
+    for (const auto & a : args) kquant = kquant && (a.type == B200_TYPE_Q4_K || a.type == B200_TYPE_Q5_K || a.type == B200_TYPE_Q6_K || (chain_q40 && a.type == B200_TYPE_Q4_0) || (chain_q80 && a.type == B200_TYPE_Q8_0) || (chain_iq4 && a.type == B200_TYPE_IQ4_XS));
     if (chain_on && kquant && args[0].n <= 4 && (sizes.size() >= 2 || chain_single) && b200_chain_supported(args.data(), sizes.data(), (int) sizes.size())) {
         b200_chain_t chain = nullptr;
         for (auto & c : bc->chains)
