@@ -236,6 +236,10 @@ B200_API size_t b200_mul_mat_id_workspace(int type, int64_t k, int64_t n_used, i
  * stays on the per-pair GEMV. args->algo: 0 auto, 1 GEMV, 2 GEMM. */
 B200_API size_t b200_mul_mat_id_workspace_ex(const b200_mul_mat_id_args * args);
 B200_API int    b200_mul_mat_id(const b200_mul_mat_id_args * args, b200_stream_t stream);
+/* MUL_MAT_ID whose activations are still to be gated (the GLU in front of ffn_down_exps), as b200_mul_mat_glu: b rows packed token by token, at most 8
+   (token, slot) pairs */
+B200_API int    b200_mul_mat_id_glu(const b200_mul_mat_id_args * args, const float * b2, int64_t b2_row_stride, int32_t glu_op, int32_t swapped,
+                                    b200_stream_t stream);
 
 /* ---- (e) multi-GPU row split ----------------------------------------------------------------
  * rows [*row_lo, *row_hi) of an m-row weight matrix owned by `rank` of `world` (tile rounded,

@@ -1277,6 +1277,27 @@ int try_fuse_glu(backend_ctx * bc, ggml_cgraph * g, int i, enum ggml_status & st
     const int im = next_real(g, i);
     if (im < 0) return -1;
     const ggml_tensor * M = g->nodes[im];
+    if (M->op == GGML_OP_MUL_MAT_ID && M->src[1] == G && !skipped(M)) {
+        // ffn_down_exps: per-pair GEMV with the gate in its quantiser (decode: at most 8 (token, slot) pairs)
+        const ggml_tensor * as = M->src[0], * ids = M->src[2], * a = G->src[0], * b = G->src[1];
+        const int64_t n_used = ids->ne[0], n_tokens = ids->ne[1];
+        if (n_used * n_tokens > 8 || G->ne[1] != n_used || in_split_buffer(as) || !ggml_is_contiguous(G) || !ggml_are_same_shape(a, b) || a->ne[0] != G->ne[0] ||
+            a->nb[0] != sizeof(float) || b->nb[0] != sizeof(float) || a->nb[2] != a->nb[1] * a->ne[1] || b->nb[2] != b->nb[1] * b->ne[1] || a->ne[3] != 1) return -1;
+        b200_mul_mat_id_args q = {};
+        q.type = (int32_t) as->type; q.layout = weight_layout(as);
+        q.m = as->ne[1]; q.k = as->ne[0]; q.n_as = as->ne[2]; q.n_used = n_used; q.nb1 = G->ne[1]; q.n_tokens = n_tokens;
+        q.as = as->data; q.as_expert_stride = (int64_t) as->nb[2];
+        q.b = (const float *) a->data; q.b_row_stride = (int64_t) (a->nb[1] / sizeof(float)); q.b_token_stride = (int64_t) (a->nb[2] / sizeof(float));
+        q.ids = (const int32_t *) ids->data; q.ids_row_stride = (int64_t) (ids->nb[1] / sizeof(int32_t));
+        q.y = (float *) M->data; q.y_row_stride = (int64_t) (M->nb[1] / sizeof(float)); q.y_token_stride = (int64_t) (M->nb[2] / sizeof(float));
+        const size_t need = b200_mul_mat_id_workspace_ex(&q);
+        if (!backend_reserve(bc, need)) { st = GGML_STATUS_ALLOC_FAILED; return im; }
+        q.workspace = bc->workspace; q.workspace_size = bc->workspace_size; q.flavour = B200_Q8_X86; q.flags = mm_flags(); q.algo = 1;
+        if (b200_mul_mat_id_glu(&q, (const float *) b->data, (int64_t) (b->nb[1] / sizeof(float)), ggml_get_op_params_i32(G, 0), ggml_get_op_params_i32(G, 1), bc->stream) != 0) {
+            GGML_LOG_ERROR("ggml-b200: fused glu + MUL_MAT_ID (%s) failed: %s\n", M->name, b200_last_error()); st = GGML_STATUS_FAILED;
+        }
+        return im;
+    }
     if (!plain_mul_mat(M) || M->src[1] != G || M->src[1]->ne[1] > 8) return -1;
     const ggml_tensor * a = G->src[0], * b = G->src[1];
     if (a->ne[2] != 1 || a->ne[3] != 1 || !ggml_are_same_shape(a, b) || a->ne[0] != G->ne[0] || a->nb[0] != sizeof(float) || b->nb[0] != sizeof(float) ||

@@ -386,7 +386,18 @@ size_t b200_mul_mat_id_workspace_ex(const b200_mul_mat_id_args * a) {
     return v > g ? v : g;
 }
 
-int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
+static int mul_mat_id_impl(const b200_mul_mat_id_args * a, b200_stream_t stream, const ActGlu * glu);
+int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) { return mul_mat_id_impl(a, stream, nullptr); }
+// Y = W_expert * glu(b, b2) per (token, slot): the per-pair GEMV path with the gate folded into the activation quantiser (decode: few pairs)
+int b200_mul_mat_id_glu(const b200_mul_mat_id_args * a, const float * b2, int64_t b2_row_stride, int32_t glu_op, int32_t swapped, b200_stream_t stream) {
+    B200_REQUIRE(a && b2, "b200_mul_mat_id_glu: null pointer");
+    B200_REQUIRE(glu_op >= 0 && glu_op <= 2, "b200_mul_mat_id_glu: op %d (0 reglu, 1 geglu, 2 swiglu)", glu_op);
+    B200_REQUIRE(a->n_tokens * a->n_used <= 8 && a->algo != 2 && !(a->flags & B200_MM_X_PREQUANTISED) && a->b_token_stride == a->nb1 * a->b_row_stride,
+                 "b200_mul_mat_id_glu: decode shapes (at most 8 pairs, b rows packed token by token) on the per-pair GEMV path only");
+    const ActGlu g = {b2, b2_row_stride, (int) glu_op, (int) swapped};
+    return mul_mat_id_impl(a, stream, &g);
+}
+static int mul_mat_id_impl(const b200_mul_mat_id_args * a, b200_stream_t stream, const ActGlu * glu) {
     cudaStream_t s = (cudaStream_t) stream;
     B200_REQUIRE(a && a->as && a->b && a->ids && a->y, "b200_mul_mat_id: null pointer");
     B200_REQUIRE(b200_type_is_weight(a->type), "b200_mul_mat_id: unsupported weight type %d", a->type);
@@ -407,7 +418,7 @@ int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
         const bool fast_id = planes_fast_path(a->type, a->layout, a->m, a->k, a->as, 0) && (a->as_expert_stride % 16) == 0;
         const int64_t y_span = (a->n_tokens - 1) * a->y_token_stride + (a->n_used - 1) * a->y_row_stride + a->m;
         const bool strides_ok = a->y_token_stride >= 0 && a->y_row_stride >= 0 && a->b_row_stride >= 0 && a->b_token_stride >= 0;
-        const bool want = a->algo != 1 && fast_id && strides_ok && b200_gemm_moe_wants(a->type, a->m, a->k, a->n_as, a->n_used, a->n_tokens, y_span, a->algo == 2);
+        const bool want = !glu && a->algo != 1 && fast_id && strides_ok && b200_gemm_moe_wants(a->type, a->m, a->k, a->n_as, a->n_used, a->n_tokens, y_span, a->algo == 2);
         const bool room = a->workspace_size >= b200_gemm_moe_workspace(a->type, a->m, a->k, a->n_as, a->n_tokens * a->n_used);
         B200_REQUIRE(a->algo != 2 || (want && room), "b200_mul_mat_id: GEMM forced but the call is not eligible (layout / strides / workspace %zu bytes, see b200_mul_mat_id_workspace_ex)",
                      a->workspace_size);
@@ -419,7 +430,7 @@ int b200_mul_mat_id(const b200_mul_mat_id_args * a, b200_stream_t stream) {
     // these rows in the workspace (ffn_gate_exps / ffn_up_exps read the same activations)
     if (a->flags & B200_MM_X_PREQUANTISED) {
     } else if (a->b_token_stride == a->nb1 * a->b_row_stride) {
-        int rc = b200_act_quant_planes(act, a->flavour, a->b, a->b_row_stride, pl, rows, a->k, s, pdl);
+        int rc = b200_act_quant_planes(act, a->flavour, a->b, a->b_row_stride, pl, rows, a->k, s, pdl, glu);
         if (rc) return rc;
     } else {
         for (int64_t t = 0; t < a->n_tokens; ++t) {
