@@ -1147,7 +1147,26 @@ enum ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgr
         GGML_LOG_WARN("ggml-b200: graph replay failed (%s), running the nodes one by one\n", b200_last_error());
         b200_graph_destroy(hit->exec); hit->exec = nullptr; hit->bad = true;
     }
-    if (hit->bad || ++hit->seen < 2) return graph_issue(bc, cgraph);      // first sight: eager (allocations, chains, layout changes happen here)
+    if (hit->bad) return graph_issue(bc, cgraph);
+    if (++hit->seen < 2) {
+        // first sight: eager (allocations, chains, layout changes happen here) -- and, right behind it, the same launch sequence once more under stream capture
+        // (nothing executes), so that the SECOND call of this graph is already a replay (GGML_B200_GRAPH_EARLY=0: capture at the second call instead)
+        static const bool early = env_on("GGML_B200_GRAPH_EARLY");
+        const std::vector<uint64_t> key_copy = hit->key;
+        const enum ggml_status st = graph_issue(bc, cgraph);
+        if (st != GGML_STATUS_SUCCESS || !early) return st;
+        hit = nullptr;                                                  // (the eager pass may have dropped the cache: a grown workspace invalidates every capture)
+        for (auto & c : bc->graphs) if (c.key == key_copy) { hit = &c; break; }
+        if (!hit) { bc->graphs.emplace_back(); hit = &bc->graphs.back(); hit->key = key_copy; hit->seen = 1; hit->stamp = ++bc->graph_stamp; }
+        if (b200_graph_begin(bc->stream) != 0) return st;
+        bc->capturing = true;
+        const enum ggml_status st2 = graph_issue(bc, cgraph);
+        bc->capturing = false;
+        b200_graph_t exec = b200_graph_end(bc->stream);
+        if (st2 == GGML_STATUS_SUCCESS && exec) hit->exec = exec;
+        else { if (exec) b200_graph_destroy(exec); }                    // (no harm done: the second call tries again the old way)
+        return st;
+    }
     // second sight: capture the very same launch sequence
     if (b200_graph_begin(bc->stream) != 0) { hit->bad = true; return graph_issue(bc, cgraph); }
     bc->capturing = true;
