@@ -714,7 +714,7 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void cons_bar() { asm volatile("bar.sync 3, %0;" :: "n"(CH_CONSUMERS) : "memory"); }
 
 // KS = which item kinds are compiled in: 0 Q4_K / Q6_K one block per lane (what the 8B Q4_K_M file needs), 1 + Q5_K (70B) and Q6_K rows that are not a
-// multiple of 8 units, 2 + Q4_0 / Q8_0 / IQ4_XS. Code a chain never runs still costs it: with every item kind in one kernel the 8B token runs at 770
+// multiple of 8 units, 2 + Q4_0 / IQ4_XS, 3 + Q8_0. Code a chain never runs still costs it: with every item kind in one kernel the 8B token runs at 770
 // tokens/s, 785 with Q4_K / Q5_K / Q6_K, 813 with KS = 0. (The effect is ptxas scheduling, not size as such: compiling the row-split and timeline branches
 // out as well gave 760.)
 template <int NCOLS, int KS>
@@ -890,8 +890,10 @@ __global__ void __launch_bounds__(CH_THREADS, 1) gemv_chain_kernel(const ChainAr
                 if (a.lanes8) item_lanes8<B200_TYPE_Q4_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
                 else          item_q4k<NCOLS, LU_Q40>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
             } else {
-                if (a.lanes8) item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
-                else          item_q4k<NCOLS, LU_Q80>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
+                if constexpr (KS >= 3) {       // (its own instantiation: in the same kernel the unit-per-lane Q8_0 code cost the Q4_0 path 8 %)
+                    if (a.lanes8) item_lanes8<B200_TYPE_Q8_0, NCOLS>(stage, nrows, upr, xs, x_col_stride, nd.act_block, pl, part, a.max_units, out, first, lane);
+                    else          item_q4k<NCOLS, LU_Q80>(stage, nrows, upr, xs, x_col_stride, pl, part, a.max_units, out, first, lane, q4_rp, q4_sub, q4_b);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_bar(grp, st));     // this warp is done with the stage (and its descriptor)
@@ -1276,7 +1278,7 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     { int total = 0; for (int g = 0; g < n_groups; ++g) total += group_sizes[g];
       for (int i = 0; i < total; ++i) {
           const int t = nodes[i].type;
-          const int need = (t == B200_TYPE_Q4_K || (t == B200_TYPE_Q6_K && q6_swizzled_shape(nodes[i]))) ? 0 : (t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K) ? 1 : 2;
+          const int need = (t == B200_TYPE_Q4_K || (t == B200_TYPE_Q6_K && q6_swizzled_shape(nodes[i]))) ? 0 : (t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K) ? 1 : t == B200_TYPE_Q8_0 ? 3 : 2;
           kset = need > kset ? need : kset;
       } }
     if (split && (world < 2 || world > B200_MAX_PEERS || split->rank < 0 || split->rank >= world || !split->scratch || !split->row_lo || !split->m_full ||
@@ -1491,16 +1493,20 @@ b200_chain_t b200_chain_create_split(int device, const b200_mul_mat_args * nodes
     if (c->xreg) e = CX_NW == 12 ? cudaFuncSetAttribute(gemv_chainx_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                  : cudaFuncSetAttribute(gemv_chainx_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem);
     else switch (ncols) {
-        case 1: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+        case 1: e = kset == 3 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
                         kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                   : cudaFuncSetAttribute(gemv_chain_kernel<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        case 2: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+        case 2: e = kset == 3 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
                         kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                   : cudaFuncSetAttribute(gemv_chain_kernel<2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        case 3: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+        case 3: e = kset == 3 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
                         kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                   : cudaFuncSetAttribute(gemv_chain_kernel<3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
-        default: e = kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+        default: e = kset == 3 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
+                        kset == 2 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem) :
                         kset == 1 ? cudaFuncSetAttribute(gemv_chain_kernel<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem)
                                   : cudaFuncSetAttribute(gemv_chain_kernel<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, total_smem); break;
     }
@@ -1518,10 +1524,10 @@ int b200_chain_launch(b200_chain_t chain, b200_stream_t stream) {
     cudaError_t e;
     if (c->xreg) e = chainx_launch(*c, s);
     else switch (c->ncols) {
-        case 1: e = c->kset == 2 ? chain_launch_t<1, 2>(*c, s) : c->kset == 1 ? chain_launch_t<1, 1>(*c, s) : chain_launch_t<1, 0>(*c, s); break;
-        case 2: e = c->kset == 2 ? chain_launch_t<2, 2>(*c, s) : c->kset == 1 ? chain_launch_t<2, 1>(*c, s) : chain_launch_t<2, 0>(*c, s); break;
-        case 3: e = c->kset == 2 ? chain_launch_t<3, 2>(*c, s) : c->kset == 1 ? chain_launch_t<3, 1>(*c, s) : chain_launch_t<3, 0>(*c, s); break;
-        default: e = c->kset == 2 ? chain_launch_t<4, 2>(*c, s) : c->kset == 1 ? chain_launch_t<4, 1>(*c, s) : chain_launch_t<4, 0>(*c, s); break;
+        case 1: e = c->kset == 3 ? chain_launch_t<1, 3>(*c, s) : c->kset == 2 ? chain_launch_t<1, 2>(*c, s) : c->kset == 1 ? chain_launch_t<1, 1>(*c, s) : chain_launch_t<1, 0>(*c, s); break;
+        case 2: e = c->kset == 3 ? chain_launch_t<2, 3>(*c, s) : c->kset == 2 ? chain_launch_t<2, 2>(*c, s) : c->kset == 1 ? chain_launch_t<2, 1>(*c, s) : chain_launch_t<2, 0>(*c, s); break;
+        case 3: e = c->kset == 3 ? chain_launch_t<3, 3>(*c, s) : c->kset == 2 ? chain_launch_t<3, 2>(*c, s) : c->kset == 1 ? chain_launch_t<3, 1>(*c, s) : chain_launch_t<3, 0>(*c, s); break;
+        default: e = c->kset == 3 ? chain_launch_t<4, 3>(*c, s) : c->kset == 2 ? chain_launch_t<4, 2>(*c, s) : c->kset == 1 ? chain_launch_t<4, 1>(*c, s) : chain_launch_t<4, 0>(*c, s); break;
     }
     B200_CHECK(e);
     return 0;
