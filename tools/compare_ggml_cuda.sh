@@ -11,7 +11,8 @@ mkdir -p "$OUT"
 BIN="$ROOT/oracle/_ref/avx512vnni/test-backend-ops"
 grep -q avx512_vnni /proc/cpuinfo || { echo "host CPU lacks avx512_vnni: the prebuilt reference cannot run here"; exit 3; }
 TYPES='type_a=(q4_0|q8_0|q4_K|q6_K|iq4_xs),'
-for be in cuda b200; do
+# ONLY=b200: re-run this plugin only and reuse cuda_*.txt already in the output directory (the reference does not change)
+for be in ${ONLY:-cuda b200}; do
     if [ $be = cuda ]; then lib="$ROOT/oracle/_ref/cuda/libggml-cuda.so"; else lib="$ROOT/zyk-llama.cpp_b200/lib/libggml-b200.so"; fi
     [ -f "$lib" ] || { echo "$lib missing"; exit 4; }
     GGML_BACKEND_PATH="$lib" "$BIN" perf -o MUL_MAT -p "$TYPES" > "$OUT/${be}_mul_mat.txt" 2>&1
