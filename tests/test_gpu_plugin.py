@@ -101,10 +101,10 @@ def test_row_split_buffer_type_logits_match_reference_cpu_backend(tiny_gguf, gra
 
 @pytest.fixture(scope="module")
 def tiny_kquant_gguf(tmp_path_factory):
-    """3 layers of Llama-3-8B shapes in the Q4_K_M recipe (Q4_K + Q6_K on the use_more_bits layers, Q6_K output), random-init"""
+    """layers 3..5 of Llama-3-8B in the Q4_K_M recipe (one use_more_bits layer with Q6_K attn_v / ffn_down, two without; Q6_K output), random-init"""
     import sys
     path = tmp_path_factory.mktemp("gguf") / "tiny-8b-q4_k_m.gguf"
-    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "llama-3-8b-q4_k_m", "--layers", "3", "--out", str(path)],
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "llama-3-8b-q4_k_m", "--layers", "3", "--layer-offset", "3", "--out", str(path)],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:]
     return path
@@ -129,7 +129,7 @@ def tiny_moe_gguf(tmp_path_factory):
     """2 layers of Mixtral-8x7B shapes (8 experts, 2 used; Q4_K_M recipe: Q8_0 attn_k / attn_v, Q6_K on the use_more_bits layers), random-init"""
     import sys
     path = tmp_path_factory.mktemp("gguf") / "tiny-mixtral.gguf"
-    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "mixtral-8x7b-q4_k_m", "--layers", "2", "--out", str(path)],
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", "mixtral-8x7b-q4_k_m", "--layers", "2", "--layer-offset", "3", "--out", str(path)],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:]
     return path

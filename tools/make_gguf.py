@@ -84,12 +84,15 @@ def main():
     ap.add_argument("--model", default="llama-3-8b-q4_k_m")
     ap.add_argument("--out", required=True)
     ap.add_argument("--layers", type=int, default=0, help="truncate to this many layers (0 = the model's own count)")
+    ap.add_argument("--layer-offset", type=int, default=0, help="with --layers: the file's layer i takes the per-tensor types of layer i + offset of the full model")
     ap.add_argument("--seed", type=int, default=1234)
     a = ap.parse_args()
     W = _workloads()
     cfg = dict(W.MODELS[a.model])
     if a.layers:
+        cfg["recipe_layers"] = cfg["n_layer"]          # the per-tensor types of the full model (70B: Q5_K attn_v), on fewer layers
         cfg["n_layer"] = a.layers
+        cfg["recipe_offset"] = a.layer_offset
     ops = W.llama_dense(**cfg)
     n_embd, n_ff, n_head, n_kv, n_vocab, n_layer = cfg["n_embd"], cfg["n_ff"], cfg["n_head"], cfg["n_kv"], cfg["n_vocab"], cfg["n_layer"]
     n_expert, n_used = cfg.get("n_expert", 0), cfg.get("n_used", 0)

@@ -48,20 +48,21 @@ def use_more_bits(i: int, n: int) -> bool:
 
 
 def llama_dense(n_layer: int, n_embd: int, n_ff: int, n_head: int, n_kv: int, n_vocab: int, ftype: str,
-                n_expert: int = 0, n_used: int = 0) -> list[MatMul]:
+                n_expert: int = 0, n_used: int = 0, recipe_layers: int = 0, recipe_offset: int = 0) -> list[MatMul]:
     """The quantised MUL_MAT / MUL_MAT_ID nodes of one llama-arch forward pass, in graph order
     (src/models/llama.cpp: wq, wk, wv, wo, ffn_gate, ffn_up, ffn_down; output once)."""
     hd = n_embd // n_head
     kvd = hd * n_kv
+    rl = recipe_layers or n_layer          # a file cut to a few layers (tests) keeps the recipe of the full model it was cut from
     base = {"q4_k_m": Q4_K, "q8_0": Q8_0, "iq4_xs": IQ4_XS, "q4_0": Q4_0}[ftype]
     out_t = Q8_0 if ftype == "q8_0" else Q6_K
     ops: list[MatMul] = []
     for i in range(n_layer):
-        more = ftype == "q4_k_m" and use_more_bits(i, n_layer)
+        more = ftype == "q4_k_m" and use_more_bits(i + recipe_offset, rl)      # (recipe_offset: layer i of a cut file is layer i + offset of the full model)
         tv = Q6_K if more else base
         td = Q6_K if more else base
         tk = base
-        if n_layer == 80 and tv == Q4_K:            # llama-quant.cpp:305-310: the 70B model (8 heads share attn_v) takes Q5_K where Q4_K was due
+        if rl == 80 and tv == Q4_K:            # llama-quant.cpp:305-310: the 70B model (8 heads share attn_v) takes Q5_K where Q4_K was due
             tv = Q5_K
         if n_expert == 8 and ftype == "q4_k_m":     # llama-quant.cpp:311-322: 8-expert models keep attn_k/attn_v in Q8_0
             tv = tk = Q8_0
