@@ -110,7 +110,7 @@ B200_API int  b200_graph_launch(b200_graph_t graph, b200_stream_t stream);
 B200_API int  b200_graph_destroy(b200_graph_t graph);
 
 /* ---- formats -------------------------------------------------------------------------------- */
-B200_API int    b200_type_is_weight(int type);               /* Q4_0 Q8_0 Q4_K Q6_K IQ4_XS          */
+B200_API int    b200_type_is_weight(int type);               /* Q4_0 Q8_0 Q4_K Q5_K Q6_K IQ4_XS     */
 B200_API int    b200_block_elems(int type);                  /* ggml_blck_size                      */
 B200_API size_t b200_block_bytes(int type);                  /* ggml_type_size                      */
 B200_API size_t b200_row_size(int type, int64_t k);          /* ggml_row_size                       */
@@ -311,14 +311,14 @@ B200_API int b200_op_binary(int op, const b200_tensor * a, const b200_tensor * b
 /* the router of a mixture-of-experts layer (build_moe_ffn, src/llama-graph.cpp:1000-1150): ggml_compute_forward_scale (op 0: x * p0 + p1) and
    _clamp (op 1: to [p0, p1]); _sum_rows (f32 [k, ...] -> [1, ...]); _argsort_f32 (i32 indices that sort each row; order 0 ascending, 1
    descending as enum ggml_sort_order; rows of up to 1024 elements) -- ggml-cpu/ops.cpp */
+B200_API int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, float p0, float p1, b200_stream_t stream);
+B200_API int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
+B200_API int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, b200_stream_t stream);
 /* the six router nodes of build_moe_ffn in one launch (softmax gating, weights renormalised over the used experts: Mixtral): probs = softmax(logits),
    order = argsort(probs, descending), picked = probs at the first n_used indices, sum = clamp(sum(picked), lo, hi), weights = picked / sum.
    logits [n_expert <= 32, n_tokens]; every output is the contiguous tensor of its node; probs, picked and sum may be NULL (not needed by anyone else). */
 B200_API int b200_op_moe_route(const b200_tensor * logits, const b200_tensor * probs, const b200_tensor * order, const b200_tensor * picked, const b200_tensor * sum,
                                const b200_tensor * weights, int n_used, float clamp_lo, float clamp_hi, b200_stream_t stream);
-B200_API int b200_op_unary(int op, const b200_tensor * src, const b200_tensor * dst, float p0, float p1, b200_stream_t stream);
-B200_API int b200_op_sum_rows(const b200_tensor * src, const b200_tensor * dst, b200_stream_t stream);
-B200_API int b200_op_argsort(const b200_tensor * src, const b200_tensor * dst, int order, b200_stream_t stream);
 /* ggml_compute_forward_rope_flt (ops.cpp:5655-5790) for mode 0 (normal) and 2 (neox), ext_factor == 0; pos i32 [n_tokens], freq_factors f32 [n_dims / 2] or NULL */
 typedef struct b200_rope_params { int32_t n_dims, mode; float freq_base, freq_scale, ext_factor, attn_factor; } b200_rope_params;
 B200_API int b200_op_rope(const b200_tensor * src, const b200_tensor * pos, const b200_tensor * freq_factors, const b200_tensor * dst,
