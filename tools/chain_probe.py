@@ -97,11 +97,11 @@ def main():
     if a.only in ("both", "chain"):
         ms, info, o1 = run(ops, True, a.steps)
         res["chain"] = o1
-        print(f"persistent chain : {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms:7.1f} GB/s  {info}", flush=True)
+        print(f"persistent chain : {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms * 1e3:7.0f} GB/s  {info}", flush=True)
     if a.only in ("both", "nodes"):
         ms, _, o2 = run(ops, False, a.steps)
         res["nodes"] = o2
-        print(f"per-node launches: {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms:7.1f} GB/s", flush=True)
+        print(f"per-node launches: {ms * 1e3:8.1f} us/token  {1e3 / ms:7.1f} tokens/s  {gb / ms * 1e3:7.0f} GB/s", flush=True)
     if len(res) == 2:
         for k in res["chain"]:
             x, y = res["chain"][k].double(), res["nodes"][k].double()
