@@ -18,11 +18,12 @@ def _bench_bin():
     return exe
 
 
-@pytest.mark.parametrize("model,layers,offset,expect", [("llama-3.2-1b-q4_0", 2, 0, "q4_0"), ("llama-3-70b-q4_k_m", 1, 10, "q5_K"), ("mixtral-8x7b-q4_k_m", 1, 0, "q8_0")])
-def test_reference_loader_runs_the_random_init_gguf(tmp_path, ref, model, layers, offset, expect):
+@pytest.mark.parametrize("model,layers,offset,expect,extra", [("llama-3.2-1b-q4_0", 2, 0, "q4_0", []), ("llama-3-70b-q4_k_m", 1, 10, "q5_K", []),
+                                                             ("mixtral-8x7b-q4_k_m", 1, 0, "q8_0", []), ("llama-3-8b-iq4_xs", 1, 0, "q5_K", ["--exact-recipe"])])
+def test_reference_loader_runs_the_random_init_gguf(tmp_path, ref, model, layers, offset, expect, extra):
     exe = _bench_bin()
     gguf = tmp_path / "m.gguf"
-    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", model, "--layers", str(layers), "--layer-offset", str(offset), "--out", str(gguf)],
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "make_gguf.py"), "--model", model, "--layers", str(layers), "--layer-offset", str(offset), "--out", str(gguf)] + extra,
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:]
     assert f"'{expect}'" in r.stdout, r.stdout[-1500:]          # the type histogram the script prints

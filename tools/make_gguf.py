@@ -86,9 +86,16 @@ def main():
     ap.add_argument("--layers", type=int, default=0, help="truncate to this many layers (0 = the model's own count)")
     ap.add_argument("--layer-offset", type=int, default=0, help="with --layers: the file's layer i takes the per-tensor types of layer i + offset of the full model")
     ap.add_argument("--seed", type=int, default=1234)
+    ap.add_argument("--exact-recipe", action="store_true", help="per-tensor types exactly as llama-quantize writes them (workloads.llama_dense(exact=True): Q5_K in the IQ4_XS and Mixtral files)")
+    ap.add_argument("--tiny", action="store_true", help="same layer count, head ratio and expert count, but n_embd = n_ff = n_vocab = 256 (input of tests/test_quant_recipe.py)")
+    ap.add_argument("--f32", action="store_true", help="every tensor in f32, general.file_type 0: an unquantised source for the reference's llama-quantize")
     a = ap.parse_args()
     W = _workloads()
     cfg = dict(W.MODELS[a.model])
+    if a.tiny:
+        cfg.update(n_embd=256, n_ff=256, n_vocab=256, n_head=cfg["n_head"] // cfg["n_kv"], n_kv=1)
+    if a.exact_recipe:
+        cfg["exact"] = True
     if a.layers:
         cfg["recipe_layers"] = cfg["n_layer"]          # the per-tensor types of the full model (70B: Q5_K attn_v), on fewer layers
         cfg["n_layer"] = a.layers
@@ -114,6 +121,8 @@ def main():
     tensors.append(("output_norm.weight", [n_embd], F32))
     out_op = [o for o in ops if o.name == "output"][0]
     tensors.append(("output.weight", [out_op.k, out_op.m], out_op.type))
+    if a.f32:
+        tensors, ftype_id = [(name, dims, F32) for name, dims, _ in tensors], 0
 
     meta = [kv("general.architecture", T_STR, "llama"), kv("general.name", T_STR, f"random-init {a.model}"),
             kv("general.file_type", T_U32, ftype_id), kv("general.quantization_version", T_U32, 2), kv("general.alignment", T_U32, ALIGN),

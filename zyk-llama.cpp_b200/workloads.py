@@ -48,9 +48,14 @@ def use_more_bits(i: int, n: int) -> bool:
 
 
 def llama_dense(n_layer: int, n_embd: int, n_ff: int, n_head: int, n_kv: int, n_vocab: int, ftype: str,
-                n_expert: int = 0, n_used: int = 0, recipe_layers: int = 0, recipe_offset: int = 0) -> list[MatMul]:
+                n_expert: int = 0, n_used: int = 0, recipe_layers: int = 0, recipe_offset: int = 0, exact: bool = False) -> list[MatMul]:
     """The quantised MUL_MAT / MUL_MAT_ID nodes of one llama-arch forward pass, in graph order
-    (src/models/llama.cpp: wq, wk, wv, wo, ffn_gate, ffn_up, ffn_down; output once)."""
+    (src/models/llama.cpp: wq, wk, wv, wo, ffn_gate, ffn_up, ffn_down; output once).
+
+    exact=True gives every tensor the type llama-quantize (no imatrix) really writes, pinned against the reference's quantiser in
+    tests/test_quant_recipe.py. The default differs from it in three places, all Q5_K tensors the round-1 scope (five formats) left out
+    and the measurements of round 2 were taken without: IQ4_XS files keep attn_v (n_gqa >= 4, llama-quant.cpp:299-301) and the ffn_down of
+    the first n_layer / 8 layers (:366-368) in IQ4_XS instead of Q5_K, and 8-expert files keep attn_output in Q4_K instead of Q5_K (:383-390)."""
     hd = n_embd // n_head
     kvd = hd * n_kv
     rl = recipe_layers or n_layer          # a file cut to a few layers (tests) keeps the recipe of the full model it was cut from
@@ -64,13 +69,21 @@ def llama_dense(n_layer: int, n_embd: int, n_ff: int, n_head: int, n_kv: int, n_
         tk = base
         if rl == 80 and tv == Q4_K:            # llama-quant.cpp:305-310: the 70B model (8 heads share attn_v) takes Q5_K where Q4_K was due
             tv = Q5_K
+        to = base
+        if exact and ftype == "iq4_xs":
+            if n_head // n_kv >= 4:
+                tv = Q5_K
+            if i + recipe_offset < rl // 8:
+                td = Q5_K
         if n_expert == 8 and ftype == "q4_k_m":     # llama-quant.cpp:311-322: 8-expert models keep attn_k/attn_v in Q8_0
             tv = tk = Q8_0
+            if exact:
+                to = Q5_K
         p = f"blk.{i}."
         ops += [MatMul(p + "attn_q", base, n_embd, n_embd, "x", "q"),
                 MatMul(p + "attn_k", tk, kvd, n_embd, "x", "k"),
                 MatMul(p + "attn_v", tv, kvd, n_embd, "x", "v"),
-                MatMul(p + "attn_output", base, n_embd, n_embd, "attn", "x2")]
+                MatMul(p + "attn_output", to, n_embd, n_embd, "attn", "x2")]
         if n_expert:
             ops += [MatMul(p + "ffn_gate_exps", base, n_ff, n_embd, "x2", "gate", n_expert, n_used),
                     MatMul(p + "ffn_up_exps", base, n_ff, n_embd, "x2", "up", n_expert, n_used),
