@@ -63,9 +63,10 @@ def test_exact_recipe_is_what_the_reference_quantiser_writes(tmp_path, model):
 
 
 @pytest.mark.parametrize("model", BASELINE_MODELS)
-def test_default_recipe_differs_from_the_exact_one_only_where_documented(model):
+def test_default_recipe_differs_from_the_exact_one_only_where_documented(model, monkeypatch):
     """the recipe the round's measurements were taken on: identical to llama-quantize's for the Q4_0, Q8_0 and dense Q4_K_M files (8B, 70B);
     IQ4_XS without its Q5_K attn_v / first-eighth ffn_down, Mixtral without its Q5_K attn_output (workloads.llama_dense docstring)"""
+    monkeypatch.delenv("B200_EXACT_RECIPE", raising=False)
     W = _workloads()
     cfg = dict(W.MODELS[model])
     default, exact = W.llama_dense(**cfg), W.llama_dense(**cfg, exact=True)

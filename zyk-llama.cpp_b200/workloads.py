@@ -8,6 +8,7 @@ Pure host logic + torch for device memory; no arithmetic of the hot path lives h
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 
 import torch
@@ -56,6 +57,7 @@ def llama_dense(n_layer: int, n_embd: int, n_ff: int, n_head: int, n_kv: int, n_
     tests/test_quant_recipe.py. The default differs from it in three places, all Q5_K tensors the round-1 scope (five formats) left out
     and the measurements of round 2 were taken without: IQ4_XS files keep attn_v (n_gqa >= 4, llama-quant.cpp:299-301) and the ffn_down of
     the first n_layer / 8 layers (:366-368) in IQ4_XS instead of Q5_K, and 8-expert files keep attn_output in Q4_K instead of Q5_K (:383-390)."""
+    exact = exact or os.environ.get("B200_EXACT_RECIPE", "0") == "1"      # flips every caller (bench.py configs, make_gguf.py) at once for an A/B run
     hd = n_embd // n_head
     kvd = hd * n_kv
     rl = recipe_layers or n_layer          # a file cut to a few layers (tests) keeps the recipe of the full model it was cut from
