@@ -134,3 +134,61 @@ def test_kernel_choice(B):
     assert plan(B, [[node(B, ar, Q4_K, 4096, 4096, x0, y, n=2)]])[1] == 0      # activations in registers: n = 1 only
     assert plan(B, [[node(B, ar, Q6_K, 4096, 1024, x0, y)]])[1] == 0           # 4 units per row: no swizzled tensor copies
     assert plan(B, [[node(B, ar, Q4_K, 4096, 24576, x0, y)]])[1] == 0          # 96 units per row = 3 warp classes, 8 warps
+
+
+def test_random_pointer_patterns_never_get_a_weaker_boundary_than_their_hazards_need(B):
+    """safety of the planner against an independent restatement of the hazard rules, on 400 seeded random chains whose X / Y pointers are
+    drawn from a small pool of buffers with offsets (so exact feeds, partial overlaps, aliasing one and two groups back and unrelated
+    buffers all occur): a hazard never gets a weaker boundary than it needs, and the cheap boundaries appear exactly where they may"""
+    import random
+    rng = random.Random(20261106)
+    seen = {NONE: 0, FENCED: 0, RELAXED: 0, TAGGED: 0}
+    for case in range(400):
+        ar = Arena()
+        pool = [ar.take(4 * 16384) for _ in range(6)]
+        groups, meta = [], []                       # meta: per group (x_lo, x_hi, [(y_lo, y_hi, m)])
+        for g in range(rng.randint(2, 7)):
+            k = rng.choice([1024, 2048, 4096])
+            if groups and rng.random() < 0.5:       # read exactly what a matrix of the previous group wrote, when the sizes allow it
+                ylo, yhi, m_prev = rng.choice(meta[-1][2])
+                x, k = ylo, m_prev
+            else:
+                x = rng.choice(pool) + 4 * rng.choice([0, 0, 512, 1024, 3072])
+            ys, nodes = [], []
+            for i in range(rng.randint(1, 3)):
+                m = rng.choice([1024, 2048, 4096])
+                for _ in range(50):                 # a Y that overlaps neither this group's X nor its other Ys
+                    y = rng.choice(pool) + 4 * rng.choice([0, 0, 1024, 4096, 8192])
+                    if (y + 4 * m <= x or x + 4 * k <= y) and all(y + 4 * m <= a or b_ <= y for a, b_, _ in ys):
+                        break
+                else:
+                    y = ar.take(4 * m)
+                ys.append((y, y + 4 * m, m))
+                nodes.append(node(B, ar, rng.choice([Q4_K, Q6_K]), m, k, x, y))
+            groups.append(nodes)
+            meta.append((x, x + 4 * k, ys))
+        modes, _ = plan(B, groups)
+        assert modes[0] == NONE
+        for g in range(1, len(groups)):
+            xlo, xhi, ys = meta[g]
+            raw = any(xlo < yhi and ylo < xhi for h in range(g) for ylo, yhi, _ in meta[h][2])
+            waw_war = any((ylo < meta[h][1] and meta[h][0] < yhi) or any(ylo < bhi and blo < yhi for blo, bhi, _ in meta[h][2])
+                          for h in range(max(0, g - 2), g) for ylo, yhi, _ in ys)
+            feeds = [(ylo, m) for ylo, yhi, m in meta[g - 1][2] if ylo == xlo and yhi == xhi]
+            where = f"case {case} group {g}: modes {modes}"
+            if waw_war:
+                assert modes[g] == FENCED, where
+            elif raw and not feeds:
+                assert modes[g] == FENCED, where
+            elif feeds and len(meta[g - 1][2]) == 1:
+                assert modes[g] == TAGGED, where          # the only matrix of its group, >= 1024 rows: every CTA owns rows of it
+            elif feeds:
+                assert modes[g] in (TAGGED, FENCED), where  # depends on the shares of the group's matrices
+            else:
+                assert modes[g] == RELAXED, where
+            if modes[g] == TAGGED:
+                assert feeds and not waw_war, where
+            if modes[g] == RELAXED:
+                assert not raw and not waw_war, where
+            seen[modes[g]] += 1
+    assert min(seen[FENCED], seen[RELAXED], seen[TAGGED]) > 50, seen      # the generator reaches every kind of boundary
