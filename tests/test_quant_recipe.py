@@ -12,8 +12,18 @@ from pathlib import Path
 import pytest
 
 ROOT = Path(__file__).resolve().parents[1]
-VAR = ROOT / "oracle" / "_ref" / os.environ.get("B200_REF_VARIANT", "avx512vnni")
-TOOL = VAR / "llama_quantize_types"
+
+
+def _tool():
+    """the reference quantiser driver of the CPU variant this host can run (oracle.ref_dir), or None"""
+    sys.path.insert(0, str(ROOT))
+    from oracle.oracle import ref_dir
+    d = ref_dir()
+    exe = d / "llama_quantize_types" if d else None
+    return exe if exe is not None and exe.exists() else None
+
+
+TOOL = _tool()
 FTYPE_ID = {"q4_0": 2, "q8_0": 7, "q4_k_m": 15, "iq4_xs": 30}          # enum llama_ftype (include/llama.h)
 TYPE_NAME = {0: "f32", 2: "q4_0", 8: "q8_0", 12: "q4_K", 13: "q5_K", 14: "q6_K", 23: "iq4_xs"}
 BASELINE_MODELS = ["llama-3.2-1b-q4_0", "llama-3-8b-q4_k_m", "llama-3-8b-q8_0", "llama-3-8b-iq4_xs", "llama-3-70b-q4_k_m", "mixtral-8x7b-q4_k_m"]
@@ -45,7 +55,7 @@ def _reference_types(tmp_path, model, ftype):
     return dict(line.split() for line in r.stdout.splitlines() if line.strip())
 
 
-@pytest.mark.skipif(not TOOL.exists(), reason="reference quantiser not built (oracle/Makefile.llama)")
+@pytest.mark.skipif(TOOL is None, reason="reference quantiser not built (oracle/Makefile.llama)")
 @pytest.mark.parametrize("model", BASELINE_MODELS)
 def test_exact_recipe_is_what_the_reference_quantiser_writes(tmp_path, model):
     W = _workloads()
